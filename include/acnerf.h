@@ -1,0 +1,239 @@
+/* acnerf.h - C ABI of libacnerf_sm100a.so: the B200 (sm_100a) per-ray hot path of
+ * Adaptive City NeRF (psklavos1/NeRF-Sys).
+ *
+ * Every entry point replaces one piece of the reference's PyTorch path; the
+ * reference interface is cited as file:line under /root/reference/adaptive_nerf/.
+ * The reference has no FFI of its own (it is pure Python): this header is what a
+ * ctypes / torch custom-op binding on the reference side binds.
+ *
+ * Conventions
+ *  - every pointer is a DEVICE pointer unless the name ends in _host;
+ *  - the caller owns all memory, including workspaces (sizes via acn_*_ws_bytes);
+ *  - every call is asynchronous on `stream` (a cudaStream_t passed as void*),
+ *    re-entrant, and holds no global device state;
+ *  - return value: 0 = ok, 1 = invalid argument, 2 = CUDA error, 3 = unsupported
+ *    device; acn_last_error() returns a thread-local message. Nothing throws
+ *    across the ABI, nothing calls exit();
+ *  - there is no CPU path: a NULL/host pointer where a device pointer is
+ *    expected is an error, not a fallback.
+ *  - all tensors fp32 row-major unless stated; indices int32; masks uint8.
+ */
+#ifndef ACNERF_H_
+#define ACNERF_H_
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+#if defined(__GNUC__)
+#pragma GCC visibility push(default) /* the library is built -fvisibility=hidden; only this header is exported */
+#endif
+
+#define ACN_OK 0
+#define ACN_EINVAL 1
+#define ACN_ECUDA 2
+#define ACN_EDEVICE 3
+
+#define ACN_MAX_LEVELS 32
+#define ACN_MAX_EXPERTS 16 /* experts per launch (kernel-parameter table) */
+#define ACN_TILE 128       /* pair segments are padded to this many slots */
+
+/* ---- library ------------------------------------------------------------ */
+int acn_version(void);                  /* ABI version, currently 1 */
+const char* acn_last_error(void);       /* thread-local, never NULL */
+int acn_device_ok(int device);          /* ACN_OK iff `device` is compute capability 10.x */
+int acn_num_sms(int device);            /* multiprocessor count (148 on B200), <0 on error */
+
+/* ---- descriptors -------------------------------------------------------- */
+/* models/encodings.py:180-286 (HashGridEncoder ctor): levels, features_per_level,
+ * log2_hashmap_size, interpolation, and the per-level resolutions the reference
+ * computes as floor(min_res * g^l) in fp32 (encodings.py:203-215); the host side
+ * computes them with the same torch expression and passes them here. */
+typedef struct AcnGridDesc {
+  int32_t levels;   /* L <= 32 */
+  int32_t features; /* F, must be 2 */
+  int32_t log2_T;   /* rows per level = 1 << log2_T */
+  int32_t interp;   /* 0 Linear, 1 Smoothstep, 2 Nearest */
+  int32_t res[ACN_MAX_LEVELS];
+} AcnGridDesc;
+
+/* Where sample points come from.  Either explicit (P,6) [xyz,dir] rows
+ * (MetaNGP.forward's argument, meta_ngp.py:226-241) or implicit: point
+ * p = ray (p / S), sample (p % S), xyz = o + d*t, dir = d (ray_rendering.py:317-319),
+ * which never materialises the (N*S,6) tensor. */
+typedef struct AcnPoints {
+  const float* x6;   /* (P,6) or NULL */
+  const float* rays; /* (N,8) [o,d,near,far] when x6 == NULL */
+  const float* t;    /* (N,S) */
+  int32_t S;
+  int64_t P;         /* number of points */
+} AcnPoints;
+
+/* Routed (point, expert) pairs, grouped by expert, each group padded to a
+ * multiple of ACN_TILE slots.  All-NULL = identity: one expert, slot m == point m,
+ * weight 1 (the active_module path, meta_container.py:302-304). */
+typedef struct AcnPairs {
+  const int32_t* point; /* (Mcap,) point id, -1 = padding */
+  const float* weight;  /* (Mcap,) routing weight */
+  const int32_t* seg;   /* (E+1,) segment starts (multiples of ACN_TILE); seg[E] = used slots */
+  int64_t Mcap;         /* capacity of the pair arrays (identity: == P) */
+} AcnPairs;
+
+/* One hash-grid expert (MetaNGP, meta_ngp.py:21-142) in the production shape
+ * L*F=32 -> 64 -> 64 -> {sigma 1, geo 15}; [geo15|SH16]=31 -> 64 -> 64 -> 3.
+ * Weights are nn.Linear layout (out,in), i.e. exactly the reference's
+ * state_dict tensors or the caller's fast-weight overrides (metamodule.py:129-156).
+ * layer order: 0 sigma_trunk.0, 1 sigma_trunk.1, 2 sigma_head, 3 geo_head,
+ *              4 color_mlp.0, 5 color_mlp.1, 6 color_mlp.2 */
+#define ACN_NGP_LAYERS 7
+typedef struct AcnNgpExpert {
+  const float* table;              /* (L*T, 2) */
+  const float* w[ACN_NGP_LAYERS];
+  const float* b[ACN_NGP_LAYERS];
+  float box_min[3];                /* expert's own AABB (meta_ngp.py:155-158) */
+  float extent[3];
+} AcnNgpExpert;
+
+typedef struct AcnNgpExpertGrads { /* outputs of the backward pass; NULL = not wanted */
+  float* table;                    /* (L*T, 2), ACCUMULATED into (caller zeroes) */
+  float* w[ACN_NGP_LAYERS];        /* overwritten */
+  float* b[ACN_NGP_LAYERS];
+} AcnNgpExpertGrads;
+
+/* ---- a1-a3: rays -------------------------------------------------------- */
+/* nerfs/ray_sampling.py:111-136 get_ray_directions -> dirs (H,W,3) */
+int acn_ray_directions(int H, int W, float fx, float fy, float cx, float cy, int center_pixels,
+                       float* dirs, void* stream);
+/* nerfs/ray_sampling.py:50-108 get_rays (+ scene_box.py:45-107 ray_aabb_intersect):
+ * dirs (n,3) camera frame, c2w_host 12 floats row-major (3,4); aabb_host 6 floats
+ * [min,max] or NULL (then near/far constants) -> rays (n,8). */
+int acn_get_rays(const float* dirs, int64_t n, const float* c2w_host, const float* aabb_host,
+                 float near_c, float far_c, float aabb_max_bound, float aabb_invalid_value,
+                 float* rays, void* stream);
+/* fused a1+a2 for a full frame; rows [row0,row0+rows) of an HxW image (ray-sharded render) */
+int acn_raygen(int H, int W, int row0, int rows, float fx, float fy, float cx, float cy, int center_pixels,
+               const float* c2w_host, const float* aabb_host, float near_c, float far_c,
+               float* rays, void* stream);
+/* scene_box.py:45-107 on explicit origins/directions */
+int acn_ray_aabb(const float* o, const float* d, int64_t n, const float* aabb_host, float max_bound,
+                 float invalid_value, float* near_out, float* far_out, void* stream);
+/* nerfs/ray_sampling.py:139-176 clamp_rays_near_far.  has_near/has_far select the
+ * override bounds; override_none!=0 = the `near_far_override=None` branch (rays untouched). */
+int acn_clamp_near_far(const float* rays_in, int64_t n, int override_none, int has_near, float near_v,
+                       int has_far, float far_v, float eps, float invalid_value, float* rays_out,
+                       uint8_t* valid, void* stream);
+
+/* ---- a4-a5: stratified sampling ----------------------------------------- */
+/* nerfs/ray_rendering.py:262-287.  tau = torch.linspace(0,1,S) values (S,), u (N,S)
+ * jitter in [0,1) or NULL (eval).  t (N,S). */
+int acn_stratified_t(const float* rays, int64_t N, int S, const float* tau, const float* u, float* t,
+                     void* stream);
+/* nerfs/ray_rendering.py:317-319: (N,8),(N,S) -> x6 (N*S,6).  API parity / tests only;
+ * the render path never materialises this. */
+int acn_sample_points(const float* rays, const float* t, int64_t N, int S, float* x6, void* stream);
+
+/* ---- a6-a7: routing ------------------------------------------------------ */
+/* models/inr/meta_container.py:97-134 _routing.  centroids_host (K,3) HOST floats (they
+ * travel in the kernel-parameter block).  margin>1: weights (P,K) written, hard
+ * untouched; else hard (P,) int64 argmin written. */
+int acn_routing(const AcnPoints* pts, const float* centroids_host, int K, float margin, int cluster_2d,
+                float* weights, int64_t* hard, void* stream);
+/* Fused routing + stable pack-by-expert (replaces K x nonzero/index_select,
+ * meta_container.py:305-337).  Outputs the pair arrays (capacity Mcap slots; a
+ * speculative size comes from acn_route_pack_capacity) and seg (K+1).  Nothing is
+ * written past Mcap; seg[K] always reports the slots NEEDED, so a caller that reads
+ * seg[K] > Mcap re-runs with larger arrays.  ws: acn_route_pack_ws_bytes(P,K). */
+int64_t acn_route_pack_capacity(int64_t P, int K);
+int64_t acn_route_pack_ws_bytes(int64_t P, int K);
+int acn_route_pack(const AcnPoints* pts, const float* centroids_host, int K, float margin, int cluster_2d,
+                   int32_t* pair_point, float* pair_weight, int32_t* seg, int64_t Mcap, void* ws,
+                   void* stream);
+
+/* ---- a8-a11: encoders ---------------------------------------------------- */
+/* models/encodings.py:331-358: table row ids of the 8 corners, idx (P,L,8) int32,
+ * corner c = 4*bx+2*by+bz, level offset included (bit-exact contract). */
+int acn_hashgrid_indices(const float* x01, int64_t P, const AcnGridDesc* g, int32_t* idx, void* stream);
+/* HashGridEncoder.forward (encodings.py:293-305, 331-381): x01 (P,3) -> y (P,L*F) */
+int acn_hashgrid_fwd(const float* x01, int64_t P, const float* table, const AcnGridDesc* g, float* y,
+                     void* stream);
+/* its autograd backward: grad_table (L*T,F) += scatter(dy); caller zeroes grad_table */
+int acn_hashgrid_bwd(const float* x01, int64_t P, const float* dy, const AcnGridDesc* g,
+                     float* grad_table, void* stream);
+/* SHEncoder.forward (encodings.py:27-81,133-151): d (P,3) -> (P,16) */
+int acn_sh16(const float* d, int64_t P, float* out, void* stream);
+/* FrequencyEncoder.torch_forward (encodings.py:437-444): x (P,3) -> (P, 3 + 6*n_freq) or (P,6*n_freq) */
+int acn_freq_encode(const float* x, int64_t P, int n_freq, int include_input, float* out, void* stream);
+
+/* ---- a8-a14 fused: hash-grid experts over routed pairs ------------------- */
+/* The expert evaluation is two stream-ordered stages that exchange the encoding in a
+ * feature-major buffer enc (32, ld), ld = acn_ngp_ld(Mcap) (slot index contiguous):
+ *   encode: world -> unit cube of the expert's own box -> hash grid   (meta_ngp.py:155-163)
+ *   mlp   : sigma trunk, heads, trunc_exp, SH16, colour MLP, sigmoid  (meta_ngp.py:171-241)
+ *           and the container's combine out[p] (+)= w*y                (meta_container.py:305-321)
+ * Two stages so that autograd can ask for the MLP gradients alone (the meta inner loop,
+ * meta_core.py:54-59) without paying for the hash-table scatter. */
+int64_t acn_ngp_ld(int64_t Mcap);
+int64_t acn_ngp_save_bytes(int64_t Mcap);
+int64_t acn_ngp_bwd_ws_bytes(int64_t Mcap, int E);
+int acn_ngp_encode_fwd(const AcnPoints* pts, const AcnPairs* pairs, const AcnNgpExpert* experts, int E,
+                       const AcnGridDesc* g, float* enc, void* stream);
+/* grads[e].table (L*T,2) is ACCUMULATED into (caller zeroes); NULL = skip that expert */
+int acn_ngp_encode_bwd(const AcnPoints* pts, const AcnPairs* pairs, const AcnNgpExpert* experts, int E,
+                       const AcnGridDesc* g, const float* d_enc, const AcnNgpExpertGrads* grads, void* stream);
+/* out (P,4) [rgb,sigma]: identity pairs -> plain store; routed -> out[p] += w*y (caller
+ * zeroes out).  save: acn_ngp_save_bytes(Mcap) bytes kept for backward, or NULL (inference). */
+int acn_ngp_mlp_fwd(const AcnPoints* pts, const AcnPairs* pairs, const AcnNgpExpert* experts, int E,
+                    const float* enc, float* out, void* save, void* stream);
+/* d_out (P,4) -> grads[e].w/b (overwritten; NULL = not wanted) and d_enc (32, ld).
+ * ws: acn_ngp_bwd_ws_bytes(Mcap,E). */
+int acn_ngp_mlp_bwd(const AcnPairs* pairs, const AcnNgpExpert* experts, int E, const float* enc,
+                    const float* d_out, const void* save, const AcnNgpExpertGrads* grads, float* d_enc,
+                    void* ws, void* stream);
+
+/* ---- a16: shared background head ----------------------------------------- */
+/* meta_container.py:347-382: d (N,3) taken at `stride` floats (stride 8 reads rays[:,3:6]
+ * in place) -> rgb (N,3).  w0 (32,16) b0 (32) w1 (3,32) b1 (3). */
+int64_t acn_bg_save_bytes(int64_t N);
+int acn_bg_forward(const float* d, int64_t stride, int64_t N, const float* w0, const float* b0,
+                   const float* w1, const float* b1, float* rgb, void* save, void* stream);
+int64_t acn_bg_bwd_ws_bytes(int64_t N);
+int acn_bg_backward(const float* d_rgb, int64_t N, const float* w0, const float* w1, const void* save,
+                    float* g_w0, float* g_b0, float* g_w1, float* g_b1, void* ws, void* stream);
+
+/* ---- a17: alpha compositing ---------------------------------------------- */
+/* nerfs/ray_rendering.py:114-165 volume_render.  rgb_sigma (N,S,4), t (N,S), bg (N,3) or NULL
+ * -> rgb (N,3), depth (N), weights (N,S) or NULL, acc (N).  No early termination. */
+int acn_composite_fwd(const float* rgb_sigma, const float* t, const float* bg, int64_t N, int S,
+                      float sigma_scale, float* rgb, float* depth, float* weights, float* acc, void* stream);
+/* its backward: g_rgb (N,3), g_depth (N) or NULL, g_acc (N) or NULL, g_weights (N,S) or NULL
+ * -> d_rgb_sigma (N,S,4), d_bg (N,3) or NULL */
+int acn_composite_bwd(const float* rgb_sigma, const float* t, const float* bg, int64_t N, int S,
+                      float sigma_scale, const float* g_rgb, const float* g_depth, const float* g_acc,
+                      const float* g_weights, float* d_rgb_sigma, float* d_bg, void* stream);
+
+/* ---- a18: photometric loss ------------------------------------------------ */
+/* nerfs/losses.py:10-32 + color_space.py:22-66.  space: 0 linear, 1 srgb, 2 identity.
+ * loss (1,) = mean((pred'-gt')^2); d_pred (N,3) = dloss/dpred (unit upstream grad) or NULL.
+ * ws: 2048 floats. */
+int acn_mse_loss(const float* pred, const float* gt, int64_t N, int space, float* loss, float* d_pred,
+                 float* ws, void* stream);
+
+/* ---- (f)2: fused optimiser ------------------------------------------------ */
+/* torch.optim.Adam single-tensor math (common/utils.py:16-76 builds torch Adam):
+ * step is the 1-based step count; grad_scale multiplies the gradient first
+ * (clip coefficient and/or 1/loss-scale). */
+int acn_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, float lr,
+                  float beta1, float beta2, float eps, float weight_decay, int64_t step,
+                  const float* grad_scale_dev, void* stream);
+/* fast-weight SGD step of the inner loop (pipelines/offline_stage/meta_core.py:61-64): out = w - lr*g */
+int acn_sgd_axpy(const float* w, const float* g, float lr, int64_t n, float* out, void* stream);
+/* sum of squares of a tensor accumulated into acc (1,) (clip_grad_norm_ building block) */
+int acn_sumsq_accum(const float* x, int64_t n, float* acc, void* stream);
+
+#if defined(__GNUC__)
+#pragma GCC visibility pop
+#endif
+#ifdef __cplusplus
+}
+#endif
+#endif /* ACNERF_H_ */

@@ -1,0 +1,553 @@
+// a8-a14 fused: hash-grid experts (MetaNGP, models/inr/meta_ngp.py:155-241) over routed
+// (point, expert) pairs, forward and backward.  fp32 CUDA-core ("exact") MLP path.
+//
+// Pipeline per call (all stream-ordered, no host sync):
+//   fwd : k_ngp_hash_fwd   pairs -> enc   (L2/HBM gather-bound, 1024 B table rows / pair)
+//         k_ngp_mlp_fwd    enc,dir -> rgb,sigma ; combine out[p] (+)= w*y   (FFMA-bound, 13 440 MAC / pair)
+//   bwd : k_ngp_mlp_bwd    d_out -> dz of every layer + d_enc              (FFMA-bound)
+//         wgrad_launch x7  dW = dz^T x per layer, per expert               (FFMA-bound, deterministic)
+//         k_ngp_hash_bwd   d_enc -> grad table scatter                     (L2 atomic-bound)
+// Activations are kept feature-major [feature][slot] so thread-per-slot kernels read
+// and write coalesced 128-byte rows.
+#include "hashgrid.cuh"
+
+namespace acn {
+
+constexpr int NT = ACN_TILE;  // threads per CTA == slots per tile
+
+// save-buffer rows (each row = ld floats)
+constexpr int R_H0 = 0, R_H1 = 64, R_CIN = 128, R_C0 = 160, R_C1 = 224, R_Y = 288, R_SAVE = 292;
+// backward workspace rows
+constexpr int R_DZ5 = 0, R_DZ4 = 4, R_DZ3 = 68, R_DZH = 132, R_DZ1 = 148, R_DZ0 = 212, R_WS = 276;
+
+// smem weight block (floats)
+constexpr int W0_OFF = 0;                    // 64 x 32
+constexpr int W1_OFF = W0_OFF + 64 * 32;     // 64 x 64
+constexpr int WH_OFF = W1_OFF + 64 * 64;     // 16 x 64  (rows 0..14 geo_head, row 15 sigma_head)
+constexpr int W3_OFF = WH_OFF + 16 * 64;     // 64 x 32  (31 padded to 32)
+constexpr int W4_OFF = W3_OFF + 64 * 32;     // 64 x 64
+constexpr int W5_OFF = W4_OFF + 64 * 64;     // 4 x 64   (3 padded to 4)
+constexpr int B_OFF = W5_OFF + 4 * 64;       // biases: 64,64,16,64,64,4
+constexpr int B0 = B_OFF, B1 = B0 + 64, BH = B1 + 64, B3 = BH + 16, B4 = B3 + 64, B5 = B4 + 64;
+constexpr int W_FLOATS = B5 + 4;
+constexpr int ACT_FLOATS = 64 * NT;
+constexpr size_t MLP_SMEM = sizeof(float) * (W_FLOATS + ACT_FLOATS) + 64 * sizeof(int);
+
+struct ExpertTable {
+  AcnNgpExpert ex[ACN_MAX_EXPERTS];
+  int E;
+};
+
+__device__ __forceinline__ int64_t round_ld(int64_t m) { return (m + 127) / 128 * 128; }
+static inline int64_t h_round_ld(int64_t m) { return (m + 127) / 128 * 128; }
+
+// expert owning slot m (segments are tile-aligned, so a tile never straddles experts)
+__device__ __forceinline__ int find_expert(const int* s_seg, int E, int64_t m) {
+  int e = 0;
+  for (int k = 1; k < E; ++k)
+    if (m >= s_seg[k]) e = k;
+  return e;
+}
+
+// ---------------------------------------------------------------------------------------
+// hash-grid forward over pairs: grid.y = level
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_ngp_hash_fwd(PointSrc src, const int32_t* __restrict__ pair_point, const int32_t* __restrict__ seg,
+                                                      int64_t M_ident, ExpertTable tab, GridParams g, float* __restrict__ enc, int64_t ld) {
+  __shared__ int s_seg[ACN_MAX_EXPERTS + 1];
+  if (threadIdx.x <= tab.E) s_seg[threadIdx.x] = seg ? seg[threadIdx.x] : (threadIdx.x == 0 ? 0 : (int)M_ident);
+  __syncthreads();
+  int64_t M = seg ? s_seg[tab.E] : M_ident;
+  int l = blockIdx.y;
+  uint32_t mask = (1u << g.log2_T) - 1u, base = (uint32_t)l << g.log2_T;
+  for (int64_t m = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; m < M; m += (int64_t)gridDim.x * blockDim.x) {
+    int64_t p = pair_point ? (int64_t)pair_point[m] : m;
+    float2 v = make_float2(0.f, 0.f);
+    if (p >= 0) {
+      int e = seg ? find_expert(s_seg, tab.E, m) : 0;
+      const AcnNgpExpert& ex = tab.ex[e];
+      float x, y, z;
+      load_xyz(src, p, x, y, z);
+      Cell c = make_cell(to_unit(x, ex.box_min[0], ex.extent[0]), to_unit(y, ex.box_min[1], ex.extent[1]),
+                         to_unit(z, ex.box_min[2], ex.extent[2]), g.res[l], g.interp);
+      v = level_encode(reinterpret_cast<const float2*>(ex.table), c, mask, base, g.interp);
+    }
+    enc[(int64_t)(2 * l) * ld + m] = v.x;
+    enc[(int64_t)(2 * l + 1) * ld + m] = v.y;
+  }
+}
+
+struct GradTables {
+  float* t[ACN_MAX_EXPERTS];
+};
+
+__global__ void __launch_bounds__(256) k_ngp_hash_bwd(PointSrc src, const int32_t* __restrict__ pair_point, const int32_t* __restrict__ seg,
+                                                      int64_t M_ident, ExpertTable tab, GridParams g, const float* __restrict__ denc, int64_t ld,
+                                                      GradTables gts) {
+  __shared__ int s_seg[ACN_MAX_EXPERTS + 1];
+  if (threadIdx.x <= tab.E) s_seg[threadIdx.x] = seg ? seg[threadIdx.x] : (threadIdx.x == 0 ? 0 : (int)M_ident);
+  __syncthreads();
+  int64_t M = seg ? s_seg[tab.E] : M_ident;
+  int l = blockIdx.y;
+  uint32_t mask = (1u << g.log2_T) - 1u, base = (uint32_t)l << g.log2_T;
+  for (int64_t m = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; m < M; m += (int64_t)gridDim.x * blockDim.x) {
+    int64_t p = pair_point ? (int64_t)pair_point[m] : m;
+    if (p < 0) continue;
+    int e = seg ? find_expert(s_seg, tab.E, m) : 0;
+    float* gt = gts.t[e];
+    if (!gt) continue;
+    const AcnNgpExpert& ex = tab.ex[e];
+    float x, y, z;
+    load_xyz(src, p, x, y, z);
+    Cell c = make_cell(to_unit(x, ex.box_min[0], ex.extent[0]), to_unit(y, ex.box_min[1], ex.extent[1]),
+                       to_unit(z, ex.box_min[2], ex.extent[2]), g.res[l], g.interp);
+    float2 gv = make_float2(__ldg(denc + (int64_t)(2 * l) * ld + m), __ldg(denc + (int64_t)(2 * l + 1) * ld + m));
+    level_scatter(reinterpret_cast<float2*>(gt), c, mask, base, g.interp, gv);
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// MLP helpers: thread-per-slot, weights broadcast from shared memory as float4
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ void load_weights(float* sw, const AcnNgpExpert& ex) {
+  // nn.Linear (out,in) row-major tensors copied into the padded smem block
+  for (int i = threadIdx.x; i < 64 * 32; i += NT) sw[W0_OFF + i] = __ldg(ex.w[0] + i);
+  for (int i = threadIdx.x; i < 64 * 64; i += NT) sw[W1_OFF + i] = __ldg(ex.w[1] + i);
+  for (int i = threadIdx.x; i < 15 * 64; i += NT) sw[WH_OFF + i] = __ldg(ex.w[3] + i);
+  for (int i = threadIdx.x; i < 64; i += NT) sw[WH_OFF + 15 * 64 + i] = __ldg(ex.w[2] + i);
+  for (int i = threadIdx.x; i < 64 * 32; i += NT) {
+    int o = i >> 5, c = i & 31;
+    sw[W3_OFF + i] = (c < 31) ? __ldg(ex.w[4] + o * 31 + c) : 0.f;
+  }
+  for (int i = threadIdx.x; i < 64 * 64; i += NT) sw[W4_OFF + i] = __ldg(ex.w[5] + i);
+  for (int i = threadIdx.x; i < 4 * 64; i += NT) sw[W5_OFF + i] = (i < 3 * 64) ? __ldg(ex.w[6] + i) : 0.f;
+  for (int i = threadIdx.x; i < 64; i += NT) {
+    sw[B0 + i] = __ldg(ex.b[0] + i);
+    sw[B1 + i] = __ldg(ex.b[1] + i);
+    sw[B3 + i] = __ldg(ex.b[4] + i);
+    sw[B4 + i] = __ldg(ex.b[5] + i);
+    if (i < 15) sw[BH + i] = __ldg(ex.b[3] + i);
+    if (i == 15) sw[BH + 15] = __ldg(ex.b[2]);
+    if (i < 4) sw[B5 + i] = (i < 3) ? __ldg(ex.b[6] + i) : 0.f;
+  }
+}
+
+// y[o] = b[o] + sum_i W[o][i] x[i], produced OC outputs at a time and handed to `emit(o, value)`.
+template <int IN, int OUT, int OC, class Emit>
+__device__ __forceinline__ void dense_fwd(const float* __restrict__ W, const float* __restrict__ b, const float (&x)[IN], Emit emit) {
+  static_assert(IN % 4 == 0 && OUT % OC == 0, "shape");
+#pragma unroll 1
+  for (int o0 = 0; o0 < OUT; o0 += OC) {
+    float acc[OC];
+#pragma unroll
+    for (int oo = 0; oo < OC; ++oo) acc[oo] = b[o0 + oo];
+#pragma unroll
+    for (int i = 0; i < IN; i += 4) {
+#pragma unroll
+      for (int oo = 0; oo < OC; ++oo) {
+        float4 w = *reinterpret_cast<const float4*>(W + (o0 + oo) * IN + i);
+        acc[oo] = fmaf(w.x, x[i], acc[oo]);
+        acc[oo] = fmaf(w.y, x[i + 1], acc[oo]);
+        acc[oo] = fmaf(w.z, x[i + 2], acc[oo]);
+        acc[oo] = fmaf(w.w, x[i + 3], acc[oo]);
+      }
+    }
+#pragma unroll
+    for (int oo = 0; oo < OC; ++oo) emit(o0 + oo, acc[oo]);
+  }
+}
+
+// dx[i] = sum_o W[o][i] dz[o], produced 8 inputs at a time.
+template <int IN, int OUT, class Emit>
+__device__ __forceinline__ void dense_bwd(const float* __restrict__ W, const float (&dz)[OUT], Emit emit) {
+  static_assert(IN % 8 == 0, "shape");
+#pragma unroll 1
+  for (int i0 = 0; i0 < IN; i0 += 8) {
+    float acc[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) acc[k] = 0.f;
+#pragma unroll
+    for (int o = 0; o < OUT; ++o) {
+      float4 a = *reinterpret_cast<const float4*>(W + o * IN + i0);
+      float4 c = *reinterpret_cast<const float4*>(W + o * IN + i0 + 4);
+      acc[0] = fmaf(a.x, dz[o], acc[0]);
+      acc[1] = fmaf(a.y, dz[o], acc[1]);
+      acc[2] = fmaf(a.z, dz[o], acc[2]);
+      acc[3] = fmaf(a.w, dz[o], acc[3]);
+      acc[4] = fmaf(c.x, dz[o], acc[4]);
+      acc[5] = fmaf(c.y, dz[o], acc[5]);
+      acc[6] = fmaf(c.z, dz[o], acc[6]);
+      acc[7] = fmaf(c.w, dz[o], acc[7]);
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) emit(i0 + k, acc[k]);
+  }
+}
+
+struct TileIter {
+  int64_t tile, tile_end;
+};
+
+// contiguous tile ranges per CTA so a CTA reloads weights only when the expert changes
+__device__ __forceinline__ TileIter my_tiles(int64_t ntiles) {
+  TileIter it;
+  it.tile = ntiles * blockIdx.x / gridDim.x;
+  it.tile_end = ntiles * (blockIdx.x + 1) / gridDim.x;
+  return it;
+}
+
+// ---------------------------------------------------------------------------------------
+// MLP forward
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(NT) k_ngp_mlp_fwd(PointSrc src, const int32_t* __restrict__ pair_point, const float* __restrict__ pair_w,
+                                                    const int32_t* __restrict__ seg, int64_t M_ident, ExpertTable tab,
+                                                    const float* __restrict__ enc, float* __restrict__ sv, int64_t ld, int keep,
+                                                    float* __restrict__ out) {
+  extern __shared__ __align__(16) float smem[];
+  float* sw = smem;
+  float* act = smem + W_FLOATS;
+  int* s_seg = reinterpret_cast<int*>(act + ACT_FLOATS);
+  if (threadIdx.x <= tab.E) s_seg[threadIdx.x] = seg ? seg[threadIdx.x] : (threadIdx.x == 0 ? 0 : (int)M_ident);
+  __syncthreads();
+  int64_t M = seg ? s_seg[tab.E] : M_ident;
+  TileIter it = my_tiles((M + NT - 1) / NT);
+  int cur_e = -1;
+  float* a = act + threadIdx.x;  // this thread's activation column: a[o*NT]
+  for (; it.tile < it.tile_end; ++it.tile) {
+    int64_t m = it.tile * NT + threadIdx.x;
+    int e = seg ? find_expert(s_seg, tab.E, it.tile * NT) : 0;
+    if (e != cur_e) {
+      __syncthreads();
+      load_weights(sw, tab.ex[e]);
+      __syncthreads();
+      cur_e = e;
+    }
+    bool in_range = m < M;
+    int64_t p = in_range ? (pair_point ? (int64_t)pair_point[m] : m) : -1;
+    int64_t mm = in_range ? m : 0;  // clamped slot for loads
+    float* svm = sv + mm;  // only dereferenced when `save`
+    bool save = keep && in_range;
+
+    float x32[32];
+#pragma unroll
+    for (int i = 0; i < 32; ++i) x32[i] = in_range ? __ldg(enc + (int64_t)i * ld + mm) : 0.f;
+    dense_fwd<32, 64, 8>(sw + W0_OFF, sw + B0, x32, [&](int o, float v) {
+      v = fmaxf(v, 0.f);
+      a[o * NT] = v;
+      if (save) svm[(int64_t)(R_H0 + o) * ld] = v;
+    });
+    float x64[64];
+#pragma unroll
+    for (int i = 0; i < 64; ++i) x64[i] = a[i * NT];
+    dense_fwd<64, 64, 8>(sw + W1_OFF, sw + B1, x64, [&](int o, float v) {
+      v = fmaxf(v, 0.f);
+      a[o * NT] = v;
+      if (save) svm[(int64_t)(R_H1 + o) * ld] = v;
+    });
+#pragma unroll
+    for (int i = 0; i < 64; ++i) x64[i] = a[i * NT];
+    // heads: rows 0..14 geo, row 15 sigma
+    float sigma = 0.f;
+    dense_fwd<64, 16, 8>(sw + WH_OFF, sw + BH, x64, [&](int o, float v) {
+      if (o == 15) {
+        // trunc_exp (models/trunc_exp.py:30-57)
+        sigma = expf(fminf(fmaxf(v, -88.722839111f), 88.722839111f));
+        a[31 * NT] = 0.f;
+        if (save) svm[(int64_t)(R_CIN + 31) * ld] = 0.f;
+      } else {
+        a[o * NT] = v;
+        if (save) svm[(int64_t)(R_CIN + o) * ld] = v;
+      }
+    });
+    {
+      float dx = 0.f, dy = 0.f, dz = 1.f;
+      if (p >= 0) load_dir(src, p, dx, dy, dz);
+      normalize3(dx, dy, dz, 1e-9f);  // meta_ngp.py:165-168
+      normalize3(dx, dy, dz, 1e-9f);  // encodings.py:141
+      float sh[16];
+      sh16_eval(dx, dy, dz, sh);
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        a[(15 + i) * NT] = sh[i];
+        if (save) svm[(int64_t)(R_CIN + 15 + i) * ld] = sh[i];
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 32; ++i) x32[i] = a[i * NT];
+    dense_fwd<32, 64, 8>(sw + W3_OFF, sw + B3, x32, [&](int o, float v) {
+      v = fmaxf(v, 0.f);
+      a[o * NT] = v;
+      if (save) svm[(int64_t)(R_C0 + o) * ld] = v;
+    });
+#pragma unroll
+    for (int i = 0; i < 64; ++i) x64[i] = a[i * NT];
+    dense_fwd<64, 64, 8>(sw + W4_OFF, sw + B4, x64, [&](int o, float v) {
+      v = fmaxf(v, 0.f);
+      a[o * NT] = v;
+      if (save) svm[(int64_t)(R_C1 + o) * ld] = v;
+    });
+#pragma unroll
+    for (int i = 0; i < 64; ++i) x64[i] = a[i * NT];
+    float rgb[4];
+    dense_fwd<64, 4, 4>(sw + W5_OFF, sw + B5, x64, [&](int o, float v) { rgb[o] = 1.f / (1.f + expf(-v)); });
+    if (save) {
+      svm[(int64_t)(R_Y + 0) * ld] = rgb[0];
+      svm[(int64_t)(R_Y + 1) * ld] = rgb[1];
+      svm[(int64_t)(R_Y + 2) * ld] = rgb[2];
+      svm[(int64_t)(R_Y + 3) * ld] = sigma;
+    }
+    if (p >= 0) {
+      if (pair_point) {
+        float w = pair_w[m];
+        float* o = out + p * 4;
+        atomicAdd(o + 0, rgb[0] * w);
+        atomicAdd(o + 1, rgb[1] * w);
+        atomicAdd(o + 2, rgb[2] * w);
+        atomicAdd(o + 3, sigma * w);
+      } else {
+        *reinterpret_cast<float4*>(out + p * 4) = make_float4(rgb[0], rgb[1], rgb[2], sigma);
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// MLP backward (dgrad chain); weight gradients are reduced afterwards by wgrad_launch
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(NT) k_ngp_mlp_bwd(const int32_t* __restrict__ pair_point, const float* __restrict__ pair_w,
+                                                    const int32_t* __restrict__ seg, int64_t M_ident, ExpertTable tab,
+                                                    const float* __restrict__ sv, int64_t ld, const float* __restrict__ d_out,
+                                                    float* __restrict__ ws, float* __restrict__ d_enc) {
+  extern __shared__ __align__(16) float smem[];
+  float* sw = smem;
+  float* act = smem + W_FLOATS;
+  int* s_seg = reinterpret_cast<int*>(act + ACT_FLOATS);
+  if (threadIdx.x <= tab.E) s_seg[threadIdx.x] = seg ? seg[threadIdx.x] : (threadIdx.x == 0 ? 0 : (int)M_ident);
+  __syncthreads();
+  int64_t M = seg ? s_seg[tab.E] : M_ident;
+  int64_t Mld = round_ld(M);
+  TileIter it = my_tiles(Mld / NT);
+  int cur_e = -1;
+  float* a = act + threadIdx.x;
+  for (; it.tile < it.tile_end; ++it.tile) {
+    int64_t m = it.tile * NT + threadIdx.x;  // m < ld always: every ws row is fully written (zeros for padding)
+    int e = seg ? find_expert(s_seg, tab.E, it.tile * NT) : 0;
+    if (e != cur_e) {
+      __syncthreads();
+      load_weights(sw, tab.ex[e]);
+      __syncthreads();
+      cur_e = e;
+    }
+    bool in_range = m < M;
+    int64_t p = in_range ? (pair_point ? (int64_t)pair_point[m] : m) : -1;
+    const float* svm = sv + (in_range ? m : 0);
+    float* wsm = ws + m;
+    float4 dy = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (p >= 0) {
+      dy = __ldg(reinterpret_cast<const float4*>(d_out + p * 4));
+      if (pair_point) {
+        float w = pair_w[m];
+        dy.x *= w; dy.y *= w; dy.z *= w; dy.w *= w;
+      }
+    }
+    bool live = p >= 0;
+    float r0 = svm[(int64_t)(R_Y + 0) * ld], r1 = svm[(int64_t)(R_Y + 1) * ld], r2 = svm[(int64_t)(R_Y + 2) * ld];
+    float sg = svm[(int64_t)(R_Y + 3) * ld];
+    float dz5[4];
+    dz5[0] = live ? dy.x * r0 * (1.f - r0) : 0.f;
+    dz5[1] = live ? dy.y * r1 * (1.f - r1) : 0.f;
+    dz5[2] = live ? dy.z * r2 * (1.f - r2) : 0.f;
+    dz5[3] = 0.f;
+    float dsraw = live ? dy.w * sg : 0.f;  // trunc_exp backward: g * exp(clamped)
+#pragma unroll
+    for (int i = 0; i < 4; ++i) wsm[(int64_t)(R_DZ5 + i) * ld] = dz5[i];
+
+    // dz4 = (W5^T dz5) * [c1 > 0]
+    dense_bwd<64, 4>(sw + W5_OFF, dz5, [&](int i, float v) {
+      v = (live && svm[(int64_t)(R_C1 + i) * ld] > 0.f) ? v : 0.f;
+      a[i * NT] = v;
+      wsm[(int64_t)(R_DZ4 + i) * ld] = v;
+    });
+    float d64[64];
+#pragma unroll
+    for (int i = 0; i < 64; ++i) d64[i] = a[i * NT];
+    // dz3 = (W4^T dz4) * [c0 > 0]
+    dense_bwd<64, 64>(sw + W4_OFF, d64, [&](int i, float v) {
+      v = (live && svm[(int64_t)(R_C0 + i) * ld] > 0.f) ? v : 0.f;
+      a[i * NT] = v;
+      wsm[(int64_t)(R_DZ3 + i) * ld] = v;
+    });
+#pragma unroll
+    for (int i = 0; i < 64; ++i) d64[i] = a[i * NT];
+    // dcin = W3^T dz3 ; geo part -> dzh[0..14], dzh[15] = d sigma_raw
+    float dzh[16];
+    dense_bwd<32, 64>(sw + W3_OFF, d64, [&](int i, float v) { a[i * NT] = live ? v : 0.f; });
+#pragma unroll
+    for (int i = 0; i < 15; ++i) dzh[i] = a[i * NT];
+    dzh[15] = dsraw;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) wsm[(int64_t)(R_DZH + i) * ld] = dzh[i];
+    // dz1 = (Wh^T dzh) * [h1 > 0]
+    dense_bwd<64, 16>(sw + WH_OFF, dzh, [&](int i, float v) {
+      v = (live && svm[(int64_t)(R_H1 + i) * ld] > 0.f) ? v : 0.f;
+      a[i * NT] = v;
+      wsm[(int64_t)(R_DZ1 + i) * ld] = v;
+    });
+#pragma unroll
+    for (int i = 0; i < 64; ++i) d64[i] = a[i * NT];
+    // dz0 = (W1^T dz1) * [h0 > 0]
+    dense_bwd<64, 64>(sw + W1_OFF, d64, [&](int i, float v) {
+      v = (live && svm[(int64_t)(R_H0 + i) * ld] > 0.f) ? v : 0.f;
+      a[i * NT] = v;
+      wsm[(int64_t)(R_DZ0 + i) * ld] = v;
+    });
+#pragma unroll
+    for (int i = 0; i < 64; ++i) d64[i] = a[i * NT];
+    // d_enc = W0^T dz0
+    dense_bwd<32, 64>(sw + W0_OFF, d64, [&](int i, float v) { d_enc[(int64_t)i * ld + m] = live ? v : 0.f; });
+  }
+}
+
+static int fill_table(ExpertTable& tab, const AcnNgpExpert* experts, int E) {
+  tab.E = E;
+  for (int e = 0; e < E; ++e) tab.ex[e] = experts[e];
+  for (int e = E; e < ACN_MAX_EXPERTS; ++e) tab.ex[e] = experts[0];
+  return 0;
+}
+
+static int check_common(const AcnPoints* pts, const AcnPairs* pairs, const AcnNgpExpert* experts, int E, const AcnGridDesc* g,
+                        const char* who) {
+  ACN_REQUIRE(pts && pairs && experts && g, "%s: NULL argument", who);
+  ACN_REQUIRE(E >= 1 && E <= ACN_MAX_EXPERTS, "%s: E must be in [1,%d]", who, ACN_MAX_EXPERTS);
+  ACN_REQUIRE(g->levels == 16 && g->features == 2, "%s: fused expert path needs L=16, F=2 (got L=%d F=%d)", who, g->levels, g->features);
+  ACN_REQUIRE(g->log2_T >= 1 && g->log2_T <= 24 && g->interp >= 0 && g->interp <= 2, "%s: bad grid descriptor", who);
+  ACN_REQUIRE(pts->x6 || (pts->rays && pts->t && pts->S >= 1), "%s: points need x6 or (rays,t,S)", who);
+  bool ident = pairs->point == nullptr;
+  ACN_REQUIRE(ident ? (E == 1 && pairs->Mcap == pts->P) : (pairs->weight && pairs->seg), "%s: inconsistent pair list", who);
+  ACN_REQUIRE(pairs->Mcap < ((int64_t)1 << 31), "%s: chunk the pair list below 2^31", who);
+  return ACN_OK;
+}
+
+}  // namespace acn
+
+using namespace acn;
+
+extern "C" {
+
+int64_t acn_ngp_ld(int64_t Mcap) { return h_round_ld(Mcap); }
+int64_t acn_ngp_save_bytes(int64_t Mcap) { return sizeof(float) * R_SAVE * h_round_ld(Mcap); }
+int64_t acn_ngp_bwd_ws_bytes(int64_t Mcap, int E) { return sizeof(float) * (R_WS * h_round_ld(Mcap) + wgrad_partial_floats(E)); }
+
+int acn_ngp_encode_fwd(const AcnPoints* pts, const AcnPairs* pairs, const AcnNgpExpert* experts, int E, const AcnGridDesc* g,
+                       float* enc, void* stream) {
+  int rc = check_common(pts, pairs, experts, E, g, "acn_ngp_encode_fwd");
+  if (rc) return rc;
+  ACN_REQUIRE(enc, "acn_ngp_encode_fwd: enc is NULL");
+  int64_t Mcap = pairs->Mcap;
+  if (Mcap == 0) return ACN_OK;
+  ExpertTable tab;
+  fill_table(tab, experts, E);
+  dim3 hg(persistent_grid((Mcap + 255) / 256, 4), g->levels);
+  k_ngp_hash_fwd<<<hg, 256, 0, as_stream(stream)>>>(make_src(pts), pairs->point, pairs->seg, Mcap, tab, make_grid(g), enc, h_round_ld(Mcap));
+  ACN_LAUNCH_CHECK();
+  return ACN_OK;
+}
+
+int acn_ngp_encode_bwd(const AcnPoints* pts, const AcnPairs* pairs, const AcnNgpExpert* experts, int E, const AcnGridDesc* g,
+                       const float* d_enc, const AcnNgpExpertGrads* grads, void* stream) {
+  int rc = check_common(pts, pairs, experts, E, g, "acn_ngp_encode_bwd");
+  if (rc) return rc;
+  ACN_REQUIRE(d_enc && grads, "acn_ngp_encode_bwd: NULL argument");
+  int64_t Mcap = pairs->Mcap;
+  if (Mcap == 0) return ACN_OK;
+  ExpertTable tab;
+  fill_table(tab, experts, E);
+  bool any_table = false;
+  GradTables gts;
+  for (int e = 0; e < ACN_MAX_EXPERTS; ++e) {
+    gts.t[e] = (e < E) ? grads[e].table : nullptr;
+    any_table = any_table || gts.t[e];
+  }
+  if (!any_table) return ACN_OK;
+  dim3 hg(persistent_grid((Mcap + 255) / 256, 4), g->levels);
+  k_ngp_hash_bwd<<<hg, 256, 0, as_stream(stream)>>>(make_src(pts), pairs->point, pairs->seg, Mcap, tab, make_grid(g), d_enc, h_round_ld(Mcap), gts);
+  ACN_LAUNCH_CHECK();
+  return ACN_OK;
+}
+
+static int set_mlp_attrs() {
+  static thread_local int done_dev = -1;
+  int dev = 0;
+  ACN_CUDA(cudaGetDevice(&dev));
+  if (done_dev != dev) {
+    ACN_CUDA(cudaFuncSetAttribute(k_ngp_mlp_fwd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MLP_SMEM));
+    ACN_CUDA(cudaFuncSetAttribute(k_ngp_mlp_bwd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MLP_SMEM));
+    done_dev = dev;
+  }
+  return ACN_OK;
+}
+
+int acn_ngp_mlp_fwd(const AcnPoints* pts, const AcnPairs* pairs, const AcnNgpExpert* experts, int E, const float* enc, float* out,
+                    void* save, void* stream) {
+  ACN_REQUIRE(pts && pairs && experts && enc && out, "acn_ngp_mlp_fwd: NULL argument");
+  ACN_REQUIRE(E >= 1 && E <= ACN_MAX_EXPERTS, "acn_ngp_mlp_fwd: E must be in [1,%d]", ACN_MAX_EXPERTS);
+  ACN_REQUIRE(pts->x6 || (pts->rays && pts->S >= 1), "acn_ngp_mlp_fwd: points need x6 or rays");
+  bool ident = pairs->point == nullptr;
+  ACN_REQUIRE(ident ? (E == 1 && pairs->Mcap == pts->P) : (pairs->weight && pairs->seg), "acn_ngp_mlp_fwd: inconsistent pair list");
+  int64_t Mcap = pairs->Mcap;
+  if (Mcap == 0) return ACN_OK;
+  int rc = set_mlp_attrs();
+  if (rc) return rc;
+  ExpertTable tab;
+  fill_table(tab, experts, E);
+  int grid = persistent_grid((Mcap + NT - 1) / NT, 2);
+  k_ngp_mlp_fwd<<<grid, NT, MLP_SMEM, as_stream(stream)>>>(make_src(pts), pairs->point, pairs->weight, pairs->seg, Mcap, tab, enc,
+                                                            reinterpret_cast<float*>(save), h_round_ld(Mcap), save ? 1 : 0, out);
+  ACN_LAUNCH_CHECK();
+  return ACN_OK;
+}
+
+int acn_ngp_mlp_bwd(const AcnPairs* pairs, const AcnNgpExpert* experts, int E, const float* enc, const float* d_out, const void* save,
+                    const AcnNgpExpertGrads* grads, float* d_enc, void* ws, void* stream) {
+  ACN_REQUIRE(pairs && experts && enc && d_out && save && grads && d_enc && ws, "acn_ngp_mlp_bwd: NULL argument");
+  ACN_REQUIRE(E >= 1 && E <= ACN_MAX_EXPERTS, "acn_ngp_mlp_bwd: E must be in [1,%d]", ACN_MAX_EXPERTS);
+  bool ident = pairs->point == nullptr;
+  ACN_REQUIRE(ident ? E == 1 : (pairs->weight && pairs->seg), "acn_ngp_mlp_bwd: inconsistent pair list");
+  int64_t Mcap = pairs->Mcap;
+  if (Mcap == 0) return ACN_OK;
+  int rc = set_mlp_attrs();
+  if (rc) return rc;
+  cudaStream_t st = as_stream(stream);
+  ExpertTable tab;
+  fill_table(tab, experts, E);
+  int64_t ld = h_round_ld(Mcap);
+  const float* sv = reinterpret_cast<const float*>(save);
+  float* w = reinterpret_cast<float*>(ws);
+  float* partial = w + (int64_t)R_WS * ld;
+  int grid = persistent_grid(ld / NT, 2);
+  k_ngp_mlp_bwd<<<grid, NT, MLP_SMEM, st>>>(pairs->point, pairs->weight, pairs->seg, Mcap, tab, sv, ld, d_out, w, d_enc);
+  ACN_LAUNCH_CHECK();
+  // weight gradients: layer -> (dz rows, x rows, OUT, IN); x of layer 0 is the encoding itself
+  struct L {
+    int layer, dz_row, x_row, OUT, IN;
+  };
+  const L jobs[7] = {{0, R_DZ0, -1, 64, 32},  {1, R_DZ1, R_H0, 64, 64}, {3, R_DZH, R_H1, 15, 64}, {2, R_DZH + 15, R_H1, 1, 64},
+                     {4, R_DZ3, R_CIN, 64, 31}, {5, R_DZ4, R_C0, 64, 64}, {6, R_DZ5, R_C1, 3, 64}};
+  for (const L& j : jobs) {
+    float* dW[ACN_MAX_EXPERTS];
+    float* db[ACN_MAX_EXPERTS];
+    bool any = false;
+    for (int e = 0; e < E; ++e) {
+      dW[e] = grads[e].w[j.layer];
+      db[e] = grads[e].b[j.layer];
+      any = any || dW[e] || db[e];
+    }
+    if (!any) continue;
+    WgradJob job{w + (int64_t)j.dz_row * ld, j.x_row < 0 ? enc : sv + (int64_t)j.x_row * ld, j.OUT, j.IN, ld};
+    rc = wgrad_launch(job, pairs->seg, E, Mcap, dW, db, partial, st);
+    if (rc) return rc;
+  }
+  return ACN_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,157 @@
+"""K-expert container with the reference's interface (``models/inr/meta_container.py``
+MetaContainer :21-503): same constructor, buffers / sub-module names (state_dict keys),
+``forward``, ``_routing``, ``background_color``, ``get_param_groups``.
+
+Dispatch differs by design: instead of K x (nonzero -> index_select -> expert -> index_add_),
+one routing+pack kernel groups the (point, expert) pairs by expert and ONE fused launch
+evaluates every expert over its own segment (csrc/routing.cu, csrc/ngp.cu)."""
+from __future__ import annotations
+
+from typing import Dict, List, Optional, Tuple
+
+import torch
+import torch.nn as nn
+
+from ... import ops
+from ..encodings import FrequencyEncoder, SHEncoder
+from ..metamodule import MetaModule
+from .meta_ngp import MetaNGP
+
+
+def build_expert(nerf_variant: str, **nerf_kwargs) -> nn.Module:
+    if nerf_variant == "instant":
+        return MetaNGP(**nerf_kwargs)
+    raise NotImplementedError(
+        f"nerf_variant={nerf_variant!r}: the reference's 'vanilla' expert cannot be built through its own container "
+        "(SURVEY.md note V); the PE-MLP expert is driven stand-alone (nerf_sys_b200.models.inr.meta_vanilla)")
+
+
+class MetaContainer(MetaModule):
+    def __init__(self, num_submodules: int, centroids: torch.Tensor, aabb: torch.Tensor, nerf_variant: str = "instant",
+                 boundary_margin: float = 1.0, cluster_2d: bool = True, joint_training: bool = False, use_bg_nerf: bool = True,
+                 bg_hidden: int = 32, bg_encoding: str = "spherical", occ_conf: Optional[Dict] = None, **nerf_kwargs):
+        super().__init__()
+        assert num_submodules > 0
+        assert centroids.ndim == 2 and centroids.size(0) == num_submodules
+        assert boundary_margin >= 1.0
+        occ_conf = occ_conf or {}
+        self.register_buffer("scene_aabb_vec", torch.cat([aabb[0], aabb[1]], dim=0).float(), persistent=True)
+        self.register_buffer("centroids", centroids.to(torch.float32), persistent=True)
+        self.use_occ = bool(occ_conf.get("use_occ", False))
+        self.boundary_margin, self.cluster_2d = float(boundary_margin), bool(cluster_2d)
+        self.joint_training = bool(joint_training)
+        self._coord_idx = (1, 2) if self.cluster_2d else (0, 1, 2)
+        self.nerf_variant, self.dim_out = nerf_variant, 4
+
+        expert_box_list = nerf_kwargs.pop("expert_box_list")
+        self.submodules = nn.ModuleList()
+        for box in expert_box_list:
+            self.submodules.append(build_expert(nerf_variant, **{**nerf_kwargs, "occ_conf": occ_conf, "scene_box": box}))
+
+        self.use_bg_nerf = bool(use_bg_nerf)
+        if self.use_bg_nerf:
+            if bg_encoding == "spherical":
+                self.bg_dir_enc = SHEncoder(levels=4)
+            else:
+                self.bg_dir_enc = FrequencyEncoder(pe_dim=4, include_input=True, use_pi=False)
+            self.bg_hidden_dim = int(bg_hidden)
+            self.bg_mlp = nn.Sequential(nn.Linear(self.bg_dir_enc.out_dim, self.bg_hidden_dim, bias=True), nn.ReLU(),
+                                        nn.Linear(self.bg_hidden_dim, 3, bias=True), nn.Sigmoid())
+        self._cent_host = None
+
+    # ---- host copy of the centroids (they travel in the kernel-parameter block) ----
+    def centroids_host(self) -> List[float]:
+        key = (self.centroids.data_ptr(), self.centroids._version)
+        if self._cent_host is None or self._cent_host[0] != key:
+            self._cent_host = (key, self.centroids.detach().float().cpu().reshape(-1).tolist())
+        return self._cent_host[1]
+
+    # ---- routing ------------------------------------------------------------------
+    def _routing(self, pts: torch.Tensor) -> Tuple[Optional[torch.Tensor], Optional[torch.Tensor]]:
+        """(N,3) world points -> (weights (N,K), None) for soft routing or (None, argmin (N,))."""
+        assert pts.dim() == 2 and pts.shape[-1] == 3, "pts must be (N,3)"
+        x6 = torch.cat([pts.float(), torch.zeros_like(pts, dtype=torch.float32)], dim=-1)
+        with torch.no_grad():
+            return ops.routing(ops.PointSet(x6=x6), self.centroids_host(), len(self.submodules), self.boundary_margin, self.cluster_2d)
+
+    def expert_spec(self) -> ops.ExpertSpec:
+        boxes = [sub.box_host() for sub in self.submodules]
+        return ops.ExpertSpec(self.submodules[0].xyz_encoder.grid_desc(), [b[0] for b in boxes], [b[1] for b in boxes])
+
+    def _sub_params(self, params, k: int):
+        return None if params is None else self.get_subdict(params, f"submodules.{k}")
+
+    def evaluate(self, pts: ops.PointSet, params=None, active_module: Optional[int] = None) -> torch.Tensor:
+        """(P,4) [rgb, sigma] for a point set (explicit rows or implicit ray samples)."""
+        K = len(self.submodules)
+        if active_module is not None:
+            sub = self.submodules[active_module]
+            sub._require_fused()
+            return ops.ngp_experts(pts, ops.PairList(pts.P), sub.expert_spec(), [sub.xyz_encoder.hash_table],
+                                   sub.mlp_tensors(self._sub_params(params, active_module)))
+        for sub in self.submodules:
+            sub._require_fused()
+        if K == 1 and self.boundary_margin > 1.0:
+            # a single centroid always gets weight 1: skip the pack, keep the fused launch
+            sub = self.submodules[0]
+            return ops.ngp_experts(pts, ops.PairList(pts.P), sub.expert_spec(), [sub.xyz_encoder.hash_table],
+                                   sub.mlp_tensors(self._sub_params(params, 0)))
+        with torch.no_grad():
+            pairs = ops.route_pack(pts, self.centroids_host(), K, self.boundary_margin, self.cluster_2d)
+        tables = [sub.xyz_encoder.hash_table for sub in self.submodules]
+        mlp: List[torch.Tensor] = []
+        for k, sub in enumerate(self.submodules):
+            mlp.extend(sub.mlp_tensors(self._sub_params(params, k)))
+        return ops.ngp_experts(pts, pairs, self.expert_spec(), tables, mlp)
+
+    def forward(self, x: torch.Tensor, params=None, active_module: Optional[int] = None) -> torch.Tensor:
+        assert x.dim() == 2 and x.shape[-1] >= 6, "x must be (N,D>=6)"
+        x6 = x if x.shape[-1] == 6 else x[:, :6]
+        return self.evaluate(ops.PointSet(x6=x6), params=params, active_module=active_module)
+
+    # ---- background ---------------------------------------------------------------
+    def background_color(self, d: torch.Tensor) -> torch.Tensor:
+        if not self.use_bg_nerf:
+            raise RuntimeError("background_color called but use_bg_nerf=False")
+        if d.dim() not in (2, 3):
+            raise ValueError(f"background_color expects (N,3) or (B,N,3), got {tuple(d.shape)}")
+        if not isinstance(self.bg_dir_enc, SHEncoder) or self.bg_hidden_dim != 32:
+            raise NotImplementedError("the sm_100a background kernel implements SH16 -> 32 -> 3")
+        l0, l1 = self.bg_mlp[0], self.bg_mlp[2]
+        rgb = ops.background(d.reshape(-1, 3) if d.dim() == 3 else d, l0.weight, l0.bias, l1.weight, l1.bias)
+        return rgb.view(*d.shape[:-1], 3)
+
+    # ---- occupancy hooks (not built) -------------------------------
+    def maybe_update_expert_occupancies(self, step: int, params=None) -> None:
+        return None
+
+    def freeze_expert_occupancies(self, flag: bool) -> None:
+        return None
+
+    def premark_invisible_expert_cells(self, metas, near_plane: float = 0.0, chunk: int = 32 ** 3) -> List[int]:
+        return [0] * len(self.submodules)
+
+    @property
+    def occ_ready(self) -> bool:
+        return all(getattr(sub, "occ_ready", False) for sub in self.submodules)
+
+    @property
+    def cells_premarked(self) -> bool:
+        return all(getattr(sub, "occ_premarked", False) for sub in self.submodules)
+
+    # ---- optimiser groups ----------------------------------------------------------
+    def get_param_groups(self) -> Dict[str, Dict]:
+        enc, sig, col, bg = [], [], [], []
+        for sub in self.submodules:
+            g = sub.get_param_groups()
+            enc.extend(g["encoding"]["params"])
+            sig.extend(g["sigma"]["params"])
+            col.extend(g["color"]["params"])
+        if self.use_bg_nerf:
+            bg.extend(list(self.bg_dir_enc.parameters()))
+            bg.extend(list(self.bg_mlp.parameters()))
+        groups: Dict[str, Dict] = {}
+        for name, ps in (("encoding", enc), ("sigma", sig), ("color", col), ("background", bg)):
+            if ps:
+                groups[name] = {"params": ps}
+        return groups

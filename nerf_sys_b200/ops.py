@@ -1,0 +1,644 @@
+"""Tensor-level wrappers and autograd Functions over the C ABI (include/acnerf.h).
+
+PyTorch is plumbing here: it owns device memory (caching allocator), the current
+stream and the autograd graph.  Every computation is a call into
+libacnerf_sm100a.so; inputs must be CUDA fp32 tensors - CPU tensors raise.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import List, Optional, Sequence, Tuple
+
+import torch
+
+from . import _lib
+from ._lib import (ACN_MAX_EXPERTS, ACN_NGP_LAYERS, ACN_TILE, AcnGridDesc, AcnNgpExpert, AcnNgpExpertGrads, AcnPairs,
+                   AcnPoints, check, host_floats, lib)
+
+Tensor = torch.Tensor
+
+# per-expert MLP tensors in ABI layer order (include/acnerf.h: AcnNgpExpert)
+NGP_LAYER_KEYS = ("sigma_trunk.0.linear", "sigma_trunk.1.linear", "sigma_head", "geo_head", "color_mlp.0.linear",
+                  "color_mlp.1.linear", "color_mlp.2")
+NGP_LAYER_SHAPES = ((64, 32), (64, 64), (1, 64), (15, 64), (64, 31), (64, 64), (3, 64))
+INTERP = {"linear": 0, "smoothstep": 1, "nearest": 2}
+
+_launches = 0  # kernels launched through this module (bench.py's gpu_launches claim)
+
+
+def launches() -> int:
+    return _launches
+
+
+def _count(n: int):
+    global _launches
+    _launches += n
+
+
+def _stream() -> C.c_void_p:
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _ptr(t: Optional[Tensor]):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def _need(t: Tensor, name: str, dtype=torch.float32) -> Tensor:
+    if not isinstance(t, torch.Tensor):
+        raise TypeError(f"{name} must be a tensor")
+    if not t.is_cuda:
+        raise RuntimeError(f"{name} is on {t.device}: nerf_sys_b200 runs on CUDA (sm_100a) only, there is no CPU path")
+    if t.dtype != dtype:
+        raise TypeError(f"{name} must be {dtype}, got {t.dtype}")
+    return t if t.is_contiguous() else t.contiguous()
+
+
+def _f32(t: Tensor, name: str) -> Tensor:
+    """CUDA check + cast to contiguous fp32 (callers may hand fp16 under autocast)."""
+    if not t.is_cuda:
+        raise RuntimeError(f"{name} is on {t.device}: nerf_sys_b200 runs on CUDA (sm_100a) only, there is no CPU path")
+    if t.dtype != torch.float32:
+        t = t.float()
+    return t if t.is_contiguous() else t.contiguous()
+
+
+def device_ok(index: Optional[int] = None):
+    idx = torch.cuda.current_device() if index is None else index
+    check(lib().acn_device_ok(idx), "acn_device_ok")
+
+
+# --------------------------------------------------------------------------
+# descriptors
+# --------------------------------------------------------------------------
+def grid_desc(levels: int, log2_T: int, interp: str, res: Sequence[int], features: int = 2) -> AcnGridDesc:
+    g = AcnGridDesc()
+    g.levels, g.features, g.log2_T = int(levels), int(features), int(log2_T)
+    g.interp = INTERP[str(interp).lower()]
+    for i in range(_lib.ACN_MAX_LEVELS):
+        g.res[i] = int(res[i]) if i < len(res) else 0
+    return g
+
+
+class PointSet:
+    """Sample points: explicit (P,6) rows, or implicit (rays (N,8), t (N,S))."""
+
+    def __init__(self, x6: Optional[Tensor] = None, rays: Optional[Tensor] = None, t: Optional[Tensor] = None):
+        if x6 is not None:
+            self.x6 = _f32(x6, "x6")
+            self.rays = self.t = None
+            self.S, self.P = 1, self.x6.shape[0]
+            self.device = self.x6.device
+        else:
+            self.x6 = None
+            self.rays, self.t = _f32(rays, "rays"), _f32(t, "t")
+            self.S, self.P = int(self.t.shape[1]), int(self.t.numel())
+            self.device = self.rays.device
+
+    def c(self) -> AcnPoints:
+        p = AcnPoints()
+        p.x6, p.rays, p.t = _ptr(self.x6), _ptr(self.rays), _ptr(self.t)
+        p.S, p.P = self.S, self.P
+        return p
+
+
+class PairList:
+    """Routed (point, expert) pairs grouped by expert; identity when point is None."""
+
+    def __init__(self, M: int, point: Optional[Tensor] = None, weight: Optional[Tensor] = None, seg: Optional[Tensor] = None,
+                 seg_host: Optional[List[int]] = None):
+        self.M, self.point, self.weight, self.seg, self.seg_host = int(M), point, weight, seg, seg_host
+
+    @property
+    def identity(self) -> bool:
+        return self.point is None
+
+    def c(self) -> AcnPairs:
+        p = AcnPairs()
+        p.point, p.weight, p.seg, p.Mcap = _ptr(self.point), _ptr(self.weight), _ptr(self.seg), self.M
+        return p
+
+
+# --------------------------------------------------------------------------
+# a1-a5 rays and sampling
+# --------------------------------------------------------------------------
+def ray_directions(H: int, W: int, fx: float, fy: float, cx: float, cy: float, center_pixels: bool, device) -> Tensor:
+    out = torch.empty(H, W, 3, device=device, dtype=torch.float32)
+    with torch.cuda.device(out.device):
+        check(lib().acn_ray_directions(H, W, fx, fy, cx, cy, int(bool(center_pixels)), _ptr(out), _stream()), "acn_ray_directions")
+    _count(1)
+    return out
+
+
+def _c2w_host(c2w: Tensor):
+    m = c2w.detach().to("cpu", torch.float32)
+    return host_floats(m[:3, :4].reshape(-1).tolist())
+
+
+def _aabb_host(aabb: Optional[Tensor]):
+    if aabb is None:
+        return None
+    return host_floats(aabb.detach().to("cpu", torch.float32).reshape(-1).tolist())
+
+
+def get_rays(dirs: Tensor, c2w: Tensor, aabb: Optional[Tensor], near: Optional[float], far: Optional[float],
+             max_bound: float = 1e10, invalid_value: float = 1e10) -> Tensor:
+    d = _f32(dirs, "directions").reshape(-1, 3)
+    out = torch.empty(d.shape[0], 8, device=d.device, dtype=torch.float32)
+    with torch.cuda.device(d.device):
+        check(lib().acn_get_rays(_ptr(d), d.shape[0], _c2w_host(c2w), _aabb_host(aabb), float(near or 0.0), float(far or 0.0),
+                                 float(max_bound), float(invalid_value), _ptr(out), _stream()), "acn_get_rays")
+    _count(1)
+    return out.reshape(*dirs.shape[:-1], 8)
+
+
+def raygen(H: int, W: int, fx, fy, cx, cy, center_pixels: bool, c2w: Tensor, aabb: Optional[Tensor], device, near=0.0, far=0.0,
+           row0: int = 0, rows: Optional[int] = None) -> Tensor:
+    rows = H - row0 if rows is None else rows
+    out = torch.empty(rows * W, 8, device=device, dtype=torch.float32)
+    with torch.cuda.device(out.device):
+        check(lib().acn_raygen(H, W, row0, rows, fx, fy, cx, cy, int(bool(center_pixels)), _c2w_host(c2w), _aabb_host(aabb),
+                               float(near), float(far), _ptr(out), _stream()), "acn_raygen")
+    _count(1)
+    return out
+
+
+def ray_aabb(o: Tensor, d: Tensor, aabb: Tensor, max_bound: float = 1e10, invalid_value: float = 1e10) -> Tuple[Tensor, Tensor]:
+    o, d = _f32(o, "origins"), _f32(d, "directions")
+    n = o.shape[0]
+    tn, tf = torch.empty(n, device=o.device), torch.empty(n, device=o.device)
+    with torch.cuda.device(o.device):
+        check(lib().acn_ray_aabb(_ptr(o), _ptr(d), n, _aabb_host(aabb), float(max_bound), float(invalid_value), _ptr(tn), _ptr(tf),
+                                 _stream()), "acn_ray_aabb")
+    _count(1)
+    return tn, tf
+
+
+def clamp_near_far(rays: Tensor, override, eps: float = 1e-6, invalid_value: float = float("inf")) -> Tuple[Tensor, Tensor]:
+    r = _f32(rays, "rays")
+    n = r.shape[0]
+    valid = torch.empty(n, device=r.device, dtype=torch.uint8)
+    with torch.cuda.device(r.device):
+        if override is None:
+            check(lib().acn_clamp_near_far(_ptr(r), n, 1, 0, 0.0, 0, 0.0, float(eps), float(invalid_value), None, _ptr(valid),
+                                           _stream()), "acn_clamp_near_far")
+            out = rays
+        else:
+            lo, hi = override
+            out = torch.empty_like(r)
+            check(lib().acn_clamp_near_far(_ptr(r), n, 0, int(lo is not None), float(lo or 0.0), int(hi is not None),
+                                           float(hi or 0.0), float(eps), float(invalid_value), _ptr(out), _ptr(valid), _stream()),
+                  "acn_clamp_near_far")
+    _count(1)
+    return out, valid.bool()
+
+
+_tau_cache = {}
+
+
+def _tau(S: int, device) -> Tensor:
+    """torch.linspace(0,1,S) evaluated by the CPU kernel (the reference's values), cached on the device."""
+    key = (S, str(device))
+    if key not in _tau_cache:
+        _tau_cache[key] = torch.linspace(0.0, 1.0, S).to(device)
+    return _tau_cache[key]
+
+
+def stratified_t(rays: Tensor, S: int, u: Optional[Tensor]) -> Tensor:
+    r = _f32(rays, "rays")
+    N = r.shape[0]
+    t = torch.empty(N, S, device=r.device, dtype=torch.float32)
+    if u is not None:
+        u = _f32(u, "u")
+        if tuple(u.shape) != (N, S):
+            raise ValueError(f"u must be ({N},{S}), got {tuple(u.shape)}")
+    with torch.cuda.device(r.device):
+        check(lib().acn_stratified_t(_ptr(r), N, S, _ptr(_tau(S, r.device)), _ptr(u), _ptr(t), _stream()), "acn_stratified_t")
+    _count(1)
+    return t
+
+
+def sample_points(rays: Tensor, t: Tensor) -> Tensor:
+    r, tt = _f32(rays, "rays"), _f32(t, "t")
+    N, S = tt.shape
+    x6 = torch.empty(N * S, 6, device=r.device, dtype=torch.float32)
+    with torch.cuda.device(r.device):
+        check(lib().acn_sample_points(_ptr(r), _ptr(tt), N, S, _ptr(x6), _stream()), "acn_sample_points")
+    _count(1)
+    return x6
+
+
+# --------------------------------------------------------------------------
+# a6-a7 routing
+# --------------------------------------------------------------------------
+def routing(pts: PointSet, centroids_host: Sequence[float], K: int, margin: float, cluster_2d: bool):
+    if K > ACN_MAX_EXPERTS:
+        raise ValueError(f"at most {ACN_MAX_EXPERTS} experts per routing call (got {K})")
+    ch = host_floats(centroids_host)
+    cp = pts.c()
+    with torch.cuda.device(pts.device):
+        if margin > 1.0:
+            w = torch.empty(pts.P, K, device=pts.device, dtype=torch.float32)
+            check(lib().acn_routing(C.byref(cp), ch, K, float(margin), int(cluster_2d), _ptr(w), None, _stream()), "acn_routing")
+            _count(1)
+            return w, None
+        hard = torch.empty(pts.P, device=pts.device, dtype=torch.int64)
+        check(lib().acn_routing(C.byref(cp), ch, K, float(margin), int(cluster_2d), None, _ptr(hard), _stream()), "acn_routing")
+    _count(1)
+    return None, hard
+
+
+def route_pack(pts: PointSet, centroids_host: Sequence[float], K: int, margin: float, cluster_2d: bool) -> PairList:
+    """Routing + stable pack by expert.  One 4*(K+1)-byte device->host read fixes the exact
+    pair count (the reference syncs K times through nonzero(), meta_container.py:309)."""
+    if K > ACN_MAX_EXPERTS:
+        raise ValueError(f"at most {ACN_MAX_EXPERTS} experts per routing call (got {K})")
+    L = lib()
+    ch = host_floats(centroids_host)
+    cp = pts.c()
+    dev = pts.device
+    with torch.cuda.device(dev):
+        cap = int(L.acn_route_pack_capacity(pts.P, K))
+        ws = torch.empty(int(L.acn_route_pack_ws_bytes(pts.P, K)) // 4 + 1, device=dev, dtype=torch.int32)
+        seg = torch.empty(K + 1, device=dev, dtype=torch.int32)
+        while True:
+            point = torch.empty(cap, device=dev, dtype=torch.int32)
+            weight = torch.empty(cap, device=dev, dtype=torch.float32)
+            check(L.acn_route_pack(C.byref(cp), ch, K, float(margin), int(cluster_2d), _ptr(point), _ptr(weight), _ptr(seg), cap,
+                                   _ptr(ws), _stream()), "acn_route_pack")
+            _count(3)
+            seg_host = seg.tolist()
+            if seg_host[K] <= cap:
+                break
+            cap = seg_host[K]
+    M = seg_host[K]
+    return PairList(M, point[:M], weight[:M], seg, seg_host)
+
+
+# --------------------------------------------------------------------------
+# a9-a11 stand-alone encoders
+# --------------------------------------------------------------------------
+def hashgrid_indices(x01: Tensor, g: AcnGridDesc) -> Tensor:
+    x = _need(x01, "x01")
+    idx = torch.empty(x.shape[0], g.levels, 8, device=x.device, dtype=torch.int32)
+    with torch.cuda.device(x.device):
+        check(lib().acn_hashgrid_indices(_ptr(x), x.shape[0], C.byref(g), _ptr(idx), _stream()), "acn_hashgrid_indices")
+    _count(1)
+    return idx
+
+
+class HashGridFn(torch.autograd.Function):
+    """HashGridEncoder.forward and its autograd backward (models/encodings.py:293-381)."""
+
+    @staticmethod
+    def forward(ctx, x01: Tensor, table: Tensor, g: AcnGridDesc):
+        x = _need(x01.detach().reshape(-1, 3), "x01")
+        tb = _need(table.detach(), "hash_table")
+        y = torch.empty(x.shape[0], g.levels * g.features, device=x.device, dtype=torch.float32)
+        with torch.cuda.device(x.device):
+            check(lib().acn_hashgrid_fwd(_ptr(x), x.shape[0], _ptr(tb), C.byref(g), _ptr(y), _stream()), "acn_hashgrid_fwd")
+        _count(1)
+        ctx.g, ctx.shape = g, table.shape
+        ctx.save_for_backward(x)
+        return y.reshape(*x01.shape[:-1], g.levels * g.features)
+
+    @staticmethod
+    def backward(ctx, dy):
+        (x,) = ctx.saved_tensors
+        g = ctx.g
+        dy = _f32(dy, "dy").reshape(x.shape[0], -1)
+        grad = torch.zeros(ctx.shape, device=x.device, dtype=torch.float32)
+        with torch.cuda.device(x.device):
+            check(lib().acn_hashgrid_bwd(_ptr(x), x.shape[0], _ptr(dy), C.byref(g), _ptr(grad), _stream()), "acn_hashgrid_bwd")
+        _count(1)
+        return None, grad, None
+
+
+def sh16(d: Tensor) -> Tensor:
+    x = _f32(d, "d").reshape(-1, 3)
+    out = torch.empty(x.shape[0], 16, device=x.device, dtype=torch.float32)
+    with torch.cuda.device(x.device):
+        check(lib().acn_sh16(_ptr(x), x.shape[0], _ptr(out), _stream()), "acn_sh16")
+    _count(1)
+    return out.reshape(*d.shape[:-1], 16)
+
+
+def freq_encode(x: Tensor, n_freq: int, include_input: bool = True) -> Tensor:
+    xx = _f32(x, "x").reshape(-1, 3)
+    width = (3 if include_input else 0) + 6 * n_freq
+    out = torch.empty(xx.shape[0], width, device=xx.device, dtype=torch.float32)
+    with torch.cuda.device(xx.device):
+        check(lib().acn_freq_encode(_ptr(xx), xx.shape[0], int(n_freq), int(include_input), _ptr(out), _stream()), "acn_freq_encode")
+    _count(1)
+    return out.reshape(*x.shape[:-1], width)
+
+
+# --------------------------------------------------------------------------
+# a8-a14 hash-grid experts over routed pairs
+# --------------------------------------------------------------------------
+class ExpertSpec:
+    """Static (non-tensor) description of E experts for one fused call."""
+
+    def __init__(self, grid: AcnGridDesc, box_min: Sequence[Sequence[float]], extent: Sequence[Sequence[float]]):
+        self.grid, self.box_min, self.extent = grid, [list(map(float, b)) for b in box_min], [list(map(float, e)) for e in extent]
+        self.E = len(self.box_min)
+        if self.E > ACN_MAX_EXPERTS:
+            raise ValueError(f"at most {ACN_MAX_EXPERTS} experts per fused call (got {self.E})")
+
+
+def _expert_array(spec: ExpertSpec, tables: Optional[Sequence[Tensor]], mlp: Optional[Sequence[Tensor]]):
+    arr = (AcnNgpExpert * spec.E)()
+    for e in range(spec.E):
+        if tables is not None:
+            arr[e].table = _ptr(tables[e])
+        if mlp is not None:
+            for l in range(ACN_NGP_LAYERS):
+                arr[e].w[l] = _ptr(mlp[e * 14 + 2 * l])
+                arr[e].b[l] = _ptr(mlp[e * 14 + 2 * l + 1])
+        for a in range(3):
+            arr[e].box_min[a] = spec.box_min[e][a]
+            arr[e].extent[a] = spec.extent[e][a]
+    return arr
+
+
+def _check_mlp(mlp: Sequence[Tensor], E: int) -> List[Tensor]:
+    if len(mlp) != 14 * E:
+        raise ValueError(f"expected {14 * E} MLP tensors, got {len(mlp)}")
+    out = []
+    for i, t in enumerate(mlp):
+        l = (i % 14) // 2
+        shape = NGP_LAYER_SHAPES[l] if i % 2 == 0 else (NGP_LAYER_SHAPES[l][0],)
+        if tuple(t.shape) != shape:
+            raise ValueError(f"expert {i // 14} {NGP_LAYER_KEYS[l]}.{'weight' if i % 2 == 0 else 'bias'} must be {shape}, got "
+                             f"{tuple(t.shape)}: the fused sm_100a expert is specialised on the production shape "
+                             "hidden=64, sigma_depth=2, color_depth=2, geo_feat_dim=15, SH16")
+        out.append(_need(t.detach(), "mlp tensor"))
+    return out
+
+
+class NgpEncodeFn(torch.autograd.Function):
+    """pairs -> enc (32, ld) feature-major; backward scatters into each expert's table grad."""
+
+    @staticmethod
+    def forward(ctx, pts: PointSet, pairs: PairList, spec: ExpertSpec, *tables: Tensor):
+        L = lib()
+        tb = [_need(t.detach(), "hash_table") for t in tables]
+        rows = spec.grid.levels << spec.grid.log2_T
+        for t in tb:
+            if tuple(t.shape) != (rows, 2):
+                raise ValueError(f"hash_table must be ({rows},2), got {tuple(t.shape)}")
+        ld = int(L.acn_ngp_ld(pairs.M))
+        enc = torch.empty(32, ld, device=pts.device, dtype=torch.float32)
+        ex = _expert_array(spec, tb, None)
+        cp, cq = pts.c(), pairs.c()
+        with torch.cuda.device(pts.device):
+            check(L.acn_ngp_encode_fwd(C.byref(cp), C.byref(cq), ex, spec.E, C.byref(spec.grid), _ptr(enc), _stream()),
+                  "acn_ngp_encode_fwd")
+        _count(1)
+        ctx.pts, ctx.pairs, ctx.spec = pts, pairs, spec
+        ctx.save_for_backward(*tb)
+        return enc
+
+    @staticmethod
+    def backward(ctx, d_enc):
+        L = lib()
+        tb = ctx.saved_tensors
+        pts, pairs, spec = ctx.pts, ctx.pairs, ctx.spec
+        d_enc = _f32(d_enc, "d_enc")
+        grads = (AcnNgpExpertGrads * spec.E)()
+        outs = []
+        for e in range(spec.E):
+            if ctx.needs_input_grad[3 + e] and _segment_len(pairs, e) > 0:
+                g = torch.zeros_like(tb[e])
+                grads[e].table = _ptr(g)
+                outs.append(g)
+            else:
+                outs.append(None)
+        ex = _expert_array(spec, tb, None)
+        cp, cq = pts.c(), pairs.c()
+        with torch.cuda.device(pts.device):
+            check(L.acn_ngp_encode_bwd(C.byref(cp), C.byref(cq), ex, spec.E, C.byref(spec.grid), _ptr(d_enc), grads, _stream()),
+                  "acn_ngp_encode_bwd")
+        _count(1)
+        return (None, None, None, *outs)
+
+
+def _segment_len(pairs: PairList, e: int) -> int:
+    if pairs.identity:
+        return pairs.M
+    return pairs.seg_host[e + 1] - pairs.seg_host[e]
+
+
+class NgpMlpFn(torch.autograd.Function):
+    """enc (32, ld) + directions -> out (P,4) = combine_k w_k * [rgb, sigma]_k."""
+
+    @staticmethod
+    def forward(ctx, enc: Tensor, pts: PointSet, pairs: PairList, spec: ExpertSpec, *mlp: Tensor):
+        L = lib()
+        ws = _check_mlp(mlp, spec.E)
+        enc_c = _need(enc.detach(), "enc")
+        need_grad = any(ctx.needs_input_grad)  # False under no_grad: inference keeps no activations
+        dev = pts.device
+        out = torch.empty(pts.P, 4, device=dev, dtype=torch.float32) if pairs.identity else torch.zeros(pts.P, 4, device=dev,
+                                                                                                        dtype=torch.float32)
+        save = torch.empty(int(L.acn_ngp_save_bytes(pairs.M)) // 4, device=dev, dtype=torch.float32) if need_grad else None
+        ex = _expert_array(spec, None, ws)
+        cp, cq = pts.c(), pairs.c()
+        with torch.cuda.device(dev):
+            check(L.acn_ngp_mlp_fwd(C.byref(cp), C.byref(cq), ex, spec.E, _ptr(enc_c), _ptr(out), _ptr(save), _stream()),
+                  "acn_ngp_mlp_fwd")
+        _count(1)
+        ctx.pts, ctx.pairs, ctx.spec, ctx.save = pts, pairs, spec, save
+        ctx.save_for_backward(enc_c, *ws)
+        return out
+
+    @staticmethod
+    def backward(ctx, d_out):
+        L = lib()
+        enc, *ws = ctx.saved_tensors
+        pts, pairs, spec = ctx.pts, ctx.pairs, ctx.spec
+        if ctx.save is None:
+            raise RuntimeError("NgpMlpFn.backward without saved activations (forward ran under no_grad)")
+        dev = pts.device
+        d_out = _f32(d_out, "d_out")
+        grads = (AcnNgpExpertGrads * spec.E)()
+        outs: List[Optional[Tensor]] = []
+        for e in range(spec.E):
+            live = _segment_len(pairs, e) > 0
+            for l in range(ACN_NGP_LAYERS):
+                for j in range(2):
+                    i = e * 14 + 2 * l + j
+                    if ctx.needs_input_grad[4 + i] and live:
+                        g = torch.empty_like(ws[i])
+                        if j == 0:
+                            grads[e].w[l] = _ptr(g)
+                        else:
+                            grads[e].b[l] = _ptr(g)
+                        outs.append(g)
+                    else:
+                        outs.append(None)
+        d_enc = torch.empty_like(enc)
+        wsb = torch.empty(int(L.acn_ngp_bwd_ws_bytes(pairs.M, spec.E)) // 4, device=dev, dtype=torch.float32)
+        ex = _expert_array(spec, None, ws)
+        cq = pairs.c()
+        with torch.cuda.device(dev):
+            check(L.acn_ngp_mlp_bwd(C.byref(cq), ex, spec.E, _ptr(enc), _ptr(d_out), _ptr(ctx.save), grads, _ptr(d_enc), _ptr(wsb),
+                                    _stream()), "acn_ngp_mlp_bwd")
+        _count(1 + 14)
+        ctx.save = None
+        return (d_enc if ctx.needs_input_grad[0] else None, None, None, None, *outs)
+
+
+def ngp_experts(pts: PointSet, pairs: PairList, spec: ExpertSpec, tables: Sequence[Tensor], mlp: Sequence[Tensor]) -> Tensor:
+    """(P,4) [rgb, sigma] of E hash-grid experts over `pairs` (MetaNGP.forward / MetaContainer.forward)."""
+    enc = NgpEncodeFn.apply(pts, pairs, spec, *tables)
+    return NgpMlpFn.apply(enc, pts, pairs, spec, *mlp)
+
+
+# --------------------------------------------------------------------------
+# a16 background head
+# --------------------------------------------------------------------------
+class BgFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, d: Tensor, stride: int, N: int, w0: Tensor, b0: Tensor, w1: Tensor, b1: Tensor):
+        L = lib()
+        dd = _need(d.detach(), "directions")
+        p = [_need(t.detach(), "bg parameter") for t in (w0, b0, w1, b1)]
+        if tuple(p[0].shape) != (32, 16) or tuple(p[2].shape) != (3, 32):
+            raise ValueError("background head must be SH16 -> 32 -> 3 (bg_hidden=32, spherical encoding)")
+        need_grad = any(ctx.needs_input_grad)
+        rgb = torch.empty(N, 3, device=dd.device, dtype=torch.float32)
+        save = torch.empty(int(L.acn_bg_save_bytes(N)) // 4, device=dd.device, dtype=torch.float32) if need_grad else None
+        with torch.cuda.device(dd.device):
+            check(L.acn_bg_forward(_ptr(dd), stride, N, _ptr(p[0]), _ptr(p[1]), _ptr(p[2]), _ptr(p[3]), _ptr(rgb), _ptr(save),
+                                   _stream()), "acn_bg_forward")
+        _count(1)
+        ctx.N, ctx.save = N, save
+        ctx.save_for_backward(*p)
+        return rgb
+
+    @staticmethod
+    def backward(ctx, d_rgb):
+        L = lib()
+        w0, b0, w1, b1 = ctx.saved_tensors
+        if ctx.save is None:
+            raise RuntimeError("BgFn.backward without saved activations")
+        d_rgb = _f32(d_rgb, "d_rgb")
+        g = [torch.empty_like(t) for t in (w0, b0, w1, b1)]
+        ws = torch.empty(int(L.acn_bg_bwd_ws_bytes(ctx.N)) // 4, device=w0.device, dtype=torch.float32)
+        with torch.cuda.device(w0.device):
+            check(L.acn_bg_backward(_ptr(d_rgb), ctx.N, _ptr(w0), _ptr(w1), _ptr(ctx.save), _ptr(g[0]), _ptr(g[1]), _ptr(g[2]),
+                                    _ptr(g[3]), _ptr(ws), _stream()), "acn_bg_backward")
+        _count(5)
+        ctx.save = None
+        return (None, None, None, *g)
+
+
+def background(d: Tensor, w0: Tensor, b0: Tensor, w1: Tensor, b1: Tensor) -> Tensor:
+    """(N,3) directions (any row stride that keeps the 3 components adjacent) -> (N,3) rgb."""
+    if d.dim() != 2 or d.shape[1] != 3 or d.stride(1) != 1:
+        d = d.reshape(-1, 3).contiguous()
+    if not d.is_cuda:
+        raise RuntimeError("background(): CUDA tensors only")
+    if d.dtype != torch.float32:
+        d = d.float().contiguous()
+    return BgFn.apply(d, int(d.stride(0)), int(d.shape[0]), w0, b0, w1, b1)
+
+
+# --------------------------------------------------------------------------
+# a17 compositing
+# --------------------------------------------------------------------------
+class CompositeFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, rgb_sigma: Tensor, t: Tensor, bg: Optional[Tensor], sigma_scale: float):
+        rs = _f32(rgb_sigma.detach(), "rgb_sigma")
+        tt = _f32(t.detach(), "t_vals")
+        N, S = tt.shape
+        if tuple(rs.shape) != (N, S, 4):
+            raise ValueError(f"rgb_sigma must be ({N},{S},4), got {tuple(rs.shape)}")
+        b = None if bg is None else _f32(bg.detach(), "bg_rgb")
+        dev = rs.device
+        rgb, depth = torch.empty(N, 3, device=dev), torch.empty(N, device=dev)
+        w, acc = torch.empty(N, S, device=dev), torch.empty(N, device=dev)
+        with torch.cuda.device(dev):
+            check(lib().acn_composite_fwd(_ptr(rs), _ptr(tt), _ptr(b), N, S, float(sigma_scale), _ptr(rgb), _ptr(depth), _ptr(w),
+                                          _ptr(acc), _stream()), "acn_composite_fwd")
+        _count(1)
+        ctx.scale, ctx.has_bg = float(sigma_scale), b is not None
+        ctx.save_for_backward(rs, tt, b if b is not None else rs.new_empty(0))
+        return rgb, depth, w, acc
+
+    @staticmethod
+    def backward(ctx, g_rgb, g_depth, g_w, g_acc):
+        rs, tt, b = ctx.saved_tensors
+        N, S = tt.shape
+        dev = rs.device
+        b = b if ctx.has_bg else None
+        g_rgb = torch.zeros(N, 3, device=dev) if g_rgb is None else _f32(g_rgb, "g_rgb")
+        g_depth = None if g_depth is None else _f32(g_depth, "g_depth")
+        g_acc = None if g_acc is None else _f32(g_acc, "g_acc")
+        g_w = None if g_w is None else _f32(g_w, "g_weights")
+        d_rs = torch.empty_like(rs)
+        d_bg = torch.empty_like(b) if (b is not None and ctx.needs_input_grad[2]) else None
+        with torch.cuda.device(dev):
+            check(lib().acn_composite_bwd(_ptr(rs), _ptr(tt), _ptr(b), N, S, ctx.scale, _ptr(g_rgb), _ptr(g_depth), _ptr(g_acc),
+                                          _ptr(g_w), _ptr(d_rs), _ptr(d_bg), _stream()), "acn_composite_bwd")
+        _count(1)
+        return d_rs, None, d_bg, None
+
+
+def composite(rgb_sigma: Tensor, t: Tensor, bg: Optional[Tensor], sigma_scale: float = 1.0):
+    return CompositeFn.apply(rgb_sigma, t, bg, float(sigma_scale))
+
+
+# --------------------------------------------------------------------------
+# a18 loss, (f)2 optimiser pieces
+# --------------------------------------------------------------------------
+class MseFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, pred: Tensor, gt: Tensor, space: int):
+        p, g = _f32(pred.detach(), "pred"), _f32(gt.detach(), "gt")
+        N = p.shape[0]
+        loss = torch.empty(1, device=p.device)
+        d_pred = torch.empty_like(p)
+        ws = torch.empty(2048, device=p.device)
+        with torch.cuda.device(p.device):
+            check(lib().acn_mse_loss(_ptr(p), _ptr(g), N, int(space), _ptr(loss), _ptr(d_pred), _ptr(ws), _stream()), "acn_mse_loss")
+        _count(2)
+        ctx.save_for_backward(d_pred)
+        return loss.reshape(())
+
+    @staticmethod
+    def backward(ctx, g):
+        (d_pred,) = ctx.saved_tensors
+        return d_pred * g, None, None
+
+
+def mse_loss(pred: Tensor, gt: Tensor, color_space: str = "linear") -> Tensor:
+    return MseFn.apply(pred, gt, {"linear": 0, "srgb": 1, "identity": 2}[str(color_space).lower()])
+
+
+def adam_step(param: Tensor, grad: Tensor, exp_avg: Tensor, exp_avg_sq: Tensor, lr: float, beta1: float, beta2: float, eps: float,
+              weight_decay: float, step: int, grad_scale: Optional[Tensor] = None):
+    for t, n in ((param, "param"), (grad, "grad"), (exp_avg, "exp_avg"), (exp_avg_sq, "exp_avg_sq")):
+        if not (t.is_cuda and t.dtype == torch.float32 and t.is_contiguous()):
+            raise RuntimeError(f"adam_step: {n} must be a contiguous CUDA fp32 tensor")
+    with torch.cuda.device(param.device):
+        check(lib().acn_adam_step(_ptr(param), _ptr(grad), _ptr(exp_avg), _ptr(exp_avg_sq), param.numel(), lr, beta1, beta2, eps,
+                                  weight_decay, int(step), _ptr(grad_scale), _stream()), "acn_adam_step")
+    _count(1)
+
+
+def sgd_axpy(w: Tensor, g: Tensor, lr: float) -> Tensor:
+    ww, gg = _need(w.detach(), "w"), _need(g.detach(), "g")
+    out = torch.empty_like(ww)
+    with torch.cuda.device(ww.device):
+        check(lib().acn_sgd_axpy(_ptr(ww), _ptr(gg), float(lr), ww.numel(), _ptr(out), _stream()), "acn_sgd_axpy")
+    _count(1)
+    return out
+
+
+def sumsq_accum(x: Tensor, acc: Tensor):
+    xx = _need(x.detach(), "x")
+    with torch.cuda.device(xx.device):
+        check(lib().acn_sumsq_accum(_ptr(xx), xx.numel(), _ptr(acc), _stream()), "acn_sumsq_accum")
+    _count(1)

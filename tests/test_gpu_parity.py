@@ -1,0 +1,454 @@
+"""GPU parity: every CUDA entry point (through the C ABI, via nerf_sys_b200.ops and the drop-in
+modules) against (a) the golden vectors produced by the real reference and (b) the CPU oracle
+on seeded inputs.  Integer / index / mask outputs must be bit-exact; fp32 tolerances are
+written beside each check (relative to the tensor's max magnitude unless stated)."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import T, load_golden, state_from
+from oracle import acnerf_oracle as O
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def close(a, b, tol, what=""):
+    a = torch.as_tensor(a).detach().float().cpu()
+    b = torch.as_tensor(b).detach().float().cpu()
+    assert a.shape == b.shape, (what, a.shape, b.shape)
+    fin = torch.isfinite(b)
+    assert torch.equal(torch.isfinite(a), fin), what
+    assert torch.equal(a[~fin], b[~fin]), what
+    if fin.any():
+        err = (a[fin] - b[fin]).abs().max().item()
+        scale = max(1.0, b[fin].abs().max().item())
+        assert err <= tol * scale, f"{what}: max-abs err {err:.3e} > {tol:.1e} * {scale:.3e}"
+
+
+def rel_close(a, b, tol, what=""):
+    """max|a-b| <= tol * max|b| (for gradients, whose scale is arbitrary)."""
+    a = torch.as_tensor(a).detach().float().cpu()
+    b = torch.as_tensor(b).detach().float().cpu()
+    assert a.shape == b.shape, (what, a.shape, b.shape)
+    scale = b.abs().max().item()
+    err = (a - b).abs().max().item()
+    assert err <= tol * max(scale, 1e-30), f"{what}: max-abs err {err:.3e} > {tol:.1e} * {scale:.3e}"
+
+
+@pytest.fixture(scope="module", autouse=True)
+def _device():
+    from nerf_sys_b200 import ops
+    ops.device_ok()
+    yield
+
+
+# ----------------------------------------------------------------------------- a1-a3
+def test_rays_golden():
+    from nerf_sys_b200.nerfs.ray_sampling import clamp_rays_near_far, get_ray_directions, get_rays
+    from nerf_sys_b200.nerfs.scene_box import SceneBox
+    from nerf_sys_b200 import ops
+    z = load_golden("rays")
+    H, W, fx, fy, cx, cy = z["intr"]
+    H, W = int(H), int(W)
+    aabb, c2w = T(z["aabb"]).to(DEV), T(z["c2w"]).to(DEV)
+    box = SceneBox(aabb)
+    for cp in (0, 1):
+        d = get_ray_directions(H, W, fx, fy, cx, cy, bool(cp), DEV)
+        close(d, z[f"dirs_cp{cp}"], 2e-7, "dirs")  # fp32, <=2 ulp of 1.0
+        rays = get_rays(d, c2w, scene_box=box)
+        assert rays.shape == (H, W, 8)
+        close(rays, z[f"rays_cp{cp}"], 1e-6, "rays")
+        fused = ops.raygen(H, W, fx, fy, cx, cy, bool(cp), c2w, aabb, DEV)
+        close(fused.view(H, W, 8), z[f"rays_cp{cp}"], 1e-6, "raygen")
+        # row-sharded generation is the same pixels
+        part = ops.raygen(H, W, fx, fy, cx, cy, bool(cp), c2w, aabb, DEV, row0=5, rows=4)
+        assert torch.equal(part, fused.view(H, W, 8)[5:9].reshape(-1, 8))
+        # with the golden directions as input the world rays are a pure 3x3 product + slab test
+        rays2 = get_rays(T(z[f"dirs_cp{cp}"]).to(DEV), c2w, scene_box=box)
+        close(rays2, z[f"rays_cp{cp}"], 5e-7, "rays from golden dirs")
+    n, f = box.ray_aabb_intersect(T(z["extra_o"]).to(DEV), T(z["extra_d"]).to(DEV))
+    assert np.array_equal(n.cpu().numpy(), z["extra_near"]) and np.array_equal(f.cpu().numpy(), z["extra_far"])  # exact
+    flat = T(z["rays_cp1"]).view(-1, 8).to(DEV)
+    r, v = clamp_rays_near_far(flat, (0.05, 1.2))
+    assert np.array_equal(r.cpu().numpy(), z["clamp_a"]) and np.array_equal(v.cpu().numpy(), z["valid_a"])
+    r, v = clamp_rays_near_far(flat, (None, 0.4))
+    assert np.array_equal(r.cpu().numpy(), z["clamp_b"]) and np.array_equal(v.cpu().numpy(), z["valid_b"])
+    r, v = clamp_rays_near_far(flat, None)
+    assert r is flat and np.array_equal(v.cpu().numpy(), z["valid_none"])
+    near_const = get_rays(T(z["dirs_cp1"]).to(DEV).view(-1, 3), c2w, None, near=0.1, far=2.5)
+    assert torch.all(near_const[:, 6] == 0.1) and torch.all(near_const[:, 7] == 2.5)
+
+
+# ----------------------------------------------------------------------------- a4-a5
+def test_stratified_t_and_points_bit_exact():
+    from nerf_sys_b200 import ops
+    z = load_golden("t_vals")
+    near, far = T(z["near"]), T(z["far"])
+    rays = torch.zeros(near.numel(), 8)
+    rays[:, :3] = torch.randn(near.numel(), 3, generator=torch.Generator().manual_seed(1))
+    rays[:, 3:6] = torch.randn(near.numel(), 3, generator=torch.Generator().manual_seed(2))
+    rays[:, 6], rays[:, 7] = near, far
+    rd = rays.to(DEV)
+    for S in (2, 7, 64, 96):
+        tt = ops.stratified_t(rd, S, T(z[f"u{S}"]).to(DEV))
+        te = ops.stratified_t(rd, S, None)
+        assert np.array_equal(tt.cpu().numpy(), z[f"t_train{S}"]), f"train t, S={S}"  # bit-exact
+        assert np.array_equal(te.cpu().numpy(), z[f"t_eval{S}"]), f"eval t, S={S}"
+        x6 = ops.sample_points(rd, tt)
+        ref = O.sample_points(rays, T(z[f"t_train{S}"]))
+        assert torch.equal(x6.cpu(), ref), "sample positions must be bit-exact (mul then add, no FMA)"
+
+
+# ----------------------------------------------------------------------------- a6-a7
+@pytest.mark.parametrize("tag,margin,c2d", [("soft2d", 1.05, True), ("hard2d", 1.0, True), ("soft3d", 1.2, False), ("hard3d", 1.0, False)])
+def test_routing_golden(tag, margin, c2d):
+    from nerf_sys_b200 import ops
+    z = load_golden("routing")
+    pts, cent = T(z["pts"]), T(z["centroids"])
+    x6 = torch.cat([pts, torch.zeros_like(pts)], -1).to(DEV)
+    ps = ops.PointSet(x6=x6)
+    K = cent.shape[0]
+    w, hard = ops.routing(ps, cent.reshape(-1).tolist(), K, margin, c2d)
+    wd, hd = O.routing(pts, cent, margin, c2d, direct=True)  # the kernel's contract: direct fp32 distances
+    if w is not None:
+        assert torch.equal((w > 0).cpu(), wd > 0), "membership mask must be bit-exact vs the direct-distance oracle"
+        close(w, wd, 2e-7, "weights")
+        ref = T(z[tag])  # the reference's cdist form: identical decisions except on planted bisector points
+        diff = ((w.cpu() > 0) != (ref > 0)).any(dim=1)
+        assert diff.sum().item() <= 160 and not diff[160:].any()
+        close(w.cpu()[~diff], ref[~diff], 1e-4, "weights vs reference cdist")
+    else:
+        assert torch.equal(hard.cpu(), hd), "argmin must be bit-exact vs the direct-distance oracle"
+        bad = hard.cpu().numpy() != z[tag]
+        assert bad.sum() <= 160 and not bad[160:].any()
+
+
+def test_route_pack_is_a_stable_partition():
+    from nerf_sys_b200 import ops
+    g = torch.Generator().manual_seed(3)
+    aabb, cent, _ = O.grid_scene(2, 4)
+    for P in (1, 777, 5000, 70001):
+        pts = torch.rand(P, 3, generator=g) * (aabb[1] - aabb[0]) + aabb[0]
+        x6 = torch.cat([pts, torch.zeros_like(pts)], -1).to(DEV)
+        ps = ops.PointSet(x6=x6)
+        for margin in (1.0, 1.05, 1.6):
+            pairs = ops.route_pack(ps, cent.reshape(-1).tolist(), 8, margin, True)
+            wd, hd = O.routing(pts, cent, margin, True, direct=True)
+            seg = pairs.seg_host
+            assert seg[0] == 0 and all(s % 128 == 0 for s in seg) and seg[-1] == pairs.M
+            point, weight = pairs.point.cpu(), pairs.weight.cpu()
+            for k in range(8):
+                sl = point[seg[k]:seg[k + 1]]
+                live = sl[sl >= 0]
+                exp = ((wd[:, k] > 0) if wd is not None else (hd == k)).nonzero().squeeze(1)
+                assert torch.equal(live.long(), exp), f"expert {k}: members must equal nonzero() in order"
+                assert (sl[live.numel():] == -1).all(), "padding slots are -1"
+                if wd is not None:
+                    close(weight[seg[k]:seg[k] + live.numel()], wd[exp, k], 2e-7, "pair weights")
+                else:
+                    assert (weight[seg[k]:seg[k] + live.numel()] == 1).all()
+
+
+# ----------------------------------------------------------------------------- a9-a11
+def test_hash_indices_bit_exact_and_encoders_golden():
+    from nerf_sys_b200 import ops
+    from nerf_sys_b200.models.encodings import FrequencyEncoder, HashGridEncoder, SHEncoder
+    z = load_golden("encodings")
+    x01 = T(z["x01"]).to(DEV)
+    enc20 = HashGridEncoder(levels=16, min_res=16, max_res=4096, log2_hashmap_size=8).to(DEV)
+    assert np.array_equal(enc20.level_resolutions.cpu().numpy(), z["res"])
+    g20 = ops.grid_desc(16, 20, "Linear", z["res"].tolist())
+    idx = ops.hashgrid_indices(x01, g20)
+    assert np.array_equal(idx.cpu().numpy(), z["idx20"]), "hash-table rows (incl. level offset) must be bit-exact"
+    for tag, interp in (("lin8", "Linear"), ("smooth8", "Smoothstep"), ("near8", "Nearest")):
+        enc = HashGridEncoder(levels=16, min_res=16, max_res=4096, log2_hashmap_size=8, interpolation=interp).to(DEV)
+        with torch.no_grad():
+            enc.hash_table.copy_(T(z[f"{tag}_table"]))
+        y = enc(x01)
+        close(y, z[f"{tag}_y"], 1e-6, f"{tag} features")
+        (y * T(z[f"{tag}_gy"]).to(DEV)).sum().backward()
+        rel_close(enc.hash_table.grad, z[f"{tag}_gtable"], 2e-6, f"{tag} table grad")  # atomics: order-dependent fp32 sums
+    d = T(z["dirs"]).to(DEV)
+    close(SHEncoder(levels=4)(d), z["sh16"], 1e-6, "sh16")
+    close(FrequencyEncoder(3, 10)(d), z["freq10"], 2e-6, "freq10")  # |2^9 x| up to ~2e3 rad: 1 ulp of the argument
+    close(FrequencyEncoder(3, 4)(d), z["freq4"], 1e-6, "freq4")
+
+
+def test_hash_indices_full_size_vs_oracle():
+    from nerf_sys_b200 import ops
+    g = torch.Generator().manual_seed(11)
+    x01 = torch.rand(200_000, 3, generator=g).clamp(1e-6, 1 - 1e-6)
+    x01[:1000] = (torch.randint(0, 4096, (1000, 3), generator=g).float() / 4095.0).clamp(1e-6, 1 - 1e-6)  # on cell faces
+    res = O.level_resolutions()
+    ref, _ = O.hash_indices(x01, res, 20)
+    idx = ops.hashgrid_indices(x01.to(DEV), ops.grid_desc(16, 20, "Linear", res.tolist()))
+    assert torch.equal(idx.cpu().long(), ref)
+
+
+# ----------------------------------------------------------------------------- a17
+def test_composite_golden_fwd_bwd():
+    from nerf_sys_b200.nerfs.ray_rendering import volume_render
+    z = load_golden("composite")
+    rs = T(z["rgb_sigma"]).to(DEV).requires_grad_(True)
+    bg = T(z["bg"]).to(DEV).requires_grad_(True)
+    t = T(z["t"]).to(DEV)
+    rgb, depth, w, acc = volume_render(rs, t, bg_rgb=bg)
+    for a, k in ((rgb, "rgb"), (depth, "depth"), (w, "weights"), (acc, "acc")):
+        close(a, z[k], 1e-6, k)  # warp-scan product vs sequential cumprod: a few ulp
+    ((rgb * T(z["g_rgb"]).to(DEV)).sum() + (depth * T(z["g_depth"]).to(DEV)).sum() + (acc * T(z["g_acc"]).to(DEV)).sum()).backward()
+    rel_close(rs.grad, z["d_rgb_sigma"], 5e-6, "d_rgb_sigma")
+    rel_close(bg.grad, z["d_bg"], 2e-6, "d_bg")
+    rgb, depth, _, acc = volume_render(rs.detach(), t, bg_rgb=None, sigma_scale=2.5)
+    close(rgb, z["rgb_s25"], 1e-6)
+    close(acc, z["acc_s25"], 1e-6)
+
+
+@pytest.mark.parametrize("S", [2, 33, 96, 200, 700])
+def test_composite_vs_oracle_all_chunkings(S):
+    from nerf_sys_b200 import ops
+    g = torch.Generator().manual_seed(S)
+    N = 301
+    rs = torch.rand(N, S, 4, generator=g) * 1.2 - 0.1
+    rs[..., 3] = torch.randn(N, S, generator=g).exp() * (30.0 / S) - 0.05
+    t = torch.sort(torch.rand(N, S, generator=g) * 3, dim=1).values
+    bg = torch.rand(N, 3, generator=g)
+    gw = torch.randn(N, S, generator=g)
+    a = rs.clone().requires_grad_(True)
+    ab = bg.clone().requires_grad_(True)
+    rgb, depth, w, acc = O.composite(a, t, ab)
+    (rgb.sum() * 0.7 + (depth * depth).sum() + acc.sum() * 0.3 + (w * gw).sum()).backward()
+    b = rs.to(DEV).requires_grad_(True)
+    bb = bg.to(DEV).requires_grad_(True)
+    rgb2, depth2, w2, acc2 = ops.composite(b, t.to(DEV), bb)
+    (rgb2.sum() * 0.7 + (depth2 * depth2).sum() + acc2.sum() * 0.3 + (w2 * gw.to(DEV)).sum()).backward()
+    close(rgb2, rgb, 2e-6)
+    close(depth2, depth, 2e-6)
+    close(w2, w, 2e-6)
+    close(acc2, acc, 2e-6)
+    rel_close(b.grad, a.grad, 2e-5, "d_rgb_sigma")
+    rel_close(bb.grad, ab.grad, 1e-5, "d_bg")
+
+
+# ----------------------------------------------------------------------------- a8, a12-a16
+def _golden_model():
+    from nerf_sys_b200.models.inr import MetaContainer
+    from nerf_sys_b200.nerfs.scene_box import SceneBox
+    z = load_golden("ngp_path")
+    st = state_from(z)
+    aabb, cent, boxes = O.grid_scene(1, 2)
+    cfg = dict(O.HASH_CFG)
+    cfg["log2_hashmap_size"] = int(z["log2_T"])
+    m = MetaContainer(2, cent, aabb, "instant", boundary_margin=1.05, cluster_2d=True, use_bg_nerf=True, occ_conf={"use_occ": False},
+                      expert_box_list=[SceneBox(b) for b in boxes], hidden=64, sigma_depth=2, color_depth=2, color_hidden=64,
+                      dir_encoding="spherical", use_sigmoid_rgb=True, hash_enc_conf=cfg)
+    m.load_state_dict(st, strict=True)
+    return m.to(DEV), z, st, cfg, [T(z["box_min"][k]) for k in range(2)]
+
+
+def test_expert_container_background_golden():
+    m, z, *_ = _golden_model()
+    x6 = T(z["x6"]).to(DEV)
+    with torch.no_grad():
+        close(m.submodules[0](x6), z["expert0_y"], 2e-6, "expert forward")       # fp32 FFMA vs CPU fp32: sum-order only
+        close(m(x6), z["container_y"], 2e-6, "container forward")
+        close(m(x6, active_module=0), z["expert0_y"], 2e-6, "active_module forward")
+        close(m.background_color(T(z["rays"]).to(DEV)[:, 3:6]), z["bg_rgb"], 1e-6, "background")
+        # layer-wise API parity
+        d = m.submodules[0].density(x6[:, :3], return_feats=True)
+        rgb = m.submodules[0].color(x6[:, 3:6], d["geo_feat"])
+        close(torch.cat([rgb, d["sigma"]], -1), z["expert0_y"], 1e-4, "density()/color()")  # cuBLAS TF32-free fp32 but other order
+
+
+@pytest.mark.parametrize("tag,active", [("full", None), ("act1", 1)])
+def test_render_rays_and_grads_golden(tag, active):
+    from nerf_sys_b200.nerfs.losses import compute_mse_loss
+    from nerf_sys_b200.nerfs.ray_rendering import render_rays
+    m, z, *_ = _golden_model()
+    rays, u, gt = T(z["rays"]).to(DEV), T(z["u"]).to(DEV), T(z["gt"]).to(DEV)
+    S = u.shape[1]
+    m.train()
+    rgb, depth, w, acc = render_rays(m, rays, ray_samples=S, active_module=active, u=u)
+    close(rgb, z[f"{tag}_rgb"], 2e-6, "rgb")
+    close(depth, z[f"{tag}_depth"], 2e-6, "depth")
+    close(w, z[f"{tag}_w"], 2e-6, "weights")
+    close(acc, z[f"{tag}_acc"], 2e-6, "acc")
+    from nerf_sys_b200 import ops
+    loss = ops.mse_loss(rgb, gt, "linear")
+    close(loss, z[f"{tag}_loss"], 1e-6, "loss")
+    loss.backward()
+    n = 0
+    for k, v in z.items():
+        if k.startswith(f"{tag}_grad/"):
+            name = k.split("/", 1)[1]
+            p = dict(m.named_parameters())[name]
+            assert p.grad is not None, name
+            rel_close(p.grad, v, 2e-5, name)
+            n += 1
+    assert n >= 18
+    if active is not None:  # the other expert was never touched
+        other = dict(m.named_parameters())[f"submodules.{1 - active}.xyz_encoder.hash_table"]
+        assert other.grad is None
+    m.eval()
+    with torch.no_grad():
+        rgb, depth, _, acc = render_rays(m, rays, ray_samples=S, active_module=active, bg_color_default="black")
+    close(rgb, z[f"{tag}_eval_rgb"], 2e-6)
+    close(depth, z[f"{tag}_eval_depth"], 2e-6)
+    close(acc, z[f"{tag}_eval_acc"], 2e-6)
+    if active is None:
+        m.use_bg_nerf = False
+        with torch.no_grad():
+            rgb, *_ = render_rays(m, rays, ray_samples=S, bg_color_default="black")
+        close(rgb, z["full_eval_rgb_blackbg"], 2e-6)
+
+
+def test_fast_weights_and_inner_loop_grads():
+    """meta_core.task_adapt's contract: autograd.grad wrt the 14 override tensors of one expert
+    (allow_unused), the hash table untouched by the inner step."""
+    from nerf_sys_b200 import ops
+    from nerf_sys_b200.nerfs.ray_rendering import render_rays
+    m, z, st, cfg, mins = _golden_model()
+    rays, u, gt = T(z["rays"]).to(DEV), T(z["u"]).to(DEV), T(z["gt"]).to(DEV)
+    S = u.shape[1]
+    sub = m.submodules[1]
+    fast = {n: (p.detach() * 1.01).requires_grad_(True) for n, p in sub.meta_named_parameters()}
+    m.train()
+    rgb, *_ = render_rays(m, rays, ray_samples=S, params=fast, active_module=1, u=u)
+    loss = ops.mse_loss(rgb, gt)
+    grads = torch.autograd.grad(loss, tuple(fast.values()), allow_unused=True)
+    assert all(g is not None for g in grads)
+    assert sub.xyz_encoder.hash_table.grad is None
+    # oracle with the same overrides
+    st2 = {k: v.clone() for k, v in st.items()}
+    for n, p in fast.items():
+        st2[f"submodules.1.{n}"] = p.detach().cpu().clone().requires_grad_(True)
+    rgb_o, *_ = O.render_rays(T(z["rays"]), st2, mins, cfg, S=S, margin=1.05, u=T(z["u"]), active=1)
+    loss_o = O.mse_loss(rgb_o, T(z["gt"]))
+    close(loss, loss_o, 1e-6)
+    go = torch.autograd.grad(loss_o, [st2[f"submodules.1.{n}"] for n in fast])
+    for (n, _), a, b in zip(fast.items(), grads, go):
+        rel_close(a, b, 2e-5, n)
+    new = ops.sgd_axpy(fast["sigma_head.weight"], grads[list(fast).index("sigma_head.weight")], 0.015)
+    close(new, fast["sigma_head.weight"].detach().cpu() - 0.015 * go[list(fast).index("sigma_head.weight")], 1e-6)
+
+
+# ----------------------------------------------------------------------------- BASELINE sizes
+def _big_scene(K, gy, gz, log2_T, seed=0, table_std=0.1):
+    from nerf_sys_b200.models.inr import MetaContainer
+    from nerf_sys_b200.nerfs.scene_box import SceneBox
+    aabb, cent, boxes = O.grid_scene(gy, gz)
+    cfg = dict(O.HASH_CFG)
+    cfg["log2_hashmap_size"] = log2_T
+    st = O.init_ngp_state(K, aabb, cent, boxes, cfg, seed=seed, table_std=table_std)
+    m = MetaContainer(K, cent, aabb, "instant", boundary_margin=1.05, cluster_2d=True, use_bg_nerf=True, occ_conf={"use_occ": False},
+                      expert_box_list=[SceneBox(b) for b in boxes], hidden=64, sigma_depth=2, color_depth=2, color_hidden=64,
+                      dir_encoding="spherical", use_sigmoid_rgb=True, hash_enc_conf=cfg)
+    m.load_state_dict(st, strict=True)
+    return m.to(DEV), st, cfg, [b[0] for b in boxes], aabb
+
+
+def test_config2_single_expert_full_table_vs_oracle():
+    """C2 shape (K=1, T=2^20, S=96) on 2048 rays: forward and every gradient vs the CPU oracle."""
+    from nerf_sys_b200 import ops
+    from nerf_sys_b200.nerfs.ray_rendering import render_rays
+    m, st, cfg, mins, aabb = _big_scene(1, 1, 1, 20)
+    N, S = 2048, 96
+    rays = O.aerial_rays(N, aabb, seed=1)
+    g = torch.Generator().manual_seed(5)
+    u, gt = torch.rand(N, S, generator=g), torch.rand(N, 3, generator=g)
+    m.train()
+    rgb, depth, w, acc = render_rays(m, rays.to(DEV), ray_samples=S, u=u.to(DEV))
+    loss = ops.mse_loss(rgb, gt.to(DEV))
+    loss.backward()
+    for k, v in st.items():
+        if "weight" in k or "bias" in k or "hash_table" in k:
+            v.requires_grad_(True)
+    rgb_o, depth_o, w_o, acc_o = O.render_rays(rays, st, mins, cfg, S=S, margin=1.05, u=u)
+    loss_o = O.mse_loss(rgb_o, gt)
+    loss_o.backward()
+    close(rgb, rgb_o, 5e-6, "rgb")      # stated tolerance for the fp32 path: per-ray max-abs 5e-6
+    close(depth, depth_o, 5e-6, "depth")
+    close(acc, acc_o, 5e-6, "acc")
+    close(loss, loss_o, 1e-6, "loss")
+    for n, p in m.named_parameters():
+        rel_close(p.grad, st[n].grad, 5e-5, n)
+    # exactly the rows the oracle touched are non-zero
+    gt_rows = (st["submodules.0.xyz_encoder.hash_table"].grad != 0).any(dim=1)
+    my_rows = (m.submodules[0].xyz_encoder.hash_table.grad != 0).any(dim=1).cpu()
+    assert (gt_rows & ~my_rows).sum().item() <= 0.001 * gt_rows.sum().item()  # only exact-zero products may differ
+    assert (~gt_rows & my_rows).sum().item() == 0
+
+
+def test_config3_eight_experts_soft_routing_vs_oracle():
+    """C3 shape (K=8 on a 2x4 grid, margin 1.05) on 1536 aerial rays x 64 samples, T=2^16."""
+    from nerf_sys_b200 import ops
+    from nerf_sys_b200.nerfs.ray_rendering import render_rays
+    m, st, cfg, mins, aabb = _big_scene(8, 2, 4, 16)
+    N, S = 1536, 64
+    rays = O.aerial_rays(N, aabb, seed=2)
+    g = torch.Generator().manual_seed(6)
+    u, gt = torch.rand(N, S, generator=g), torch.rand(N, 3, generator=g)
+    m.train()
+    rgb, depth, w, acc = render_rays(m, rays.to(DEV), ray_samples=S, u=u.to(DEV))
+    loss = ops.mse_loss(rgb, gt.to(DEV))
+    loss.backward()
+    for k, v in st.items():
+        if "weight" in k or "bias" in k or "hash_table" in k:
+            v.requires_grad_(True)
+    rgb_o, depth_o, w_o, acc_o = O.render_rays(rays, st, mins, cfg, S=S, margin=1.05, u=u, direct_routing=True)
+    loss_o = O.mse_loss(rgb_o, gt)
+    loss_o.backward()
+    close(rgb, rgb_o, 5e-6, "rgb")
+    close(depth, depth_o, 5e-6, "depth")
+    close(acc, acc_o, 5e-6, "acc")
+    n_checked = 0
+    for n, p in m.named_parameters():
+        ref = st[n].grad
+        if ref is None or p.grad is None:
+            assert (ref is None or ref.abs().max() == 0) and (p.grad is None or p.grad.abs().max() == 0), n
+            continue
+        rel_close(p.grad, ref, 5e-5, n)
+        n_checked += 1
+    assert n_checked >= 8 * 15
+
+
+def test_config4_untouched_experts_stay_frozen():
+    """C4: a batch whose samples fall in experts {2,5} only leaves the other six without gradients."""
+    from nerf_sys_b200 import ops
+    from nerf_sys_b200.nerfs.ray_rendering import render_rays
+    m, st, cfg, mins, aabb = _big_scene(8, 2, 4, 14)
+    cent = st["centroids"]
+    g = torch.Generator().manual_seed(9)
+    N, S = 512, 32
+    rays = torch.zeros(N, 8)
+    for i, k in enumerate((2, 5)):
+        sl = slice(i * N // 2, (i + 1) * N // 2)
+        rays[sl, 0] = -0.04
+        rays[sl, 1:3] = cent[k, 1:3] + (torch.rand(N // 2, 2, generator=g) - 0.5) * 0.2
+        rays[sl, 3] = 1.0  # straight down: the YZ position (the routing key) never changes
+        rays[sl, 6], rays[sl, 7] = 0.0, 0.5
+    m.train()
+    rgb, *_ = render_rays(m, rays.to(DEV), ray_samples=S)
+    ops.mse_loss(rgb, torch.rand(N, 3, generator=g).to(DEV)).backward()
+    for k, sub in enumerate(m.submodules):
+        touched = any(p.grad is not None and p.grad.abs().max() > 0 for p in sub.parameters())
+        assert touched == (k in (2, 5)), k
+
+
+def test_adam_matches_torch():
+    from nerf_sys_b200 import ops
+    g = torch.Generator().manual_seed(0)
+    n = 100_003
+    p0 = torch.randn(n + 1, generator=g)[:n].contiguous()
+    p = p0.clone().to(DEV)
+    m, v = torch.zeros(n, device=DEV), torch.zeros(n, device=DEV)
+    q = torch.nn.Parameter(p0.clone())
+    opt = torch.optim.Adam([q], lr=1e-2, betas=(0.9, 0.99), eps=1e-15, weight_decay=0.0)
+    for step in range(1, 6):
+        gr = torch.randn(n, generator=g) * (10.0 ** -step)
+        q.grad = gr.clone()
+        opt.step()
+        ops.adam_step(p, gr.to(DEV), m, v, 1e-2, 0.9, 0.99, 1e-15, 0.0, step)
+    close(p, q.detach(), 1e-6, "adam params")
+    close(m, opt.state[q]["exp_avg"], 1e-6)
+    close(v, opt.state[q]["exp_avg_sq"], 1e-6)
