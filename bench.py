@@ -1,0 +1,399 @@
+#!/usr/bin/env python
+"""bench.py - train & render rays/s of the per-ray hot path (BASELINE.json metric).
+
+    python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path
+    python bench.py --impl reference --gpus N --steps K --warmup W   # the reference's CPU PyTorch path
+
+Workload at N=1 = BASELINE.json configs[1]: single-expert hash-grid NeRF (L16 F2 T2^20, 64-wide MLPs)
+trained on synthetic 800x800 views, 8192-ray batch x 96 samples.  A step is one training pass of
+the hot path over one batch: stratified sampling -> hash grid -> MLPs -> compositing -> MSE ->
+backward -> clip(1.0) -> Adam on every tensor (incl. the dense 128 MiB table).  At N>1 every rank
+owns one spatial expert and its own 8192-ray batch (the meta-training shard of SURVEY 8(e): tasks
+never cross experts); the only collective is the NCCL all-reduce of the shared background head's
+643 gradient floats - weak scaling.
+
+`value` times K steps with inputs resident in HBM; `e2e` times the same step through the
+reference-facing API (compute_mse_loss -> backward -> optimizer.step) with the batch copied from
+pinned host memory and the loss read back every step.  L2: the per-step working set (table +
+gradient + Adam moments = 512 MiB) exceeds the 126 MB L2, so there is no explicit flush.
+"""
+import argparse
+import json
+import math
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+N_RAYS, S_TRAIN, LOG2_T = 8192, 96, 20
+IMG, FOCAL, N_VIEWS = 800, 1111.0, 40
+WORKLOAD = "config[1]: single-expert hash-grid NeRF training, synthetic 800x800 views, 8192-ray batch x 96 samples"
+
+# algorithmic bytes / flops per sample point (DESIGN.md "Kernels")
+ALGO = {
+    "hash_fwd": ("hbm", 12 + 1024 + 128),       # xyz + 16 levels x 8 corners x 8 B + 32 features out
+    "hash_bwd": ("hbm", 12 + 128 + 2 * 1024),   # xyz + d_enc + read-modify-write of the same rows
+    "mlp_fwd": ("tensor", 26880),               # 13 440 MAC
+    "mlp_bwd": ("tensor", 53760),               # dgrad + wgrad
+    "composite_fwd": ("hbm", 24),
+    "composite_bwd": ("hbm", 40),
+}
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return {"hbm": d["hbm_gbs"], "tensor": d["bf16_tflops_sustained"], "src": "MEASURED_PEAKS.json (sustained bf16)"}
+    return {"hbm": 6650.0, "tensor": 1400.0, "src": "fallback (B200_PROFILING.md)"}
+
+
+class Clocks:
+    """nvidia-smi sampled every 200 ms during the timed region."""
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, device):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        try:
+            uuid = str(torch.cuda.get_device_properties(device).uuid)
+            sel = ["-i", uuid if uuid.startswith("GPU-") else "GPU-" + uuid]
+        except Exception:
+            sel = ["-i", str(device)]
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", *sel, f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200"],
+                                      stdout=self.f, stderr=subprocess.DEVNULL)
+        except Exception:
+            self.p = None
+
+    def stop(self):
+        if self.p is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except Exception:
+            self.p.kill()
+        self.f.flush()
+        self.f.seek(0)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in self.f.read().splitlines():
+            c = [x.strip() for x in line.split(",")]
+            if len(c) < 7:
+                continue
+            try:
+                sm.append(float(c[0]))
+                mx.append(float(c[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, c[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        os.unlink(self.f.name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def dist_env():
+    rank, world, local = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
+    return rank, world, local
+
+
+# ------------------------------------------------------------------------------------------
+# scene, data
+# ------------------------------------------------------------------------------------------
+def build_scene(rank, world, device, seed=0, table_std=None):
+    """One expert per rank: rank r owns tile r of a 1 x gy x gz grid over the global box."""
+    from nerf_sys_b200.models.inr import MetaContainer
+    from nerf_sys_b200.nerfs.scene_box import SceneBox
+    from oracle import acnerf_oracle as O  # scene constants / initial weights only (shared with the CPU baseline)
+    gy, gz = {1: (1, 1), 2: (1, 2), 4: (2, 2), 8: (2, 4)}.get(world, (1, world))
+    aabb, cent, boxes = O.grid_scene(gy, gz)
+    cfg = dict(O.HASH_CFG)
+    cfg["log2_hashmap_size"] = LOG2_T
+    box, c = boxes[rank], cent[rank:rank + 1]
+    st = O.init_ngp_state(1, box, c, [box], cfg, seed=seed + 17 * rank, table_std=table_std)
+    g = torch.Generator().manual_seed(1234)  # the shared background head starts identical on every rank
+    for k in ("bg_mlp.0.weight", "bg_mlp.0.bias", "bg_mlp.2.weight", "bg_mlp.2.bias"):
+        st[k] = (torch.rand(st[k].shape, generator=g) * 2 - 1) * (0.25 if "0." in k else 0.17)
+    model = MetaContainer(1, c, box, "instant", boundary_margin=1.05, cluster_2d=True, use_bg_nerf=True, occ_conf={"use_occ": False},
+                          expert_box_list=[SceneBox(box)], hidden=64, sigma_depth=2, color_depth=2, color_hidden=64,
+                          dir_encoding="spherical", use_sigmoid_rgb=True, hash_enc_conf=cfg)
+    model.load_state_dict(st, strict=True)
+    return model.to(device), st, cfg, box
+
+
+def ring_pose_in(box, i, n):
+    from oracle import acnerf_oracle as O
+    c2w = O.ring_pose(i, n, radius=0.4)
+    ctr = (box[0] + box[1]) * 0.5
+    half = (box[1] - box[0]) * 0.5
+    c2w = c2w.clone()
+    c2w[1, 3] = ctr[1] + c2w[1, 3] * half[1] / 0.5
+    c2w[2, 3] = ctr[2] + c2w[2, 3] * half[2] / 0.5
+    return c2w
+
+
+def make_pool(box, device, batches, seed):
+    """`batches` x 8192 rays drawn from random pixels of 40 synthetic 800x800 ring views of this rank's box."""
+    from nerf_sys_b200 import ops
+    g = torch.Generator().manual_seed(seed)
+    per_view = (batches * N_RAYS + N_VIEWS - 1) // N_VIEWS
+    out = []
+    for v in range(N_VIEWS):
+        rays = ops.raygen(IMG, IMG, FOCAL, FOCAL, IMG / 2, IMG / 2, True, ring_pose_in(box, v, N_VIEWS), box, device)
+        _, valid = ops.clamp_near_far(rays, None)
+        idx = torch.randint(0, IMG * IMG, (per_view * 2,), generator=g).to(device)
+        idx = idx[valid[idx]][:per_view]
+        out.append(rays[idx])
+    rays = torch.cat(out)[torch.randperm(len(out) * per_view, generator=g).to(device)][:batches * N_RAYS]
+    return rays.view(batches, N_RAYS, 8).contiguous()
+
+
+@torch.no_grad()
+def teacher_colors(pool, rank, world, device):
+    """Targets = the same rays rendered once through a frozen teacher (seed 1, N(0,0.1) table): exactly representable."""
+    from nerf_sys_b200.nerfs.ray_rendering import render_rays
+    teacher, *_ = build_scene(rank, world, device, seed=1, table_std=0.1)
+    teacher.eval()
+    out = torch.empty(pool.shape[0], N_RAYS, 3, device=device)
+    for b in range(pool.shape[0]):
+        out[b] = render_rays(teacher, pool[b], ray_samples=S_TRAIN)[0].clamp(0, 1)
+    del teacher
+    torch.cuda.empty_cache()
+    return out
+
+
+class P:  # the argparse namespace fields compute_mse_loss reads (common/args.py)
+    ray_samples, chunk_points, color_space = S_TRAIN, 4456448, "identity"
+
+
+def allreduce_bg(model, world):
+    """Shared background head: NCCL all-reduce (mean) of its 643 gradient floats."""
+    if world == 1:
+        return
+    import torch.distributed as dist
+    gs = [p.grad for p in model.bg_mlp.parameters() if p.grad is not None]
+    flat = torch.cat([g.reshape(-1) for g in gs])
+    dist.all_reduce(flat)
+    flat /= world
+    o = 0
+    for g in gs:
+        g.copy_(flat[o:o + g.numel()].view_as(g))
+        o += g.numel()
+
+
+def train_step(model, opt, rays, rgbs, world):
+    from nerf_sys_b200.nerfs.losses import compute_mse_loss
+    opt.zero_grad(set_to_none=True)
+    loss = compute_mse_loss(P, model, {"rays": rays, "rgbs": rgbs})
+    loss.backward()
+    allreduce_bg(model, world)
+    opt.step()
+    return loss
+
+
+# ------------------------------------------------------------------------------------------
+# CPU arm: the reference's PyTorch path as restated by the oracle (bit-identical on the goldens)
+# ------------------------------------------------------------------------------------------
+def cpu_train_rays_per_s(n_rays, steps, warmup, seed=0):
+    from oracle import acnerf_oracle as O
+    torch.set_num_threads(os.cpu_count() or 1)
+    aabb, cent, boxes = O.grid_scene(1, 1)
+    cfg = dict(O.HASH_CFG)
+    cfg["log2_hashmap_size"] = LOG2_T
+    st = O.init_ngp_state(1, aabb, cent, boxes, cfg, seed=seed)
+    params = [v.requires_grad_(True) for k, v in st.items() if ("weight" in k or "bias" in k or "hash_table" in k)]
+    opt = torch.optim.Adam(params, lr=2e-3)
+    g = torch.Generator().manual_seed(7)
+    times = []
+    for i in range(warmup + steps):
+        rays = O.aerial_rays(n_rays, aabb, seed=100 + i)
+        u, gt = torch.rand(n_rays, S_TRAIN, generator=g), torch.rand(n_rays, 3, generator=g)
+        t0 = time.perf_counter()
+        opt.zero_grad(set_to_none=True)
+        rgb, *_ = O.render_rays(rays, st, [boxes[0][0]], cfg, S=S_TRAIN, margin=1.05, u=u)
+        loss = O.mse_loss(rgb, gt, "identity")
+        loss.backward()
+        torch.nn.utils.clip_grad_norm_(params, 1.0)
+        opt.step()
+        dt = time.perf_counter() - t0
+        if i >= warmup:
+            times.append(dt)
+    return n_rays * len(times) / sum(times), sum(times) / len(times)
+
+
+def run_reference(args):
+    rank, world, _ = dist_env()
+    if rank != 0:
+        return
+    n = 2048
+    t0 = time.perf_counter()
+    rps, sec = cpu_train_rays_per_s(n, args.steps, args.warmup)
+    cores = os.cpu_count() or 1
+    sample = f"{n}-ray x {S_TRAIN}-sample slices of the 8192-ray batch, fwd+bwd+clip+Adam, torch {torch.__version__} CPU fp32"
+    print(json.dumps({
+        "impl": "reference", "metric": "train_rays_per_sec", "value": rps, "unit": "rays/s", "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic", "config": {"workload": WORKLOAD, "l2": "n/a (CPU)"},
+        "cpu_baseline": {"value": rps, "unit": "rays/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": rps, "unit": "rays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "note": "reference = its pure-PyTorch path on the host cores via oracle/ (the reference is Python and does not exist on the GPU "
+                "box; the oracle is bit-identical to it on tests/golden)", "wall_s": time.perf_counter() - t0}))
+
+
+# ------------------------------------------------------------------------------------------
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-render", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+
+    from nerf_sys_b200 import ops
+    from nerf_sys_b200.optim import build_optimizer
+    rank, world, local = dist_env()
+    assert world == args.gpus, f"--gpus {args.gpus} but WORLD_SIZE={world}: launch N>1 under torch.distributed.run"
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    ops.device_ok(local)
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+    K, W = args.steps, max(args.warmup, 3)
+
+    model, st, cfg, box = build_scene(rank, world, dev)
+    model.train()
+    opt = build_optimizer(model, max_grad_norm=1.0)
+    nb = min(32, K + W)
+    pool = make_pool(box, dev, nb, seed=10 + rank)
+    rgbs = teacher_colors(pool, rank, world, dev)
+    pool_h, rgbs_h = pool.cpu().pin_memory(), rgbs.cpu().pin_memory()
+
+    def barrier():
+        if world > 1:
+            torch.distributed.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(ms):
+        if world == 1:
+            return ms
+        t = torch.tensor([ms], device=dev)
+        torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+        return t.item()
+
+    # ---- resident-input arm ------------------------------------------------------------
+    for i in range(W):
+        train_step(model, opt, pool[i % nb], rgbs[i % nb], world)
+    barrier()
+    clocks = Clocks(local)
+    timing = ops.kernel_timing(True)
+    l0 = ops.launches()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for i in range(K):
+        loss = train_step(model, opt, pool[(W + i) % nb], rgbs[(W + i) % nb], world)
+    e1.record()
+    barrier()
+    ms = max_over_ranks(e0.elapsed_time(e1))
+    launches = ops.launches() - l0
+    ops.kernel_timing(False)
+    final_loss = float(loss.item())
+
+    # ---- end-to-end arm: host batches in, loss out, every step -------------------------------
+    barrier()
+    e0.record()
+    for i in range(K):
+        r = pool_h[(W + i) % nb].to(dev, non_blocking=True)
+        c = rgbs_h[(W + i) % nb].to(dev, non_blocking=True)
+        _ = train_step(model, opt, r, c, world).item()
+    e1.record()
+    barrier()
+    ms_e2e = max_over_ranks(e0.elapsed_time(e1))
+    clk = clocks.stop()
+
+    # ---- per-call device time -> roofline ------------------------------------------------
+    pk = peaks()
+    P_step = N_RAYS * S_TRAIN
+    kern = {}
+    for name, evs in timing.items():
+        tot = sum(a.elapsed_time(b) for a, b in evs)
+        kern[name] = {"ms_per_step": tot / K, "calls_per_step": len(evs) / K}
+        if name in ALGO:
+            bound, per_pt = ALGO[name]
+            sec = tot / len(evs) / 1e3
+            ach = per_pt * P_step / sec / (1e9 if bound == "hbm" else 1e12)
+            kern[name].update({"bound": bound, "achieved": ach, "unit": "GB/s" if bound == "hbm" else "TFLOP/s", "frac": ach / pk[bound]})
+    top = max((n for n in kern if n in ALGO), key=lambda n: kern[n]["ms_per_step"])
+    traffic = None
+    tp = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tp):
+        traffic = json.load(open(tp)).get(top)
+    roofline = {"kernel": top, "bound": kern[top]["bound"], "achieved": kern[top]["achieved"], "peak": pk[kern[top]["bound"]],
+                "unit": kern[top]["unit"], "frac": kern[top]["frac"], "traffic": traffic, "peak_source": pk["src"],
+                "algorithmic_per_point": ALGO[top][1]}
+
+    # ---- render throughput (no_grad, eval), one 800x800 view per measurement ---------------
+    render = None
+    if not args.no_render:
+        from nerf_sys_b200.nerfs.ray_rendering import render_image
+        from nerf_sys_b200.nerfs.scene_box import SceneBox
+        model.eval()
+        sb = SceneBox(box.to(dev))
+        for v in range(2):
+            render_image(model, H=IMG, W=IMG, fx=FOCAL, fy=FOCAL, cx=IMG / 2, cy=IMG / 2, c2w=ring_pose_in(box, v, N_VIEWS), scene_box=sb,
+                         ray_samples=64)
+        barrier()
+        e0.record()
+        nv = 5
+        for v in range(nv):
+            render_image(model, H=IMG, W=IMG, fx=FOCAL, fy=FOCAL, cx=IMG / 2, cy=IMG / 2, c2w=ring_pose_in(box, v + 2, N_VIEWS),
+                         scene_box=sb, ray_samples=64)
+        e1.record()
+        barrier()
+        rms = max_over_ranks(e0.elapsed_time(e1))
+        render = {"value": world * nv * IMG * IMG / (rms / 1e3), "unit": "rays/s", "config": "800x800 x 64 samples, eval, no_grad, raygen on device",
+                  "ms_per_frame": rms / nv}
+        model.train()
+
+    cpu = None
+    if rank == 0 and not args.no_cpu_baseline:
+        n = 2048
+        rps, sec = cpu_train_rays_per_s(n, 6, 1)
+        cpu = {"value": rps, "unit": "rays/s", "cores": os.cpu_count() or 1, "kind": "port",
+               "sample": f"6 steps of a {n}-ray x {S_TRAIN}-sample slice of the same batch shape (fwd+bwd+clip+Adam, {sec:.2f} s/step), "
+                         f"torch {torch.__version__} CPU fp32, all host threads"}
+    if rank == 0:
+        bytes_in = pool_h[0].numel() * 4 + rgbs_h[0].numel() * 4
+        print(json.dumps({
+            "metric": "train_rays_per_sec", "value": world * N_RAYS * K / (ms / 1e3), "unit": "rays/s", "n_gpus": world, "steps": K,
+            "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic", "config": {"workload": WORKLOAD, "rays_per_gpu": N_RAYS, "samples": S_TRAIN, "experts_per_gpu": 1,
+                                            "table": "2^20 x 16 levels x 2 fp32 = 128 MiB", "mlp_math": "fp32 FFMA (exact mode)",
+                                            "l2": "per-step working set 512 MiB (table+grad+Adam moments) > 126 MB L2, no flush",
+                                            "collective": "none" if world == 1 else "nccl all-reduce of 643 bg-head grads"},
+            "clocks": clk, "e2e": {"value": world * N_RAYS * K / (ms_e2e / 1e3), "unit": "rays/s", "h2d_bytes_per_step": bytes_in,
+                                   "d2h_bytes_per_step": 4, "ms_per_step": ms_e2e / K},
+            "gpu_launches": launches, "roofline": roofline, "kernels": kern, "render": render, "cpu_baseline": cpu,
+            "final_loss": final_loss}))
+    if world > 1:
+        torch.distributed.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -85,17 +85,12 @@ class MetaContainer(MetaModule):
         """(P,4) [rgb, sigma] for a point set (explicit rows or implicit ray samples)."""
         K = len(self.submodules)
         if active_module is not None:
-            sub = self.submodules[active_module]
-            sub._require_fused()
-            return ops.ngp_experts(pts, ops.PairList(pts.P), sub.expert_spec(), [sub.xyz_encoder.hash_table],
-                                   sub.mlp_tensors(self._sub_params(params, active_module)))
+            return self.submodules[active_module].evaluate(pts, self._sub_params(params, active_module))
         for sub in self.submodules:
             sub._require_fused()
         if K == 1 and self.boundary_margin > 1.0:
             # a single centroid always gets weight 1: skip the pack, keep the fused launch
-            sub = self.submodules[0]
-            return ops.ngp_experts(pts, ops.PairList(pts.P), sub.expert_spec(), [sub.xyz_encoder.hash_table],
-                                   sub.mlp_tensors(self._sub_params(params, 0)))
+            return self.submodules[0].evaluate(pts, self._sub_params(params, 0))
         with torch.no_grad():
             pairs = ops.route_pack(pts, self.centroids_host(), K, self.boundary_margin, self.cluster_2d)
         tables = [sub.xyz_encoder.hash_table for sub in self.submodules]

@@ -106,14 +106,15 @@ class MetaNGP(MetaModule):
         x01 = (x - self.scene_box.min.to(x.device)) / self.aabb_extent
         return x01.clamp(self.enc_eps, 1.0 - self.enc_eps)
 
+    def evaluate(self, pts: ops.PointSet, params=None) -> Tensor:
+        """(P,4) [rgb, sigma] for a point set (explicit rows or implicit ray samples); expert-level ``params``."""
+        self._require_fused()
+        return ops.ngp_experts(pts, ops.PairList(pts.P), self.expert_spec(), [self.xyz_encoder.hash_table], self.mlp_tensors(params))
+
     def forward(self, x_d: Tensor, params=None) -> Tensor:
         """(...,6) [xyz, dir] -> (...,4) [rgb, sigma]."""
         assert x_d.shape[-1] == 6, f"Expected (...,6) [xyz,dir], got {x_d.shape}"
-        self._require_fused()
-        flat = x_d.reshape(-1, 6)
-        pts = ops.PointSet(x6=flat)
-        out = ops.ngp_experts(pts, ops.PairList(pts.P), self.expert_spec(), [self.xyz_encoder.hash_table], self.mlp_tensors(params))
-        return out.reshape(*x_d.shape[:-1], 4)
+        return self.evaluate(ops.PointSet(x6=x_d.reshape(-1, 6)), params).reshape(*x_d.shape[:-1], 4)
 
     def density(self, x: Tensor, params=None, return_feats: bool = False) -> Union[Tensor, Dict[str, Tensor]]:
         """sigma (...,1) [and geo features] at world coordinates.  Layer-wise path (API parity for

@@ -76,10 +76,10 @@ def render_rays_stratified(model, rays: Tensor, ray_samples: int, params=None, a
             u = torch.rand(N, S, device=rays.device, dtype=torch.float32)
         t_vals = ops.stratified_t(rays, S, u if model.training else None)
     pts = ops.PointSet(rays=rays, t=t_vals)
-    if hasattr(model, "evaluate"):
-        rgb_sigma = model.evaluate(pts, params=params, active_module=active_module)
-    else:  # a bare expert passed as the model
-        rgb_sigma = ops.ngp_experts(pts, ops.PairList(pts.P), model.expert_spec(), [model.xyz_encoder.hash_table], model.mlp_tensors(params))
+    # as in the reference (:323-326): with active_module the expert is called directly and `params`
+    # holds EXPERT-level keys (meta_core.extract_module_params); otherwise container-level keys
+    model_eff = model.submodules[active_module] if active_module is not None else model
+    rgb_sigma = model_eff.evaluate(pts, params=params)
     rgb_sigma = rgb_sigma.view(N, S, 4)
     bg_rgb = _get_bg_rgb(model, rays[:, 3:6], params, rgb_sigma, N=N, bg_color_default=bg_color_default)
     return ops.composite(rgb_sigma, t_vals, bg_rgb, float(sigma_scale))

@@ -35,6 +35,37 @@ def _count(n: int):
     _launches += n
 
 
+# ---- optional per-call CUDA-event timing (bench.py's live roofline) ----------------------
+_timing = None  # None = off; else {name: [(start_event, end_event), ...]}
+
+
+def kernel_timing(enable: bool):
+    """Turn per-call event recording on (returns the dict that fills up) or off."""
+    global _timing
+    _timing = {} if enable else None
+    return _timing
+
+
+class _timed:
+    """Records a CUDA event pair on the current stream around one C-ABI call."""
+
+    def __init__(self, name: str):
+        self.name = name
+
+    def __enter__(self):
+        if _timing is not None:
+            self.a = torch.cuda.Event(enable_timing=True)
+            self.b = torch.cuda.Event(enable_timing=True)
+            self.a.record()
+        return self
+
+    def __exit__(self, *exc):
+        if _timing is not None:
+            self.b.record()
+            _timing.setdefault(self.name, []).append((self.a, self.b))
+        return False
+
+
 def _stream() -> C.c_void_p:
     return C.c_void_p(torch.cuda.current_stream().cuda_stream)
 
@@ -211,7 +242,7 @@ def stratified_t(rays: Tensor, S: int, u: Optional[Tensor]) -> Tensor:
         u = _f32(u, "u")
         if tuple(u.shape) != (N, S):
             raise ValueError(f"u must be ({N},{S}), got {tuple(u.shape)}")
-    with torch.cuda.device(r.device):
+    with torch.cuda.device(r.device), _timed("stratified_t"):
         check(lib().acn_stratified_t(_ptr(r), N, S, _ptr(_tau(S, r.device)), _ptr(u), _ptr(t), _stream()), "acn_stratified_t")
     _count(1)
     return t
@@ -390,7 +421,7 @@ class NgpEncodeFn(torch.autograd.Function):
         enc = torch.empty(32, ld, device=pts.device, dtype=torch.float32)
         ex = _expert_array(spec, tb, None)
         cp, cq = pts.c(), pairs.c()
-        with torch.cuda.device(pts.device):
+        with torch.cuda.device(pts.device), _timed("hash_fwd"):
             check(L.acn_ngp_encode_fwd(C.byref(cp), C.byref(cq), ex, spec.E, C.byref(spec.grid), _ptr(enc), _stream()),
                   "acn_ngp_encode_fwd")
         _count(1)
@@ -415,7 +446,7 @@ class NgpEncodeFn(torch.autograd.Function):
                 outs.append(None)
         ex = _expert_array(spec, tb, None)
         cp, cq = pts.c(), pairs.c()
-        with torch.cuda.device(pts.device):
+        with torch.cuda.device(pts.device), _timed("hash_bwd"):
             check(L.acn_ngp_encode_bwd(C.byref(cp), C.byref(cq), ex, spec.E, C.byref(spec.grid), _ptr(d_enc), grads, _stream()),
                   "acn_ngp_encode_bwd")
         _count(1)
@@ -443,7 +474,7 @@ class NgpMlpFn(torch.autograd.Function):
         save = torch.empty(int(L.acn_ngp_save_bytes(pairs.M)) // 4, device=dev, dtype=torch.float32) if need_grad else None
         ex = _expert_array(spec, None, ws)
         cp, cq = pts.c(), pairs.c()
-        with torch.cuda.device(dev):
+        with torch.cuda.device(dev), _timed("mlp_fwd"):
             check(L.acn_ngp_mlp_fwd(C.byref(cp), C.byref(cq), ex, spec.E, _ptr(enc_c), _ptr(out), _ptr(save), _stream()),
                   "acn_ngp_mlp_fwd")
         _count(1)
@@ -480,7 +511,7 @@ class NgpMlpFn(torch.autograd.Function):
         wsb = torch.empty(int(L.acn_ngp_bwd_ws_bytes(pairs.M, spec.E)) // 4, device=dev, dtype=torch.float32)
         ex = _expert_array(spec, None, ws)
         cq = pairs.c()
-        with torch.cuda.device(dev):
+        with torch.cuda.device(dev), _timed("mlp_bwd"):
             check(L.acn_ngp_mlp_bwd(C.byref(cq), ex, spec.E, _ptr(enc), _ptr(d_out), _ptr(ctx.save), grads, _ptr(d_enc), _ptr(wsb),
                                     _stream()), "acn_ngp_mlp_bwd")
         _count(1 + 14)
@@ -501,14 +532,16 @@ class BgFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, d: Tensor, stride: int, N: int, w0: Tensor, b0: Tensor, w1: Tensor, b1: Tensor):
         L = lib()
-        dd = _need(d.detach(), "directions")
+        dd = d.detach()  # strided view (e.g. rays[:, 3:6]); `stride` floats between rows, 3 adjacent components
+        if not (dd.is_cuda and dd.dtype == torch.float32 and dd.stride(1) == 1 and dd.stride(0) == stride):
+            raise RuntimeError("BgFn: directions must be a CUDA fp32 (N,3) view with unit inner stride")
         p = [_need(t.detach(), "bg parameter") for t in (w0, b0, w1, b1)]
         if tuple(p[0].shape) != (32, 16) or tuple(p[2].shape) != (3, 32):
             raise ValueError("background head must be SH16 -> 32 -> 3 (bg_hidden=32, spherical encoding)")
         need_grad = any(ctx.needs_input_grad)
         rgb = torch.empty(N, 3, device=dd.device, dtype=torch.float32)
         save = torch.empty(int(L.acn_bg_save_bytes(N)) // 4, device=dd.device, dtype=torch.float32) if need_grad else None
-        with torch.cuda.device(dd.device):
+        with torch.cuda.device(dd.device), _timed("bg_fwd"):
             check(L.acn_bg_forward(_ptr(dd), stride, N, _ptr(p[0]), _ptr(p[1]), _ptr(p[2]), _ptr(p[3]), _ptr(rgb), _ptr(save),
                                    _stream()), "acn_bg_forward")
         _count(1)
@@ -525,7 +558,7 @@ class BgFn(torch.autograd.Function):
         d_rgb = _f32(d_rgb, "d_rgb")
         g = [torch.empty_like(t) for t in (w0, b0, w1, b1)]
         ws = torch.empty(int(L.acn_bg_bwd_ws_bytes(ctx.N)) // 4, device=w0.device, dtype=torch.float32)
-        with torch.cuda.device(w0.device):
+        with torch.cuda.device(w0.device), _timed("bg_bwd"):
             check(L.acn_bg_backward(_ptr(d_rgb), ctx.N, _ptr(w0), _ptr(w1), _ptr(ctx.save), _ptr(g[0]), _ptr(g[1]), _ptr(g[2]),
                                     _ptr(g[3]), _ptr(ws), _stream()), "acn_bg_backward")
         _count(5)
@@ -559,7 +592,7 @@ class CompositeFn(torch.autograd.Function):
         dev = rs.device
         rgb, depth = torch.empty(N, 3, device=dev), torch.empty(N, device=dev)
         w, acc = torch.empty(N, S, device=dev), torch.empty(N, device=dev)
-        with torch.cuda.device(dev):
+        with torch.cuda.device(dev), _timed("composite_fwd"):
             check(lib().acn_composite_fwd(_ptr(rs), _ptr(tt), _ptr(b), N, S, float(sigma_scale), _ptr(rgb), _ptr(depth), _ptr(w),
                                           _ptr(acc), _stream()), "acn_composite_fwd")
         _count(1)
@@ -579,7 +612,7 @@ class CompositeFn(torch.autograd.Function):
         g_w = None if g_w is None else _f32(g_w, "g_weights")
         d_rs = torch.empty_like(rs)
         d_bg = torch.empty_like(b) if (b is not None and ctx.needs_input_grad[2]) else None
-        with torch.cuda.device(dev):
+        with torch.cuda.device(dev), _timed("composite_bwd"):
             check(lib().acn_composite_bwd(_ptr(rs), _ptr(tt), _ptr(b), N, S, ctx.scale, _ptr(g_rgb), _ptr(g_depth), _ptr(g_acc),
                                           _ptr(g_w), _ptr(d_rs), _ptr(d_bg), _stream()), "acn_composite_bwd")
         _count(1)
@@ -601,7 +634,7 @@ class MseFn(torch.autograd.Function):
         loss = torch.empty(1, device=p.device)
         d_pred = torch.empty_like(p)
         ws = torch.empty(2048, device=p.device)
-        with torch.cuda.device(p.device):
+        with torch.cuda.device(p.device), _timed("mse_loss"):
             check(lib().acn_mse_loss(_ptr(p), _ptr(g), N, int(space), _ptr(loss), _ptr(d_pred), _ptr(ws), _stream()), "acn_mse_loss")
         _count(2)
         ctx.save_for_backward(d_pred)
@@ -622,7 +655,7 @@ def adam_step(param: Tensor, grad: Tensor, exp_avg: Tensor, exp_avg_sq: Tensor, 
     for t, n in ((param, "param"), (grad, "grad"), (exp_avg, "exp_avg"), (exp_avg_sq, "exp_avg_sq")):
         if not (t.is_cuda and t.dtype == torch.float32 and t.is_contiguous()):
             raise RuntimeError(f"adam_step: {n} must be a contiguous CUDA fp32 tensor")
-    with torch.cuda.device(param.device):
+    with torch.cuda.device(param.device), _timed("adam"):
         check(lib().acn_adam_step(_ptr(param), _ptr(grad), _ptr(exp_avg), _ptr(exp_avg_sq), param.numel(), lr, beta1, beta2, eps,
                                   weight_decay, int(step), _ptr(grad_scale), _stream()), "acn_adam_step")
     _count(1)
@@ -639,6 +672,6 @@ def sgd_axpy(w: Tensor, g: Tensor, lr: float) -> Tensor:
 
 def sumsq_accum(x: Tensor, acc: Tensor):
     xx = _need(x.detach(), "x")
-    with torch.cuda.device(xx.device):
+    with torch.cuda.device(xx.device), _timed("sumsq"):
         check(lib().acn_sumsq_accum(_ptr(xx), xx.numel(), _ptr(acc), _stream()), "acn_sumsq_accum")
     _count(1)
