@@ -260,6 +260,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-render", action="store_true")
+    ap.add_argument("--mlp-math", default="f16tc", choices=["f16tc", "fp32"],
+                    help="expert-MLP arithmetic: tcgen05 fp16/fp32-accumulate (default) or the exact fp32 CUDA-core mode")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -271,6 +273,7 @@ def main():
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     ops.device_ok(local)
+    ops.set_mlp_math(args.mlp_math)
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=dev)
@@ -382,9 +385,11 @@ def main():
         bytes_in = pool_h[0].numel() * 4 + rgbs_h[0].numel() * 4
         print(json.dumps({
             "metric": "train_rays_per_sec", "value": world * N_RAYS * K / (ms / 1e3), "unit": "rays/s", "n_gpus": world, "steps": K,
-            "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f16" if args.mlp_math == "f16tc" else "f32",
             "data": "synthetic", "config": {"workload": WORKLOAD, "rays_per_gpu": N_RAYS, "samples": S_TRAIN, "experts_per_gpu": 1,
-                                            "table": "2^20 x 16 levels x 2 fp32 = 128 MiB", "mlp_math": "fp32 FFMA (exact mode)",
+                                            "table": "2^20 x 16 levels x 2 fp32 = 128 MiB", "mlp_math": ("tcgen05 kind::f16, fp16 operands, fp32 accumulate in TMEM (hash grid, compositing, loss, Adam in fp32)"
+                                                         if args.mlp_math == "f16tc" else "fp32 FFMA (exact mode)"),
                                             "l2": "per-step working set 512 MiB (table+grad+Adam moments) > 126 MB L2, no flush",
                                             "collective": "none" if world == 1 else "nccl all-reduce of 643 bg-head grads"},
             "clocks": clk, "e2e": {"value": world * N_RAYS * K / (ms_e2e / 1e3), "unit": "rays/s", "h2d_bytes_per_step": bytes_in,

@@ -190,6 +190,25 @@ int acn_ngp_mlp_bwd(const AcnPairs* pairs, const AcnNgpExpert* experts, int E, c
                     const float* d_out, const void* save, const AcnNgpExpertGrads* grads, float* d_enc,
                     void* ws, void* stream);
 
+/* ---- a11-a14 on the tensor cores (tcgen05 / TMEM) --------------------------- */
+/* Same contract as acn_ngp_mlp_fwd / _bwd (meta_ngp.py:171-241, meta_container.py:305-321), computed
+ * with fp16 operands and fp32 accumulation on the 5th-generation tensor cores - the precision class of
+ * the reference's own GPU path (TF32 matmuls, nerf_runner.py:42-43; fp16 autocast, meta_core.py:38).
+ * The backward recomputes the forward per 128-slot tile, so no activations are saved: it takes the
+ * points (for the view directions) and the encoding again.  ws: acn_ngp_bwd_tc_ws_bytes().
+ * grads[e].w/b are overwritten (NULL = not wanted); d_enc (32, ld) as in acn_ngp_mlp_bwd. */
+int acn_ngp_mlp_fwd_tc(const AcnPoints* pts, const AcnPairs* pairs, const AcnNgpExpert* experts, int E,
+                       const float* enc, float* out, void* stream);
+int64_t acn_ngp_bwd_tc_ws_bytes(void);
+int acn_ngp_mlp_bwd_tc(const AcnPoints* pts, const AcnPairs* pairs, const AcnNgpExpert* experts, int E,
+                       const float* enc, const float* d_out, const AcnNgpExpertGrads* grads, float* d_enc,
+                       void* ws, void* stream);
+/* Descriptor self-test of the three shared-memory operand layouts the kernels above use
+ * (X (128,64), Y (64,64), G (128,64) fp32 in; D1 = X Y^T (128,64), D2 = G^T X (64,64), D3 = G Y (128,64));
+ * G is rounded to bf16 when mixed != 0, everything else to fp16. */
+int acn_tc_selftest(const float* X, const float* Y, const float* G, int mixed, float* D1, float* D2,
+                    float* D3, void* stream);
+
 /* ---- a16: shared background head ----------------------------------------- */
 /* meta_container.py:347-382: d (N,3) taken at `stride` floats (stride 8 reads rays[:,3:6]
  * in place) -> rgb (N,3).  w0 (32,16) b0 (32) w1 (3,32) b1 (3). */

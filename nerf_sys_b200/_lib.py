@@ -75,6 +75,10 @@ SIGNATURES = {
                                      P(AcnNgpExpertGrads), vp]),
     "acn_ngp_mlp_fwd": (C.c_int, [P(AcnPoints), P(AcnPairs), P(AcnNgpExpert), C.c_int, vp, vp, vp, vp]),
     "acn_ngp_mlp_bwd": (C.c_int, [P(AcnPairs), P(AcnNgpExpert), C.c_int, vp, vp, vp, P(AcnNgpExpertGrads), vp, vp, vp]),
+    "acn_ngp_mlp_fwd_tc": (C.c_int, [P(AcnPoints), P(AcnPairs), P(AcnNgpExpert), C.c_int, vp, vp, vp]),
+    "acn_ngp_bwd_tc_ws_bytes": (i64, []),
+    "acn_ngp_mlp_bwd_tc": (C.c_int, [P(AcnPoints), P(AcnPairs), P(AcnNgpExpert), C.c_int, vp, vp, P(AcnNgpExpertGrads), vp, vp, vp]),
+    "acn_tc_selftest": (C.c_int, [vp, vp, vp, C.c_int, vp, vp, vp, vp]),
     "acn_bg_save_bytes": (i64, [i64]),
     "acn_bg_forward": (C.c_int, [vp, i64, i64, vp, vp, vp, vp, vp, vp, vp]),
     "acn_bg_bwd_ws_bytes": (i64, [i64]),

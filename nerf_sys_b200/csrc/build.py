@@ -27,6 +27,7 @@ SOURCES = {
     "hashgrid.cu": ["-fmad=false"],
     "wgrad.cu": [],
     "ngp.cu": [],
+    "ngp_tc.cu": [],
     "render.cu": [],
     "optim.cu": [],
 }

@@ -1,0 +1,919 @@
+// a11-a14 on the 5th-generation tensor cores: the hash-grid expert MLPs (MetaNGP.density / .color,
+// models/inr/meta_ngp.py:171-241) as fused tcgen05 kernels.  fp16 operands (activations, weights),
+// fp32 accumulation in TMEM; gradient tiles are fp16 too, multiplied by a per-launch power-of-two scale derived
+// from max|d_out| (k_absmax) so they sit high in the fp16 range, saturated at +-65504, and unscaled exactly on the way out.
+// This is the precision class the reference itself runs on a GPU (TF32 matmuls, nerf_runner.py:42-43,
+// fp16 under autocast, meta_core.py:38); the fp32 CUDA-core kernels in ngp.cu stay as the "exact" mode.
+//
+//   k_ngp_mlp_fwd_tc : 4 independent 128-row pipelines per CTA; per layer one thread issues the MMAs
+//                      (A = activations in smem, B = weights in smem, D in TMEM), the pipeline's 128 threads
+//                      read their row back with tcgen05.ld, apply ReLU / trunc_exp / sigmoid and write the
+//                      next layer's A operand in place.  Biases ride along as an extra K chunk ([1,0..] x [b,0..]).
+//   k_ngp_mlp_bwd_tc : recomputes the forward for a 128-row tile (no activation round trip through HBM),
+//                      then runs the dgrad chain; every weight gradient dW = dZ^T A is an M=64 MMA over the
+//                      SAME smem buffers read MN-major, accumulated in TMEM across all tiles of the CTA and
+//                      written once as a per-CTA partial; k_tc_wgrad_reduce sums partials in a fixed order.
+// CTAs are partitioned over experts in proportion to their tile counts, so a CTA loads one expert's
+// weights once and the partial sums of an expert live in a contiguous CTA range (deterministic reduce).
+#include "common.cuh"
+#include "tc.cuh"
+
+namespace acn {
+
+#ifndef ACN_TC_G_BF16
+#define ACN_TC_G_BF16 0  // mixed fp16 x bf16 operands in one kind::f16 MMA raise an illegal-instruction fault on sm_100a (measured)
+#endif
+
+using namespace tc;
+
+constexpr uint32_t ROWS = 128;
+constexpr uint32_t CH = ROWS * 16;  // bytes of one 8-column chunk of a 128-row activation tile
+
+// smem weight block: B operands, chunk-major; chunk 0 = [bias,0,..], chunks 1..in/8 = W, last chunk = 0
+constexpr uint32_t OW0 = 0;                     // 64 rows x (8 + 32 + 8)
+constexpr uint32_t OW1 = OW0 + 64 * 16 * 6;     // 64 rows x (8 + 64 + 8)
+constexpr uint32_t OWH = OW1 + 64 * 16 * 10;    // 16 rows x (8 + 64 + 8): rows 0..14 geo_head, row 15 sigma_head
+constexpr uint32_t OW3 = OWH + 16 * 16 * 10;    // 64 rows x (8 + 32 + 8): 31 inputs padded to 32
+constexpr uint32_t OW4 = OW3 + 64 * 16 * 6;     // 64 rows x (8 + 64 + 8)
+constexpr uint32_t OW5 = OW4 + 64 * 16 * 10;    // 16 rows x (8 + 64 + 8): rows 0..2 rgb
+constexpr uint32_t W_BYTES = OW5 + 16 * 16 * 10;
+
+struct ExpertTableTc {
+  AcnNgpExpert ex[ACN_MAX_EXPERTS];
+  int E;
+};
+
+// padded layer views of the nn.Linear tensors (layer ids of acnerf.h: 0 trunk.0, 1 trunk.1, 2 sigma_head,
+// 3 geo_head, 4 color.0, 5 color.1, 6 color.2)
+__device__ __forceinline__ float wval(const AcnNgpExpert& ex, int L, int o, int i) {
+  switch (L) {
+    case 0: return __ldg(ex.w[0] + o * 32 + i);
+    case 1: return __ldg(ex.w[1] + o * 64 + i);
+    case 2: return o < 15 ? __ldg(ex.w[3] + o * 64 + i) : __ldg(ex.w[2] + i);
+    case 3: return i < 31 ? __ldg(ex.w[4] + o * 31 + i) : 0.f;
+    case 4: return __ldg(ex.w[5] + o * 64 + i);
+    default: return o < 3 ? __ldg(ex.w[6] + o * 64 + i) : 0.f;
+  }
+}
+__device__ __forceinline__ float bval(const AcnNgpExpert& ex, int L, int o) {
+  switch (L) {
+    case 0: return __ldg(ex.b[0] + o);
+    case 1: return __ldg(ex.b[1] + o);
+    case 2: return o < 15 ? __ldg(ex.b[3] + o) : __ldg(ex.b[2]);
+    case 3: return __ldg(ex.b[4] + o);
+    case 4: return __ldg(ex.b[5] + o);
+    default: return o < 3 ? __ldg(ex.b[6] + o) : 0.f;
+  }
+}
+
+__device__ __forceinline__ void load_layer_tc(uint8_t* dst, const AcnNgpExpert& ex, int L, int nrows, int in_pad, int tid, int nthr) {
+  __half* d = reinterpret_cast<__half*>(dst);
+  int total = nrows * (in_pad + 16);
+  for (int e = tid; e < total; e += nthr) {
+    int c = e / (nrows * 8), rem = e - c * nrows * 8;
+    int o = rem >> 3, j = rem & 7;
+    int k = c * 8 + j - 8;
+    float v;
+    if (c == 0)
+      v = (j == 0) ? bval(ex, L, o) : 0.f;
+    else
+      v = (k < in_pad) ? wval(ex, L, o, k) : 0.f;
+    d[e] = __float2half_rn(v);
+  }
+}
+
+__device__ __forceinline__ void load_weights_tc(uint8_t* sw, const AcnNgpExpert& ex, int tid, int nthr) {
+  load_layer_tc(sw + OW0, ex, 0, 64, 32, tid, nthr);
+  load_layer_tc(sw + OW1, ex, 1, 64, 64, tid, nthr);
+  load_layer_tc(sw + OWH, ex, 2, 16, 64, tid, nthr);
+  load_layer_tc(sw + OW3, ex, 3, 64, 32, tid, nthr);
+  load_layer_tc(sw + OW4, ex, 4, 64, 64, tid, nthr);
+  load_layer_tc(sw + OW5, ex, 5, 16, 64, tid, nthr);
+}
+
+// ---- CTA -> (expert, tile range) ------------------------------------------------------------
+// Deterministic function of the segment table only (recomputed identically by the reduce kernel).
+// Expert e with t_e > 0 tiles gets n_e = 1 + floor((G - nnz) * t_e / T) CTAs, the remainder goes one
+// each to the first non-empty experts.  CTA j of expert e takes tiles [t_e*j/n_e, t_e*(j+1)/n_e).
+struct CtaPart {
+  int e;          // -1 = no work
+  int first, n;   // CTA range of this expert
+  int tile0, tile1;
+};
+
+// CTA ranges of every expert: first[e], n[e] (n = 0 for an empty expert); returns the number of CTAs used.
+__device__ __forceinline__ int expert_ranges(const int* s_seg, int E, int G, int* first, int* n) {
+  int T = s_seg[E] / (int)ROWS;
+  for (int e = 0; e < E; ++e) first[e] = n[e] = 0;
+  if (T <= 0) return 0;
+  int Geff = G < T ? G : T;
+  int nnz = 0;
+  for (int e = 0; e < E; ++e) nnz += (s_seg[e + 1] > s_seg[e]) ? 1 : 0;
+  int R = Geff - nnz, given = 0;
+  for (int e = 0; e < E; ++e) {
+    int t = (s_seg[e + 1] - s_seg[e]) / (int)ROWS;
+    n[e] = t > 0 ? 1 + (int)(((int64_t)R * t) / T) : 0;
+    given += n[e];
+  }
+  int leftover = Geff - given, start = 0;
+  for (int e = 0; e < E; ++e) {
+    if (n[e] > 0 && leftover > 0) {
+      ++n[e];
+      --leftover;
+    }
+    first[e] = start;
+    start += n[e];
+  }
+  return start;
+}
+
+__device__ __forceinline__ CtaPart cta_partition(const int* s_seg, int E, int cta, int G) {
+  CtaPart r{-1, 0, 0, 0, 0};
+  int first[ACN_MAX_EXPERTS], n[ACN_MAX_EXPERTS];
+  expert_ranges(s_seg, E, G, first, n);
+  for (int e = 0; e < E; ++e) {
+    if (n[e] > 0 && cta >= first[e] && cta < first[e] + n[e]) {
+      int t = (s_seg[e + 1] - s_seg[e]) / (int)ROWS, j = cta - first[e], base = s_seg[e] / (int)ROWS;
+      r.e = e;
+      r.first = first[e];
+      r.n = n[e];
+      r.tile0 = base + (int)(((int64_t)t * j) / n[e]);
+      r.tile1 = base + (int)(((int64_t)t * (j + 1)) / n[e]);
+      return r;
+    }
+  }
+  return r;
+}
+
+__device__ __forceinline__ int round_up128(int64_t m) { return (int)((m + 127) / 128 * 128); }
+
+// ---- row-wise epilogue helpers --------------------------------------------------------------
+constexpr float F16_MAX = 65504.f;
+
+// v[0..8n) -> n fp16 chunks of row `r` starting at chunk c0 of the tile at smem address `buf`
+template <int NV>
+__device__ __forceinline__ void store_h(uint32_t buf, uint32_t r, int c0, const float (&v)[NV]) {
+#pragma unroll
+  for (int c = 0; c < NV / 8; ++c)
+    st_chunk(buf + (uint32_t)(c0 + c) * CH + r * 16, pack_h2(v[8 * c], v[8 * c + 1]), pack_h2(v[8 * c + 2], v[8 * c + 3]),
+             pack_h2(v[8 * c + 4], v[8 * c + 5]), pack_h2(v[8 * c + 6], v[8 * c + 7]));
+}
+template <int NV>
+__device__ __forceinline__ void store_g(uint32_t buf, uint32_t r, int c0, const float (&v)[NV]) {
+#pragma unroll
+  for (int c = 0; c < NV / 8; ++c) {
+#if ACN_TC_G_BF16
+    st_chunk(buf + (uint32_t)(c0 + c) * CH + r * 16, pack_bf2(v[8 * c], v[8 * c + 1]), pack_bf2(v[8 * c + 2], v[8 * c + 3]),
+             pack_bf2(v[8 * c + 4], v[8 * c + 5]), pack_bf2(v[8 * c + 6], v[8 * c + 7]));
+#else
+    float w[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) w[i] = fminf(fmaxf(v[8 * c + i], -F16_MAX), F16_MAX);
+    st_chunk(buf + (uint32_t)(c0 + c) * CH + r * 16, pack_h2(w[0], w[1]), pack_h2(w[2], w[3]), pack_h2(w[4], w[5]), pack_h2(w[6], w[7]));
+#endif
+  }
+}
+__device__ __forceinline__ void store_zero_chunk(uint32_t buf, uint32_t r, int c) { st_chunk(buf + (uint32_t)c * CH + r * 16, 0u, 0u, 0u, 0u); }
+__device__ __forceinline__ void store_ones_chunk(uint32_t buf, uint32_t r, int c) {
+  st_chunk(buf + (uint32_t)c * CH + r * 16, 0x00003C00u /* fp16 (1, 0) */, 0u, 0u, 0u);
+}
+
+// ReLU (+ fp16 saturation) in place; returns the bit mask of positive entries
+template <int NV>
+__device__ __forceinline__ uint32_t relu_mask(float (&v)[NV]) {
+  uint32_t m = 0;
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    m |= (v[i] > 0.f ? 1u : 0u) << i;
+    v[i] = fminf(fmaxf(v[i], 0.f), F16_MAX);
+  }
+  return m;
+}
+
+// ---- MMA issue helpers (called by one thread) -----------------------------------------------
+// forward layer: D(128 x N) = A(128 x (8+IN+8), K-major) * W(N x (8+IN+8), K-major)^T
+template <int IN, int N>
+__device__ __forceinline__ void issue_fwd(uint32_t d_tmem, uint32_t a_base, uint32_t w_base) {
+  constexpr uint32_t id = idesc_f16(128, N, F16, F16, K_MAJOR, K_MAJOR);
+#pragma unroll
+  for (int s = 0; s < (IN + 16) / 16; ++s)
+    mma(d_tmem, smem_desc(a_base + s * 2 * CH, CH, 128), smem_desc(w_base + s * 2 * (N * 16), N * 16, 128), id, s > 0);
+}
+
+constexpr uint32_t GFMT = ACN_TC_G_BF16 ? BF16 : F16;
+
+// dgrad: D(128 x IN) = G(128 x OUT, K-major) * W(OUT x IN) ; W read MN-major from the forward weight block
+// (skipping its bias chunk).  WN = rows of the weight block (= padded OUT).
+template <int OUT, int IN, int WN>
+__device__ __forceinline__ void issue_dgrad(uint32_t d_tmem, uint32_t g_base, uint32_t w_base) {
+  constexpr uint32_t id = idesc_f16(128, IN, GFMT, F16, K_MAJOR, MN_MAJOR);
+#pragma unroll
+  for (int s = 0; s < OUT / 16; ++s)
+    mma(d_tmem, smem_desc(g_base + s * 2 * CH, CH, 128), smem_desc(w_base + WN * 16 + s * 256, 128, WN * 16), id, s > 0);
+}
+
+// wgrad: ACC(64 x (8+IN)) += G(128 x 64)^T * [1 | A](128 x (8+IN)), both read MN-major, K = 128 rows
+template <int IN>
+__device__ __forceinline__ void issue_wgrad(uint32_t acc_tmem, uint32_t g_base, uint32_t a_base, uint32_t accumulate) {
+  constexpr uint32_t id = idesc_f16(64, 8 + IN, GFMT, F16, MN_MAJOR, MN_MAJOR);
+#pragma unroll
+  for (int s = 0; s < 8; ++s) mma(acc_tmem, smem_desc(g_base + s * 256, 128, CH), smem_desc(a_base + s * 256, 128, CH), id, accumulate | (s > 0));
+}
+
+__device__ __forceinline__ float trunc_exp_f(float v) { return expf(fminf(fmaxf(v, -88.722839111f), 88.722839111f)); }
+__device__ __forceinline__ float sigmoid_f(float v) { return 1.f / (1.f + expf(-v)); }
+
+// cin = [geo 0..14 | sh 0..15 | 0] : first / second half as fp16 chunks
+__device__ __forceinline__ void dir_sh16(const PointSrc& src, int64_t p, float* sh) {
+  float dx = 0.f, dy = 0.f, dz = 1.f;
+  if (p >= 0) load_dir(src, p, dx, dy, dz);
+  normalize3(dx, dy, dz, 1e-9f);  // meta_ngp.py:165-168
+  normalize3(dx, dy, dz, 1e-9f);  // encodings.py:141
+  sh16_eval(dx, dy, dz, sh);
+}
+
+// =============================================================================================
+// forward
+// =============================================================================================
+constexpr int FWD_PIPES = 4;
+constexpr int FWD_THREADS = 128 * FWD_PIPES;
+constexpr uint32_t ABUF = 10 * CH;  // chunk 0 ones | chunks 1..8 data | chunk 9 zero (chunk 5 zero for 32-wide inputs)
+constexpr size_t FWD_SMEM = W_BYTES + FWD_PIPES * ABUF;
+constexpr uint32_t FWD_TMEM_COLS = 64 * FWD_PIPES;
+
+__global__ void __launch_bounds__(FWD_THREADS, 1)
+    k_ngp_mlp_fwd_tc(PointSrc src, const int32_t* __restrict__ pair_point, const float* __restrict__ pair_w, const int32_t* __restrict__ seg,
+                     int64_t M_ident, ExpertTableTc tab, const float* __restrict__ enc, int64_t ld, float* __restrict__ out) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  __shared__ __align__(8) uint64_t s_bar[FWD_PIPES];
+  __shared__ uint32_t s_tmem;
+  __shared__ int s_seg[ACN_MAX_EXPERTS + 1];
+  __shared__ CtaPart s_part;
+  const int tid = threadIdx.x, q = tid >> 7;
+  const uint32_t r = tid & 127;
+  if (tid <= tab.E) s_seg[tid] = seg ? seg[tid] : (tid == 0 ? 0 : round_up128(M_ident));
+  __syncthreads();
+  const int64_t M = seg ? (int64_t)s_seg[tab.E] : M_ident;
+  if (tid == 0) {
+    s_part = cta_partition(s_seg, tab.E, blockIdx.x, gridDim.x);
+    for (int i = 0; i < FWD_PIPES; ++i) mbar_init(smem_u32(&s_bar[i]), 1);
+    mbar_init_fence();
+  }
+  if (tid < 32) tmem_alloc(&s_tmem, FWD_TMEM_COLS);
+  __syncthreads();
+  const CtaPart part = s_part;
+  const uint32_t sw = smem_u32(smem), abuf = sw + W_BYTES + q * ABUF;
+  if (part.e >= 0) load_weights_tc(smem, tab.ex[part.e], tid, FWD_THREADS);
+  store_ones_chunk(abuf, r, 0);
+  store_zero_chunk(abuf, r, 9);
+  fence_async_smem();
+  fence_before();
+  __syncthreads();
+  fence_after();
+  const uint32_t tbase = s_tmem;
+  const uint32_t dcol = tbase + q * 64;                       // this pipeline's accumulator columns
+  const uint32_t trow = dcol + ((uint32_t)((tid >> 5) & 3) << 21);  // + lane base (32 * warp-in-group) << 16
+  const uint32_t bar = smem_u32(&s_bar[q]);
+  uint32_t phase = 0;
+
+  if (part.e >= 0) {
+    for (int tile = part.tile0 + q; tile < part.tile1; tile += FWD_PIPES) {
+      const int64_t m = (int64_t)tile * ROWS + r;
+      const bool in_range = m < M;
+      const int64_t p = in_range ? (pair_point ? (int64_t)pair_point[m] : m) : -1;
+      const int64_t mm = in_range ? m : 0;
+      {  // encoding -> chunks 1..4, chunk 5 zero
+        float x[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) x[i] = in_range ? __ldg(enc + (int64_t)i * ld + mm) : 0.f;
+#pragma unroll
+        for (int i = 0; i < 32; ++i) x[i] = fminf(fmaxf(x[i], -F16_MAX), F16_MAX);
+        store_h<32>(abuf, r, 1, x);
+        store_zero_chunk(abuf, r, 5);
+      }
+      fence_async_smem();
+      bar_sync(1 + q, 128);
+      if (r == 0) {
+        fence_after();
+        issue_fwd<32, 64>(dcol, abuf, sw + OW0);
+        commit(bar);
+      }
+      mbar_wait(bar, phase);
+      phase ^= 1;
+      fence_after();
+      // two 64-wide ReLU layers share this epilogue; `next` issues the following MMAs
+      float v[32];
+#pragma unroll 1
+      for (int layer = 0; layer < 2; ++layer) {
+        tmem_ld32(trow, v);
+        tmem_ld_wait();
+        relu_mask<32>(v);
+        store_h<32>(abuf, r, 1, v);
+        tmem_ld32(trow + 32, v);
+        tmem_ld_wait();
+        relu_mask<32>(v);
+        store_h<32>(abuf, r, 5, v);
+        fence_before();
+        fence_async_smem();
+        bar_sync(1 + q, 128);
+        if (r == 0) {
+          fence_after();
+          if (layer == 0)
+            issue_fwd<64, 64>(dcol, abuf, sw + OW1);
+          else
+            issue_fwd<64, 16>(dcol, abuf, sw + OWH);
+          commit(bar);
+        }
+        mbar_wait(bar, phase);
+        phase ^= 1;
+        fence_after();
+      }
+      float sigma;
+      {  // heads -> cin = [geo15 | sh16 | 0] in chunks 1..4, chunk 5 zero
+        float h[16], sh[16], c[32];
+        tmem_ld16(trow, h);
+        tmem_ld_wait();
+        sigma = trunc_exp_f(h[15]);
+        dir_sh16(src, p, sh);
+#pragma unroll
+        for (int i = 0; i < 15; ++i) c[i] = fminf(fmaxf(h[i], -F16_MAX), F16_MAX);
+#pragma unroll
+        for (int i = 0; i < 16; ++i) c[15 + i] = sh[i];
+        c[31] = 0.f;
+        store_h<32>(abuf, r, 1, c);
+        store_zero_chunk(abuf, r, 5);
+      }
+      fence_before();
+      fence_async_smem();
+      bar_sync(1 + q, 128);
+      if (r == 0) {
+        fence_after();
+        issue_fwd<32, 64>(dcol, abuf, sw + OW3);
+        commit(bar);
+      }
+      mbar_wait(bar, phase);
+      phase ^= 1;
+      fence_after();
+#pragma unroll 1
+      for (int layer = 0; layer < 2; ++layer) {
+        tmem_ld32(trow, v);
+        tmem_ld_wait();
+        relu_mask<32>(v);
+        store_h<32>(abuf, r, 1, v);
+        tmem_ld32(trow + 32, v);
+        tmem_ld_wait();
+        relu_mask<32>(v);
+        store_h<32>(abuf, r, 5, v);
+        fence_before();
+        fence_async_smem();
+        bar_sync(1 + q, 128);
+        if (r == 0) {
+          fence_after();
+          if (layer == 0)
+            issue_fwd<64, 64>(dcol, abuf, sw + OW4);
+          else
+            issue_fwd<64, 16>(dcol, abuf, sw + OW5);
+          commit(bar);
+        }
+        mbar_wait(bar, phase);
+        phase ^= 1;
+        fence_after();
+      }
+      float o8[8];
+      tmem_ld8(trow, o8);
+      tmem_ld_wait();
+      fence_before();  // the next tile's first MMA overwrites these columns after the bar_sync above it
+      float r0 = sigmoid_f(o8[0]), r1 = sigmoid_f(o8[1]), r2 = sigmoid_f(o8[2]);
+      if (p >= 0) {
+        if (pair_point) {
+          float w = pair_w[m];
+          float* o = out + p * 4;
+          atomicAdd(o + 0, r0 * w);
+          atomicAdd(o + 1, r1 * w);
+          atomicAdd(o + 2, r2 * w);
+          atomicAdd(o + 3, sigma * w);
+        } else {
+          *reinterpret_cast<float4*>(out + p * 4) = make_float4(r0, r1, r2, sigma);
+        }
+      }
+    }
+  }
+  fence_before();
+  __syncthreads();
+  if (tid < 32) tmem_dealloc(tbase, FWD_TMEM_COLS);
+}
+
+// =============================================================================================
+// backward (forward recompute + dgrad chain + TMEM-resident weight gradients)
+// =============================================================================================
+constexpr int BWD_THREADS = 256;  // thread = (row r, column half hf): 32 of the 64 columns of every epilogue
+constexpr uint32_t B_ENC = W_BYTES;            // [1 | enc32 | 0]   6 chunks
+constexpr uint32_t B_H0 = B_ENC + 6 * CH;      // [1 | h0 64 | 0]  10 chunks
+constexpr uint32_t B_H1 = B_H0 + 10 * CH;
+constexpr uint32_t B_CIN = B_H1 + 10 * CH;     // [1 | geo15 sh16 0 | 0]  6 chunks
+constexpr uint32_t B_C0 = B_CIN + 6 * CH;
+constexpr uint32_t B_C1 = B_C0 + 10 * CH;
+constexpr uint32_t B_GA = B_C1 + 10 * CH;      // gradient tiles, 8 chunks each (bf16)
+constexpr uint32_t B_GB = B_GA + 8 * CH;
+constexpr size_t BWD_SMEM = B_GB + 8 * CH;
+// TMEM columns: D (64) then the six weight-gradient accumulators (M = 64 rows -> lanes 16i..16i+15 of each quarter)
+constexpr uint32_t T_D = 0, T_A0 = 64, T_A1 = T_A0 + 40, T_AH = T_A1 + 72, T_A3 = T_AH + 72, T_A4 = T_A3 + 40, T_A5 = T_A4 + 72;
+static_assert(T_A5 + 72 <= 512, "TMEM budget");
+// per-CTA partial layout (floats): row-major (rows, 8+IN) blocks; column 0 = bias gradient, columns 8.. = dW
+constexpr int P_A0 = 0, P_A1 = P_A0 + 64 * 40, P_AH = P_A1 + 64 * 72, P_A3 = P_AH + 16 * 72, P_A4 = P_A3 + 64 * 40, P_A5 = P_A4 + 64 * 72;
+constexpr int P_FLOATS = P_A5 + 16 * 72;
+
+// dump rows [0, 16*nq) of an M=64 accumulator (N columns) to `dst` (row-major, N floats per row)
+template <int N>
+__device__ __forceinline__ void dump_acc(uint32_t tbase, uint32_t col, int nq, float* __restrict__ dst, int tid, bool valid, float inv_s) {
+  const int w = tid >> 5, l = tid & 31;
+  if (tid >= 128 || w >= nq) return;  // warp-uniform
+  float v[8];
+#pragma unroll 1
+  for (int c = 0; c < N; c += 8) {
+    tmem_ld8(tbase + col + c + ((uint32_t)w << 21), v);
+    tmem_ld_wait();
+    if (l < 16) {
+      float* d = dst + (16 * w + l) * N + c;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) d[i] = valid ? v[i] * inv_s : 0.f;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(BWD_THREADS, 1)
+    k_ngp_mlp_bwd_tc(PointSrc src, const int32_t* __restrict__ pair_point, const float* __restrict__ pair_w, const int32_t* __restrict__ seg,
+                     int64_t M_ident, ExpertTableTc tab, const float* __restrict__ enc, int64_t ld, const float* __restrict__ d_out,
+                     float* __restrict__ d_enc, float* __restrict__ partial, const float* __restrict__ gmax) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  __shared__ __align__(8) uint64_t s_bar;
+  __shared__ uint32_t s_tmem;
+  __shared__ int s_seg[ACN_MAX_EXPERTS + 1];
+  __shared__ CtaPart s_part;
+  const int tid = threadIdx.x, hf = tid >> 7;
+  const uint32_t r = tid & 127;
+  if (tid <= tab.E) s_seg[tid] = seg ? seg[tid] : (tid == 0 ? 0 : round_up128(M_ident));
+  __syncthreads();
+  const int64_t M = seg ? (int64_t)s_seg[tab.E] : M_ident;
+  if (tid == 0) {
+    s_part = cta_partition(s_seg, tab.E, blockIdx.x, gridDim.x);
+    mbar_init(smem_u32(&s_bar), 1);
+    mbar_init_fence();
+  }
+  __syncwarp();
+  if (tid < 32) tmem_alloc(&s_tmem, 512);
+  __syncthreads();
+  const CtaPart part = s_part;
+  const uint32_t sb = smem_u32(smem);
+  if (part.e >= 0) load_weights_tc(smem, tab.ex[part.e], tid, BWD_THREADS);
+  if (hf == 0) {
+    store_ones_chunk(sb + B_ENC, r, 0);
+    store_ones_chunk(sb + B_H0, r, 0);
+    store_ones_chunk(sb + B_H1, r, 0);
+    store_ones_chunk(sb + B_CIN, r, 0);
+    store_ones_chunk(sb + B_C0, r, 0);
+    store_ones_chunk(sb + B_C1, r, 0);
+  } else {
+    store_zero_chunk(sb + B_ENC, r, 5);
+    store_zero_chunk(sb + B_H0, r, 9);
+    store_zero_chunk(sb + B_H1, r, 9);
+    store_zero_chunk(sb + B_CIN, r, 5);
+    store_zero_chunk(sb + B_C0, r, 9);
+    store_zero_chunk(sb + B_C1, r, 9);
+  }
+  // gradient tiles start finite (rows 16.. of the 16-wide stages are read by the M=64 wgrad MMAs and ignored)
+  for (int c = hf; c < 8; c += 2) {
+    store_zero_chunk(sb + B_GA, r, c);
+    store_zero_chunk(sb + B_GB, r, c);
+  }
+  fence_async_smem();
+  fence_before();
+  __syncthreads();
+  fence_after();
+  const uint32_t tbase = s_tmem;
+  const uint32_t tD = tbase + T_D;
+  const uint32_t trow = tD + ((uint32_t)((tid >> 5) & 3) << 21) + 32 * hf;  // this thread's 32 columns of D
+  const uint32_t trow0 = tD + ((uint32_t)((tid >> 5) & 3) << 21);          // column 0 of this thread's row
+  const uint32_t bar = smem_u32(&s_bar);
+  uint32_t phase = 0;
+  uint32_t acc = 0;  // 0 on the CTA's first tile: the weight-gradient accumulators are overwritten
+  // gradient scale: the largest |d_out| lands near 2^10 in fp16 (power of two: unscaling is exact)
+  float gscale = 1.f;
+  {
+    float gm = __ldg(gmax);
+    if (gm > 0.f && gm < 3.0e38f) gscale = exp2f(fminf(fmaxf(floorf(log2f(1024.f / gm)), -100.f), 100.f));
+  }
+  const float inv_s = 1.f / gscale;
+
+#define TC_STEP(ISSUE)      \
+  do {                      \
+    fence_before();         \
+    fence_async_smem();     \
+    __syncthreads();        \
+    if (tid == 0) {         \
+      fence_after();        \
+      ISSUE;                \
+      commit(bar);          \
+    }                       \
+    mbar_wait(bar, phase);  \
+    phase ^= 1;             \
+    fence_after();          \
+  } while (0)
+
+  if (part.e >= 0) {
+    for (int tile = part.tile0; tile < part.tile1; ++tile) {
+      const int64_t m = (int64_t)tile * ROWS + r;
+      const bool in_range = m < M;
+      const int64_t p = in_range ? (pair_point ? (int64_t)pair_point[m] : m) : -1;
+      const int64_t mm = in_range ? m : 0;
+      uint32_t m0, m1, m3, m4;  // ReLU masks of this thread's 32 columns of h0, h1, c0, c1
+      float v[32];
+      // ---- forward recompute ----
+      {
+        float x[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) x[i] = in_range ? __ldg(enc + (int64_t)(16 * hf + i) * ld + mm) : 0.f;
+#pragma unroll
+        for (int i = 0; i < 16; ++i) x[i] = fminf(fmaxf(x[i], -F16_MAX), F16_MAX);
+        store_h<16>(sb + B_ENC, r, 1 + 2 * hf, x);
+      }
+      TC_STEP((issue_fwd<32, 64>(tD, sb + B_ENC, sb + OW0)));
+      tmem_ld32(trow, v);
+      tmem_ld_wait();
+      m0 = relu_mask<32>(v);
+      store_h<32>(sb + B_H0, r, 1 + 4 * hf, v);
+      TC_STEP((issue_fwd<64, 64>(tD, sb + B_H0, sb + OW1)));
+      tmem_ld32(trow, v);
+      tmem_ld_wait();
+      m1 = relu_mask<32>(v);
+      store_h<32>(sb + B_H1, r, 1 + 4 * hf, v);
+      TC_STEP((issue_fwd<64, 16>(tD, sb + B_H1, sb + OWH)));
+      float sigma = 0.f;
+      {
+        float sh[16], c[16];
+        dir_sh16(src, p, sh);
+        if (hf == 0) {
+          float h[16];
+          tmem_ld16(trow0, h);
+          tmem_ld_wait();
+          sigma = trunc_exp_f(h[15]);
+#pragma unroll
+          for (int i = 0; i < 15; ++i) c[i] = fminf(fmaxf(h[i], -F16_MAX), F16_MAX);
+          c[15] = sh[0];
+        } else {
+#pragma unroll
+          for (int i = 0; i < 15; ++i) c[i] = sh[1 + i];
+          c[15] = 0.f;
+        }
+        store_h<16>(sb + B_CIN, r, 1 + 2 * hf, c);
+      }
+      TC_STEP((issue_fwd<32, 64>(tD, sb + B_CIN, sb + OW3)));
+      tmem_ld32(trow, v);
+      tmem_ld_wait();
+      m3 = relu_mask<32>(v);
+      store_h<32>(sb + B_C0, r, 1 + 4 * hf, v);
+      TC_STEP((issue_fwd<64, 64>(tD, sb + B_C0, sb + OW4)));
+      tmem_ld32(trow, v);
+      tmem_ld_wait();
+      m4 = relu_mask<32>(v);
+      store_h<32>(sb + B_C1, r, 1 + 4 * hf, v);
+      TC_STEP((issue_fwd<64, 16>(tD, sb + B_C1, sb + OW5)));
+      // ---- output gradients ----
+      float dsraw = 0.f;
+      {
+        float g[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) g[i] = 0.f;
+        if (hf == 0) {
+          float o8[8];
+          tmem_ld8(trow0, o8);
+          tmem_ld_wait();
+          if (p >= 0) {
+            float4 dy = __ldg(reinterpret_cast<const float4*>(d_out + p * 4));
+            if (pair_point) {
+              float w = pair_w[m];
+              dy.x *= w; dy.y *= w; dy.z *= w; dy.w *= w;
+            }
+            float r0 = sigmoid_f(o8[0]), r1 = sigmoid_f(o8[1]), r2 = sigmoid_f(o8[2]);
+            g[0] = gscale * dy.x * r0 * (1.f - r0);
+            g[1] = gscale * dy.y * r1 * (1.f - r1);
+            g[2] = gscale * dy.z * r2 * (1.f - r2);
+            dsraw = gscale * dy.w * sigma;  // trunc_exp backward: g * exp(clamped x)  (trunc_exp.py:44-57)
+          }
+        }
+        store_g<8>(sb + B_GA, r, hf, g);  // chunk 0 = dz5 (3 of 8), chunk 1 = 0
+      }
+      // ---- dgrad chain; every step also accumulates the weight gradient of the layer just left ----
+      TC_STEP((issue_dgrad<16, 64, 16>(tD, sb + B_GA, sb + OW5), issue_wgrad<64>(tbase + T_A5, sb + B_GA, sb + B_C1, acc)));
+      tmem_ld32(trow, v);
+      tmem_ld_wait();
+#pragma unroll
+      for (int i = 0; i < 32; ++i) v[i] = (m4 >> i & 1u) ? v[i] : 0.f;
+      store_g<32>(sb + B_GB, r, 4 * hf, v);
+      TC_STEP((issue_dgrad<64, 64, 64>(tD, sb + B_GB, sb + OW4), issue_wgrad<64>(tbase + T_A4, sb + B_GB, sb + B_C0, acc)));
+      tmem_ld32(trow, v);
+      tmem_ld_wait();
+#pragma unroll
+      for (int i = 0; i < 32; ++i) v[i] = (m3 >> i & 1u) ? v[i] : 0.f;
+      store_g<32>(sb + B_GA, r, 4 * hf, v);
+      TC_STEP((issue_dgrad<64, 32, 64>(tD, sb + B_GA, sb + OW3), issue_wgrad<32>(tbase + T_A3, sb + B_GA, sb + B_CIN, acc)));
+      if (hf == 0) {  // head gradient [d geo 0..14 | d sigma_raw] -> chunks 0, 1
+        float g[16];
+        tmem_ld16(trow0, g);
+        tmem_ld_wait();
+        g[15] = dsraw;
+        store_g<16>(sb + B_GB, r, 0, g);
+      }
+      TC_STEP((issue_dgrad<16, 64, 16>(tD, sb + B_GB, sb + OWH), issue_wgrad<64>(tbase + T_AH, sb + B_GB, sb + B_H1, acc)));
+      tmem_ld32(trow, v);
+      tmem_ld_wait();
+#pragma unroll
+      for (int i = 0; i < 32; ++i) v[i] = (m1 >> i & 1u) ? v[i] : 0.f;
+      store_g<32>(sb + B_GA, r, 4 * hf, v);
+      TC_STEP((issue_dgrad<64, 64, 64>(tD, sb + B_GA, sb + OW1), issue_wgrad<64>(tbase + T_A1, sb + B_GA, sb + B_H0, acc)));
+      tmem_ld32(trow, v);
+      tmem_ld_wait();
+#pragma unroll
+      for (int i = 0; i < 32; ++i) v[i] = (m0 >> i & 1u) ? v[i] : 0.f;
+      store_g<32>(sb + B_GB, r, 4 * hf, v);
+      TC_STEP((issue_dgrad<64, 32, 64>(tD, sb + B_GB, sb + OW0), issue_wgrad<32>(tbase + T_A0, sb + B_GB, sb + B_ENC, acc)));
+      {
+        float g[16];
+        tmem_ld16(trow0 + 16 * hf, g);
+        tmem_ld_wait();
+        if (m < ld) {
+#pragma unroll
+          for (int i = 0; i < 16; ++i) d_enc[(int64_t)(16 * hf + i) * ld + m] = g[i] * inv_s;
+        }
+      }
+      acc = 1;
+    }
+  }
+#undef TC_STEP
+  fence_before();
+  __syncthreads();
+  fence_after();
+  {
+    float* dst = partial + (int64_t)blockIdx.x * P_FLOATS;
+    const bool valid = acc != 0;
+    dump_acc<40>(tbase, T_A0, 4, dst + P_A0, tid, valid, inv_s);
+    dump_acc<72>(tbase, T_A1, 4, dst + P_A1, tid, valid, inv_s);
+    dump_acc<72>(tbase, T_AH, 1, dst + P_AH, tid, valid, inv_s);
+    dump_acc<40>(tbase, T_A3, 4, dst + P_A3, tid, valid, inv_s);
+    dump_acc<72>(tbase, T_A4, 4, dst + P_A4, tid, valid, inv_s);
+    dump_acc<72>(tbase, T_A5, 1, dst + P_A5, tid, valid, inv_s);
+  }
+  fence_before();
+  __syncthreads();
+  if (tid < 32) tmem_dealloc(tbase, 512);
+}
+
+// max |x| over a tensor (non-negative floats order like their bit patterns; NaN sorts above inf -> scale 1)
+__global__ void __launch_bounds__(256) k_absmax(const float4* __restrict__ x, int64_t n4, float* __restrict__ out) {
+  float m = 0.f;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+    float4 v = __ldg(x + i);
+    m = fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fmaxf(fabsf(v.z), fabsf(v.w)), m));
+    if (!(v.x == v.x && v.y == v.y && v.z == v.z && v.w == v.w)) m = __int_as_float(0x7fc00000);
+  }
+  int b = __float_as_int(m);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) b = max(b, __shfl_xor_sync(0xffffffffu, b, o));
+  if ((threadIdx.x & 31) == 0) atomicMax(reinterpret_cast<int*>(out), b);
+}
+
+// ---- fixed-order reduction of the per-CTA partials into the nn.Linear-shaped gradients -------
+struct GradPtrsTc {
+  float* w[ACN_MAX_EXPERTS][ACN_NGP_LAYERS];
+  float* b[ACN_MAX_EXPERTS][ACN_NGP_LAYERS];
+};
+
+__global__ void __launch_bounds__(256) k_tc_wgrad_reduce(const float* __restrict__ partial, const int32_t* __restrict__ seg, int64_t M_ident, int E,
+                                                         int G, const GradPtrsTc gp) {
+  __shared__ int s_seg[ACN_MAX_EXPERTS + 1];
+  __shared__ int s_first[ACN_MAX_EXPERTS], s_n[ACN_MAX_EXPERTS];
+  if ((int)threadIdx.x <= E) s_seg[threadIdx.x] = seg ? seg[threadIdx.x] : (threadIdx.x == 0 ? 0 : round_up128(M_ident));
+  __syncthreads();
+  if (threadIdx.x == 0) expert_ranges(s_seg, E, G, s_first, s_n);
+  __syncthreads();
+  const int e = blockIdx.y;
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= P_FLOATS) return;
+  float acc = 0.f;
+  const float* src = partial + (int64_t)s_first[e] * P_FLOATS + j;
+  for (int c = 0; c < s_n[e]; ++c) acc += __ldg(src + (int64_t)c * P_FLOATS);
+  // j -> (block, row, col)
+  int blk, row, col, N;
+  if (j < P_A1) { blk = 0; N = 40; row = (j - P_A0) / N; col = (j - P_A0) % N; }
+  else if (j < P_AH) { blk = 1; N = 72; row = (j - P_A1) / N; col = (j - P_A1) % N; }
+  else if (j < P_A3) { blk = 2; N = 72; row = (j - P_AH) / N; col = (j - P_AH) % N; }
+  else if (j < P_A4) { blk = 3; N = 40; row = (j - P_A3) / N; col = (j - P_A3) % N; }
+  else if (j < P_A5) { blk = 4; N = 72; row = (j - P_A4) / N; col = (j - P_A4) % N; }
+  else { blk = 5; N = 72; row = (j - P_A5) / N; col = (j - P_A5) % N; }
+  if (col >= 1 && col < 8) return;
+  const bool is_b = col == 0;
+  const int i = col - 8;
+  int layer, o = row, in_real;
+  switch (blk) {
+    case 0: layer = 0; in_real = 32; break;
+    case 1: layer = 1; in_real = 64; break;
+    case 2: if (row < 15) { layer = 3; } else { layer = 2; o = 0; } in_real = 64; break;
+    case 3: layer = 4; in_real = 31; break;
+    case 4: layer = 5; in_real = 64; break;
+    default: if (row >= 3) return; layer = 6; in_real = 64; break;
+  }
+  if (is_b) {
+    float* d = gp.b[e][layer];
+    if (d) d[o] = acc;
+  } else if (i < in_real) {
+    float* d = gp.w[e][layer];
+    if (d) d[o * in_real + i] = acc;
+  }
+}
+
+// ---- descriptor self-test: the three operand-layout combinations the kernels above rely on ----
+//   D1 = X Y^T        X (128,64) fp16 K-major, Y (64,64) fp16 K-major                  (forward)
+//   D3 = G Y          G (128,64) K-major, Y read MN-major                              (dgrad)
+//   D2 = G^T [X]      G and X read MN-major, M = 64 accumulator                        (wgrad)
+// G is bf16 when `mixed` (mixed fp16 x bf16 operands), fp16 otherwise.
+__global__ void __launch_bounds__(128, 1) k_tc_selftest(const float* __restrict__ X, const float* __restrict__ Y, const float* __restrict__ Gm, int mixed,
+                                                        float* __restrict__ D1, float* __restrict__ D2, float* __restrict__ D3) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  __shared__ __align__(8) uint64_t s_bar;
+  __shared__ uint32_t s_tmem;
+  const int tid = threadIdx.x;
+  const uint32_t r = tid;
+  const uint32_t sb = smem_u32(smem), bx = sb, by = sb + 8 * CH, bg = by + 8 * 64 * 16;
+  if (tid == 0) {
+    mbar_init(smem_u32(&s_bar), 1);
+    mbar_init_fence();
+  }
+  __syncwarp();
+  if (tid < 32) tmem_alloc(&s_tmem, 256);
+  {
+    float v[32];
+    for (int h = 0; h < 2; ++h) {
+      for (int i = 0; i < 32; ++i) v[i] = X[r * 64 + 32 * h + i];
+      store_h<32>(bx, r, 4 * h, v);
+      for (int i = 0; i < 32; ++i) v[i] = Gm[r * 64 + 32 * h + i];
+      if (mixed) {
+        for (int c = 0; c < 4; ++c)
+          st_chunk(bg + (uint32_t)(4 * h + c) * CH + r * 16, pack_bf2(v[8 * c], v[8 * c + 1]), pack_bf2(v[8 * c + 2], v[8 * c + 3]),
+                   pack_bf2(v[8 * c + 4], v[8 * c + 5]), pack_bf2(v[8 * c + 6], v[8 * c + 7]));
+      } else {
+        store_h<32>(bg, r, 4 * h, v);
+      }
+    }
+    if (r < 64) {  // Y: 64 rows, chunk stride 64*16
+      for (int c = 0; c < 8; ++c) {
+        for (int i = 0; i < 8; ++i) v[i] = Y[r * 64 + 8 * c + i];
+        st_chunk(by + (uint32_t)c * (64 * 16) + r * 16, pack_h2(v[0], v[1]), pack_h2(v[2], v[3]), pack_h2(v[4], v[5]), pack_h2(v[6], v[7]));
+      }
+    }
+  }
+  fence_async_smem();
+  fence_before();
+  __syncthreads();
+  fence_after();
+  const uint32_t tbase = s_tmem;
+  const uint32_t gf = mixed ? BF16 : F16;
+  if (tid == 0) {
+    const uint32_t id1 = idesc_f16(128, 64, F16, F16, K_MAJOR, K_MAJOR);
+    for (int s = 0; s < 4; ++s) mma(tbase + 0, smem_desc(bx + s * 2 * CH, CH, 128), smem_desc(by + s * 2 * (64 * 16), 64 * 16, 128), id1, s > 0);
+    const uint32_t id3 = idesc_f16(128, 64, gf, F16, K_MAJOR, MN_MAJOR);
+    for (int s = 0; s < 4; ++s) mma(tbase + 64, smem_desc(bg + s * 2 * CH, CH, 128), smem_desc(by + s * 256, 128, 64 * 16), id3, s > 0);
+    const uint32_t id2 = idesc_f16(64, 64, gf, F16, MN_MAJOR, MN_MAJOR);
+    for (int s = 0; s < 8; ++s) mma(tbase + 128, smem_desc(bg + s * 256, 128, CH), smem_desc(bx + s * 256, 128, CH), id2, s > 0);
+    commit(smem_u32(&s_bar));
+  }
+  mbar_wait(smem_u32(&s_bar), 0);
+  fence_after();
+  const uint32_t lane_off = (uint32_t)(tid >> 5) << 21;
+  float v[32];
+  for (int h = 0; h < 2; ++h) {
+    tmem_ld32(tbase + 0 + 32 * h + lane_off, v);
+    tmem_ld_wait();
+    for (int i = 0; i < 32; ++i) D1[r * 64 + 32 * h + i] = v[i];
+    tmem_ld32(tbase + 64 + 32 * h + lane_off, v);
+    tmem_ld_wait();
+    for (int i = 0; i < 32; ++i) D3[r * 64 + 32 * h + i] = v[i];
+    tmem_ld32(tbase + 128 + 32 * h + lane_off, v);
+    tmem_ld_wait();
+    if ((tid & 31) < 16) {
+      int o = 16 * (tid >> 5) + (tid & 31);
+      for (int i = 0; i < 32; ++i) D2[o * 64 + 32 * h + i] = v[i];
+    }
+  }
+  fence_before();
+  __syncthreads();
+  if (tid < 32) tmem_dealloc(tbase, 256);
+}
+
+static void fill_table_tc(ExpertTableTc& tab, const AcnNgpExpert* experts, int E) {
+  tab.E = E;
+  for (int e = 0; e < E; ++e) tab.ex[e] = experts[e];
+  for (int e = E; e < ACN_MAX_EXPERTS; ++e) tab.ex[e] = experts[0];
+}
+
+static int tc_grid(int64_t Mcap) {
+  int64_t tiles = (Mcap + ROWS - 1) / ROWS;
+  int g = num_sms_cached();
+  if (tiles < g) g = (int)tiles;
+  return g < 1 ? 1 : g;
+}
+
+static int set_tc_attrs() {
+  static thread_local int done_dev = -1;
+  int dev = 0;
+  ACN_CUDA(cudaGetDevice(&dev));
+  if (done_dev != dev) {
+    ACN_CUDA(cudaFuncSetAttribute(k_ngp_mlp_fwd_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FWD_SMEM));
+    ACN_CUDA(cudaFuncSetAttribute(k_ngp_mlp_bwd_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BWD_SMEM));
+    ACN_CUDA(cudaFuncSetAttribute(k_tc_selftest, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+    done_dev = dev;
+  }
+  return ACN_OK;
+}
+
+}  // namespace acn
+
+using namespace acn;
+
+extern "C" {
+
+int acn_ngp_mlp_fwd_tc(const AcnPoints* pts, const AcnPairs* pairs, const AcnNgpExpert* experts, int E, const float* enc, float* out,
+                       void* stream) {
+  ACN_REQUIRE(pts && pairs && experts && enc && out, "acn_ngp_mlp_fwd_tc: NULL argument");
+  ACN_REQUIRE(E >= 1 && E <= ACN_MAX_EXPERTS, "acn_ngp_mlp_fwd_tc: E must be in [1,%d]", ACN_MAX_EXPERTS);
+  ACN_REQUIRE(pts->x6 || (pts->rays && pts->S >= 1), "acn_ngp_mlp_fwd_tc: points need x6 or rays");
+  bool ident = pairs->point == nullptr;
+  ACN_REQUIRE(ident ? (E == 1 && pairs->Mcap == pts->P) : (pairs->weight && pairs->seg), "acn_ngp_mlp_fwd_tc: inconsistent pair list");
+  ACN_REQUIRE(pairs->Mcap < ((int64_t)1 << 31) - 128, "acn_ngp_mlp_fwd_tc: chunk the pair list below 2^31");
+  int64_t Mcap = pairs->Mcap;
+  if (Mcap == 0) return ACN_OK;
+  int rc = set_tc_attrs();
+  if (rc) return rc;
+  ExpertTableTc tab;
+  fill_table_tc(tab, experts, E);
+  int64_t ld = (Mcap + 127) / 128 * 128;
+  k_ngp_mlp_fwd_tc<<<tc_grid(Mcap), FWD_THREADS, FWD_SMEM, as_stream(stream)>>>(make_src(pts), pairs->point, pairs->weight, pairs->seg, Mcap,
+                                                                               tab, enc, ld, out);
+  ACN_LAUNCH_CHECK();
+  return ACN_OK;
+}
+
+int64_t acn_ngp_bwd_tc_ws_bytes(void) {
+  return (int64_t)sizeof(float) * (P_FLOATS * (int64_t)num_sms_cached() + 4);
+}
+
+int acn_ngp_mlp_bwd_tc(const AcnPoints* pts, const AcnPairs* pairs, const AcnNgpExpert* experts, int E, const float* enc, const float* d_out,
+                       const AcnNgpExpertGrads* grads, float* d_enc, void* ws, void* stream) {
+  ACN_REQUIRE(pts && pairs && experts && enc && d_out && grads && d_enc && ws, "acn_ngp_mlp_bwd_tc: NULL argument");
+  ACN_REQUIRE(E >= 1 && E <= ACN_MAX_EXPERTS, "acn_ngp_mlp_bwd_tc: E must be in [1,%d]", ACN_MAX_EXPERTS);
+  ACN_REQUIRE(pts->x6 || (pts->rays && pts->S >= 1), "acn_ngp_mlp_bwd_tc: points need x6 or rays");
+  bool ident = pairs->point == nullptr;
+  ACN_REQUIRE(ident ? (E == 1 && pairs->Mcap == pts->P) : (pairs->weight && pairs->seg), "acn_ngp_mlp_bwd_tc: inconsistent pair list");
+  ACN_REQUIRE(pairs->Mcap < ((int64_t)1 << 31) - 128, "acn_ngp_mlp_bwd_tc: chunk the pair list below 2^31");
+  int64_t Mcap = pairs->Mcap;
+  if (Mcap == 0) return ACN_OK;
+  int rc = set_tc_attrs();
+  if (rc) return rc;
+  cudaStream_t st = as_stream(stream);
+  ExpertTableTc tab;
+  fill_table_tc(tab, experts, E);
+  int64_t ld = (Mcap + 127) / 128 * 128;
+  int G = tc_grid(Mcap);
+  float* partial = reinterpret_cast<float*>(ws);
+  GradPtrsTc gp;
+  bool any = false;
+  for (int e = 0; e < ACN_MAX_EXPERTS; ++e)
+    for (int l = 0; l < ACN_NGP_LAYERS; ++l) {
+      gp.w[e][l] = e < E ? grads[e].w[l] : nullptr;
+      gp.b[e][l] = e < E ? grads[e].b[l] : nullptr;
+      any = any || gp.w[e][l] || gp.b[e][l];
+    }
+  float* gmax = partial + (int64_t)P_FLOATS * num_sms_cached();
+  ACN_CUDA(cudaMemsetAsync(gmax, 0, sizeof(float), st));
+  k_absmax<<<persistent_grid((pts->P + 255) / 256, 4), 256, 0, st>>>(reinterpret_cast<const float4*>(d_out), pts->P, gmax);
+  ACN_LAUNCH_CHECK();
+  k_ngp_mlp_bwd_tc<<<G, BWD_THREADS, BWD_SMEM, st>>>(make_src(pts), pairs->point, pairs->weight, pairs->seg, Mcap, tab, enc, ld, d_out, d_enc,
+                                                     partial, gmax);
+  ACN_LAUNCH_CHECK();
+  if (any) {
+    dim3 grid((P_FLOATS + 255) / 256, E);
+    k_tc_wgrad_reduce<<<grid, 256, 0, st>>>(partial, pairs->seg, Mcap, E, G, gp);
+    ACN_LAUNCH_CHECK();
+  }
+  return ACN_OK;
+}
+
+int acn_tc_selftest(const float* X, const float* Y, const float* G, int mixed, float* D1, float* D2, float* D3, void* stream) {
+  ACN_REQUIRE(X && Y && G && D1 && D2 && D3, "acn_tc_selftest: NULL argument");
+  int rc = set_tc_attrs();
+  if (rc) return rc;
+  k_tc_selftest<<<1, 128, 64 * 1024, as_stream(stream)>>>(X, Y, G, mixed, D1, D2, D3);
+  ACN_LAUNCH_CHECK();
+  return ACN_OK;
+}
+
+}  // extern "C"

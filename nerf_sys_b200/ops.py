@@ -23,6 +23,39 @@ NGP_LAYER_KEYS = ("sigma_trunk.0.linear", "sigma_trunk.1.linear", "sigma_head", 
 NGP_LAYER_SHAPES = ((64, 32), (64, 64), (1, 64), (15, 64), (64, 31), (64, 64), (3, 64))
 INTERP = {"linear": 0, "smoothstep": 1, "nearest": 2}
 
+# Arithmetic of the fused expert MLPs: "f16tc" = tcgen05 tensor cores, fp16 operands / fp32 accumulate (the
+# precision class of the reference's own GPU path); "fp32" = exact CUDA-core mode used by the tight parity tests.
+_mlp_math = "fp32"
+
+
+def set_mlp_math(mode: str) -> str:
+    """Select the expert-MLP arithmetic for subsequent forward calls; returns the previous mode."""
+    global _mlp_math
+    if mode not in ("f16tc", "fp32"):
+        raise ValueError(f"mlp math must be 'f16tc' or 'fp32', got {mode!r}")
+    prev, _mlp_math = _mlp_math, mode
+    return prev
+
+
+def get_mlp_math() -> str:
+    return _mlp_math
+
+
+class mlp_math:
+    """Context manager: `with ops.mlp_math("f16tc"): ...`"""
+
+    def __init__(self, mode: str):
+        self.mode = mode
+
+    def __enter__(self):
+        self.prev = set_mlp_math(self.mode)
+        return self
+
+    def __exit__(self, *exc):
+        set_mlp_math(self.prev)
+        return False
+
+
 _launches = 0  # kernels launched through this module (bench.py's gpu_launches claim)
 
 
@@ -471,14 +504,20 @@ class NgpMlpFn(torch.autograd.Function):
         dev = pts.device
         out = torch.empty(pts.P, 4, device=dev, dtype=torch.float32) if pairs.identity else torch.zeros(pts.P, 4, device=dev,
                                                                                                         dtype=torch.float32)
-        save = torch.empty(int(L.acn_ngp_save_bytes(pairs.M)) // 4, device=dev, dtype=torch.float32) if need_grad else None
+        tc = _mlp_math == "f16tc"
+        save = None
+        if need_grad and not tc:  # the tensor-core backward recomputes the forward per tile instead
+            save = torch.empty(int(L.acn_ngp_save_bytes(pairs.M)) // 4, device=dev, dtype=torch.float32)
         ex = _expert_array(spec, None, ws)
         cp, cq = pts.c(), pairs.c()
         with torch.cuda.device(dev), _timed("mlp_fwd"):
-            check(L.acn_ngp_mlp_fwd(C.byref(cp), C.byref(cq), ex, spec.E, _ptr(enc_c), _ptr(out), _ptr(save), _stream()),
-                  "acn_ngp_mlp_fwd")
+            if tc:
+                check(L.acn_ngp_mlp_fwd_tc(C.byref(cp), C.byref(cq), ex, spec.E, _ptr(enc_c), _ptr(out), _stream()), "acn_ngp_mlp_fwd_tc")
+            else:
+                check(L.acn_ngp_mlp_fwd(C.byref(cp), C.byref(cq), ex, spec.E, _ptr(enc_c), _ptr(out), _ptr(save), _stream()),
+                      "acn_ngp_mlp_fwd")
         _count(1)
-        ctx.pts, ctx.pairs, ctx.spec, ctx.save = pts, pairs, spec, save
+        ctx.pts, ctx.pairs, ctx.spec, ctx.save, ctx.tc = pts, pairs, spec, save, tc
         ctx.save_for_backward(enc_c, *ws)
         return out
 
@@ -487,7 +526,7 @@ class NgpMlpFn(torch.autograd.Function):
         L = lib()
         enc, *ws = ctx.saved_tensors
         pts, pairs, spec = ctx.pts, ctx.pairs, ctx.spec
-        if ctx.save is None:
+        if ctx.save is None and not ctx.tc:
             raise RuntimeError("NgpMlpFn.backward without saved activations (forward ran under no_grad)")
         dev = pts.device
         d_out = _f32(d_out, "d_out")
@@ -508,15 +547,38 @@ class NgpMlpFn(torch.autograd.Function):
                     else:
                         outs.append(None)
         d_enc = torch.empty_like(enc)
-        wsb = torch.empty(int(L.acn_ngp_bwd_ws_bytes(pairs.M, spec.E)) // 4, device=dev, dtype=torch.float32)
         ex = _expert_array(spec, None, ws)
         cq = pairs.c()
-        with torch.cuda.device(dev), _timed("mlp_bwd"):
-            check(L.acn_ngp_mlp_bwd(C.byref(cq), ex, spec.E, _ptr(enc), _ptr(d_out), _ptr(ctx.save), grads, _ptr(d_enc), _ptr(wsb),
-                                    _stream()), "acn_ngp_mlp_bwd")
-        _count(1 + 14)
+        if ctx.tc:
+            wsb = torch.empty(int(L.acn_ngp_bwd_tc_ws_bytes()) // 4, device=dev, dtype=torch.float32)
+            cp = pts.c()
+            with torch.cuda.device(dev), _timed("mlp_bwd"):
+                check(L.acn_ngp_mlp_bwd_tc(C.byref(cp), C.byref(cq), ex, spec.E, _ptr(enc), _ptr(d_out), grads, _ptr(d_enc), _ptr(wsb),
+                                           _stream()), "acn_ngp_mlp_bwd_tc")
+            _count(3)
+        else:
+            wsb = torch.empty(int(L.acn_ngp_bwd_ws_bytes(pairs.M, spec.E)) // 4, device=dev, dtype=torch.float32)
+            with torch.cuda.device(dev), _timed("mlp_bwd"):
+                check(L.acn_ngp_mlp_bwd(C.byref(cq), ex, spec.E, _ptr(enc), _ptr(d_out), _ptr(ctx.save), grads, _ptr(d_enc), _ptr(wsb),
+                                        _stream()), "acn_ngp_mlp_bwd")
+            _count(1 + 14)
         ctx.save = None
         return (d_enc if ctx.needs_input_grad[0] else None, None, None, None, *outs)
+
+
+def tc_selftest(X: Tensor, Y: Tensor, G: Tensor, mixed: bool):
+    """acn_tc_selftest: (D1 = X Y^T, D2 = G^T X, D3 = G Y) through the three tcgen05 operand layouts."""
+    L = lib()
+    X, Y, G = _need(X, "X"), _need(Y, "Y"), _need(G, "G")
+    if tuple(X.shape) != (128, 64) or tuple(Y.shape) != (64, 64) or tuple(G.shape) != (128, 64):
+        raise ValueError("tc_selftest shapes: X (128,64), Y (64,64), G (128,64)")
+    D1 = torch.empty(128, 64, device=X.device)
+    D2 = torch.empty(64, 64, device=X.device)
+    D3 = torch.empty(128, 64, device=X.device)
+    with torch.cuda.device(X.device):
+        check(L.acn_tc_selftest(_ptr(X), _ptr(Y), _ptr(G), int(bool(mixed)), _ptr(D1), _ptr(D2), _ptr(D3), _stream()), "acn_tc_selftest")
+    _count(1)
+    return D1, D2, D3
 
 
 def ngp_experts(pts: PointSet, pairs: PairList, spec: ExpertSpec, tables: Sequence[Tensor], mlp: Sequence[Tensor]) -> Tensor:
