@@ -260,6 +260,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-render", action="store_true")
+    ap.add_argument("--no-graph", action="store_true", help="drive every step from Python instead of replaying a CUDA graph")
     ap.add_argument("--mlp-math", default="f16tc", choices=["f16tc", "fp32"],
                     help="expert-MLP arithmetic: tcgen05 fp16/fp32-accumulate (default) or the exact fp32 CUDA-core mode")
     args = ap.parse_args()
@@ -299,23 +300,34 @@ def main():
         torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
         return t.item()
 
+    from nerf_sys_b200.nerfs.losses import compute_mse_loss
+    use_graph = not args.no_graph
+    if use_graph:
+        from nerf_sys_b200.engine import GraphedTrainStep
+        gstep = GraphedTrainStep(opt, lambda r, c: compute_mse_loss(P, model, {"rays": r, "rgbs": c}), (pool[0], rgbs[0]), warmup=W,
+                                 post_backward=lambda: allreduce_bg(model, world))
+
+        def step(r, c):
+            return gstep(r, c)
+    else:
+        def step(r, c):
+            return train_step(model, opt, r, c, world)
+
     # ---- resident-input arm ------------------------------------------------------------
     for i in range(W):
-        train_step(model, opt, pool[i % nb], rgbs[i % nb], world)
+        step(pool[i % nb], rgbs[i % nb])
     barrier()
     clocks = Clocks(local)
-    timing = ops.kernel_timing(True)
     l0 = ops.launches()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     e0.record()
     for i in range(K):
-        loss = train_step(model, opt, pool[(W + i) % nb], rgbs[(W + i) % nb], world)
+        loss = step(pool[(W + i) % nb], rgbs[(W + i) % nb])
     e1.record()
     barrier()
     ms = max_over_ranks(e0.elapsed_time(e1))
     launches = ops.launches() - l0
-    ops.kernel_timing(False)
     final_loss = float(loss.item())
 
     # ---- end-to-end arm: host batches in, loss out, every step -------------------------------
@@ -324,11 +336,19 @@ def main():
     for i in range(K):
         r = pool_h[(W + i) % nb].to(dev, non_blocking=True)
         c = rgbs_h[(W + i) % nb].to(dev, non_blocking=True)
-        _ = train_step(model, opt, r, c, world).item()
+        _ = step(r, c).item()
     e1.record()
     barrier()
     ms_e2e = max_over_ranks(e0.elapsed_time(e1))
     clk = clocks.stop()
+
+    # ---- per-kernel device time: the same K steps driven eagerly with an event pair around every C-ABI call
+    # (events cannot be recorded between the nodes of a replayed graph)
+    timing = ops.kernel_timing(True)
+    for i in range(K):
+        train_step(model, opt, pool[(W + i) % nb], rgbs[(W + i) % nb], world)
+    barrier()
+    ops.kernel_timing(False)
 
     # ---- per-call device time -> roofline ------------------------------------------------
     pk = peaks()
@@ -391,6 +411,8 @@ def main():
                                             "table": "2^20 x 16 levels x 2 fp32 = 128 MiB", "mlp_math": ("tcgen05 kind::f16, fp16 operands, fp32 accumulate in TMEM (hash grid, compositing, loss, Adam in fp32)"
                                                          if args.mlp_math == "f16tc" else "fp32 FFMA (exact mode)"),
                                             "l2": "per-step working set 512 MiB (table+grad+Adam moments) > 126 MB L2, no flush",
+                                            "launch": "CUDA graph replay of zero_grad+fwd+bwd+clip+Adam" if use_graph else "eager Python launches",
+                                            "kernel_timing": "separate eager pass of the same K steps, CUDA-event pair per C-ABI call",
                                             "collective": "none" if world == 1 else "nccl all-reduce of 643 bg-head grads"},
             "clocks": clk, "e2e": {"value": world * N_RAYS * K / (ms_e2e / 1e3), "unit": "rays/s", "h2d_bytes_per_step": bytes_in,
                                    "d2h_bytes_per_step": 4, "ms_per_step": ms_e2e / K},

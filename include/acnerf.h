@@ -249,6 +249,29 @@ int acn_sgd_axpy(const float* w, const float* g, float lr, int64_t n, float* out
 /* sum of squares of a tensor accumulated into acc (1,) (clip_grad_norm_ building block) */
 int acn_sumsq_accum(const float* x, int64_t n, float* acc, void* stream);
 
+/* Multi-tensor forms: the whole parameter set in one launch each (a 15-tensor expert plus its 128 MiB table
+ * otherwise costs ~40 launches per step).  Step counts live on the device (steps_dev[step_index], int32,
+ * incremented by the call) so the step can be replayed from a CUDA graph; bias corrections are evaluated in
+ * double like torch's.  coef = min(1, max_norm / (sqrt(*sumsq_dev) + 1e-6)) [if sumsq_dev && max_norm > 0]
+ * * (*grad_scale_dev) [if given] is written to coef_dev when write_coef (first chunk of a step) and applied
+ * to every gradient (clip_grad_norm_ + GradScaler.unscale_ semantics, meta_core.py:123-141, 181-190). */
+#define ACN_ADAM_MAX_TENSORS 64
+typedef struct AcnAdamTensor {
+  float* param;
+  const float* grad;
+  float* exp_avg;
+  float* exp_avg_sq;
+  int64_t n;
+  float lr;
+  float weight_decay;
+  int32_t step_index;
+  int32_t reserved;
+} AcnAdamTensor;
+int acn_sumsq_multi(const AcnAdamTensor* tensors_host, int count, float* acc, void* stream);
+int acn_adam_multi(const AcnAdamTensor* tensors_host, int count, float beta1, float beta2, float eps,
+                   int32_t* steps_dev, const float* sumsq_dev, float max_norm, const float* grad_scale_dev,
+                   float* coef_dev, int write_coef, void* stream);
+
 #if defined(__GNUC__)
 #pragma GCC visibility pop
 #endif

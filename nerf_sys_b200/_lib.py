@@ -42,6 +42,12 @@ class AcnNgpExpertGrads(C.Structure):
     _fields_ = [("table", vp), ("w", vp * ACN_NGP_LAYERS), ("b", vp * ACN_NGP_LAYERS)]
 
 
+class AcnAdamTensor(C.Structure):
+    _fields_ = [("param", vp), ("grad", vp), ("exp_avg", vp), ("exp_avg_sq", vp), ("n", i64), ("lr", f32), ("weight_decay", f32),
+                ("step_index", i32), ("reserved", i32)]
+
+
+ACN_ADAM_MAX_TENSORS = 64
 P = C.POINTER
 fp = P(f32)  # host float arrays
 
@@ -89,6 +95,8 @@ SIGNATURES = {
     "acn_adam_step": (C.c_int, [vp, vp, vp, vp, i64, f32, f32, f32, f32, f32, i64, vp, vp]),
     "acn_sgd_axpy": (C.c_int, [vp, vp, f32, i64, vp, vp]),
     "acn_sumsq_accum": (C.c_int, [vp, i64, vp, vp]),
+    "acn_sumsq_multi": (C.c_int, [P(AcnAdamTensor), C.c_int, vp, vp]),
+    "acn_adam_multi": (C.c_int, [P(AcnAdamTensor), C.c_int, f32, f32, f32, vp, vp, f32, vp, vp, C.c_int, vp]),
 }
 
 _lock = threading.Lock()

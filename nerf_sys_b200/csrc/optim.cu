@@ -66,6 +66,118 @@ __global__ void __launch_bounds__(256) k_sumsq(const float* __restrict__ x, int6
   }
 }
 
+
+// ---- multi-tensor variants: one launch for the whole parameter set -------------------------------
+struct MultiDesc {
+  AcnAdamTensor t[ACN_ADAM_MAX_TENSORS];
+  int blk0[ACN_ADAM_MAX_TENSORS + 1];  // first block of each tensor
+  int count;
+};
+
+__device__ __forceinline__ int find_tensor(const MultiDesc& d, int b) {
+  int t = 0;
+  while (t + 1 < d.count && b >= d.blk0[t + 1]) ++t;
+  return t;
+}
+
+__global__ void __launch_bounds__(256) k_sumsq_multi(const __grid_constant__ MultiDesc d, float* __restrict__ acc) {
+  __shared__ float red[8];
+  const int t = find_tensor(d, blockIdx.x);
+  const int nb = d.blk0[t + 1] - d.blk0[t], b = blockIdx.x - d.blk0[t];
+  const float* __restrict__ x = d.t[t].grad;
+  const int64_t n = d.t[t].n, n4 = n >> 2;
+  const float4* x4 = reinterpret_cast<const float4*>(x);
+  float s = 0.f;
+  for (int64_t i = b * 256 + threadIdx.x; i < n4; i += (int64_t)nb * 256) {
+    float4 v = __ldg(x4 + i);
+    s = fmaf(v.x, v.x, s);
+    s = fmaf(v.y, v.y, s);
+    s = fmaf(v.z, v.z, s);
+    s = fmaf(v.w, v.w, s);
+  }
+  for (int64_t i = (n4 << 2) + b * 256 + threadIdx.x; i < n; i += (int64_t)nb * 256) s = fmaf(x[i], x[i], s);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float tot = 0.f;
+    for (int i = 0; i < 8; ++i) tot += red[i];
+    atomicAdd(acc, tot);
+  }
+}
+
+// steps[step_index] += 1 for every listed tensor; coef = clip coefficient * optional external gradient scale
+__global__ void k_adam_prep(const __grid_constant__ MultiDesc d, int32_t* __restrict__ steps, const float* __restrict__ sumsq, float max_norm,
+                            const float* __restrict__ grad_scale, float* __restrict__ coef, int write_coef) {
+  int i = threadIdx.x;
+  if (i < d.count) steps[d.t[i].step_index] += 1;
+  if (i == 0 && write_coef) {
+    float c = 1.f;
+    if (sumsq && max_norm > 0.f) c = fminf(1.f, max_norm / (sqrtf(*sumsq) + 1e-6f));  // torch.nn.utils.clip_grad_norm_
+    if (grad_scale) c *= *grad_scale;
+    *coef = c;
+  }
+}
+
+__global__ void __launch_bounds__(256) k_adam_multi(const __grid_constant__ MultiDesc d, float beta1, float beta2, float eps,
+                                                    const int32_t* __restrict__ steps, const float* __restrict__ coef) {
+  __shared__ AdamK sk;
+  const int t = find_tensor(d, blockIdx.x);
+  const AcnAdamTensor& a = d.t[t];
+  if (threadIdx.x == 0) {
+    double step = (double)steps[a.step_index];
+    double bc1 = 1.0 - pow((double)beta1, step), bc2 = 1.0 - pow((double)beta2, step);
+    sk.lr_step = (float)((double)a.lr / bc1);
+    sk.inv_bc2s = (float)(1.0 / sqrt(bc2));
+    sk.beta1 = beta1;
+    sk.beta2 = beta2;
+    sk.eps = eps;
+    sk.wd = a.weight_decay;
+  }
+  __syncthreads();
+  const AdamK k = sk;
+  const float gs = coef ? __ldg(coef) : 1.f;
+  const int nb = d.blk0[t + 1] - d.blk0[t], b = blockIdx.x - d.blk0[t];
+  const int64_t n = a.n, n4 = n >> 2;
+  float4* p4 = reinterpret_cast<float4*>(a.param);
+  const float4* g4 = reinterpret_cast<const float4*>(a.grad);
+  float4* m4 = reinterpret_cast<float4*>(a.exp_avg);
+  float4* v4 = reinterpret_cast<float4*>(a.exp_avg_sq);
+  for (int64_t i = b * 256 + threadIdx.x; i < n4; i += (int64_t)nb * 256) {
+    float4 pa = p4[i], gb = __ldg(g4 + i), mc = m4[i], vd = v4[i];
+    adam_one(pa.x, gb.x, mc.x, vd.x, k, gs);
+    adam_one(pa.y, gb.y, mc.y, vd.y, k, gs);
+    adam_one(pa.z, gb.z, mc.z, vd.z, k, gs);
+    adam_one(pa.w, gb.w, mc.w, vd.w, k, gs);
+    p4[i] = pa;
+    m4[i] = mc;
+    v4[i] = vd;
+  }
+  for (int64_t i = (n4 << 2) + b * 256 + threadIdx.x; i < n; i += (int64_t)nb * 256)
+    adam_one(a.param[i], a.grad[i], a.exp_avg[i], a.exp_avg_sq[i], k, gs);
+}
+
+static int fill_multi(MultiDesc& d, const AcnAdamTensor* tensors, int count, const char* who) {
+  ACN_REQUIRE(tensors && count >= 1 && count <= ACN_ADAM_MAX_TENSORS, "%s: 1..%d tensors per call", who, ACN_ADAM_MAX_TENSORS);
+  int64_t per_wave = (int64_t)num_sms_cached() * 8;
+  int blk = 0;
+  for (int i = 0; i < count; ++i) {
+    d.t[i] = tensors[i];
+    ACN_REQUIRE(tensors[i].grad && tensors[i].n >= 0, "%s: tensor %d has no gradient pointer", who, i);
+    ACN_REQUIRE((((uintptr_t)tensors[i].param | (uintptr_t)tensors[i].grad | (uintptr_t)tensors[i].exp_avg | (uintptr_t)tensors[i].exp_avg_sq) & 15) == 0,
+                "%s: tensor %d is not 16-byte aligned", who, i);
+    int64_t nb = (tensors[i].n / 4 + 1023) / 1024;  // >= 4 float4 per thread before adding blocks
+    if (nb < 1) nb = 1;
+    if (nb > per_wave) nb = per_wave;
+    d.blk0[i] = blk;
+    blk += (int)nb;
+  }
+  for (int i = count; i <= ACN_ADAM_MAX_TENSORS; ++i) d.blk0[i] = blk;
+  d.count = count;
+  return ACN_OK;
+}
+
 }  // namespace acn
 
 using namespace acn;
@@ -103,6 +215,34 @@ int acn_sumsq_accum(const float* x, int64_t n, float* acc, void* stream) {
   ACN_REQUIRE(x && acc && n >= 0, "acn_sumsq_accum: bad arguments");
   if (n == 0) return ACN_OK;
   k_sumsq<<<persistent_grid((n + 255) / 256, 4), 256, 0, as_stream(stream)>>>(x, n, acc);
+  ACN_LAUNCH_CHECK();
+  return ACN_OK;
+}
+
+int acn_sumsq_multi(const AcnAdamTensor* tensors_host, int count, float* acc, void* stream) {
+  ACN_REQUIRE(acc, "acn_sumsq_multi: acc is NULL");
+  MultiDesc d;
+  int rc = fill_multi(d, tensors_host, count, "acn_sumsq_multi");
+  if (rc) return rc;
+  k_sumsq_multi<<<d.blk0[count], 256, 0, as_stream(stream)>>>(d, acc);
+  ACN_LAUNCH_CHECK();
+  return ACN_OK;
+}
+
+int acn_adam_multi(const AcnAdamTensor* tensors_host, int count, float beta1, float beta2, float eps, int32_t* steps_dev,
+                   const float* sumsq_dev, float max_norm, const float* grad_scale_dev, float* coef_dev, int write_coef, void* stream) {
+  ACN_REQUIRE(steps_dev, "acn_adam_multi: steps_dev is NULL");
+  ACN_REQUIRE(!write_coef || coef_dev, "acn_adam_multi: write_coef needs coef_dev");
+  MultiDesc d;
+  int rc = fill_multi(d, tensors_host, count, "acn_adam_multi");
+  if (rc) return rc;
+  for (int i = 0; i < count; ++i)
+    ACN_REQUIRE(tensors_host[i].param && tensors_host[i].exp_avg && tensors_host[i].exp_avg_sq && tensors_host[i].step_index >= 0,
+                "acn_adam_multi: tensor %d is incomplete", i);
+  cudaStream_t st = as_stream(stream);
+  k_adam_prep<<<1, ACN_ADAM_MAX_TENSORS, 0, st>>>(d, steps_dev, sumsq_dev, max_norm, grad_scale_dev, coef_dev, write_coef);
+  ACN_LAUNCH_CHECK();
+  k_adam_multi<<<d.blk0[count], 256, 0, st>>>(d, beta1, beta2, eps, steps_dev, coef_dev);
   ACN_LAUNCH_CHECK();
   return ACN_OK;
 }

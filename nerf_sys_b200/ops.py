@@ -25,7 +25,7 @@ INTERP = {"linear": 0, "smoothstep": 1, "nearest": 2}
 
 # Arithmetic of the fused expert MLPs: "f16tc" = tcgen05 tensor cores, fp16 operands / fp32 accumulate (the
 # precision class of the reference's own GPU path); "fp32" = exact CUDA-core mode used by the tight parity tests.
-_mlp_math = "fp32"
+_mlp_math = "f16tc"
 
 
 def set_mlp_math(mode: str) -> str:
@@ -77,6 +77,10 @@ def kernel_timing(enable: bool):
     global _timing
     _timing = {} if enable else None
     return _timing
+
+
+def kernel_timing_enabled() -> bool:
+    return _timing is not None
 
 
 class _timed:

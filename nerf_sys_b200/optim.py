@@ -11,32 +11,73 @@ from typing import Optional
 
 import torch
 
+import ctypes as C
+
 from . import ops
+from ._lib import ACN_ADAM_MAX_TENSORS, AcnAdamTensor, check, lib
 
 
 class FusedAdam(torch.optim.Optimizer):
+    """torch.optim.Adam over the C ABI's multi-tensor kernels: per step one sum-of-squares launch (clip_grad_norm_),
+    one prep launch (device step counters + clip coefficient) and one Adam launch per 64 tensors.  Nothing in
+    ``step()`` reads device memory from the host, so a whole training step can be captured in a CUDA graph
+    (nerf_sys_b200.engine.GraphedTrainStep).  ``state[p]["step"]`` is refreshed from the device counters by
+    ``state_dict()`` (the checkpoint layout is torch Adam's)."""
+
     def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0, max_grad_norm: Optional[float] = None):
         defaults = dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay)
         super().__init__(params, defaults)
         self.max_grad_norm = max_grad_norm
-        self._scale = None
+        self._steps_dev = None
+        self._index = {}
 
-    @torch.no_grad()
-    def clip_coef(self, max_norm: float) -> torch.Tensor:
-        """Device scalar min(1, max_norm / (||g|| + 1e-6)) over every gradient (torch.nn.utils.clip_grad_norm_)."""
-        dev = None
-        acc = None
+    # ---- device-side bookkeeping -------------------------------------------------------------
+    def _ensure(self, dev):
+        if self._steps_dev is not None and self._steps_dev.device == dev:
+            return
+        plist = [p for g in self.param_groups for p in g["params"]]
+        self._index = {id(p): i for i, p in enumerate(plist)}
+        steps = [int(float(self.state[p]["step"])) if (p in self.state and "step" in self.state[p]) else 0 for p in plist]
+        self._steps_dev = torch.tensor(steps, dtype=torch.int32, device=dev)
+        self._acc = torch.zeros(1, dtype=torch.float32, device=dev)
+        self._coef = torch.ones(1, dtype=torch.float32, device=dev)
+
+    def sync_steps(self):
+        """Copy the device step counters into state[p]['step'] (host sync; checkpoint time only)."""
+        if self._steps_dev is None:
+            return
+        host = self._steps_dev.cpu().tolist()
+        for g in self.param_groups:
+            for p in g["params"]:
+                if p in self.state and len(self.state[p]):
+                    self.state[p]["step"] = torch.tensor(float(host[self._index[id(p)]]), dtype=torch.float32)
+
+    def state_dict(self):
+        self.sync_steps()
+        return super().state_dict()
+
+    def load_state_dict(self, state_dict):
+        super().load_state_dict(state_dict)
+        self._steps_dev = None  # re-seeded from the loaded state on the next step
+
+    def _descs(self):
+        descs = []
         for group in self.param_groups:
+            if tuple(group["betas"]) != tuple(self.param_groups[0]["betas"]) or group["eps"] != self.param_groups[0]["eps"]:
+                raise NotImplementedError("FusedAdam: betas / eps must be shared by all groups")
             for p in group["params"]:
                 if p.grad is None:
                     continue
-                if acc is None:
-                    dev = p.device
-                    acc = torch.zeros(1, device=dev, dtype=torch.float32)
-                ops.sumsq_accum(p.grad, acc)
-        if acc is None:
-            return None
-        return (max_norm / (acc.sqrt() + 1e-6)).clamp_(max=1.0)
+                st = self.state[p]
+                if "exp_avg" not in st:
+                    st["step"] = torch.tensor(0.0, dtype=torch.float32)
+                    st["exp_avg"] = torch.zeros_like(p, memory_format=torch.preserve_format)
+                    st["exp_avg_sq"] = torch.zeros_like(p, memory_format=torch.preserve_format)
+                g = p.grad if p.grad.is_contiguous() else p.grad.contiguous()
+                if not (p.is_cuda and p.dtype == torch.float32 and p.is_contiguous()):
+                    raise RuntimeError("FusedAdam: parameters must be contiguous CUDA fp32 tensors (no CPU path)")
+                descs.append((p, g, st, float(group["lr"]), float(group["weight_decay"])))
+        return descs
 
     @torch.no_grad()
     def step(self, closure=None, grad_scale: Optional[torch.Tensor] = None):
@@ -44,25 +85,39 @@ class FusedAdam(torch.optim.Optimizer):
         if closure is not None:
             with torch.enable_grad():
                 loss = closure()
-        scale = grad_scale
-        if self.max_grad_norm is not None:
-            c = self.clip_coef(self.max_grad_norm)
-            if c is not None:
-                scale = c if scale is None else c * scale
-        for group in self.param_groups:
-            b1, b2 = group["betas"]
-            for p in group["params"]:
-                if p.grad is None:
-                    continue
-                st = self.state[p]
-                if len(st) == 0:
-                    st["step"] = torch.tensor(0.0, dtype=torch.float32)
-                    st["exp_avg"] = torch.zeros_like(p, memory_format=torch.preserve_format)
-                    st["exp_avg_sq"] = torch.zeros_like(p, memory_format=torch.preserve_format)
-                st["step"] += 1
-                g = p.grad if p.grad.is_contiguous() else p.grad.contiguous()
-                ops.adam_step(p.data, g, st["exp_avg"], st["exp_avg_sq"], float(group["lr"]), float(b1), float(b2), float(group["eps"]),
-                              float(group["weight_decay"]), int(st["step"].item()), scale)
+        descs = self._descs()
+        if not descs:
+            return loss
+        dev = descs[0][0].device
+        self._ensure(dev)
+        L = lib()
+        stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        b1, b2 = self.param_groups[0]["betas"]
+        eps = float(self.param_groups[0]["eps"])
+        chunks = []
+        for c0 in range(0, len(descs), ACN_ADAM_MAX_TENSORS):
+            part = descs[c0:c0 + ACN_ADAM_MAX_TENSORS]
+            arr = (AcnAdamTensor * len(part))()
+            for i, (p, g, st, lr, wd) in enumerate(part):
+                arr[i].param, arr[i].grad = p.data_ptr(), g.data_ptr()
+                arr[i].exp_avg, arr[i].exp_avg_sq = st["exp_avg"].data_ptr(), st["exp_avg_sq"].data_ptr()
+                arr[i].n, arr[i].lr, arr[i].weight_decay, arr[i].step_index = p.numel(), lr, wd, self._index[id(p)]
+            chunks.append((arr, len(part)))
+        clip = self.max_grad_norm is not None
+        with torch.cuda.device(dev):
+            if clip:
+                self._acc.zero_()
+                with ops._timed("sumsq"):
+                    for arr, n in chunks:
+                        check(L.acn_sumsq_multi(arr, n, self._acc.data_ptr(), stream), "acn_sumsq_multi")
+                ops._count(len(chunks) + 1)
+            with ops._timed("adam"):
+                for ci, (arr, n) in enumerate(chunks):
+                    check(L.acn_adam_multi(arr, n, float(b1), float(b2), eps, self._steps_dev.data_ptr(),
+                                           self._acc.data_ptr() if clip else None, float(self.max_grad_norm or 0.0),
+                                           grad_scale.data_ptr() if grad_scale is not None else None, self._coef.data_ptr(),
+                                           1 if ci == 0 else 0, stream), "acn_adam_multi")
+            ops._count(2 * len(chunks))
         return loss
 
 

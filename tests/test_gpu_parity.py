@@ -56,7 +56,9 @@ def table_grad_close(a, b, tol, what="", outlier_frac=2e-4):
 def _device():
     from nerf_sys_b200 import ops
     ops.device_ok()
+    prev = ops.set_mlp_math("fp32")  # this module pins the exact fp32 mode; tests/test_gpu_tc.py covers the tensor-core mode
     yield
+    ops.set_mlp_math(prev)
 
 
 # ----------------------------------------------------------------------------- a1-a3
