@@ -98,6 +98,10 @@ int wgrad_launch(const WgradJob& job, const int32_t* seg_dev, int E, int64_t M_s
   ACN_REQUIRE(job.OUT >= 1 && job.OUT <= WG_MAXF && job.IN >= 0 && job.IN <= WG_MAXF, "wgrad: layer shape out of range");
   ACN_REQUIRE(E >= 1 && E <= ACN_MAX_EXPERTS, "wgrad: bad expert count");
   int gx = wg_gx(E);
+  if (!seg_dev) {  // single segment of known length: no more CTAs than 8-tile work items (the reduce walks gx partials serially)
+    int64_t want = (M_single + WG_T * 8 - 1) / (WG_T * 8);
+    if (want < gx) gx = (int)(want < 1 ? 1 : want);
+  }
   dim3 grid(gx, E);
   k_wgrad_partial<<<grid, 256, 0, st>>>(job.dzT, job.xT ? job.xT : job.dzT, job.OUT, job.xT ? job.IN : 0, job.ld, seg_dev, M_single, partial);
   ACN_LAUNCH_CHECK();

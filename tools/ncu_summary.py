@@ -16,8 +16,8 @@ import subprocess
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 GROUP = {"k_ngp_hash_fwd": "hash_fwd", "k_ngp_hash_bwd": "hash_bwd", "k_ngp_mlp_fwd": "mlp_fwd", "k_ngp_mlp_bwd": "mlp_bwd",
-         "k_wgrad_partial": "mlp_bwd", "k_wgrad_reduce": "mlp_bwd", "k_ngp_tc_fwd": "mlp_fwd", "k_ngp_tc_bwd": "mlp_bwd",
-         "k_composite_fwd": "composite_fwd", "k_composite_bwd": "composite_bwd", "k_adam": "adam"}
+         "k_wgrad_partial": "mlp_bwd", "k_wgrad_reduce": "mlp_bwd", "k_ngp_mlp_fwd_tc": "mlp_fwd", "k_ngp_mlp_bwd_tc": "mlp_bwd",
+         "k_composite_fwd": "composite_fwd", "k_composite_bwd": "composite_bwd", "k_adam": "adam", "k_adam_multi": "adam", "k_sumsq_multi": "sumsq"}
 METRICS = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum", "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed",
            "lts__t_bytes.sum", "lts__t_sector_hit_rate.pct", "l1tex__t_sector_hit_rate.pct", "sm__throughput.avg.pct_of_peak_sustained_elapsed",
            "sm__warps_active.avg.pct_of_peak_sustained_active", "launch__registers_per_thread", "launch__grid_size", "launch__block_size",
@@ -100,10 +100,12 @@ def main():
         traffic = collections.defaultdict(list)
         for k in ks:
             g = GROUP.get(k["kernel"].split("<")[0])
+            if g == "mlp_bwd" and "wgrad" in k["kernel"]:
+                continue
             if g and "dram__bytes_read.sum" in k:
                 traffic[g].append(to_bytes(k["dram__bytes_read.sum"], k["dram__bytes_read.sum__unit"])
                                   + to_bytes(k["dram__bytes_write.sum"], k["dram__bytes_write.sum__unit"]))
-        tj = {g: (sum(v) if g == "mlp_bwd" else sum(v) / len(v)) for g, v in traffic.items()}
+        tj = {g: sum(v) / len(v) for g, v in traffic.items()}
         json.dump(tj, open(os.path.join(prof, "traffic.json"), "w"), indent=1)
         for k in ks:
             print(k["kernel"][:40], k.get("gpu__time_duration.sum"), k.get("gpu__time_duration.sum__unit"), "dram MB",
