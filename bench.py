@@ -395,7 +395,7 @@ def main():
         model.train()
 
     cpu = None
-    if rank == 0 and not args.no_cpu_baseline:
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
         n = 2048
         rps, sec = cpu_train_rays_per_s(n, 6, 1)
         cpu = {"value": rps, "unit": "rays/s", "cores": os.cpu_count() or 1, "kind": "port",
@@ -419,7 +419,13 @@ def main():
             "gpu_launches": launches, "roofline": roofline, "kernels": kern, "render": render, "cpu_baseline": cpu,
             "final_loss": final_loss}))
     if world > 1:
-        torch.distributed.destroy_process_group()
+        # Leave without tearing NCCL down: the captured graph still references the communicator's kernels and
+        # destroy_process_group() was seen to hang behind it.  All ranks meet, flush, and exit 0.
+        sys.stdout.flush()
+        sys.stderr.flush()
+        torch.cuda.synchronize()
+        torch.distributed.barrier()
+        os._exit(0)
 
 
 if __name__ == "__main__":

@@ -406,7 +406,7 @@ __global__ void __launch_bounds__(FWD_THREADS, 1)
 // =============================================================================================
 // backward (forward recompute + dgrad chain + TMEM-resident weight gradients)
 // =============================================================================================
-constexpr int BWD_THREADS = 256;  // thread = (row r, column half hf): 32 of the 64 columns of every epilogue
+constexpr int BWD_THREADS = 512;  // thread = (row r, column quarter q): 16 of the 64 columns of every epilogue (4 warps per scheduler)
 constexpr uint32_t B_ENC = W_BYTES;            // [1 | enc32 | 0]   6 chunks
 constexpr uint32_t B_H0 = B_ENC + 6 * CH;      // [1 | h0 64 | 0]  10 chunks
 constexpr uint32_t B_H1 = B_H0 + 10 * CH;
@@ -450,7 +450,7 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
   __shared__ uint32_t s_tmem;
   __shared__ int s_seg[ACN_MAX_EXPERTS + 1];
   __shared__ CtaPart s_part;
-  const int tid = threadIdx.x, hf = tid >> 7;
+  const int tid = threadIdx.x, q = tid >> 7;  // q: which 16 of the 64 columns this thread owns in every epilogue
   const uint32_t r = tid & 127;
   if (tid <= tab.E) s_seg[tid] = seg ? seg[tid] : (tid == 0 ? 0 : round_up128(M_ident));
   __syncthreads();
@@ -466,23 +466,25 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
   const CtaPart part = s_part;
   const uint32_t sb = smem_u32(smem);
   if (part.e >= 0) load_weights_tc(smem, tab.ex[part.e], tid, BWD_THREADS);
-  if (hf == 0) {
+  if (q == 0) {
     store_ones_chunk(sb + B_ENC, r, 0);
     store_ones_chunk(sb + B_H0, r, 0);
     store_ones_chunk(sb + B_H1, r, 0);
+  } else if (q == 1) {
     store_ones_chunk(sb + B_CIN, r, 0);
     store_ones_chunk(sb + B_C0, r, 0);
     store_ones_chunk(sb + B_C1, r, 0);
-  } else {
+  } else if (q == 2) {
     store_zero_chunk(sb + B_ENC, r, 5);
     store_zero_chunk(sb + B_H0, r, 9);
     store_zero_chunk(sb + B_H1, r, 9);
+  } else {
     store_zero_chunk(sb + B_CIN, r, 5);
     store_zero_chunk(sb + B_C0, r, 9);
     store_zero_chunk(sb + B_C1, r, 9);
   }
   // gradient tiles start finite (rows 16.. of the 16-wide stages are read by the M=64 wgrad MMAs and ignored)
-  for (int c = hf; c < 8; c += 2) {
+  for (int c = q; c < 8; c += 4) {
     store_zero_chunk(sb + B_GA, r, c);
     store_zero_chunk(sb + B_GB, r, c);
   }
@@ -492,8 +494,8 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
   fence_after();
   const uint32_t tbase = s_tmem;
   const uint32_t tD = tbase + T_D;
-  const uint32_t trow = tD + ((uint32_t)((tid >> 5) & 3) << 21) + 32 * hf;  // this thread's 32 columns of D
-  const uint32_t trow0 = tD + ((uint32_t)((tid >> 5) & 3) << 21);          // column 0 of this thread's row
+  const uint32_t trow0 = tD + ((uint32_t)((tid >> 5) & 3) << 21);  // column 0 of this thread's row
+  const uint32_t trow = trow0 + 16 * q;                            // this thread's 16 columns of D
   const uint32_t bar = smem_u32(&s_bar);
   uint32_t phase = 0;
   uint32_t acc = 0;  // 0 on the CTA's first tile: the weight-gradient accumulators are overwritten
@@ -505,19 +507,23 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
   }
   const float inv_s = 1.f / gscale;
 
-#define TC_STEP(ISSUE)      \
-  do {                      \
-    fence_before();         \
-    fence_async_smem();     \
-    __syncthreads();        \
-    if (tid == 0) {         \
-      fence_after();        \
-      ISSUE;                \
-      commit(bar);          \
-    }                       \
-    mbar_wait(bar, phase);  \
-    phase ^= 1;             \
-    fence_after();          \
+  // One chain step: publish this thread's smem writes, one thread issues ISSUE and commits, everyone waits for the
+  // accumulator.  LATE (weight-gradient MMAs) is issued after the commit: it runs on the tensor pipe while the
+  // epilogue of this step executes, and is covered by the NEXT step's commit before its operands are overwritten.
+#define TC_STEP(ISSUE, LATE) \
+  do {                       \
+    fence_before();          \
+    fence_async_smem();      \
+    __syncthreads();         \
+    if (tid == 0) {          \
+      fence_after();         \
+      ISSUE;                 \
+      commit(bar);           \
+      LATE;                  \
+    }                        \
+    mbar_wait(bar, phase);   \
+    phase ^= 1;              \
+    fence_after();           \
   } while (0)
 
   if (part.e >= 0) {
@@ -526,65 +532,63 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
       const bool in_range = m < M;
       const int64_t p = in_range ? (pair_point ? (int64_t)pair_point[m] : m) : -1;
       const int64_t mm = in_range ? m : 0;
-      uint32_t m0, m1, m3, m4;  // ReLU masks of this thread's 32 columns of h0, h1, c0, c1
-      float v[32];
+      uint32_t m0, m1, m3, m4;  // ReLU masks of this thread's 16 columns of h0, h1, c0, c1
+      float v[16];
       // ---- forward recompute ----
       {
-        float x[16];
+        float x[8];
 #pragma unroll
-        for (int i = 0; i < 16; ++i) x[i] = in_range ? __ldg(enc + (int64_t)(16 * hf + i) * ld + mm) : 0.f;
+        for (int i = 0; i < 8; ++i) x[i] = in_range ? __ldg(enc + (int64_t)(8 * q + i) * ld + mm) : 0.f;
 #pragma unroll
-        for (int i = 0; i < 16; ++i) x[i] = fminf(fmaxf(x[i], -F16_MAX), F16_MAX);
-        store_h<16>(sb + B_ENC, r, 1 + 2 * hf, x);
+        for (int i = 0; i < 8; ++i) x[i] = fminf(fmaxf(x[i], -F16_MAX), F16_MAX);
+        store_h<8>(sb + B_ENC, r, 1 + q, x);
       }
-      TC_STEP((issue_fwd<32, 64>(tD, sb + B_ENC, sb + OW0)));
-      tmem_ld32(trow, v);
+      TC_STEP((issue_fwd<32, 64>(tD, sb + B_ENC, sb + OW0)), (void)0);
+      tmem_ld16(trow, v);
       tmem_ld_wait();
-      m0 = relu_mask<32>(v);
-      store_h<32>(sb + B_H0, r, 1 + 4 * hf, v);
-      TC_STEP((issue_fwd<64, 64>(tD, sb + B_H0, sb + OW1)));
-      tmem_ld32(trow, v);
+      m0 = relu_mask<16>(v);
+      store_h<16>(sb + B_H0, r, 1 + 2 * q, v);
+      TC_STEP((issue_fwd<64, 64>(tD, sb + B_H0, sb + OW1)), (void)0);
+      tmem_ld16(trow, v);
       tmem_ld_wait();
-      m1 = relu_mask<32>(v);
-      store_h<32>(sb + B_H1, r, 1 + 4 * hf, v);
-      TC_STEP((issue_fwd<64, 16>(tD, sb + B_H1, sb + OWH)));
+      m1 = relu_mask<16>(v);
+      store_h<16>(sb + B_H1, r, 1 + 2 * q, v);
+      TC_STEP((issue_fwd<64, 16>(tD, sb + B_H1, sb + OWH)), (void)0);
       float sigma = 0.f;
-      {
-        float sh[16], c[16];
+      if (q == 0) {  // cin[0..15] = geo 0..14, sh 0
+        tmem_ld16(trow0, v);
+        tmem_ld_wait();
+        sigma = trunc_exp_f(v[15]);
+#pragma unroll
+        for (int i = 0; i < 15; ++i) v[i] = fminf(fmaxf(v[i], -F16_MAX), F16_MAX);
+        v[15] = 0.28209479177387814f;
+        store_h<16>(sb + B_CIN, r, 1, v);
+      } else if (q == 1) {  // cin[16..31] = sh 1..15, 0
+        float sh[16];
         dir_sh16(src, p, sh);
-        if (hf == 0) {
-          float h[16];
-          tmem_ld16(trow0, h);
-          tmem_ld_wait();
-          sigma = trunc_exp_f(h[15]);
 #pragma unroll
-          for (int i = 0; i < 15; ++i) c[i] = fminf(fmaxf(h[i], -F16_MAX), F16_MAX);
-          c[15] = sh[0];
-        } else {
-#pragma unroll
-          for (int i = 0; i < 15; ++i) c[i] = sh[1 + i];
-          c[15] = 0.f;
-        }
-        store_h<16>(sb + B_CIN, r, 1 + 2 * hf, c);
+        for (int i = 0; i < 15; ++i) v[i] = sh[1 + i];
+        v[15] = 0.f;
+        store_h<16>(sb + B_CIN, r, 3, v);
       }
-      TC_STEP((issue_fwd<32, 64>(tD, sb + B_CIN, sb + OW3)));
-      tmem_ld32(trow, v);
+      TC_STEP((issue_fwd<32, 64>(tD, sb + B_CIN, sb + OW3)), (void)0);
+      tmem_ld16(trow, v);
       tmem_ld_wait();
-      m3 = relu_mask<32>(v);
-      store_h<32>(sb + B_C0, r, 1 + 4 * hf, v);
-      TC_STEP((issue_fwd<64, 64>(tD, sb + B_C0, sb + OW4)));
-      tmem_ld32(trow, v);
+      m3 = relu_mask<16>(v);
+      store_h<16>(sb + B_C0, r, 1 + 2 * q, v);
+      TC_STEP((issue_fwd<64, 64>(tD, sb + B_C0, sb + OW4)), (void)0);
+      tmem_ld16(trow, v);
       tmem_ld_wait();
-      m4 = relu_mask<32>(v);
-      store_h<32>(sb + B_C1, r, 1 + 4 * hf, v);
-      TC_STEP((issue_fwd<64, 16>(tD, sb + B_C1, sb + OW5)));
+      m4 = relu_mask<16>(v);
+      store_h<16>(sb + B_C1, r, 1 + 2 * q, v);
+      TC_STEP((issue_fwd<64, 16>(tD, sb + B_C1, sb + OW5)), (void)0);
       // ---- output gradients ----
       float dsraw = 0.f;
-      {
+      if (q < 2) {
         float g[8];
 #pragma unroll
         for (int i = 0; i < 8; ++i) g[i] = 0.f;
-        if (hf == 0) {
+        if (q == 0) {
           float o8[8];
           tmem_ld8(trow0, o8);
           tmem_ld_wait();
@@ -601,49 +605,49 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
             dsraw = gscale * dy.w * sigma;  // trunc_exp backward: g * exp(clamped x)  (trunc_exp.py:44-57)
           }
         }
-        store_g<8>(sb + B_GA, r, hf, g);  // chunk 0 = dz5 (3 of 8), chunk 1 = 0
+        store_g<8>(sb + B_GA, r, q, g);  // chunk 0 = dz5 (3 of 8), chunk 1 = 0
       }
-      // ---- dgrad chain; every step also accumulates the weight gradient of the layer just left ----
-      TC_STEP((issue_dgrad<16, 64, 16>(tD, sb + B_GA, sb + OW5), issue_wgrad<64>(tbase + T_A5, sb + B_GA, sb + B_C1, acc)));
-      tmem_ld32(trow, v);
+      // ---- dgrad chain; the weight gradient of the layer just left is issued behind the commit ----
+      TC_STEP((issue_dgrad<16, 64, 16>(tD, sb + B_GA, sb + OW5)), (issue_wgrad<64>(tbase + T_A5, sb + B_GA, sb + B_C1, acc)));
+      tmem_ld16(trow, v);
       tmem_ld_wait();
 #pragma unroll
-      for (int i = 0; i < 32; ++i) v[i] = (m4 >> i & 1u) ? v[i] : 0.f;
-      store_g<32>(sb + B_GB, r, 4 * hf, v);
-      TC_STEP((issue_dgrad<64, 64, 64>(tD, sb + B_GB, sb + OW4), issue_wgrad<64>(tbase + T_A4, sb + B_GB, sb + B_C0, acc)));
-      tmem_ld32(trow, v);
+      for (int i = 0; i < 16; ++i) v[i] = (m4 >> i & 1u) ? v[i] : 0.f;
+      store_g<16>(sb + B_GB, r, 2 * q, v);
+      TC_STEP((issue_dgrad<64, 64, 64>(tD, sb + B_GB, sb + OW4)), (issue_wgrad<64>(tbase + T_A4, sb + B_GB, sb + B_C0, acc)));
+      tmem_ld16(trow, v);
       tmem_ld_wait();
 #pragma unroll
-      for (int i = 0; i < 32; ++i) v[i] = (m3 >> i & 1u) ? v[i] : 0.f;
-      store_g<32>(sb + B_GA, r, 4 * hf, v);
-      TC_STEP((issue_dgrad<64, 32, 64>(tD, sb + B_GA, sb + OW3), issue_wgrad<32>(tbase + T_A3, sb + B_GA, sb + B_CIN, acc)));
-      if (hf == 0) {  // head gradient [d geo 0..14 | d sigma_raw] -> chunks 0, 1
-        float g[16];
-        tmem_ld16(trow0, g);
+      for (int i = 0; i < 16; ++i) v[i] = (m3 >> i & 1u) ? v[i] : 0.f;
+      store_g<16>(sb + B_GA, r, 2 * q, v);
+      TC_STEP((issue_dgrad<64, 32, 64>(tD, sb + B_GA, sb + OW3)), (issue_wgrad<32>(tbase + T_A3, sb + B_GA, sb + B_CIN, acc)));
+      if (q == 0) {  // head gradient [d geo 0..14 | d sigma_raw] -> chunks 0, 1
+        tmem_ld16(trow0, v);
         tmem_ld_wait();
-        g[15] = dsraw;
-        store_g<16>(sb + B_GB, r, 0, g);
+        v[15] = dsraw;
+        store_g<16>(sb + B_GB, r, 0, v);
       }
-      TC_STEP((issue_dgrad<16, 64, 16>(tD, sb + B_GB, sb + OWH), issue_wgrad<64>(tbase + T_AH, sb + B_GB, sb + B_H1, acc)));
-      tmem_ld32(trow, v);
+      TC_STEP((issue_dgrad<16, 64, 16>(tD, sb + B_GB, sb + OWH)), (issue_wgrad<64>(tbase + T_AH, sb + B_GB, sb + B_H1, acc)));
+      tmem_ld16(trow, v);
       tmem_ld_wait();
 #pragma unroll
-      for (int i = 0; i < 32; ++i) v[i] = (m1 >> i & 1u) ? v[i] : 0.f;
-      store_g<32>(sb + B_GA, r, 4 * hf, v);
-      TC_STEP((issue_dgrad<64, 64, 64>(tD, sb + B_GA, sb + OW1), issue_wgrad<64>(tbase + T_A1, sb + B_GA, sb + B_H0, acc)));
-      tmem_ld32(trow, v);
+      for (int i = 0; i < 16; ++i) v[i] = (m1 >> i & 1u) ? v[i] : 0.f;
+      store_g<16>(sb + B_GA, r, 2 * q, v);
+      TC_STEP((issue_dgrad<64, 64, 64>(tD, sb + B_GA, sb + OW1)), (issue_wgrad<64>(tbase + T_A1, sb + B_GA, sb + B_H0, acc)));
+      tmem_ld16(trow, v);
       tmem_ld_wait();
 #pragma unroll
-      for (int i = 0; i < 32; ++i) v[i] = (m0 >> i & 1u) ? v[i] : 0.f;
-      store_g<32>(sb + B_GB, r, 4 * hf, v);
-      TC_STEP((issue_dgrad<64, 32, 64>(tD, sb + B_GB, sb + OW0), issue_wgrad<32>(tbase + T_A0, sb + B_GB, sb + B_ENC, acc)));
-      {
-        float g[16];
-        tmem_ld16(trow0 + 16 * hf, g);
+      for (int i = 0; i < 16; ++i) v[i] = (m0 >> i & 1u) ? v[i] : 0.f;
+      store_g<16>(sb + B_GB, r, 2 * q, v);
+      // last step of the tile: its weight-gradient MMAs go BEFORE the commit, because the next tile's first
+      // epilogue overwrites the encoding buffer they read
+      TC_STEP((issue_dgrad<64, 32, 64>(tD, sb + B_GB, sb + OW0), issue_wgrad<32>(tbase + T_A0, sb + B_GB, sb + B_ENC, acc)), (void)0);
+      if (q < 2) {
+        tmem_ld16(trow0 + 16 * q, v);
         tmem_ld_wait();
         if (m < ld) {
 #pragma unroll
-          for (int i = 0; i < 16; ++i) d_enc[(int64_t)(16 * hf + i) * ld + m] = g[i] * inv_s;
+          for (int i = 0; i < 16; ++i) d_enc[(int64_t)(16 * q + i) * ld + m] = v[i] * inv_s;
         }
       }
       acc = 1;

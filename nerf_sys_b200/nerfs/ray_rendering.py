@@ -94,20 +94,29 @@ def render_rays(model, rays, *args, **kwargs):
 @torch.no_grad()
 def render_image(model, *, H: int, W: int, fx: float, fy: float, cx: float, cy: float, c2w: Tensor, scene_box, params=None,
                  active_module: Optional[int] = None, ray_samples: int = 64, chunk_points: int = 1 << 16,
-                 bg_color_default: str = "white", center_pixels: bool = True, use_amp: bool = False, rows_per_chunk: Optional[int] = None):
-    """Full frame: rays are generated on the device (fused a1+a2) and rendered in row blocks."""
+                 bg_color_default: str = "white", center_pixels: bool = True, use_amp: bool = False, rows_per_chunk: Optional[int] = None,
+                 row_range: Optional[Tuple[int, int]] = None):
+    """Full frame: rays are generated on the device (fused a1+a2) and rendered in row blocks.
+    ``row_range=(r0, r1)`` renders only those image rows (the ray-sharded multi-GPU render,
+    nerf_sys_b200.parallel.render_image_sharded) and returns rgb ((r1-r0)*W, 3), depth, acc for them."""
     device = next(model.parameters()).device
     aabb = None if scene_box is None else scene_box.aabb
     if rows_per_chunk is None:
         rows_per_chunk = max(1, min(H, (1 << 22) // max(1, W * ray_samples)))  # ~4M sample points per block
-    rgb = torch.empty(H * W, 3, device=device)
-    depth = torch.empty(H * W, device=device)
-    acc = torch.empty(H * W, device=device)
-    for r0 in range(0, H, rows_per_chunk):
-        rows = min(rows_per_chunk, H - r0)
+    R0, R1 = (0, H) if row_range is None else (int(row_range[0]), int(row_range[1]))
+    if not (0 <= R0 <= R1 <= H):
+        raise ValueError(f"row_range {row_range} outside [0, {H}]")
+    n_rows = R1 - R0
+    rgb = torch.empty(n_rows * W, 3, device=device)
+    depth = torch.empty(n_rows * W, device=device)
+    acc = torch.empty(n_rows * W, device=device)
+    for r0 in range(R0, R1, rows_per_chunk):
+        rows = min(rows_per_chunk, R1 - r0)
         rays = ops.raygen(H, W, fx, fy, cx, cy, center_pixels, c2w, aabb, device, row0=r0, rows=rows)
         c, d, _, a = render_rays(model, rays, ray_samples=ray_samples, params=params, active_module=active_module,
                                  bg_color_default=bg_color_default, chunk=chunk_points)
-        sl = slice(r0 * W, (r0 + rows) * W)
+        sl = slice((r0 - R0) * W, (r0 - R0 + rows) * W)
         rgb[sl], depth[sl], acc[sl] = c, d, a
+    if row_range is not None:
+        return rgb.clamp_(0, 1), depth, acc
     return rgb.view(H, W, 3).clamp_(0, 1), depth.view(-1), acc.view(-1)

@@ -1,0 +1,226 @@
+"""Single-node multi-GPU partitioning of the hot path; one process per GPU, torch.distributed
+for the plumbing (NCCL over NVLink on the box, gloo in the CPU tests of the host logic).
+
+The reference is single-GPU; the natural shards of its path are
+
+* render (config 5): image ROWS are split across ranks, every expert is replicated, no collective on the data
+  path, one gather of the finished tiles (`render_image_sharded`);
+* meta-training (config 2/3 with ``active_module``): EXPERTS (regions) are split across ranks, tasks never cross
+  experts (pipelines/offline_stage/meta_train_step.py:60-96); the only shared parameters are the 643 floats of
+  the background head (`allreduce_shared_grads`);
+* full-container training / adaptation (config 3/4, soft routing): rays are split across ranks AND experts are
+  sharded, so every routed sample travels to the rank that owns its expert and its [rgb, sigma] travels back:
+  one all-to-all per direction per step (`expert_parallel_apply`), the reverse pair in the backward pass.
+
+Everything here is index bookkeeping around collectives; the arithmetic stays in the CUDA library.
+"""
+from __future__ import annotations
+
+from typing import Callable, List, Optional, Sequence, Tuple
+
+import torch
+import torch.distributed as dist
+
+Tensor = torch.Tensor
+
+
+# ---------------------------------------------------------------------------------------------
+# partitions
+# ---------------------------------------------------------------------------------------------
+def shard_range(n: int, world: int, rank: int) -> Tuple[int, int]:
+    """Contiguous block [lo, hi) of ``n`` items for ``rank``; the first n % world ranks get one extra."""
+    if not (0 <= rank < world):
+        raise ValueError(f"rank {rank} outside world of {world}")
+    base, rem = divmod(n, world)
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+def expert_owner(K: int, world: int) -> List[int]:
+    """owner[e] = rank holding expert e: contiguous blocks (experts of one rank are neighbours on the grid)."""
+    owner = [0] * K
+    for r in range(world):
+        lo, hi = shard_range(K, world, r)
+        for e in range(lo, hi):
+            owner[e] = r
+    return owner
+
+
+def _world(group) -> Tuple[int, int]:
+    if not dist.is_available() or not dist.is_initialized():
+        return 1, 0
+    return dist.get_world_size(group), dist.get_rank(group)
+
+
+# ---------------------------------------------------------------------------------------------
+# shared parameters
+# ---------------------------------------------------------------------------------------------
+def allreduce_shared_grads(params: Sequence[Tensor], group=None, average: bool = True) -> None:
+    """One flat all-reduce over the gradients of replicated parameters (the background head: 643 floats)."""
+    world, _ = _world(group)
+    if world == 1:
+        return
+    gs = [p.grad for p in params if p.grad is not None]
+    if not gs:
+        return
+    flat = torch.cat([g.reshape(-1) for g in gs])
+    dist.all_reduce(flat, group=group)
+    if average:
+        flat /= world
+    o = 0
+    for g in gs:
+        g.copy_(flat[o:o + g.numel()].view_as(g))
+        o += g.numel()
+
+
+# ---------------------------------------------------------------------------------------------
+# ray-sharded full-frame render
+# ---------------------------------------------------------------------------------------------
+def render_image_sharded(render_rows: Callable[[int, int], Tuple[Tensor, Tensor, Tensor]], H: int, W: int, group=None,
+                         gather: bool = True):
+    """``render_rows(r0, r1)`` renders image rows [r0, r1) on this rank and returns (rgb (rows*W,3), depth (rows*W,),
+    acc (rows*W,)).  Rows are split in contiguous blocks; with ``gather`` every rank returns the full frame
+    (rgb (H,W,3), depth (H*W,), acc (H*W,)), otherwise its own block and its row range."""
+    world, rank = _world(group)
+    r0, r1 = shard_range(H, world, rank)
+    rgb, depth, acc = render_rows(r0, r1)
+    if world == 1:
+        return rgb.view(H, W, 3), depth.view(-1), acc.view(-1)
+    if not gather:
+        return (rgb, depth, acc), (r0, r1)
+    rows_max = (H + world - 1) // world
+    tile = torch.zeros(rows_max * W, 5, device=rgb.device, dtype=rgb.dtype)  # one message: rgb | depth | acc
+    n = (r1 - r0) * W
+    tile[:n, 0:3], tile[:n, 3], tile[:n, 4] = rgb.view(-1, 3), depth.view(-1), acc.view(-1)
+    tiles = [torch.empty_like(tile) for _ in range(world)]
+    dist.all_gather(tiles, tile, group=group)
+    parts = []
+    for r in range(world):
+        a, b = shard_range(H, world, r)
+        parts.append(tiles[r][:(b - a) * W])
+    full = torch.cat(parts, 0)
+    return full[:, 0:3].reshape(H, W, 3).contiguous(), full[:, 3].contiguous(), full[:, 4].contiguous()
+
+
+# ---------------------------------------------------------------------------------------------
+# expert-parallel dispatch / combine
+# ---------------------------------------------------------------------------------------------
+class _AllToAll(torch.autograd.Function):
+    """all_to_all_single with per-peer row counts; the backward pass is the same exchange with the counts swapped."""
+
+    @staticmethod
+    def forward(ctx, x: Tensor, send: List[int], recv: List[int], group):
+        ctx.send, ctx.recv, ctx.group = send, recv, group
+        out = x.new_empty((sum(recv),) + tuple(x.shape[1:]))
+        dist.all_to_all_single(out, x.contiguous(), output_split_sizes=recv, input_split_sizes=send, group=group)
+        return out
+
+    @staticmethod
+    def backward(ctx, g: Tensor):
+        out = g.new_empty((sum(ctx.send),) + tuple(g.shape[1:]))
+        dist.all_to_all_single(out, g.contiguous(), output_split_sizes=ctx.send, input_split_sizes=ctx.recv, group=ctx.group)
+        return out, None, None, None
+
+
+def exchange_counts(counts: Sequence[int], group=None) -> List[List[int]]:
+    """counts[e] = routed samples this rank holds for expert e  ->  table[s][e] of every rank s (host ints)."""
+    world, rank = _world(group)
+    if world == 1:
+        return [list(map(int, counts))]
+    table: List[Optional[List[int]]] = [None] * world
+    dist.all_gather_object(table, list(map(int, counts)), group=group)
+    return table  # type: ignore[return-value]
+
+
+def expert_parallel_apply(x: Tensor, sel_point: Tensor, sel_weight: Tensor, counts: Sequence[int], P: int,
+                          expert_fn: Callable[[Tensor, List[int], List[Tensor]], Tensor], group=None, out_dim: int = 4) -> Tensor:
+    """Soft-routed container forward with experts sharded over ranks (meta_container.py:305-321 semantics).
+
+    x          (P, D) this rank's sample points (xyz + direction)
+    sel_point  (M,) int64 point index of every routed (point, expert) pair, GROUPED BY EXPERT 0..K-1
+    sel_weight (M,) routing weight of the pair
+    counts     K host ints: pairs per expert (sum = M)
+    expert_fn(rows (R, D), local_experts, index) -> (R, out_dim): evaluates this rank's experts; ``index[j]`` holds the
+               rows of ``rows`` that belong to ``local_experts[j]`` (every row belongs to exactly one).
+    Returns out (P, out_dim) = sum over the pairs of a point of weight * expert(point), differentiable w.r.t. the
+    parameters expert_fn uses (gradients reach the owning rank through the reversed all-to-all)."""
+    world, rank = _world(group)
+    K = len(counts)
+    owner = expert_owner(K, world)
+    mine = [e for e in range(K) if owner[e] == rank]
+    if sel_point.numel() != sum(counts):
+        raise ValueError(f"sel_point has {sel_point.numel()} pairs but counts sum to {sum(counts)}")
+    rows = x.index_select(0, sel_point)
+    if world == 1:
+        bounds = [0]
+        for c in counts:
+            bounds.append(bounds[-1] + int(c))
+        index = [torch.arange(bounds[e], bounds[e + 1], device=x.device) for e in range(K)]
+        y = expert_fn(rows, list(range(K)), index)
+    else:
+        table = exchange_counts(counts, group)
+        send = [sum(int(counts[e]) for e in range(K) if owner[e] == d) for d in range(world)]
+        recv = [sum(table[s][e] for e in mine) for s in range(world)]
+        got = _AllToAll.apply(rows, send, recv, group)
+        # received layout: [source 0: expert mine[0], mine[1], ... | source 1: ...]; regroup by local expert
+        index, off = [[] for _ in mine], 0
+        for s in range(world):
+            for j, e in enumerate(mine):
+                n = table[s][e]
+                if n:
+                    index[j].append(torch.arange(off, off + n, device=x.device))
+                off += n
+        index = [torch.cat(ix) if ix else torch.empty(0, dtype=torch.long, device=x.device) for ix in index]
+        y_owner = expert_fn(got, mine, index)
+        if torch.is_grad_enabled() and not y_owner.requires_grad:
+            # every rank must take part in the backward exchange even if its own experts are frozen (config 4)
+            y_owner = y_owner + torch.zeros(1, device=x.device, dtype=y_owner.dtype, requires_grad=True)
+        y = _AllToAll.apply(y_owner, recv, send, group)
+    out = x.new_zeros(P, out_dim)
+    return out.index_add(0, sel_point, y * sel_weight.unsqueeze(1))
+
+
+def container_evaluate_ep(model, pts, params=None, group=None) -> Tensor:
+    """MetaContainer.forward over a point set with the experts sharded across ``group`` (block placement,
+    `expert_owner`): route on this rank, ship every routed sample to its expert's owner, evaluate there with the
+    fused kernels, ship [rgb, sigma] back and blend with the routing weights.  Every rank holds the full container
+    (same state_dict); only the owner's copy of an expert is evaluated and receives gradients."""
+    from . import ops
+    world, rank = _world(group)
+    K = len(model.submodules)
+    with torch.no_grad():
+        pairs = ops.route_pack(pts, model.centroids_host(), K, model.boundary_margin, model.cluster_2d)
+        valid = pairs.point >= 0
+        csum = torch.cumsum(valid.to(torch.int32), 0)
+        seg = pairs.seg.to(torch.long)
+        ends = torch.where(seg[1:] > 0, csum[(seg[1:] - 1).clamp_min(0)], torch.zeros_like(seg[1:], dtype=csum.dtype))
+        ends = ends.tolist()  # the one host read of the step (the reference reads K nonzero() sizes, meta_container.py:309)
+        counts = [int(ends[0])] + [int(ends[e] - ends[e - 1]) for e in range(1, K)]
+        sel = torch.nonzero(valid).squeeze(1)
+        sel_point = pairs.point.index_select(0, sel).to(torch.long)
+        sel_weight = pairs.weight.index_select(0, sel)
+        x6 = pts.x6 if pts.x6 is not None else ops.sample_points(pts.rays, pts.t)
+    spec_all = model.expert_spec()
+
+    def expert_fn(rows: Tensor, local: List[int], index: List[Tensor]) -> Tensor:
+        R = rows.shape[0]
+        if R == 0 or not local:
+            return rows.new_zeros(R, 4)
+        point, segs = [], [0]
+        for ix in index:
+            n = int(ix.numel())
+            pad = (-n) % ops.ACN_TILE
+            point.append(ix.to(torch.int32))
+            if pad:
+                point.append(torch.full((pad,), -1, dtype=torch.int32, device=rows.device))
+            segs.append(segs[-1] + n + pad)
+        point_t = torch.cat(point)
+        pl = ops.PairList(segs[-1], point_t, torch.ones(segs[-1], device=rows.device), torch.tensor(segs, dtype=torch.int32, device=rows.device), segs)
+        spec = ops.ExpertSpec(spec_all.grid, [spec_all.box_min[e] for e in local], [spec_all.extent[e] for e in local])
+        tables = [model.submodules[e].xyz_encoder.hash_table for e in local]
+        mlp: List[Tensor] = []
+        for e in local:
+            mlp.extend(model.submodules[e].mlp_tensors(model._sub_params(params, e)))
+        return ops.ngp_experts(ops.PointSet(x6=rows.contiguous()), pl, spec, tables, mlp)
+
+    return expert_parallel_apply(x6, sel_point, sel_weight, counts, pts.P, expert_fn, group)
