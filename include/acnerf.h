@@ -209,6 +209,37 @@ int acn_ngp_mlp_bwd_tc(const AcnPoints* pts, const AcnPairs* pairs, const AcnNgp
 int acn_tc_selftest(const float* X, const float* Y, const float* G, int mixed, float* D1, float* D2,
                     float* D3, void* stream);
 
+/* ---- a15: positional-encoding MLP expert (MetaNeRF) as tcgen05 GEMM layers ----------------- */
+/* models/inr/meta_vanilla.py:109-154 (config 1).  Activations are fp16 "chunk-major" tensors in device memory:
+ * (chunks, ld, 8) halfs, feature f of row m at ((f/8)*ld + m)*8 + f%8, ld a multiple of 128 >= rows.
+ * The host composes the network (any width / depth / skips) from these calls; weights are the reference's
+ * nn.Linear tensors (out,in) fp32, converted to fp16 operands inside the kernels, fp32 accumulation. */
+/* [prefix (n_prefix fp32 columns of `prefix`, or none) | FrequencyEncoder(xyz if which==0 else dir)]
+ * (encodings.py:437-444) -> chunks [chunk0, chunk0 + ceil(width/8)) of out_h, zero padded. */
+int acn_pe_encode_h(const AcnPoints* pts, int which, int n_freq, int include_input, const float* prefix,
+                    int64_t prefix_ld, int n_prefix, void* out_h, int64_t ld, int chunk0, void* stream);
+/* Y = act(A W^T + b) [zeroed where mask feature <= 0]: A = k_chunks chunks of a_h (k_valid real features),
+ * W element (n,k) at W[n*ldw+k] (transposed != 0: W[k*ldw+n], the dgrad form), act 0 identity / 1 ReLU.
+ * Outputs: chunk-major fp16 (feature n -> chunk out_chunk0 + n/8 if < out_chunks) and/or fp32 rows (M, out_f_ld). */
+int acn_dense_tc(const void* a_h, int k_chunks, int64_t M, int64_t ld, const float* W, int64_t ldw, int transposed,
+                 const float* bias, int n_out, int k_valid, int act, const void* mask_h, int64_t mask_ld,
+                 int mask_chunks, void* out_h, int64_t out_ld, int out_chunk0, int out_chunks, float* out_f,
+                 int64_t out_f_ld, void* stream);
+/* dW (n_out,k_valid) = dZ^T A (row stride ldw), db = column sums of dZ, both times *inv_scale_dev if given;
+ * accumulated in TMEM per CTA and reduced in a fixed order.  ws: acn_wgrad_tc_ws_bytes(n_out, k_chunks). */
+int64_t acn_wgrad_tc_ws_bytes(int n_out, int k_chunks);
+int acn_wgrad_tc(const void* dz_h, int dz_chunks, const void* a_h, int k_chunks, int64_t M, int64_t ld, int n_out,
+                 int k_valid, float* dW, int64_t ldw, float* db, const float* inv_scale_dev, void* ws, void* stream);
+/* out (P,4) = [sigmoid?(rgb_raw[:, :3]), trunc_exp(heads[:, sigma_col])] */
+int acn_pe_final_fwd(const float* rgb_raw, int64_t rgb_ld, const float* heads, int64_t heads_ld, int sigma_col,
+                     int use_sigmoid, int64_t P, float* out, void* stream);
+/* d_out (P,4), out (P,4) -> g_rgb_h (2 chunks: the scaled gradient of the 3 colour logits), dsraw (P,) scaled
+ * d sigma_raw, scale4 = [s, 1/s, max|d_out|, -] with s the power of two putting max|d_out| near 2^10. */
+int acn_pe_final_bwd(const float* d_out, const float* out, int use_sigmoid, int64_t P, void* g_rgb_h, int64_t ld,
+                     float* dsraw, float* scale4, void* stream);
+/* feature `feature` of a chunk-major fp16 tensor <- fp32 vector v (P,) */
+int acn_set_feature_h(void* t_h, int64_t ld, int feature, const float* v, int64_t P, void* stream);
+
 /* ---- a16: shared background head ----------------------------------------- */
 /* meta_container.py:347-382: d (N,3) taken at `stride` floats (stride 8 reads rays[:,3:6]
  * in place) -> rgb (N,3).  w0 (32,16) b0 (32) w1 (3,32) b1 (3). */

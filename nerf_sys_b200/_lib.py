@@ -85,6 +85,14 @@ SIGNATURES = {
     "acn_ngp_bwd_tc_ws_bytes": (i64, []),
     "acn_ngp_mlp_bwd_tc": (C.c_int, [P(AcnPoints), P(AcnPairs), P(AcnNgpExpert), C.c_int, vp, vp, P(AcnNgpExpertGrads), vp, vp, vp]),
     "acn_tc_selftest": (C.c_int, [vp, vp, vp, C.c_int, vp, vp, vp, vp]),
+    "acn_pe_encode_h": (C.c_int, [P(AcnPoints), C.c_int, C.c_int, C.c_int, vp, i64, C.c_int, vp, i64, C.c_int, vp]),
+    "acn_dense_tc": (C.c_int, [vp, C.c_int, i64, i64, vp, i64, C.c_int, vp, C.c_int, C.c_int, C.c_int, vp, i64, C.c_int, vp, i64, C.c_int,
+                               C.c_int, vp, i64, vp]),
+    "acn_wgrad_tc_ws_bytes": (i64, [C.c_int, C.c_int]),
+    "acn_wgrad_tc": (C.c_int, [vp, C.c_int, vp, C.c_int, i64, i64, C.c_int, C.c_int, vp, i64, vp, vp, vp, vp]),
+    "acn_pe_final_fwd": (C.c_int, [vp, i64, vp, i64, C.c_int, C.c_int, i64, vp, vp]),
+    "acn_pe_final_bwd": (C.c_int, [vp, vp, C.c_int, i64, vp, i64, vp, vp, vp]),
+    "acn_set_feature_h": (C.c_int, [vp, i64, C.c_int, vp, i64, vp]),
     "acn_bg_save_bytes": (i64, [i64]),
     "acn_bg_forward": (C.c_int, [vp, i64, i64, vp, vp, vp, vp, vp, vp, vp]),
     "acn_bg_bwd_ws_bytes": (i64, [i64]),

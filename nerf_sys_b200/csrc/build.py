@@ -28,6 +28,7 @@ SOURCES = {
     "wgrad.cu": [],
     "ngp.cu": [],
     "ngp_tc.cu": [],
+    "dense_tc.cu": [],
     "render.cu": [],
     "optim.cu": [],
 }

@@ -686,6 +686,12 @@ __global__ void __launch_bounds__(256) k_absmax(const float4* __restrict__ x, in
   if ((threadIdx.x & 31) == 0) atomicMax(reinterpret_cast<int*>(out), b);
 }
 
+int launch_absmax(const float* x, int64_t n4, float* out, cudaStream_t st) {
+  k_absmax<<<persistent_grid((n4 + 255) / 256, 4), 256, 0, st>>>(reinterpret_cast<const float4*>(x), n4, out);
+  ACN_LAUNCH_CHECK();
+  return ACN_OK;
+}
+
 // ---- fixed-order reduction of the per-CTA partials into the nn.Linear-shaped gradients -------
 struct GradPtrsTc {
   float* w[ACN_MAX_EXPERTS][ACN_NGP_LAYERS];
