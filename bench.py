@@ -261,6 +261,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-render", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="drive every step from Python instead of replaying a CUDA graph")
+    ap.add_argument("--bwd-chunks", type=int, default=1, help="chunks of the pipelined backward (1 = MLP backward, then table scatter)")
     ap.add_argument("--mlp-math", default="f16tc", choices=["f16tc", "fp32"],
                     help="expert-MLP arithmetic: tcgen05 fp16/fp32-accumulate (default) or the exact fp32 CUDA-core mode")
     args = ap.parse_args()
@@ -275,6 +276,7 @@ def main():
     dev = torch.device("cuda", local)
     ops.device_ok(local)
     ops.set_mlp_math(args.mlp_math)
+    ops.set_bwd_chunks(args.bwd_chunks)
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=dev)
@@ -344,11 +346,13 @@ def main():
 
     # ---- per-kernel device time: the same K steps driven eagerly with an event pair around every C-ABI call
     # (events cannot be recorded between the nodes of a replayed graph)
+    ops.set_bwd_chunks(1)  # unpipelined, so that the MLP backward and the table scatter are timed one at a time
     timing = ops.kernel_timing(True)
     for i in range(K):
         train_step(model, opt, pool[(W + i) % nb], rgbs[(W + i) % nb], world)
     barrier()
     ops.kernel_timing(False)
+    ops.set_bwd_chunks(args.bwd_chunks)
 
     # ---- per-call device time -> roofline ------------------------------------------------
     pk = peaks()
@@ -412,7 +416,9 @@ def main():
                                                          if args.mlp_math == "f16tc" else "fp32 FFMA (exact mode)"),
                                             "l2": "per-step working set 512 MiB (table+grad+Adam moments) > 126 MB L2, no flush",
                                             "launch": "CUDA graph replay of zero_grad+fwd+bwd+clip+Adam" if use_graph else "eager Python launches",
-                                            "kernel_timing": "separate eager pass of the same K steps, CUDA-event pair per C-ABI call",
+                                            "kernel_timing": "separate eager pass of the same K steps, CUDA-event pair per C-ABI call, backward unpipelined",
+                                            "backward": (f"{args.bwd_chunks}-chunk software pipeline: table scatter of chunk c on a side stream beside the "
+                                                         "MLP backward of chunk c+1") if args.bwd_chunks > 1 else "MLP backward, then table scatter",
                                             "collective": "none" if world == 1 else "nccl all-reduce of 643 bg-head grads"},
             "clocks": clk, "e2e": {"value": world * N_RAYS * K / (ms_e2e / 1e3), "unit": "rays/s", "h2d_bytes_per_step": bytes_in,
                                    "d2h_bytes_per_step": 4, "ms_per_step": ms_e2e / K},

@@ -203,6 +203,15 @@ int64_t acn_ngp_bwd_tc_ws_bytes(void);
 int acn_ngp_mlp_bwd_tc(const AcnPoints* pts, const AcnPairs* pairs, const AcnNgpExpert* experts, int E,
                        const float* enc, const float* d_out, const AcnNgpExpertGrads* grads, float* d_enc,
                        void* ws, void* stream);
+/* Training backward of the whole expert stage (MLP backward + hash-table scatter) as a software pipeline over
+ * n_chunks (1..8) chunks of the pair list: chunk c's scatter (acn_ngp_encode_bwd semantics, grads[e].table
+ * accumulated, caller zeroes) runs on side_stream while chunk c+1's MLP backward runs on stream, on the same SMs;
+ * `stream` is joined with the side stream before return.  ws: acn_ngp_bwd_tc_pipelined_ws_bytes(n_chunks). */
+int64_t acn_ngp_bwd_tc_pipelined_ws_bytes(int n_chunks);
+int acn_ngp_bwd_tc_pipelined(const AcnPoints* pts, const AcnPairs* pairs, const AcnNgpExpert* experts, int E,
+                             const AcnGridDesc* g, const float* enc, const float* d_out,
+                             const AcnNgpExpertGrads* grads, float* d_enc, void* ws, int n_chunks, void* stream,
+                             void* side_stream);
 /* Descriptor self-test of the three shared-memory operand layouts the kernels above use
  * (X (128,64), Y (64,64), G (128,64) fp32 in; D1 = X Y^T (128,64), D2 = G^T X (64,64), D3 = G Y (128,64));
  * G is rounded to bf16 when mixed != 0, everything else to fp16. */

@@ -84,6 +84,9 @@ SIGNATURES = {
     "acn_ngp_mlp_fwd_tc": (C.c_int, [P(AcnPoints), P(AcnPairs), P(AcnNgpExpert), C.c_int, vp, vp, vp]),
     "acn_ngp_bwd_tc_ws_bytes": (i64, []),
     "acn_ngp_mlp_bwd_tc": (C.c_int, [P(AcnPoints), P(AcnPairs), P(AcnNgpExpert), C.c_int, vp, vp, P(AcnNgpExpertGrads), vp, vp, vp]),
+    "acn_ngp_bwd_tc_pipelined_ws_bytes": (i64, [C.c_int]),
+    "acn_ngp_bwd_tc_pipelined": (C.c_int, [P(AcnPoints), P(AcnPairs), P(AcnNgpExpert), C.c_int, P(AcnGridDesc), vp, vp, P(AcnNgpExpertGrads), vp,
+                                           vp, C.c_int, vp, vp]),
     "acn_tc_selftest": (C.c_int, [vp, vp, vp, C.c_int, vp, vp, vp, vp]),
     "acn_pe_encode_h": (C.c_int, [P(AcnPoints), C.c_int, C.c_int, C.c_int, vp, i64, C.c_int, vp, i64, C.c_int, vp]),
     "acn_dense_tc": (C.c_int, [vp, C.c_int, i64, i64, vp, i64, C.c_int, vp, C.c_int, C.c_int, C.c_int, vp, i64, C.c_int, vp, i64, C.c_int,

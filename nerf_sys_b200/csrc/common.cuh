@@ -151,4 +151,10 @@ int wgrad_launch(const WgradJob& job, const int32_t* seg_dev, int E, int64_t M_s
                  float* const* db, float* partial, cudaStream_t st);
 int64_t wgrad_partial_floats(int E);
 
+// ngp.cu: hash-table gradient scatter over pair slots [m_lo, m_hi) (grid_x = 0: default persistent grid)
+int launch_hash_bwd_range(const AcnPoints* pts, const AcnPairs* pairs, const AcnNgpExpert* experts, int E, const AcnGridDesc* g,
+                          const float* d_enc, const AcnNgpExpertGrads* grads, int64_t m_lo, int64_t m_hi, int grid_x, cudaStream_t st);
+// ngp_tc.cu: max |x| over n4 float4s, atomically maxed into *out (caller zeroes)
+int launch_absmax(const float* x, int64_t n4, float* out, cudaStream_t st);
+
 }  // namespace acn

@@ -345,8 +345,6 @@ __global__ void __launch_bounds__(256) k_set_feature(__half* __restrict__ t, int
     t[((int64_t)(f / 8) * ld + p) * 8 + (f & 7)] = __float2half_rn(fminf(fmaxf(v[p], -65504.f), 65504.f));
 }
 
-int launch_absmax(const float* x, int64_t n4, float* out, cudaStream_t st);  // ngp_tc.cu
-
 static int dense_attrs() {
   static thread_local int done_dev = -1;
   int dev = 0;

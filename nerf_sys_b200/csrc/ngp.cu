@@ -83,14 +83,15 @@ struct GradTables {
 
 __global__ void __launch_bounds__(256) k_ngp_hash_bwd(PointSrc src, const int32_t* __restrict__ pair_point, const int32_t* __restrict__ seg,
                                                       int64_t M_ident, ExpertTable tab, GridParams g, const float* __restrict__ denc, int64_t ld,
-                                                      GradTables gts) {
+                                                      GradTables gts, int64_t m_lo, int64_t m_hi) {
   __shared__ int s_seg[ACN_MAX_EXPERTS + 1];
   if (threadIdx.x <= tab.E) s_seg[threadIdx.x] = seg ? seg[threadIdx.x] : (threadIdx.x == 0 ? 0 : (int)M_ident);
   __syncthreads();
   int64_t M = seg ? s_seg[tab.E] : M_ident;
   int l = blockIdx.y;
   uint32_t mask = (1u << g.log2_T) - 1u, base = (uint32_t)l << g.log2_T;
-  for (int64_t m = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; m < M; m += (int64_t)gridDim.x * blockDim.x) {
+  if (m_hi < M) M = m_hi;
+  for (int64_t m = m_lo + blockIdx.x * (int64_t)blockDim.x + threadIdx.x; m < M; m += (int64_t)gridDim.x * blockDim.x) {
     int64_t p = pair_point ? (int64_t)pair_point[m] : m;
     if (p < 0) continue;
     int e = seg ? find_expert(s_seg, tab.E, m) : 0;
@@ -428,6 +429,30 @@ static int check_common(const AcnPoints* pts, const AcnPairs* pairs, const AcnNg
   return ACN_OK;
 }
 
+// table-gradient scatter over slots [m_lo, m_hi) (grid_x = 0: the default persistent grid)
+int launch_hash_bwd_range(const AcnPoints* pts, const AcnPairs* pairs, const AcnNgpExpert* experts, int E, const AcnGridDesc* g,
+                          const float* d_enc, const AcnNgpExpertGrads* grads, int64_t m_lo, int64_t m_hi, int grid_x, cudaStream_t st) {
+  int rc = check_common(pts, pairs, experts, E, g, "acn_ngp_encode_bwd");
+  if (rc) return rc;
+  ACN_REQUIRE(d_enc && grads, "acn_ngp_encode_bwd: NULL argument");
+  int64_t Mcap = pairs->Mcap;
+  if (Mcap == 0 || m_lo >= Mcap) return ACN_OK;
+  ExpertTable tab;
+  fill_table(tab, experts, E);
+  bool any_table = false;
+  GradTables gts;
+  for (int e = 0; e < ACN_MAX_EXPERTS; ++e) {
+    gts.t[e] = (e < E) ? grads[e].table : nullptr;
+    any_table = any_table || gts.t[e];
+  }
+  if (!any_table) return ACN_OK;
+  int64_t span = (m_hi < Mcap ? m_hi : Mcap) - m_lo;
+  dim3 hg(grid_x > 0 ? grid_x : persistent_grid((span + 255) / 256, 4), g->levels);
+  k_ngp_hash_bwd<<<hg, 256, 0, st>>>(make_src(pts), pairs->point, pairs->seg, Mcap, tab, make_grid(g), d_enc, h_round_ld(Mcap), gts, m_lo, m_hi);
+  ACN_LAUNCH_CHECK();
+  return ACN_OK;
+}
+
 }  // namespace acn
 
 using namespace acn;
@@ -455,24 +480,7 @@ int acn_ngp_encode_fwd(const AcnPoints* pts, const AcnPairs* pairs, const AcnNgp
 
 int acn_ngp_encode_bwd(const AcnPoints* pts, const AcnPairs* pairs, const AcnNgpExpert* experts, int E, const AcnGridDesc* g,
                        const float* d_enc, const AcnNgpExpertGrads* grads, void* stream) {
-  int rc = check_common(pts, pairs, experts, E, g, "acn_ngp_encode_bwd");
-  if (rc) return rc;
-  ACN_REQUIRE(d_enc && grads, "acn_ngp_encode_bwd: NULL argument");
-  int64_t Mcap = pairs->Mcap;
-  if (Mcap == 0) return ACN_OK;
-  ExpertTable tab;
-  fill_table(tab, experts, E);
-  bool any_table = false;
-  GradTables gts;
-  for (int e = 0; e < ACN_MAX_EXPERTS; ++e) {
-    gts.t[e] = (e < E) ? grads[e].table : nullptr;
-    any_table = any_table || gts.t[e];
-  }
-  if (!any_table) return ACN_OK;
-  dim3 hg(persistent_grid((Mcap + 255) / 256, 4), g->levels);
-  k_ngp_hash_bwd<<<hg, 256, 0, as_stream(stream)>>>(make_src(pts), pairs->point, pairs->seg, Mcap, tab, make_grid(g), d_enc, h_round_ld(Mcap), gts);
-  ACN_LAUNCH_CHECK();
-  return ACN_OK;
+  return launch_hash_bwd_range(pts, pairs, experts, E, g, d_enc, grads, 0, (int64_t)1 << 62, 0, as_stream(stream));
 }
 
 static int set_mlp_attrs() {

@@ -5,7 +5,7 @@
 // This is the precision class the reference itself runs on a GPU (TF32 matmuls, nerf_runner.py:42-43,
 // fp16 under autocast, meta_core.py:38); the fp32 CUDA-core kernels in ngp.cu stay as the "exact" mode.
 //
-//   k_ngp_mlp_fwd_tc : 4 independent 128-row pipelines per CTA; per layer one thread issues the MMAs
+//   k_ngp_mlp_fwd_tc : 5 independent 128-row pipelines per CTA; per layer one thread issues the MMAs
 //                      (A = activations in smem, B = weights in smem, D in TMEM), the pipeline's 128 threads
 //                      read their row back with tcgen05.ld, apply ReLU / trunc_exp / sigmoid and write the
 //                      next layer's A operand in place.  Biases ride along as an extra K chunk ([1,0..] x [b,0..]).
@@ -103,7 +103,7 @@ struct CtaPart {
 
 // CTA ranges of every expert: first[e], n[e] (n = 0 for an empty expert); returns the number of CTAs used.
 __device__ __forceinline__ int expert_ranges(const int* s_seg, int E, int G, int* first, int* n) {
-  int T = s_seg[E] / (int)ROWS;
+  int T = (s_seg[E] - s_seg[0]) / (int)ROWS;  // s_seg may be clamped to a window of the slot list
   for (int e = 0; e < E; ++e) first[e] = n[e] = 0;
   if (T <= 0) return 0;
   int Geff = G < T ? G : T;
@@ -235,11 +235,11 @@ __device__ __forceinline__ void dir_sh16(const PointSrc& src, int64_t p, float* 
 // =============================================================================================
 // forward
 // =============================================================================================
-constexpr int FWD_PIPES = 4;
+constexpr int FWD_PIPES = 7;
 constexpr int FWD_THREADS = 128 * FWD_PIPES;
 constexpr uint32_t ABUF = 10 * CH;  // chunk 0 ones | chunks 1..8 data | chunk 9 zero (chunk 5 zero for 32-wide inputs)
 constexpr size_t FWD_SMEM = W_BYTES + FWD_PIPES * ABUF;
-constexpr uint32_t FWD_TMEM_COLS = 64 * FWD_PIPES;
+constexpr uint32_t FWD_TMEM_COLS = 512;  // power of two >= 64 * FWD_PIPES
 
 __global__ void __launch_bounds__(FWD_THREADS, 1)
     k_ngp_mlp_fwd_tc(PointSrc src, const int32_t* __restrict__ pair_point, const float* __restrict__ pair_w, const int32_t* __restrict__ seg,
@@ -406,7 +406,6 @@ __global__ void __launch_bounds__(FWD_THREADS, 1)
 // =============================================================================================
 // backward (forward recompute + dgrad chain + TMEM-resident weight gradients)
 // =============================================================================================
-constexpr int BWD_THREADS = 512;  // thread = (row r, column quarter q): 16 of the 64 columns of every epilogue (4 warps per scheduler)
 constexpr uint32_t B_ENC = W_BYTES;            // [1 | enc32 | 0]   6 chunks
 constexpr uint32_t B_H0 = B_ENC + 6 * CH;      // [1 | h0 64 | 0]  10 chunks
 constexpr uint32_t B_H1 = B_H0 + 10 * CH;
@@ -441,20 +440,28 @@ __device__ __forceinline__ void dump_acc(uint32_t tbase, uint32_t col, int nq, f
   }
 }
 
-__global__ void __launch_bounds__(BWD_THREADS, 1)
+// NQ column groups of 128 threads each: NQ = 4 (512 threads, 16 columns per thread) when the kernel has the SM to itself,
+// NQ = 2 (256 threads, 2 x 16 columns per thread, half the register file) when the hash-grid scatter of the previous
+// chunk runs beside it (acn_ngp_bwd_tc_pipelined).  [tile_lo, tile_hi) restricts the launch to a window of 128-slot tiles.
+template <int NQ>
+__global__ void __launch_bounds__(128 * NQ, NQ == 2 ? 2 : 1)  // NQ = 2: at most half the register file
     k_ngp_mlp_bwd_tc(PointSrc src, const int32_t* __restrict__ pair_point, const float* __restrict__ pair_w, const int32_t* __restrict__ seg,
                      int64_t M_ident, ExpertTableTc tab, const float* __restrict__ enc, int64_t ld, const float* __restrict__ d_out,
-                     float* __restrict__ d_enc, float* __restrict__ partial, const float* __restrict__ gmax) {
+                     float* __restrict__ d_enc, float* __restrict__ partial, const float* __restrict__ gmax, int tile_lo, int tile_hi) {
+  constexpr int PASSES = 4 / NQ;  // 16-column passes per thread in a 64-column epilogue
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ __align__(8) uint64_t s_bar;
   __shared__ uint32_t s_tmem;
   __shared__ int s_seg[ACN_MAX_EXPERTS + 1];
   __shared__ CtaPart s_part;
-  const int tid = threadIdx.x, q = tid >> 7;  // q: which 16 of the 64 columns this thread owns in every epilogue
+  const int tid = threadIdx.x, q = tid >> 7;
   const uint32_t r = tid & 127;
-  if (tid <= tab.E) s_seg[tid] = seg ? seg[tid] : (tid == 0 ? 0 : round_up128(M_ident));
+  if (tid <= tab.E) {
+    int v = seg ? seg[tid] : (tid == 0 ? 0 : round_up128(M_ident));
+    s_seg[tid] = min(max(v, tile_lo * (int)ROWS), tile_hi * (int)ROWS);  // this launch's window of the slot list
+  }
   __syncthreads();
-  const int64_t M = seg ? (int64_t)s_seg[tab.E] : M_ident;
+  const int64_t M = seg ? (int64_t)__ldg(seg + tab.E) : M_ident;
   if (tid == 0) {
     s_part = cta_partition(s_seg, tab.E, blockIdx.x, gridDim.x);
     mbar_init(smem_u32(&s_bar), 1);
@@ -465,26 +472,21 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
   __syncthreads();
   const CtaPart part = s_part;
   const uint32_t sb = smem_u32(smem);
-  if (part.e >= 0) load_weights_tc(smem, tab.ex[part.e], tid, BWD_THREADS);
-  if (q == 0) {
-    store_ones_chunk(sb + B_ENC, r, 0);
-    store_ones_chunk(sb + B_H0, r, 0);
-    store_ones_chunk(sb + B_H1, r, 0);
-  } else if (q == 1) {
-    store_ones_chunk(sb + B_CIN, r, 0);
-    store_ones_chunk(sb + B_C0, r, 0);
-    store_ones_chunk(sb + B_C1, r, 0);
-  } else if (q == 2) {
-    store_zero_chunk(sb + B_ENC, r, 5);
-    store_zero_chunk(sb + B_H0, r, 9);
-    store_zero_chunk(sb + B_H1, r, 9);
-  } else {
-    store_zero_chunk(sb + B_CIN, r, 5);
-    store_zero_chunk(sb + B_C0, r, 9);
-    store_zero_chunk(sb + B_C1, r, 9);
+  if (part.e >= 0) load_weights_tc(smem, tab.ex[part.e], tid, 128 * NQ);
+  {
+    constexpr uint32_t bufs[6] = {B_ENC, B_H0, B_H1, B_CIN, B_C0, B_C1};
+    constexpr int zc[6] = {5, 9, 9, 5, 9, 9};
+#pragma unroll
+    for (int b = 0; b < 12; ++b) {
+      if (b % NQ != q) continue;
+      if (b < 6)
+        store_ones_chunk(sb + bufs[b], r, 0);
+      else
+        store_zero_chunk(sb + bufs[b - 6], r, zc[b - 6]);
+    }
   }
   // gradient tiles start finite (rows 16.. of the 16-wide stages are read by the M=64 wgrad MMAs and ignored)
-  for (int c = q; c < 8; c += 4) {
+  for (int c = q; c < 8; c += NQ) {
     store_zero_chunk(sb + B_GA, r, c);
     store_zero_chunk(sb + B_GB, r, c);
   }
@@ -495,7 +497,7 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
   const uint32_t tbase = s_tmem;
   const uint32_t tD = tbase + T_D;
   const uint32_t trow0 = tD + ((uint32_t)((tid >> 5) & 3) << 21);  // column 0 of this thread's row
-  const uint32_t trow = trow0 + 16 * q;                            // this thread's 16 columns of D
+  const uint32_t trow = trow0 + 16 * PASSES * q;                   // this thread's columns of D
   const uint32_t bar = smem_u32(&s_bar);
   uint32_t phase = 0;
   uint32_t acc = 0;  // 0 on the CTA's first tile: the weight-gradient accumulators are overwritten
@@ -510,50 +512,87 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
   // One chain step: publish this thread's smem writes, one thread issues ISSUE and commits, everyone waits for the
   // accumulator.  LATE (weight-gradient MMAs) is issued after the commit: it runs on the tensor pipe while the
   // epilogue of this step executes, and is covered by the NEXT step's commit before its operands are overwritten.
-#define TC_STEP(ISSUE, LATE) \
-  do {                       \
-    fence_before();          \
-    fence_async_smem();      \
-    __syncthreads();         \
-    if (tid == 0) {          \
-      fence_after();         \
-      ISSUE;                 \
-      commit(bar);           \
-      LATE;                  \
-    }                        \
-    mbar_wait(bar, phase);   \
-    phase ^= 1;              \
-    fence_after();           \
+  // OVERLAP is work every thread does while the MMAs run.
+#define TC_STEP3(ISSUE, LATE, OVERLAP) \
+  do {                                 \
+    fence_before();                    \
+    fence_async_smem();                \
+    __syncthreads();                   \
+    if (tid == 0) {                    \
+      fence_after();                   \
+      ISSUE;                           \
+      commit(bar);                     \
+      LATE;                            \
+    }                                  \
+    OVERLAP;                           \
+    mbar_wait(bar, phase);             \
+    phase ^= 1;                        \
+    fence_after();                     \
+  } while (0)
+#define TC_STEP(ISSUE, LATE) TC_STEP3(ISSUE, LATE, (void)0)
+  // 64-column epilogues: ReLU + mask capture (forward recompute) / mask application (dgrad chain)
+#define EPI_RELU(BUF, MASK)                                             \
+  do {                                                                  \
+    MASK = 0;                                                           \
+    _Pragma("unroll") for (int s_ = 0; s_ < PASSES; ++s_) {             \
+      tmem_ld16(trow + 16 * s_, v);                                     \
+      tmem_ld_wait();                                                   \
+      MASK |= relu_mask<16>(v) << (16 * s_);                            \
+      store_h<16>(sb + BUF, r, 1 + 2 * (PASSES * q + s_), v);           \
+    }                                                                   \
+  } while (0)
+#define EPI_MASK(BUF, MASK)                                                                        \
+  do {                                                                                             \
+    _Pragma("unroll") for (int s_ = 0; s_ < PASSES; ++s_) {                                        \
+      tmem_ld16(trow + 16 * s_, v);                                                                \
+      tmem_ld_wait();                                                                              \
+      _Pragma("unroll") for (int i = 0; i < 16; ++i) v[i] = (MASK >> (16 * s_ + i) & 1u) ? v[i] : 0.f; \
+      store_g<16>(sb + BUF, r, 2 * (PASSES * q + s_), v);                                          \
+    }                                                                                              \
   } while (0)
 
   if (part.e >= 0) {
+    // software prefetch: the next tile's encoding rows and pair id are requested one tile ahead, this tile's output
+    // gradient at the top of the tile, so no global-load latency sits in the per-layer chain
+    constexpr int FE = 8 * PASSES;  // encoding features per thread
+    float xn[FE];
+    int64_t pn = -1;
+    auto prefetch = [&](int tile) {
+      const int64_t m_ = (int64_t)tile * ROWS + r;
+      const bool ok_ = tile < part.tile1 && m_ < M;
+#pragma unroll
+      for (int i = 0; i < FE; ++i) xn[i] = ok_ ? __ldg(enc + (int64_t)(FE * q + i) * ld + m_) : 0.f;
+      pn = ok_ ? (pair_point ? (int64_t)__ldg(pair_point + m_) : m_) : -1;
+    };
+    prefetch(part.tile0);
     for (int tile = part.tile0; tile < part.tile1; ++tile) {
       const int64_t m = (int64_t)tile * ROWS + r;
-      const bool in_range = m < M;
-      const int64_t p = in_range ? (pair_point ? (int64_t)pair_point[m] : m) : -1;
-      const int64_t mm = in_range ? m : 0;
-      uint32_t m0, m1, m3, m4;  // ReLU masks of this thread's 16 columns of h0, h1, c0, c1
+      const int64_t p = pn;
+      uint32_t m0, m1, m3, m4;  // ReLU masks of this thread's columns of h0, h1, c0, c1
       float v[16];
+      float4 dy = make_float4(0.f, 0.f, 0.f, 0.f);
       // ---- forward recompute ----
-      {
+#pragma unroll
+      for (int s_ = 0; s_ < PASSES; ++s_) {
         float x[8];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) x[i] = in_range ? __ldg(enc + (int64_t)(8 * q + i) * ld + mm) : 0.f;
-#pragma unroll
-        for (int i = 0; i < 8; ++i) x[i] = fminf(fmaxf(x[i], -F16_MAX), F16_MAX);
-        store_h<8>(sb + B_ENC, r, 1 + q, x);
+        for (int i = 0; i < 8; ++i) x[i] = fminf(fmaxf(xn[8 * s_ + i], -F16_MAX), F16_MAX);
+        store_h<8>(sb + B_ENC, r, 1 + PASSES * q + s_, x);
       }
+      if (q == 0 && p >= 0) {
+        dy = __ldg(reinterpret_cast<const float4*>(d_out + p * 4));
+        if (pair_point) {
+          float w = __ldg(pair_w + m);
+          dy.x *= w; dy.y *= w; dy.z *= w; dy.w *= w;
+        }
+      }
+      prefetch(tile + 1);
       TC_STEP((issue_fwd<32, 64>(tD, sb + B_ENC, sb + OW0)), (void)0);
-      tmem_ld16(trow, v);
-      tmem_ld_wait();
-      m0 = relu_mask<16>(v);
-      store_h<16>(sb + B_H0, r, 1 + 2 * q, v);
+      EPI_RELU(B_H0, m0);
       TC_STEP((issue_fwd<64, 64>(tD, sb + B_H0, sb + OW1)), (void)0);
-      tmem_ld16(trow, v);
-      tmem_ld_wait();
-      m1 = relu_mask<16>(v);
-      store_h<16>(sb + B_H1, r, 1 + 2 * q, v);
-      TC_STEP((issue_fwd<64, 16>(tD, sb + B_H1, sb + OWH)), (void)0);
+      EPI_RELU(B_H1, m1);
+      float sh[16];
+      TC_STEP3((issue_fwd<64, 16>(tD, sb + B_H1, sb + OWH)), (void)0, if (q == 1) dir_sh16(src, p, sh));
       float sigma = 0.f;
       if (q == 0) {  // cin[0..15] = geo 0..14, sh 0
         tmem_ld16(trow0, v);
@@ -564,23 +603,15 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
         v[15] = 0.28209479177387814f;
         store_h<16>(sb + B_CIN, r, 1, v);
       } else if (q == 1) {  // cin[16..31] = sh 1..15, 0
-        float sh[16];
-        dir_sh16(src, p, sh);
 #pragma unroll
         for (int i = 0; i < 15; ++i) v[i] = sh[1 + i];
         v[15] = 0.f;
         store_h<16>(sb + B_CIN, r, 3, v);
       }
       TC_STEP((issue_fwd<32, 64>(tD, sb + B_CIN, sb + OW3)), (void)0);
-      tmem_ld16(trow, v);
-      tmem_ld_wait();
-      m3 = relu_mask<16>(v);
-      store_h<16>(sb + B_C0, r, 1 + 2 * q, v);
+      EPI_RELU(B_C0, m3);
       TC_STEP((issue_fwd<64, 64>(tD, sb + B_C0, sb + OW4)), (void)0);
-      tmem_ld16(trow, v);
-      tmem_ld_wait();
-      m4 = relu_mask<16>(v);
-      store_h<16>(sb + B_C1, r, 1 + 2 * q, v);
+      EPI_RELU(B_C1, m4);
       TC_STEP((issue_fwd<64, 16>(tD, sb + B_C1, sb + OW5)), (void)0);
       // ---- output gradients ----
       float dsraw = 0.f;
@@ -593,11 +624,6 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
           tmem_ld8(trow0, o8);
           tmem_ld_wait();
           if (p >= 0) {
-            float4 dy = __ldg(reinterpret_cast<const float4*>(d_out + p * 4));
-            if (pair_point) {
-              float w = pair_w[m];
-              dy.x *= w; dy.y *= w; dy.z *= w; dy.w *= w;
-            }
             float r0 = sigmoid_f(o8[0]), r1 = sigmoid_f(o8[1]), r2 = sigmoid_f(o8[2]);
             g[0] = gscale * dy.x * r0 * (1.f - r0);
             g[1] = gscale * dy.y * r1 * (1.f - r1);
@@ -609,17 +635,9 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
       }
       // ---- dgrad chain; the weight gradient of the layer just left is issued behind the commit ----
       TC_STEP((issue_dgrad<16, 64, 16>(tD, sb + B_GA, sb + OW5)), (issue_wgrad<64>(tbase + T_A5, sb + B_GA, sb + B_C1, acc)));
-      tmem_ld16(trow, v);
-      tmem_ld_wait();
-#pragma unroll
-      for (int i = 0; i < 16; ++i) v[i] = (m4 >> i & 1u) ? v[i] : 0.f;
-      store_g<16>(sb + B_GB, r, 2 * q, v);
+      EPI_MASK(B_GB, m4);
       TC_STEP((issue_dgrad<64, 64, 64>(tD, sb + B_GB, sb + OW4)), (issue_wgrad<64>(tbase + T_A4, sb + B_GB, sb + B_C0, acc)));
-      tmem_ld16(trow, v);
-      tmem_ld_wait();
-#pragma unroll
-      for (int i = 0; i < 16; ++i) v[i] = (m3 >> i & 1u) ? v[i] : 0.f;
-      store_g<16>(sb + B_GA, r, 2 * q, v);
+      EPI_MASK(B_GA, m3);
       TC_STEP((issue_dgrad<64, 32, 64>(tD, sb + B_GA, sb + OW3)), (issue_wgrad<32>(tbase + T_A3, sb + B_GA, sb + B_CIN, acc)));
       if (q == 0) {  // head gradient [d geo 0..14 | d sigma_raw] -> chunks 0, 1
         tmem_ld16(trow0, v);
@@ -628,17 +646,9 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
         store_g<16>(sb + B_GB, r, 0, v);
       }
       TC_STEP((issue_dgrad<16, 64, 16>(tD, sb + B_GB, sb + OWH)), (issue_wgrad<64>(tbase + T_AH, sb + B_GB, sb + B_H1, acc)));
-      tmem_ld16(trow, v);
-      tmem_ld_wait();
-#pragma unroll
-      for (int i = 0; i < 16; ++i) v[i] = (m1 >> i & 1u) ? v[i] : 0.f;
-      store_g<16>(sb + B_GA, r, 2 * q, v);
+      EPI_MASK(B_GA, m1);
       TC_STEP((issue_dgrad<64, 64, 64>(tD, sb + B_GA, sb + OW1)), (issue_wgrad<64>(tbase + T_A1, sb + B_GA, sb + B_H0, acc)));
-      tmem_ld16(trow, v);
-      tmem_ld_wait();
-#pragma unroll
-      for (int i = 0; i < 16; ++i) v[i] = (m0 >> i & 1u) ? v[i] : 0.f;
-      store_g<16>(sb + B_GB, r, 2 * q, v);
+      EPI_MASK(B_GB, m0);
       // last step of the tile: its weight-gradient MMAs go BEFORE the commit, because the next tile's first
       // epilogue overwrites the encoding buffer they read
       TC_STEP((issue_dgrad<64, 32, 64>(tD, sb + B_GB, sb + OW0), issue_wgrad<32>(tbase + T_A0, sb + B_GB, sb + B_ENC, acc)), (void)0);
@@ -654,6 +664,9 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
     }
   }
 #undef TC_STEP
+#undef TC_STEP3
+#undef EPI_RELU
+#undef EPI_MASK
   fence_before();
   __syncthreads();
   fence_after();
@@ -698,20 +711,34 @@ struct GradPtrsTc {
   float* b[ACN_MAX_EXPERTS][ACN_NGP_LAYERS];
 };
 
+constexpr int TC_MAX_CHUNKS = 8;
+
+// chunk c of a pipelined backward covers tiles [c*chunk_tiles, (c+1)*chunk_tiles) (the last chunk is open-ended); its
+// partials are partial[c][cta][P_FLOATS].  Chunks and CTAs are summed in a fixed order.
 __global__ void __launch_bounds__(256) k_tc_wgrad_reduce(const float* __restrict__ partial, const int32_t* __restrict__ seg, int64_t M_ident, int E,
-                                                         int G, const GradPtrsTc gp) {
+                                                         int G, int n_chunks, int chunk_tiles, const GradPtrsTc gp) {
   __shared__ int s_seg[ACN_MAX_EXPERTS + 1];
-  __shared__ int s_first[ACN_MAX_EXPERTS], s_n[ACN_MAX_EXPERTS];
-  if ((int)threadIdx.x <= E) s_seg[threadIdx.x] = seg ? seg[threadIdx.x] : (threadIdx.x == 0 ? 0 : round_up128(M_ident));
-  __syncthreads();
-  if (threadIdx.x == 0) expert_ranges(s_seg, E, G, s_first, s_n);
+  __shared__ int s_first[TC_MAX_CHUNKS][ACN_MAX_EXPERTS], s_n[TC_MAX_CHUNKS][ACN_MAX_EXPERTS];
+  if ((int)threadIdx.x < n_chunks) {
+    const int c = threadIdx.x;
+    const int lo = c * chunk_tiles * (int)ROWS, hi = (c == n_chunks - 1) ? 0x7fffff80 : (c + 1) * chunk_tiles * (int)ROWS;
+    int sg[ACN_MAX_EXPERTS + 1];
+    for (int k = 0; k <= E; ++k) {
+      int v = seg ? seg[k] : (k == 0 ? 0 : round_up128(M_ident));
+      sg[k] = min(max(v, lo), hi);
+    }
+    expert_ranges(sg, E, G, s_first[c], s_n[c]);
+  }
+  (void)s_seg;
   __syncthreads();
   const int e = blockIdx.y;
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= P_FLOATS) return;
   float acc = 0.f;
-  const float* src = partial + (int64_t)s_first[e] * P_FLOATS + j;
-  for (int c = 0; c < s_n[e]; ++c) acc += __ldg(src + (int64_t)c * P_FLOATS);
+  for (int c = 0; c < n_chunks; ++c) {
+    const float* src = partial + ((int64_t)c * G + s_first[c][e]) * P_FLOATS + j;
+    for (int x = 0; x < s_n[c][e]; ++x) acc += __ldg(src + (int64_t)x * P_FLOATS);
+  }
   // j -> (block, row, col)
   int blk, row, col, N;
   if (j < P_A1) { blk = 0; N = 40; row = (j - P_A0) / N; col = (j - P_A0) % N; }
@@ -838,7 +865,8 @@ static int set_tc_attrs() {
   ACN_CUDA(cudaGetDevice(&dev));
   if (done_dev != dev) {
     ACN_CUDA(cudaFuncSetAttribute(k_ngp_mlp_fwd_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FWD_SMEM));
-    ACN_CUDA(cudaFuncSetAttribute(k_ngp_mlp_bwd_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BWD_SMEM));
+    ACN_CUDA(cudaFuncSetAttribute(k_ngp_mlp_bwd_tc<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BWD_SMEM));
+    ACN_CUDA(cudaFuncSetAttribute(k_ngp_mlp_bwd_tc<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BWD_SMEM));
     ACN_CUDA(cudaFuncSetAttribute(k_tc_selftest, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
     done_dev = dev;
   }
@@ -876,19 +904,20 @@ int64_t acn_ngp_bwd_tc_ws_bytes(void) {
   return (int64_t)sizeof(float) * (P_FLOATS * (int64_t)num_sms_cached() + 4);
 }
 
-int acn_ngp_mlp_bwd_tc(const AcnPoints* pts, const AcnPairs* pairs, const AcnNgpExpert* experts, int E, const float* enc, const float* d_out,
-                       const AcnNgpExpertGrads* grads, float* d_enc, void* ws, void* stream) {
-  ACN_REQUIRE(pts && pairs && experts && enc && d_out && grads && d_enc && ws, "acn_ngp_mlp_bwd_tc: NULL argument");
-  ACN_REQUIRE(E >= 1 && E <= ACN_MAX_EXPERTS, "acn_ngp_mlp_bwd_tc: E must be in [1,%d]", ACN_MAX_EXPERTS);
-  ACN_REQUIRE(pts->x6 || (pts->rays && pts->S >= 1), "acn_ngp_mlp_bwd_tc: points need x6 or rays");
+static int run_bwd_tc(const AcnPoints* pts, const AcnPairs* pairs, const AcnNgpExpert* experts, int E, const AcnGridDesc* g, const float* enc,
+                      const float* d_out, const AcnNgpExpertGrads* grads, float* d_enc, void* ws, int n_chunks, cudaStream_t st,
+                      cudaStream_t side, const char* who) {
+  ACN_REQUIRE(pts && pairs && experts && enc && d_out && grads && d_enc && ws, "%s: NULL argument", who);
+  ACN_REQUIRE(E >= 1 && E <= ACN_MAX_EXPERTS, "%s: E must be in [1,%d]", who, ACN_MAX_EXPERTS);
+  ACN_REQUIRE(pts->x6 || (pts->rays && pts->S >= 1), "%s: points need x6 or rays", who);
   bool ident = pairs->point == nullptr;
-  ACN_REQUIRE(ident ? (E == 1 && pairs->Mcap == pts->P) : (pairs->weight && pairs->seg), "acn_ngp_mlp_bwd_tc: inconsistent pair list");
-  ACN_REQUIRE(pairs->Mcap < ((int64_t)1 << 31) - 128, "acn_ngp_mlp_bwd_tc: chunk the pair list below 2^31");
+  ACN_REQUIRE(ident ? (E == 1 && pairs->Mcap == pts->P) : (pairs->weight && pairs->seg), "%s: inconsistent pair list", who);
+  ACN_REQUIRE(pairs->Mcap < ((int64_t)1 << 31) - 128, "%s: chunk the pair list below 2^31", who);
+  ACN_REQUIRE(n_chunks >= 1 && n_chunks <= TC_MAX_CHUNKS, "%s: 1..%d chunks", who, TC_MAX_CHUNKS);
   int64_t Mcap = pairs->Mcap;
   if (Mcap == 0) return ACN_OK;
   int rc = set_tc_attrs();
   if (rc) return rc;
-  cudaStream_t st = as_stream(stream);
   ExpertTableTc tab;
   fill_table_tc(tab, experts, E);
   int64_t ld = (Mcap + 127) / 128 * 128;
@@ -902,18 +931,70 @@ int acn_ngp_mlp_bwd_tc(const AcnPoints* pts, const AcnPairs* pairs, const AcnNgp
       gp.b[e][l] = e < E ? grads[e].b[l] : nullptr;
       any = any || gp.w[e][l] || gp.b[e][l];
     }
-  float* gmax = partial + (int64_t)P_FLOATS * num_sms_cached();
+  float* gmax = partial + (int64_t)P_FLOATS * G * n_chunks;
   ACN_CUDA(cudaMemsetAsync(gmax, 0, sizeof(float), st));
   k_absmax<<<persistent_grid((pts->P + 255) / 256, 4), 256, 0, st>>>(reinterpret_cast<const float4*>(d_out), pts->P, gmax);
   ACN_LAUNCH_CHECK();
-  k_ngp_mlp_bwd_tc<<<G, BWD_THREADS, BWD_SMEM, st>>>(make_src(pts), pairs->point, pairs->weight, pairs->seg, Mcap, tab, enc, ld, d_out, d_enc,
-                                                     partial, gmax);
-  ACN_LAUNCH_CHECK();
+  const int tiles = (int)(ld / ROWS);
+  const int chunk_tiles = (tiles + n_chunks - 1) / n_chunks;
+  static thread_local cudaEvent_t ev[TC_MAX_CHUNKS + 2];  // fork / per-chunk / join markers (never used for timing)
+  static thread_local int ev_dev = -1;
+  if (!side) {  // the kernel has the SM to itself
+    ACN_REQUIRE(n_chunks == 1, "%s: chunks need a side stream", who);
+    k_ngp_mlp_bwd_tc<4><<<G, 512, BWD_SMEM, st>>>(make_src(pts), pairs->point, pairs->weight, pairs->seg, Mcap, tab, enc, ld, d_out, d_enc,
+                                                  partial, gmax, 0, tiles);
+    ACN_LAUNCH_CHECK();
+  } else {
+    // Software pipeline over chunks of the slot list: while chunk c's table scatter (bound by the L2 atomic units, it keeps
+    // its rate with 4 CTAs per SM) runs on the side stream, chunk c+1's MLP backward (bound by its tcgen05 layer chain, half
+    // the register file) runs beside it on the same SMs.
+    int dev = 0;
+    ACN_CUDA(cudaGetDevice(&dev));
+    if (ev_dev != dev) {
+      for (int i = 0; i < TC_MAX_CHUNKS + 2; ++i) ACN_CUDA(cudaEventCreateWithFlags(&ev[i], cudaEventDisableTiming));
+      ev_dev = dev;
+    }
+    ACN_CUDA(cudaEventRecord(ev[TC_MAX_CHUNKS], st));
+    ACN_CUDA(cudaStreamWaitEvent(side, ev[TC_MAX_CHUNKS], 0));
+    const int hash_gx = (num_sms_cached() * 4 + g->levels - 1) / g->levels;
+    for (int c = 0; c < n_chunks; ++c) {
+      const int lo = c * chunk_tiles, hi = (c == n_chunks - 1) ? tiles : (c + 1) * chunk_tiles;
+      k_ngp_mlp_bwd_tc<2><<<G, 256, BWD_SMEM, st>>>(make_src(pts), pairs->point, pairs->weight, pairs->seg, Mcap, tab, enc, ld, d_out, d_enc,
+                                                    partial + (int64_t)c * G * P_FLOATS, gmax, lo, hi);
+      ACN_LAUNCH_CHECK();
+      ACN_CUDA(cudaEventRecord(ev[c], st));
+      ACN_CUDA(cudaStreamWaitEvent(side, ev[c], 0));
+      rc = launch_hash_bwd_range(pts, pairs, experts, E, g, d_enc, grads, (int64_t)lo * ROWS, (int64_t)hi * ROWS, hash_gx, side);
+      if (rc) return rc;
+    }
+    ACN_CUDA(cudaEventRecord(ev[TC_MAX_CHUNKS + 1], side));
+  }
   if (any) {
     dim3 grid((P_FLOATS + 255) / 256, E);
-    k_tc_wgrad_reduce<<<grid, 256, 0, st>>>(partial, pairs->seg, Mcap, E, G, gp);
+    k_tc_wgrad_reduce<<<grid, 256, 0, st>>>(partial, pairs->seg, Mcap, E, G, n_chunks, chunk_tiles, gp);
     ACN_LAUNCH_CHECK();
   }
+  if (side) ACN_CUDA(cudaStreamWaitEvent(st, ev[TC_MAX_CHUNKS + 1], 0));  // join: the scatter of the last chunk
+  return ACN_OK;
+}
+
+int acn_ngp_mlp_bwd_tc(const AcnPoints* pts, const AcnPairs* pairs, const AcnNgpExpert* experts, int E, const float* enc, const float* d_out,
+                       const AcnNgpExpertGrads* grads, float* d_enc, void* ws, void* stream) {
+  return run_bwd_tc(pts, pairs, experts, E, nullptr, enc, d_out, grads, d_enc, ws, 1, as_stream(stream), nullptr, "acn_ngp_mlp_bwd_tc");
+}
+
+int64_t acn_ngp_bwd_tc_pipelined_ws_bytes(int n_chunks) {
+  return (int64_t)sizeof(float) * (P_FLOATS * (int64_t)num_sms_cached() * n_chunks + 4);
+}
+
+int acn_ngp_bwd_tc_pipelined(const AcnPoints* pts, const AcnPairs* pairs, const AcnNgpExpert* experts, int E, const AcnGridDesc* g,
+                             const float* enc, const float* d_out, const AcnNgpExpertGrads* grads, float* d_enc, void* ws, int n_chunks,
+                             void* stream, void* side_stream) {
+  ACN_REQUIRE(g && side_stream && side_stream != stream, "acn_ngp_bwd_tc_pipelined: needs a grid descriptor and a distinct side stream");
+  ACN_REQUIRE(g->levels == 16 && g->features == 2, "acn_ngp_bwd_tc_pipelined: fused expert path needs L=16, F=2");
+  int rc = run_bwd_tc(pts, pairs, experts, E, g, enc, d_out, grads, d_enc, ws, n_chunks, as_stream(stream), as_stream(side_stream),
+                      "acn_ngp_bwd_tc_pipelined");
+  if (rc) return rc;
   return ACN_OK;
 }
 

@@ -76,19 +76,25 @@ __global__ void __launch_bounds__(256) k_wgrad_partial(const float* __restrict__
   }
 }
 
+// one warp per output element: lanes stride over the gx partials, then a fixed xor tree (deterministic)
 __global__ void __launch_bounds__(256) k_wgrad_reduce(const float* __restrict__ partial, int gx, int OUT, int IN, WgOut outp) {
   int e = blockIdx.y;
   int n = OUT * (IN + 1);
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+  int lane = threadIdx.x & 31;
+  for (int i = blockIdx.x * 8 + (threadIdx.x >> 5); i < n; i += gridDim.x * 8) {
     int o = i / (IN + 1), c = i - o * (IN + 1);
     int col = (c == IN) ? WG_MAXF : c;
     const float* p = partial + (int64_t)e * gx * WG_PSTRIDE + o * (WG_MAXF + 1) + col;
     float s = 0.f;
-    for (int x = 0; x < gx; ++x) s += p[(int64_t)x * WG_PSTRIDE];
-    if (c == IN) {
-      if (outp.db[e]) outp.db[e][o] = s;
-    } else {
-      if (outp.dW[e]) outp.dW[e][o * IN + c] = s;
+    for (int x = lane; x < gx; x += 32) s += p[(int64_t)x * WG_PSTRIDE];
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) s += __shfl_xor_sync(0xffffffffu, s, d);
+    if (lane == 0) {
+      if (c == IN) {
+        if (outp.db[e]) outp.db[e][o] = s;
+      } else {
+        if (outp.dW[e]) outp.dW[e][o * IN + c] = s;
+      }
     }
   }
 }
@@ -110,7 +116,7 @@ int wgrad_launch(const WgradJob& job, const int32_t* seg_dev, int E, int64_t M_s
     o.dW[e] = (e < E && dW) ? dW[e] : nullptr;
     o.db[e] = (e < E && db) ? db[e] : nullptr;
   }
-  dim3 g2((job.OUT * (job.IN + 1) + 255) / 256, E);
+  dim3 g2((job.OUT * (job.IN + 1) + 7) / 8, E);
   k_wgrad_reduce<<<g2, 256, 0, st>>>(partial, gx, job.OUT, job.IN, o);
   ACN_LAUNCH_CHECK();
   return ACN_OK;

@@ -585,8 +585,125 @@ def tc_selftest(X: Tensor, Y: Tensor, G: Tensor, mixed: bool):
     return D1, D2, D3
 
 
+# Chunks of the pipelined tensor-core backward (MLP backward of chunk c+1 beside the table scatter of chunk c on a side stream).
+# Measured on B200: the two kernels do not overlap usefully - the scatter saturates the SM's LSU queue - and the
+# half-register-file MLP variant is slower, so the default is 1 (two back-to-back launches); the path stays for experiments.
+_bwd_chunks = 1
+_side_streams = {}
+
+
+def set_bwd_chunks(n: int) -> int:
+    """1 = no pipelining (two back-to-back launches), 2..8 = software pipeline over that many chunks."""
+    global _bwd_chunks
+    if not 1 <= int(n) <= 8:
+        raise ValueError("bwd chunks must be in [1, 8]")
+    prev, _bwd_chunks = _bwd_chunks, int(n)
+    return prev
+
+
+def _side_stream(dev) -> torch.cuda.Stream:
+    key = torch.device(dev).index
+    if key not in _side_streams:
+        _side_streams[key] = torch.cuda.Stream(device=dev)
+    return _side_streams[key]
+
+
+class NgpExpertsTcFn(torch.autograd.Function):
+    """Encode + tensor-core MLPs as ONE autograd node, so that the backward can interleave the MLP backward with the
+    hash-table scatter (acn_ngp_bwd_tc_pipelined).  Inputs: E tables then 14*E MLP tensors."""
+
+    @staticmethod
+    def forward(ctx, pts: PointSet, pairs: PairList, spec: ExpertSpec, *tensors: Tensor):
+        L = lib()
+        E = spec.E
+        tb = [_need(t.detach(), "hash_table") for t in tensors[:E]]
+        ws = _check_mlp(tensors[E:], E)
+        rows = spec.grid.levels << spec.grid.log2_T
+        for t in tb:
+            if tuple(t.shape) != (rows, 2):
+                raise ValueError(f"hash_table must be ({rows},2), got {tuple(t.shape)}")
+        dev = pts.device
+        ld = int(L.acn_ngp_ld(pairs.M))
+        enc = torch.empty(32, ld, device=dev, dtype=torch.float32)
+        out = torch.empty(pts.P, 4, device=dev, dtype=torch.float32) if pairs.identity else torch.zeros(pts.P, 4, device=dev,
+                                                                                                        dtype=torch.float32)
+        cp, cq = pts.c(), pairs.c()
+        with torch.cuda.device(dev):
+            with _timed("hash_fwd"):
+                check(L.acn_ngp_encode_fwd(C.byref(cp), C.byref(cq), _expert_array(spec, tb, None), E, C.byref(spec.grid), _ptr(enc), _stream()),
+                      "acn_ngp_encode_fwd")
+            with _timed("mlp_fwd"):
+                check(L.acn_ngp_mlp_fwd_tc(C.byref(cp), C.byref(cq), _expert_array(spec, None, ws), E, _ptr(enc), _ptr(out), _stream()),
+                      "acn_ngp_mlp_fwd_tc")
+        _count(2)
+        if any(ctx.needs_input_grad):
+            ctx.pts, ctx.pairs, ctx.spec = pts, pairs, spec
+            ctx.save_for_backward(enc, *tb, *ws)
+        return out
+
+    @staticmethod
+    def backward(ctx, d_out):
+        L = lib()
+        pts, pairs, spec = ctx.pts, ctx.pairs, ctx.spec
+        E = spec.E
+        enc, *rest = ctx.saved_tensors
+        tb, ws = rest[:E], rest[E:]
+        dev = pts.device
+        d_out = _f32(d_out, "d_out")
+        grads = (AcnNgpExpertGrads * E)()
+        t_out: List[Optional[Tensor]] = []
+        m_out: List[Optional[Tensor]] = []
+        want_table = False
+        for e in range(E):
+            live = _segment_len(pairs, e) > 0
+            if ctx.needs_input_grad[3 + e] and live:
+                g = torch.zeros_like(tb[e])
+                grads[e].table = _ptr(g)
+                t_out.append(g)
+                want_table = True
+            else:
+                t_out.append(None)
+            for l in range(ACN_NGP_LAYERS):
+                for j in range(2):
+                    i = e * 14 + 2 * l + j
+                    if ctx.needs_input_grad[3 + E + i] and live:
+                        g = torch.empty_like(ws[i])
+                        if j == 0:
+                            grads[e].w[l] = _ptr(g)
+                        else:
+                            grads[e].b[l] = _ptr(g)
+                        m_out.append(g)
+                    else:
+                        m_out.append(None)
+        d_enc = torch.empty_like(enc)
+        ex = _expert_array(spec, tb, ws)
+        cp, cq = pts.c(), pairs.c()
+        with torch.cuda.device(dev):
+            if want_table and _bwd_chunks > 1:
+                wsb = torch.empty(int(L.acn_ngp_bwd_tc_pipelined_ws_bytes(_bwd_chunks)) // 4, device=dev, dtype=torch.float32)
+                side = _side_stream(dev)
+                with _timed("mlp_hash_bwd"):
+                    check(L.acn_ngp_bwd_tc_pipelined(C.byref(cp), C.byref(cq), ex, E, C.byref(spec.grid), _ptr(enc), _ptr(d_out), grads, _ptr(d_enc),
+                                                     _ptr(wsb), _bwd_chunks, _stream(), C.c_void_p(side.cuda_stream)), "acn_ngp_bwd_tc_pipelined")
+                _count(2 + 2 * _bwd_chunks + 1)
+            else:
+                wsb = torch.empty(int(L.acn_ngp_bwd_tc_ws_bytes()) // 4, device=dev, dtype=torch.float32)
+                with _timed("mlp_bwd"):
+                    check(L.acn_ngp_mlp_bwd_tc(C.byref(cp), C.byref(cq), ex, E, _ptr(enc), _ptr(d_out), grads, _ptr(d_enc), _ptr(wsb), _stream()),
+                          "acn_ngp_mlp_bwd_tc")
+                _count(3)
+                if want_table:
+                    with _timed("hash_bwd"):
+                        check(L.acn_ngp_encode_bwd(C.byref(cp), C.byref(cq), ex, E, C.byref(spec.grid), _ptr(d_enc), grads, _stream()),
+                              "acn_ngp_encode_bwd")
+                    _count(1)
+        return (None, None, None, *t_out, *m_out)
+
+
 def ngp_experts(pts: PointSet, pairs: PairList, spec: ExpertSpec, tables: Sequence[Tensor], mlp: Sequence[Tensor]) -> Tensor:
     """(P,4) [rgb, sigma] of E hash-grid experts over `pairs` (MetaNGP.forward / MetaContainer.forward)."""
+    if _mlp_math == "f16tc":
+        return NgpExpertsTcFn.apply(pts, pairs, spec, *tables, *mlp)
     enc = NgpEncodeFn.apply(pts, pairs, spec, *tables)
     return NgpMlpFn.apply(enc, pts, pairs, spec, *mlp)
 
