@@ -173,6 +173,55 @@ def teacher_colors(pool, rank, world, device):
     return out
 
 
+def build_c5(device):
+    """Config 5 scene: 8 experts on a 1x2x4 grid, 2^20-row tables (1 GiB), trained-like N(0,0.1) tables; replicated on every rank."""
+    from nerf_sys_b200.models.inr import MetaContainer
+    from nerf_sys_b200.nerfs.scene_box import SceneBox
+    from oracle import acnerf_oracle as O  # scene constants / initial weights only
+    aabb, cent, boxes = O.grid_scene(2, 4)
+    cfg = dict(O.HASH_CFG)
+    cfg["log2_hashmap_size"] = LOG2_T
+    st = O.init_ngp_state(8, aabb, cent, boxes, cfg, seed=3, table_std=0.1)
+    model = MetaContainer(8, cent, aabb, "instant", boundary_margin=1.05, cluster_2d=True, use_bg_nerf=True, occ_conf={"use_occ": False},
+                          expert_box_list=[SceneBox(b) for b in boxes], hidden=64, sigma_depth=2, color_depth=2, color_hidden=64,
+                          dir_encoding="spherical", use_sigmoid_rgb=True, hash_enc_conf=cfg)
+    model.load_state_dict(st, strict=True)
+    return model.to(device).eval(), aabb
+
+
+@torch.no_grad()
+def render_c5(device, world, barrier, max_over_ranks, frames=4):
+    """1920x1080 x 64 samples through the 8-expert container, image rows sharded over the ranks, frame gathered on every rank."""
+    from nerf_sys_b200 import parallel as PL
+    from nerf_sys_b200.nerfs.ray_rendering import render_image
+    from nerf_sys_b200.nerfs.scene_box import SceneBox
+    from oracle import acnerf_oracle as O
+    model, aabb = build_c5(device)
+    H, W, f = 1080, 1920, 1480.0
+    sb = SceneBox(aabb.to(device))
+
+    def frame(i):
+        c2w = O.ring_pose(i, 20, radius=0.9)
+        kw = dict(H=H, W=W, fx=f, fy=f, cx=W / 2, cy=H / 2, c2w=c2w, scene_box=sb, ray_samples=64)
+        return PL.render_image_sharded(lambda r0, r1: render_image(model, row_range=(r0, r1), **kw), H, W)
+
+    frame(0)
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(frames):
+        rgb, depth, acc = frame(1 + i)
+    e1.record()
+    barrier()
+    ms = max_over_ranks(e0.elapsed_time(e1))
+    cover = float((acc > 0.01).float().mean().item())
+    del model
+    torch.cuda.empty_cache()
+    return {"value": frames * H * W / (ms / 1e3), "unit": "rays/s", "ms_per_frame": ms / frames, "coverage": cover,
+            "config": f"config[4]: 1920x1080 x 64 samples, 8 experts (soft routing, margin 1.05), eval, rows sharded over {world} GPU(s), "
+                      "frame all-gathered"}
+
+
 class P:  # the argparse namespace fields compute_mse_loss reads (common/args.py)
     ray_samples, chunk_points, color_space = S_TRAIN, 4456448, "identity"
 
@@ -398,6 +447,10 @@ def main():
                   "ms_per_frame": rms / nv}
         model.train()
 
+    c5 = None
+    if not args.no_render:
+        c5 = render_c5(dev, world, barrier, max_over_ranks)
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         n = 2048
@@ -422,7 +475,7 @@ def main():
                                             "collective": "none" if world == 1 else "nccl all-reduce of 643 bg-head grads"},
             "clocks": clk, "e2e": {"value": world * N_RAYS * K / (ms_e2e / 1e3), "unit": "rays/s", "h2d_bytes_per_step": bytes_in,
                                    "d2h_bytes_per_step": 4, "ms_per_step": ms_e2e / K},
-            "gpu_launches": launches, "roofline": roofline, "kernels": kern, "render": render, "cpu_baseline": cpu,
+            "gpu_launches": launches, "roofline": roofline, "kernels": kern, "render": render, "render_c5": c5, "cpu_baseline": cpu,
             "final_loss": final_loss}))
     if world > 1:
         # Leave without tearing NCCL down: the captured graph still references the communicator's kernels and

@@ -102,7 +102,7 @@ def render_image(model, *, H: int, W: int, fx: float, fy: float, cx: float, cy: 
     device = next(model.parameters()).device
     aabb = None if scene_box is None else scene_box.aabb
     if rows_per_chunk is None:
-        rows_per_chunk = max(1, min(H, (1 << 22) // max(1, W * ray_samples)))  # ~4M sample points per block
+        rows_per_chunk = max(1, min(H, (1 << 24) // max(1, W * ray_samples)))  # ~16M sample points (~2.5 GB of staging) per block
     R0, R1 = (0, H) if row_range is None else (int(row_range[0]), int(row_range[1]))
     if not (0 <= R0 <= R1 <= H):
         raise ValueError(f"row_range {row_range} outside [0, {H}]")
