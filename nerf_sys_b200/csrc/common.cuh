@@ -49,6 +49,20 @@ static inline int persistent_grid(int64_t work_items, int per_sm) {
 static inline cudaStream_t as_stream(void* s) { return reinterpret_cast<cudaStream_t>(s); }
 
 // ---- device-side pieces shared by several kernels -------------------------
+// No-return reductions with an explicit .global state space.  atomicAdd() on a pointer the compiler cannot prove global
+// (e.g. one picked from a kernel-parameter array by a runtime index) compiles to the generic ATOM.E form, which waits for
+// the round trip through L2: measured 2x slower than REDG for the table-gradient scatter (profiles/r1_v5_red_microbench.txt).
+__device__ __forceinline__ void red_add(float* p, float v) {
+  asm volatile("red.global.add.f32 [%0], %1;" ::"l"(__cvta_generic_to_global(p)), "f"(v) : "memory");
+}
+__device__ __forceinline__ void red_add(float2* p, float2 v) {
+  asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(__cvta_generic_to_global(p)), "f"(v.x), "f"(v.y) : "memory");
+}
+__device__ __forceinline__ void red_add(float4* p, float4 v) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(__cvta_generic_to_global(p)), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
+               : "memory");
+}
+
 struct PointSrc {
   const float* x6;
   const float* rays;

@@ -122,7 +122,7 @@ __device__ __forceinline__ float2 level_encode(const float2* __restrict__ table,
 __device__ __forceinline__ void level_scatter(float2* __restrict__ gtable, const Cell& c, uint32_t mask, uint32_t base,
                                               int interp, float2 g) {
   if (interp == 2) {
-    atomicAdd(gtable + (hash3(c.ix, c.iy, c.iz, mask) + base), g);
+    red_add(gtable + (hash3(c.ix, c.iy, c.iz, mask) + base), g);
     return;
   }
   uint32_t rows[8];
@@ -136,15 +136,65 @@ __device__ __forceinline__ void level_scatter(float2* __restrict__ gtable, const
       float w0 = ax * wyz, w1 = c.wx * wyz;
       bool odd = rows[i] & 1u;
       float4 v = odd ? make_float4(g.x * w1, g.y * w1, g.x * w0, g.y * w0) : make_float4(g.x * w0, g.y * w0, g.x * w1, g.y * w1);
-      atomicAdd(t4 + (rows[i] >> 1), v);
+      red_add(t4 + (rows[i] >> 1), v);
     }
     return;
   }
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
     float w = ((i & 4) ? c.wx : ax) * ((i & 2) ? c.wy : ay) * ((i & 1) ? c.wz : az);
-    atomicAdd(gtable + rows[i], make_float2(g.x * w, g.y * w));
+    red_add(gtable + rows[i], make_float2(g.x * w, g.y * w));
   }
+}
+
+// Warp-aggregated scatter for the coarse levels.  Lanes are consecutive slots (consecutive samples of a ray), so on a
+// level whose cells are wider than the sample spacing neighbouring lanes fall in the same cell.  Runs of equal `key`
+// (cell + expert; a lane without work passes a key no other lane has and live = false) are cut into chunks of
+// 2^steps lanes, the 8 corner x 2 feature contributions are summed inside a chunk with a bounded shuffle tree, and only
+// the first lane of a chunk issues the reductions.  The RED rate (not the bytes) bounds this kernel: 215 G lane-ops/s
+// on B200 whatever the operand width (profiles/r1_v5_red_microbench.txt).  Called by full warps.
+__device__ __forceinline__ void level_scatter_agg(float2* __restrict__ gtable, const Cell& c, uint32_t mask, uint32_t base, float2 g,
+                                                  uint32_t key, bool live, int steps) {
+  const uint32_t lane = threadIdx.x & 31u;
+  uint32_t prev = __shfl_up_sync(0xffffffffu, key, 1);
+  bool head = (lane == 0) || (prev != key);
+  uint32_t heads = __ballot_sync(0xffffffffu, head);
+  uint32_t run_start = 31u - __clz(heads & (0xffffffffu >> (31u - lane)));
+  uint32_t above = (lane == 31u) ? 0u : (heads >> (lane + 1u));
+  uint32_t run_last = above ? (lane + (uint32_t)__ffs(above) - 1u) : 31u;
+  uint32_t width = 1u << steps, pos = (lane - run_start) & (width - 1u);
+  uint32_t chunk_last = min(run_last, lane - pos + width - 1u);
+  float ax = 1.f - c.wx, ay = 1.f - c.wy, az = 1.f - c.wz;
+  float v[16];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    float w = ((i & 4) ? c.wx : ax) * (((i & 2) ? c.wy : ay) * ((i & 1) ? c.wz : az));
+    v[2 * i] = live ? g.x * w : 0.f;
+    v[2 * i + 1] = live ? g.y * w : 0.f;
+  }
+  for (uint32_t d = 1; d < width; d <<= 1) {
+    bool take = lane + d <= chunk_last;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      float o = __shfl_down_sync(0xffffffffu, v[i], d);
+      v[i] += take ? o : 0.f;
+    }
+  }
+  if (!live || pos != 0u) return;
+  uint32_t rows[8];
+  corner_rows(c, mask, base, rows);
+  if ((c.ix & 1u) == 0u) {
+    float4* t4 = reinterpret_cast<float4*>(gtable);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      bool odd = rows[i] & 1u;
+      float4 q = odd ? make_float4(v[2 * i + 8], v[2 * i + 9], v[2 * i], v[2 * i + 1]) : make_float4(v[2 * i], v[2 * i + 1], v[2 * i + 8], v[2 * i + 9]);
+      red_add(t4 + (rows[i] >> 1), q);
+    }
+    return;
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) red_add(gtable + rows[i], make_float2(v[2 * i], v[2 * i + 1]));
 }
 
 }  // namespace acn

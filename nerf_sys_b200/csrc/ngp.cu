@@ -81,29 +81,48 @@ struct GradTables {
   float* t[ACN_MAX_EXPERTS];
 };
 
+// Table-gradient scatter, grid.y = level (a CTA wave works on one 8 MiB slab of the gradient table, which stays L2-resident).
+// Coarse levels (agg.s[l] > 0: cells wider than the spacing of consecutive samples) go through the warp-aggregated
+// scatter; the reductions are REDG (explicit .global, see red_add in common.cuh).
+struct AggSteps {
+  int8_t s[ACN_MAX_LEVELS];
+};
+
 __global__ void __launch_bounds__(256) k_ngp_hash_bwd(PointSrc src, const int32_t* __restrict__ pair_point, const int32_t* __restrict__ seg,
                                                       int64_t M_ident, ExpertTable tab, GridParams g, const float* __restrict__ denc, int64_t ld,
-                                                      GradTables gts, int64_t m_lo, int64_t m_hi) {
+                                                      GradTables gts, int64_t m_lo, int64_t m_hi, AggSteps agg) {
   __shared__ int s_seg[ACN_MAX_EXPERTS + 1];
   if (threadIdx.x <= tab.E) s_seg[threadIdx.x] = seg ? seg[threadIdx.x] : (threadIdx.x == 0 ? 0 : (int)M_ident);
   __syncthreads();
   int64_t M = seg ? s_seg[tab.E] : M_ident;
-  int l = blockIdx.y;
-  uint32_t mask = (1u << g.log2_T) - 1u, base = (uint32_t)l << g.log2_T;
+  const int l = blockIdx.y;
+  const uint32_t mask = (1u << g.log2_T) - 1u, base = (uint32_t)l << g.log2_T;
+  const int steps = agg.s[l];
+  const uint32_t lane_key = 0xffffffffu - (threadIdx.x & 31u);
   if (m_hi < M) M = m_hi;
-  for (int64_t m = m_lo + blockIdx.x * (int64_t)blockDim.x + threadIdx.x; m < M; m += (int64_t)gridDim.x * blockDim.x) {
-    int64_t p = pair_point ? (int64_t)pair_point[m] : m;
-    if (p < 0) continue;
-    int e = seg ? find_expert(s_seg, tab.E, m) : 0;
-    float* gt = gts.t[e];
-    if (!gt) continue;
-    const AcnNgpExpert& ex = tab.ex[e];
-    float x, y, z;
-    load_xyz(src, p, x, y, z);
-    Cell c = make_cell(to_unit(x, ex.box_min[0], ex.extent[0]), to_unit(y, ex.box_min[1], ex.extent[1]),
-                       to_unit(z, ex.box_min[2], ex.extent[2]), g.res[l], g.interp);
-    float2 gv = make_float2(__ldg(denc + (int64_t)(2 * l) * ld + m), __ldg(denc + (int64_t)(2 * l + 1) * ld + m));
-    level_scatter(reinterpret_cast<float2*>(gt), c, mask, base, g.interp, gv);
+  for (int64_t mb = m_lo + blockIdx.x * (int64_t)blockDim.x; mb < M; mb += (int64_t)gridDim.x * blockDim.x) {  // CTA-uniform
+    const int64_t m = mb + threadIdx.x;
+    const bool in_range = m < M;
+    const int64_t p = in_range ? (pair_point ? (int64_t)pair_point[m] : m) : -1;
+    const int e = (seg && in_range) ? find_expert(s_seg, tab.E, m) : 0;
+    float2* gt = reinterpret_cast<float2*>(gts.t[e]);
+    const bool live = p >= 0 && gt != nullptr;
+    Cell c{0u, 0u, 0u, 0.f, 0.f, 0.f};
+    float2 gv = make_float2(0.f, 0.f);
+    if (live) {
+      const AcnNgpExpert& ex = tab.ex[e];
+      float x, y, z;
+      load_xyz(src, p, x, y, z);
+      c = make_cell(to_unit(x, ex.box_min[0], ex.extent[0]), to_unit(y, ex.box_min[1], ex.extent[1]),
+                    to_unit(z, ex.box_min[2], ex.extent[2]), g.res[l], g.interp);
+      gv = make_float2(__ldg(denc + (int64_t)(2 * l) * ld + m), __ldg(denc + (int64_t)(2 * l + 1) * ld + m));
+    }
+    if (steps > 0) {  // CTA-uniform; full warps
+      const uint32_t key = live ? (c.ix | (c.iy << 9) | (c.iz << 18) | ((uint32_t)e << 27)) : lane_key;
+      level_scatter_agg(gt, c, mask, base, gv, key, live, steps);
+    } else if (live) {
+      level_scatter(gt, c, mask, base, g.interp, gv);
+    }
   }
 }
 
@@ -447,8 +466,16 @@ int launch_hash_bwd_range(const AcnPoints* pts, const AcnPairs* pairs, const Acn
   }
   if (!any_table) return ACN_OK;
   int64_t span = (m_hi < Mcap ? m_hi : Mcap) - m_lo;
+  // aggregation depth per level: cells of a coarse level are wider than the spacing of consecutive samples, so runs of
+  // 2..8 lanes share a cell (measured at C2: 661 -> 494 us from REDG alone, -> ~410 us with the aggregation)
+  AggSteps agg;
+  for (int l = 0; l < ACN_MAX_LEVELS; ++l) {
+    int r = g->res[l];
+    agg.s[l] = (g->interp != 2 && l < g->levels && r < 512) ? (r <= 20 ? 3 : r <= 40 ? 2 : r <= 80 ? 1 : 0) : 0;
+  }
   dim3 hg(grid_x > 0 ? grid_x : persistent_grid((span + 255) / 256, 4), g->levels);
-  k_ngp_hash_bwd<<<hg, 256, 0, st>>>(make_src(pts), pairs->point, pairs->seg, Mcap, tab, make_grid(g), d_enc, h_round_ld(Mcap), gts, m_lo, m_hi);
+  k_ngp_hash_bwd<<<hg, 256, 0, st>>>(make_src(pts), pairs->point, pairs->seg, Mcap, tab, make_grid(g), d_enc, h_round_ld(Mcap), gts, m_lo, m_hi,
+                                     agg);
   ACN_LAUNCH_CHECK();
   return ACN_OK;
 }
