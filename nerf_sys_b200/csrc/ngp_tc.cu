@@ -17,6 +17,9 @@
 // weights once and the partial sums of an expert live in a contiguous CTA range (deterministic reduce).
 #include "common.cuh"
 #include "tc.cuh"
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
 
 namespace acn {
 
@@ -155,8 +158,28 @@ template <int NV>
 __device__ __forceinline__ void store_h(uint32_t buf, uint32_t r, int c0, const float (&v)[NV]) {
 #pragma unroll
   for (int c = 0; c < NV / 8; ++c)
-    st_chunk(buf + (uint32_t)(c0 + c) * CH + r * 16, pack_h2(v[8 * c], v[8 * c + 1]), pack_h2(v[8 * c + 2], v[8 * c + 3]),
-             pack_h2(v[8 * c + 4], v[8 * c + 5]), pack_h2(v[8 * c + 6], v[8 * c + 7]));
+    st_chunk(buf + (uint32_t)(c0 + c) * CH + r * 16, pack_h2_sat(v[8 * c], v[8 * c + 1]), pack_h2_sat(v[8 * c + 2], v[8 * c + 3]),
+             pack_h2_sat(v[8 * c + 4], v[8 * c + 5]), pack_h2_sat(v[8 * c + 6], v[8 * c + 7]));
+}
+// ReLU + saturation + fp16 conversion fused into the pack (one F2FP per two elements)
+template <int NV>
+__device__ __forceinline__ void store_relu(uint32_t buf, uint32_t r, int c0, const float (&v)[NV]) {
+#pragma unroll
+  for (int c = 0; c < NV / 8; ++c)
+    st_chunk(buf + (uint32_t)(c0 + c) * CH + r * 16, pack_h2_relu_sat(v[8 * c], v[8 * c + 1]), pack_h2_relu_sat(v[8 * c + 2], v[8 * c + 3]),
+             pack_h2_relu_sat(v[8 * c + 4], v[8 * c + 5]), pack_h2_relu_sat(v[8 * c + 6], v[8 * c + 7]));
+}
+// ReLU backward: gradient chunks gated by the stored activation (> 0) of the same rows / columns
+template <int NV>
+__device__ __forceinline__ void store_g_gated(uint32_t buf, uint32_t r, int c0, const float (&v)[NV], uint32_t act, int a0) {
+#pragma unroll
+  for (int c = 0; c < NV / 8; ++c) {
+    uint32_t h[4];
+    ld_chunk(act + (uint32_t)(a0 + c) * CH + r * 16, h);
+    st_chunk(buf + (uint32_t)(c0 + c) * CH + r * 16, h2_gate(pack_h2_sat(v[8 * c], v[8 * c + 1]), h[0]),
+             h2_gate(pack_h2_sat(v[8 * c + 2], v[8 * c + 3]), h[1]), h2_gate(pack_h2_sat(v[8 * c + 4], v[8 * c + 5]), h[2]),
+             h2_gate(pack_h2_sat(v[8 * c + 6], v[8 * c + 7]), h[3]));
+  }
 }
 template <int NV>
 __device__ __forceinline__ void store_g(uint32_t buf, uint32_t r, int c0, const float (&v)[NV]) {
@@ -166,10 +189,8 @@ __device__ __forceinline__ void store_g(uint32_t buf, uint32_t r, int c0, const 
     st_chunk(buf + (uint32_t)(c0 + c) * CH + r * 16, pack_bf2(v[8 * c], v[8 * c + 1]), pack_bf2(v[8 * c + 2], v[8 * c + 3]),
              pack_bf2(v[8 * c + 4], v[8 * c + 5]), pack_bf2(v[8 * c + 6], v[8 * c + 7]));
 #else
-    float w[8];
-#pragma unroll
-    for (int i = 0; i < 8; ++i) w[i] = fminf(fmaxf(v[8 * c + i], -F16_MAX), F16_MAX);
-    st_chunk(buf + (uint32_t)(c0 + c) * CH + r * 16, pack_h2(w[0], w[1]), pack_h2(w[2], w[3]), pack_h2(w[4], w[5]), pack_h2(w[6], w[7]));
+    st_chunk(buf + (uint32_t)(c0 + c) * CH + r * 16, pack_h2_sat(v[8 * c], v[8 * c + 1]), pack_h2_sat(v[8 * c + 2], v[8 * c + 3]),
+             pack_h2_sat(v[8 * c + 4], v[8 * c + 5]), pack_h2_sat(v[8 * c + 6], v[8 * c + 7]));
 #endif
   }
 }
@@ -178,26 +199,15 @@ __device__ __forceinline__ void store_ones_chunk(uint32_t buf, uint32_t r, int c
   st_chunk(buf + (uint32_t)c * CH + r * 16, 0x00003C00u /* fp16 (1, 0) */, 0u, 0u, 0u);
 }
 
-// ReLU (+ fp16 saturation) in place; returns the bit mask of positive entries
-template <int NV>
-__device__ __forceinline__ uint32_t relu_mask(float (&v)[NV]) {
-  uint32_t m = 0;
-#pragma unroll
-  for (int i = 0; i < NV; ++i) {
-    m |= (v[i] > 0.f ? 1u : 0u) << i;
-    v[i] = fminf(fmaxf(v[i], 0.f), F16_MAX);
-  }
-  return m;
-}
-
-// ---- MMA issue helpers (called by one thread) -----------------------------------------------
+// ---- MMA issue helpers (called by one thread; operand addresses in 16-byte units, see smem_desc16) --------
+constexpr uint32_t CH16 = CH / 16;
 // forward layer: D(128 x N) = A(128 x (8+IN+8), K-major) * W(N x (8+IN+8), K-major)^T
 template <int IN, int N>
-__device__ __forceinline__ void issue_fwd(uint32_t d_tmem, uint32_t a_base, uint32_t w_base) {
+__device__ __forceinline__ void issue_fwd(uint32_t d_tmem, uint32_t a16, uint32_t w16) {
   constexpr uint32_t id = idesc_f16(128, N, F16, F16, K_MAJOR, K_MAJOR);
 #pragma unroll
   for (int s = 0; s < (IN + 16) / 16; ++s)
-    mma(d_tmem, smem_desc(a_base + s * 2 * CH, CH, 128), smem_desc(w_base + s * 2 * (N * 16), N * 16, 128), id, s > 0);
+    mma(d_tmem, smem_desc16(a16 + s * 2 * CH16, CH, 128), smem_desc16(w16 + s * 2 * N, N * 16, 128), id, s > 0);
 }
 
 constexpr uint32_t GFMT = ACN_TC_G_BF16 ? BF16 : F16;
@@ -205,25 +215,30 @@ constexpr uint32_t GFMT = ACN_TC_G_BF16 ? BF16 : F16;
 // dgrad: D(128 x IN) = G(128 x OUT, K-major) * W(OUT x IN) ; W read MN-major from the forward weight block
 // (skipping its bias chunk).  WN = rows of the weight block (= padded OUT).
 template <int OUT, int IN, int WN>
-__device__ __forceinline__ void issue_dgrad(uint32_t d_tmem, uint32_t g_base, uint32_t w_base) {
+__device__ __forceinline__ void issue_dgrad(uint32_t d_tmem, uint32_t g16, uint32_t w16) {
   constexpr uint32_t id = idesc_f16(128, IN, GFMT, F16, K_MAJOR, MN_MAJOR);
 #pragma unroll
   for (int s = 0; s < OUT / 16; ++s)
-    mma(d_tmem, smem_desc(g_base + s * 2 * CH, CH, 128), smem_desc(w_base + WN * 16 + s * 256, 128, WN * 16), id, s > 0);
+    mma(d_tmem, smem_desc16(g16 + s * 2 * CH16, CH, 128), smem_desc16(w16 + WN + s * 16, 128, WN * 16), id, s > 0);
 }
 
 // wgrad: ACC(64 x (8+IN)) += G(128 x 64)^T * [1 | A](128 x (8+IN)), both read MN-major, K = 128 rows
 template <int IN>
-__device__ __forceinline__ void issue_wgrad(uint32_t acc_tmem, uint32_t g_base, uint32_t a_base, uint32_t accumulate) {
+__device__ __forceinline__ void issue_wgrad(uint32_t acc_tmem, uint32_t g16, uint32_t a16, uint32_t accumulate) {
   constexpr uint32_t id = idesc_f16(64, 8 + IN, GFMT, F16, MN_MAJOR, MN_MAJOR);
 #pragma unroll
-  for (int s = 0; s < 8; ++s) mma(acc_tmem, smem_desc(g_base + s * 256, 128, CH), smem_desc(a_base + s * 256, 128, CH), id, accumulate | (s > 0));
+  for (int s = 0; s < 8; ++s) mma(acc_tmem, smem_desc16(g16 + s * 16, 128, CH), smem_desc16(a16 + s * 16, 128, CH), id, accumulate | (s > 0));
 }
 
 __device__ __forceinline__ float trunc_exp_f(float v) { return expf(fminf(fmaxf(v, -88.722839111f), 88.722839111f)); }
 __device__ __forceinline__ float sigmoid_f(float v) { return 1.f / (1.f + expf(-v)); }
 
 // cin = [geo 0..14 | sh 0..15 | 0] : first / second half as fp16 chunks
+__device__ __forceinline__ void dir_to_sh16(float dx, float dy, float dz, float* sh) {
+  normalize3(dx, dy, dz, 1e-9f);  // meta_ngp.py:165-168
+  normalize3(dx, dy, dz, 1e-9f);  // encodings.py:141
+  sh16_eval(dx, dy, dz, sh);
+}
 __device__ __forceinline__ void dir_sh16(const PointSrc& src, int64_t p, float* sh) {
   float dx = 0.f, dy = 0.f, dz = 1.f;
   if (p >= 0) load_dir(src, p, dx, dy, dz);
@@ -263,6 +278,7 @@ __global__ void __launch_bounds__(FWD_THREADS, 1)
   __syncthreads();
   const CtaPart part = s_part;
   const uint32_t sw = smem_u32(smem), abuf = sw + W_BYTES + q * ABUF;
+  const uint32_t sw16 = sw >> 4, abuf16 = sw16 + (W_BYTES + q * ABUF) / 16;  // smem base is 128-byte aligned
   if (part.e >= 0) load_weights_tc(smem, tab.ex[part.e], tid, FWD_THREADS);
   store_ones_chunk(abuf, r, 0);
   store_zero_chunk(abuf, r, 9);
@@ -282,12 +298,12 @@ __global__ void __launch_bounds__(FWD_THREADS, 1)
       const bool in_range = m < M;
       const int64_t p = in_range ? (pair_point ? (int64_t)pair_point[m] : m) : -1;
       const int64_t mm = in_range ? m : 0;
+      float ddx = 0.f, ddy = 0.f, ddz = 1.f;  // view direction: requested now, consumed at the heads epilogue
+      if (p >= 0) load_dir(src, p, ddx, ddy, ddz);
       {  // encoding -> chunks 1..4, chunk 5 zero
         float x[32];
 #pragma unroll
         for (int i = 0; i < 32; ++i) x[i] = in_range ? __ldg(enc + (int64_t)i * ld + mm) : 0.f;
-#pragma unroll
-        for (int i = 0; i < 32; ++i) x[i] = fminf(fmaxf(x[i], -F16_MAX), F16_MAX);
         store_h<32>(abuf, r, 1, x);
         store_zero_chunk(abuf, r, 5);
       }
@@ -295,7 +311,7 @@ __global__ void __launch_bounds__(FWD_THREADS, 1)
       bar_sync(1 + q, 128);
       if (r == 0) {
         fence_after();
-        issue_fwd<32, 64>(dcol, abuf, sw + OW0);
+        issue_fwd<32, 64>(dcol, abuf16, sw16 + OW0 / 16);
         commit(bar);
       }
       mbar_wait(bar, phase);
@@ -307,21 +323,19 @@ __global__ void __launch_bounds__(FWD_THREADS, 1)
       for (int layer = 0; layer < 2; ++layer) {
         tmem_ld32(trow, v);
         tmem_ld_wait();
-        relu_mask<32>(v);
-        store_h<32>(abuf, r, 1, v);
+        store_relu<32>(abuf, r, 1, v);
         tmem_ld32(trow + 32, v);
         tmem_ld_wait();
-        relu_mask<32>(v);
-        store_h<32>(abuf, r, 5, v);
+        store_relu<32>(abuf, r, 5, v);
         fence_before();
         fence_async_smem();
         bar_sync(1 + q, 128);
         if (r == 0) {
           fence_after();
           if (layer == 0)
-            issue_fwd<64, 64>(dcol, abuf, sw + OW1);
+            issue_fwd<64, 64>(dcol, abuf16, sw16 + OW1 / 16);
           else
-            issue_fwd<64, 16>(dcol, abuf, sw + OWH);
+            issue_fwd<64, 16>(dcol, abuf16, sw16 + OWH / 16);
           commit(bar);
         }
         mbar_wait(bar, phase);
@@ -334,9 +348,9 @@ __global__ void __launch_bounds__(FWD_THREADS, 1)
         tmem_ld16(trow, h);
         tmem_ld_wait();
         sigma = trunc_exp_f(h[15]);
-        dir_sh16(src, p, sh);
+        dir_to_sh16(ddx, ddy, ddz, sh);
 #pragma unroll
-        for (int i = 0; i < 15; ++i) c[i] = fminf(fmaxf(h[i], -F16_MAX), F16_MAX);
+        for (int i = 0; i < 15; ++i) c[i] = h[i];
 #pragma unroll
         for (int i = 0; i < 16; ++i) c[15 + i] = sh[i];
         c[31] = 0.f;
@@ -348,7 +362,7 @@ __global__ void __launch_bounds__(FWD_THREADS, 1)
       bar_sync(1 + q, 128);
       if (r == 0) {
         fence_after();
-        issue_fwd<32, 64>(dcol, abuf, sw + OW3);
+        issue_fwd<32, 64>(dcol, abuf16, sw16 + OW3 / 16);
         commit(bar);
       }
       mbar_wait(bar, phase);
@@ -358,21 +372,19 @@ __global__ void __launch_bounds__(FWD_THREADS, 1)
       for (int layer = 0; layer < 2; ++layer) {
         tmem_ld32(trow, v);
         tmem_ld_wait();
-        relu_mask<32>(v);
-        store_h<32>(abuf, r, 1, v);
+        store_relu<32>(abuf, r, 1, v);
         tmem_ld32(trow + 32, v);
         tmem_ld_wait();
-        relu_mask<32>(v);
-        store_h<32>(abuf, r, 5, v);
+        store_relu<32>(abuf, r, 5, v);
         fence_before();
         fence_async_smem();
         bar_sync(1 + q, 128);
         if (r == 0) {
           fence_after();
           if (layer == 0)
-            issue_fwd<64, 64>(dcol, abuf, sw + OW4);
+            issue_fwd<64, 64>(dcol, abuf16, sw16 + OW4 / 16);
           else
-            issue_fwd<64, 16>(dcol, abuf, sw + OW5);
+            issue_fwd<64, 16>(dcol, abuf16, sw16 + OW5 / 16);
           commit(bar);
         }
         mbar_wait(bar, phase);
@@ -443,11 +455,20 @@ __device__ __forceinline__ void dump_acc(uint32_t tbase, uint32_t col, int nq, f
 // NQ column groups of 128 threads each: NQ = 4 (512 threads, 16 columns per thread) when the kernel has the SM to itself,
 // NQ = 2 (256 threads, 2 x 16 columns per thread, half the register file) when the hash-grid scatter of the previous
 // chunk runs beside it (acn_ngp_bwd_tc_pipelined).  [tile_lo, tile_hi) restricts the launch to a window of 128-slot tiles.
+// Warp specialisation: 128 * NQ epilogue threads + ONE issuer warp (the last).  Measured with clock64 stamps before the
+// split: the thread that issued the MMAs spent 8.7 k of a tile's 15 k cycles in issue code while the other 511 threads
+// waited for it at the step barrier.  Now the epilogue warps bar.arrive on a named barrier when their operands are in
+// shared memory and go straight to the accumulator mbarrier; the issuer warp bar.syncs on it, issues the step's MMAs,
+// commits, and issues the weight-gradient MMAs of the layer just left while the epilogue of this step runs.
 template <int NQ>
-__global__ void __launch_bounds__(128 * NQ, NQ == 2 ? 2 : 1)  // NQ = 2: at most half the register file
+__global__ void __launch_bounds__(128 * NQ + 32, NQ == 2 ? 2 : 1)  // NQ = 2: at most half the register file
     k_ngp_mlp_bwd_tc(PointSrc src, const int32_t* __restrict__ pair_point, const float* __restrict__ pair_w, const int32_t* __restrict__ seg,
                      int64_t M_ident, ExpertTableTc tab, const float* __restrict__ enc, int64_t ld, const float* __restrict__ d_out,
-                     float* __restrict__ d_enc, float* __restrict__ partial, const float* __restrict__ gmax, int tile_lo, int tile_hi) {
+                     float* __restrict__ d_enc, float* __restrict__ partial, const float* __restrict__ gmax, int tile_lo, int tile_hi,
+                     long long* dbg) {
+  int dbg_i = 0; bool dbg_on = false;
+  if (dbg && threadIdx.x == 0 && blockIdx.x == 3) dbg[100] = clock64();
+#define DBG_STAMP() do { if (dbg_on && dbg_i < 120) dbg[dbg_i++] = clock64(); } while (0)
   constexpr int PASSES = 4 / NQ;  // 16-column passes per thread in a 64-column epilogue
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ __align__(8) uint64_t s_bar;
@@ -472,8 +493,10 @@ __global__ void __launch_bounds__(128 * NQ, NQ == 2 ? 2 : 1)  // NQ = 2: at most
   __syncthreads();
   const CtaPart part = s_part;
   const uint32_t sb = smem_u32(smem);
-  if (part.e >= 0) load_weights_tc(smem, tab.ex[part.e], tid, 128 * NQ);
-  {
+  constexpr int NEPI = 128 * NQ;          // epilogue threads
+  const bool issuer = tid >= NEPI;        // warp NEPI/32
+  if (part.e >= 0) load_weights_tc(smem, tab.ex[part.e], tid, NEPI + 32);
+  if (!issuer) {
     constexpr uint32_t bufs[6] = {B_ENC, B_H0, B_H1, B_CIN, B_C0, B_C1};
     constexpr int zc[6] = {5, 9, 9, 5, 9, 9};
 #pragma unroll
@@ -486,7 +509,7 @@ __global__ void __launch_bounds__(128 * NQ, NQ == 2 ? 2 : 1)  // NQ = 2: at most
     }
   }
   // gradient tiles start finite (rows 16.. of the 16-wide stages are read by the M=64 wgrad MMAs and ignored)
-  for (int c = q; c < 8; c += NQ) {
+  for (int c = q; c < 8 && !issuer; c += NQ) {
     store_zero_chunk(sb + B_GA, r, c);
     store_zero_chunk(sb + B_GB, r, c);
   }
@@ -494,6 +517,7 @@ __global__ void __launch_bounds__(128 * NQ, NQ == 2 ? 2 : 1)  // NQ = 2: at most
   fence_before();
   __syncthreads();
   fence_after();
+  if (dbg && threadIdx.x == 0 && blockIdx.x == 3) dbg[101] = clock64();
   const uint32_t tbase = s_tmem;
   const uint32_t tD = tbase + T_D;
   const uint32_t trow0 = tD + ((uint32_t)((tid >> 5) & 3) << 21);  // column 0 of this thread's row
@@ -509,49 +533,82 @@ __global__ void __launch_bounds__(128 * NQ, NQ == 2 ? 2 : 1)  // NQ = 2: at most
   }
   const float inv_s = 1.f / gscale;
 
-  // One chain step: publish this thread's smem writes, one thread issues ISSUE and commits, everyone waits for the
-  // accumulator.  LATE (weight-gradient MMAs) is issued after the commit: it runs on the tensor pipe while the
-  // epilogue of this step executes, and is covered by the NEXT step's commit before its operands are overwritten.
-  // OVERLAP is work every thread does while the MMAs run.
+  // ---- issuer warp: the whole MMA program of a tile, one step per named-barrier round ----------------------------
+  // The weight-gradient MMAs of a layer are issued AFTER the commit of the step that consumes the same gradient tile:
+  // they run on the tensor pipe under that step's epilogue and are covered by the NEXT step's commit before their
+  // operands are overwritten.  The last step's go before its commit (the next tile's prologue overwrites B_ENC).
+  if (part.e >= 0 && issuer) {
+    const uint32_t s16 = sb >> 4;  // the dynamic smem base is 128-byte aligned
+    uint32_t iacc = 0;             // 0 on the CTA's first tile: the weight-gradient accumulators are overwritten
+#define ISSUE_STEP(ISSUE, LATE)     \
+  do {                              \
+    bar_sync(1, NEPI + 32);         \
+    if (tid == NEPI) {              \
+      fence_after();                \
+      ISSUE;                        \
+      commit(bar);                  \
+      LATE;                         \
+    }                               \
+    __syncwarp();                   \
+  } while (0)
+#define A16(B) (s16 + (B) / 16)
+#pragma unroll 1
+    for (int tile = part.tile0; tile < part.tile1; ++tile) {
+      ISSUE_STEP((issue_fwd<32, 64>(tD, A16(B_ENC), A16(OW0))), (void)0);
+      ISSUE_STEP((issue_fwd<64, 64>(tD, A16(B_H0), A16(OW1))), (void)0);
+      ISSUE_STEP((issue_fwd<64, 16>(tD, A16(B_H1), A16(OWH))), (void)0);
+      ISSUE_STEP((issue_fwd<32, 64>(tD, A16(B_CIN), A16(OW3))), (void)0);
+      ISSUE_STEP((issue_fwd<64, 64>(tD, A16(B_C0), A16(OW4))), (void)0);
+      ISSUE_STEP((issue_fwd<64, 16>(tD, A16(B_C1), A16(OW5))), (void)0);
+      ISSUE_STEP((issue_dgrad<16, 64, 16>(tD, A16(B_GA), A16(OW5))), (issue_wgrad<64>(tbase + T_A5, A16(B_GA), A16(B_C1), iacc)));
+      ISSUE_STEP((issue_dgrad<64, 64, 64>(tD, A16(B_GB), A16(OW4))), (issue_wgrad<64>(tbase + T_A4, A16(B_GB), A16(B_C0), iacc)));
+      ISSUE_STEP((issue_dgrad<64, 32, 64>(tD, A16(B_GA), A16(OW3))), (issue_wgrad<32>(tbase + T_A3, A16(B_GA), A16(B_CIN), iacc)));
+      ISSUE_STEP((issue_dgrad<16, 64, 16>(tD, A16(B_GB), A16(OWH))), (issue_wgrad<64>(tbase + T_AH, A16(B_GB), A16(B_H1), iacc)));
+      ISSUE_STEP((issue_dgrad<64, 64, 64>(tD, A16(B_GA), A16(OW1))), (issue_wgrad<64>(tbase + T_A1, A16(B_GA), A16(B_H0), iacc)));
+      ISSUE_STEP((issue_dgrad<64, 32, 64>(tD, A16(B_GB), A16(OW0)), issue_wgrad<32>(tbase + T_A0, A16(B_GB), A16(B_ENC), iacc)), (void)0);
+      iacc = 1;
+    }
+#undef A16
+#undef ISSUE_STEP
+  }
+
+  // ---- epilogue warps.  One chain step: publish this thread's smem writes to the async proxy, count the warp in on the
+  // issuer's barrier (no wait), do OVERLAP work while the MMAs run, wait for the accumulator.  ISSUE / LATE only name
+  // what the issuer warp runs for this step (see above).
 #define TC_STEP3(ISSUE, LATE, OVERLAP) \
   do {                                 \
+    DBG_STAMP();                       \
     fence_before();                    \
     fence_async_smem();                \
-    __syncthreads();                   \
-    if (tid == 0) {                    \
-      fence_after();                   \
-      ISSUE;                           \
-      commit(bar);                     \
-      LATE;                            \
-    }                                  \
+    bar_arrive(1, NEPI + 32);          \
+    DBG_STAMP();                       \
     OVERLAP;                           \
+    DBG_STAMP();                       \
     mbar_wait(bar, phase);             \
     phase ^= 1;                        \
     fence_after();                     \
+    DBG_STAMP();                       \
   } while (0)
 #define TC_STEP(ISSUE, LATE) TC_STEP3(ISSUE, LATE, (void)0)
   // 64-column epilogues: ReLU + mask capture (forward recompute) / mask application (dgrad chain)
-#define EPI_RELU(BUF, MASK)                                             \
+#define EPI_RELU(BUF)                                                   \
   do {                                                                  \
-    MASK = 0;                                                           \
     _Pragma("unroll") for (int s_ = 0; s_ < PASSES; ++s_) {             \
       tmem_ld16(trow + 16 * s_, v);                                     \
       tmem_ld_wait();                                                   \
-      MASK |= relu_mask<16>(v) << (16 * s_);                            \
-      store_h<16>(sb + BUF, r, 1 + 2 * (PASSES * q + s_), v);           \
+      store_relu<16>(sb + BUF, r, 1 + 2 * (PASSES * q + s_), v);        \
     }                                                                   \
   } while (0)
-#define EPI_MASK(BUF, MASK)                                                                        \
+#define EPI_MASK(BUF, ACT)                                                                         \
   do {                                                                                             \
     _Pragma("unroll") for (int s_ = 0; s_ < PASSES; ++s_) {                                        \
       tmem_ld16(trow + 16 * s_, v);                                                                \
       tmem_ld_wait();                                                                              \
-      _Pragma("unroll") for (int i = 0; i < 16; ++i) v[i] = (MASK >> (16 * s_ + i) & 1u) ? v[i] : 0.f; \
-      store_g<16>(sb + BUF, r, 2 * (PASSES * q + s_), v);                                          \
+      store_g_gated<16>(sb + BUF, r, 2 * (PASSES * q + s_), v, sb + ACT, 1 + 2 * (PASSES * q + s_)); \
     }                                                                                              \
   } while (0)
 
-  if (part.e >= 0) {
+  if (part.e >= 0 && !issuer) {
     // software prefetch: the next tile's encoding rows and pair id are requested one tile ahead, this tile's output
     // gradient at the top of the tile, so no global-load latency sits in the per-layer chain
     constexpr int FE = 8 * PASSES;  // encoding features per thread
@@ -568,15 +625,20 @@ __global__ void __launch_bounds__(128 * NQ, NQ == 2 ? 2 : 1)  // NQ = 2: at most
     for (int tile = part.tile0; tile < part.tile1; ++tile) {
       const int64_t m = (int64_t)tile * ROWS + r;
       const int64_t p = pn;
-      uint32_t m0, m1, m3, m4;  // ReLU masks of this thread's columns of h0, h1, c0, c1
+      dbg_on = dbg && tid == 0 && blockIdx.x == 3 && tile == part.tile0 + 5;
+      DBG_STAMP();
       float v[16];
       float4 dy = make_float4(0.f, 0.f, 0.f, 0.f);
+      // view direction: requested here, consumed under the heads MMA three steps later (the load used to sit in that
+      // step's overlap slot and held the whole CTA for ~900 cycles)
+      float ddx = 0.f, ddy = 0.f, ddz = 1.f;
+      if (q == 1 && p >= 0) load_dir(src, p, ddx, ddy, ddz);
       // ---- forward recompute ----
 #pragma unroll
       for (int s_ = 0; s_ < PASSES; ++s_) {
         float x[8];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) x[i] = fminf(fmaxf(xn[8 * s_ + i], -F16_MAX), F16_MAX);
+        for (int i = 0; i < 8; ++i) x[i] = xn[8 * s_ + i];
         store_h<8>(sb + B_ENC, r, 1 + PASSES * q + s_, x);
       }
       if (q == 0 && p >= 0) {
@@ -588,18 +650,16 @@ __global__ void __launch_bounds__(128 * NQ, NQ == 2 ? 2 : 1)  // NQ = 2: at most
       }
       prefetch(tile + 1);
       TC_STEP((issue_fwd<32, 64>(tD, sb + B_ENC, sb + OW0)), (void)0);
-      EPI_RELU(B_H0, m0);
+      EPI_RELU(B_H0);
       TC_STEP((issue_fwd<64, 64>(tD, sb + B_H0, sb + OW1)), (void)0);
-      EPI_RELU(B_H1, m1);
+      EPI_RELU(B_H1);
       float sh[16];
-      TC_STEP3((issue_fwd<64, 16>(tD, sb + B_H1, sb + OWH)), (void)0, if (q == 1) dir_sh16(src, p, sh));
+      TC_STEP3((issue_fwd<64, 16>(tD, sb + B_H1, sb + OWH)), (void)0, if (q == 1) dir_to_sh16(ddx, ddy, ddz, sh));
       float sigma = 0.f;
       if (q == 0) {  // cin[0..15] = geo 0..14, sh 0
         tmem_ld16(trow0, v);
         tmem_ld_wait();
         sigma = trunc_exp_f(v[15]);
-#pragma unroll
-        for (int i = 0; i < 15; ++i) v[i] = fminf(fmaxf(v[i], -F16_MAX), F16_MAX);
         v[15] = 0.28209479177387814f;
         store_h<16>(sb + B_CIN, r, 1, v);
       } else if (q == 1) {  // cin[16..31] = sh 1..15, 0
@@ -609,9 +669,9 @@ __global__ void __launch_bounds__(128 * NQ, NQ == 2 ? 2 : 1)  // NQ = 2: at most
         store_h<16>(sb + B_CIN, r, 3, v);
       }
       TC_STEP((issue_fwd<32, 64>(tD, sb + B_CIN, sb + OW3)), (void)0);
-      EPI_RELU(B_C0, m3);
+      EPI_RELU(B_C0);
       TC_STEP((issue_fwd<64, 64>(tD, sb + B_C0, sb + OW4)), (void)0);
-      EPI_RELU(B_C1, m4);
+      EPI_RELU(B_C1);
       TC_STEP((issue_fwd<64, 16>(tD, sb + B_C1, sb + OW5)), (void)0);
       // ---- output gradients ----
       float dsraw = 0.f;
@@ -635,9 +695,9 @@ __global__ void __launch_bounds__(128 * NQ, NQ == 2 ? 2 : 1)  // NQ = 2: at most
       }
       // ---- dgrad chain; the weight gradient of the layer just left is issued behind the commit ----
       TC_STEP((issue_dgrad<16, 64, 16>(tD, sb + B_GA, sb + OW5)), (issue_wgrad<64>(tbase + T_A5, sb + B_GA, sb + B_C1, acc)));
-      EPI_MASK(B_GB, m4);
+      EPI_MASK(B_GB, B_C1);
       TC_STEP((issue_dgrad<64, 64, 64>(tD, sb + B_GB, sb + OW4)), (issue_wgrad<64>(tbase + T_A4, sb + B_GB, sb + B_C0, acc)));
-      EPI_MASK(B_GA, m3);
+      EPI_MASK(B_GA, B_C0);
       TC_STEP((issue_dgrad<64, 32, 64>(tD, sb + B_GA, sb + OW3)), (issue_wgrad<32>(tbase + T_A3, sb + B_GA, sb + B_CIN, acc)));
       if (q == 0) {  // head gradient [d geo 0..14 | d sigma_raw] -> chunks 0, 1
         tmem_ld16(trow0, v);
@@ -646,9 +706,9 @@ __global__ void __launch_bounds__(128 * NQ, NQ == 2 ? 2 : 1)  // NQ = 2: at most
         store_g<16>(sb + B_GB, r, 0, v);
       }
       TC_STEP((issue_dgrad<16, 64, 16>(tD, sb + B_GB, sb + OWH)), (issue_wgrad<64>(tbase + T_AH, sb + B_GB, sb + B_H1, acc)));
-      EPI_MASK(B_GA, m1);
+      EPI_MASK(B_GA, B_H1);
       TC_STEP((issue_dgrad<64, 64, 64>(tD, sb + B_GA, sb + OW1)), (issue_wgrad<64>(tbase + T_A1, sb + B_GA, sb + B_H0, acc)));
-      EPI_MASK(B_GB, m0);
+      EPI_MASK(B_GB, B_H0);
       // last step of the tile: its weight-gradient MMAs go BEFORE the commit, because the next tile's first
       // epilogue overwrites the encoding buffer they read
       TC_STEP((issue_dgrad<64, 32, 64>(tD, sb + B_GB, sb + OW0), issue_wgrad<32>(tbase + T_A0, sb + B_GB, sb + B_ENC, acc)), (void)0);
@@ -660,6 +720,7 @@ __global__ void __launch_bounds__(128 * NQ, NQ == 2 ? 2 : 1)  // NQ = 2: at most
           for (int i = 0; i < 16; ++i) d_enc[(int64_t)(16 * q + i) * ld + m] = v[i] * inv_s;
         }
       }
+      DBG_STAMP();
       acc = 1;
     }
   }
@@ -667,6 +728,7 @@ __global__ void __launch_bounds__(128 * NQ, NQ == 2 ? 2 : 1)  // NQ = 2: at most
 #undef TC_STEP3
 #undef EPI_RELU
 #undef EPI_MASK
+  if (dbg && threadIdx.x == 0 && blockIdx.x == 3) { dbg[102] = clock64(); dbg[104] = part.tile1 - part.tile0; }
   fence_before();
   __syncthreads();
   fence_after();
@@ -680,6 +742,7 @@ __global__ void __launch_bounds__(128 * NQ, NQ == 2 ? 2 : 1)  // NQ = 2: at most
     dump_acc<72>(tbase, T_A4, 4, dst + P_A4, tid, valid, inv_s);
     dump_acc<72>(tbase, T_A5, 1, dst + P_A5, tid, valid, inv_s);
   }
+  if (dbg && threadIdx.x == 0 && blockIdx.x == 3) dbg[103] = clock64();
   fence_before();
   __syncthreads();
   if (tid < 32) tmem_dealloc(tbase, 512);
@@ -939,11 +1002,22 @@ static int run_bwd_tc(const AcnPoints* pts, const AcnPairs* pairs, const AcnNgpE
   const int chunk_tiles = (tiles + n_chunks - 1) / n_chunks;
   static thread_local cudaEvent_t ev[TC_MAX_CHUNKS + 2];  // fork / per-chunk / join markers (never used for timing)
   static thread_local int ev_dev = -1;
+  static long long* dbgbuf = nullptr;
+  if (getenv("ACN_TC_DBG") && !dbgbuf) { cudaMalloc(&dbgbuf, 128 * 8); cudaMemset(dbgbuf, 0, 128 * 8); }
   if (!side) {  // the kernel has the SM to itself
     ACN_REQUIRE(n_chunks == 1, "%s: chunks need a side stream", who);
-    k_ngp_mlp_bwd_tc<4><<<G, 512, BWD_SMEM, st>>>(make_src(pts), pairs->point, pairs->weight, pairs->seg, Mcap, tab, enc, ld, d_out, d_enc,
-                                                  partial, gmax, 0, tiles);
+    k_ngp_mlp_bwd_tc<4><<<G, 512 + 32, BWD_SMEM, st>>>(make_src(pts), pairs->point, pairs->weight, pairs->seg, Mcap, tab, enc, ld, d_out, d_enc,
+                                                  partial, gmax, 0, tiles, dbgbuf);
     ACN_LAUNCH_CHECK();
+    if (dbgbuf) {
+      cudaStreamSynchronize(st);
+      long long hb[128];
+      cudaMemcpy(hb, dbgbuf, sizeof(hb), cudaMemcpyDeviceToHost);
+      fprintf(stderr, "TCDBG");
+      for (int i = 0; i < 50; ++i) fprintf(stderr, " %lld", hb[i] - hb[0]);
+      fprintf(stderr, "\nTCKERN setup %lld loop %lld dump %lld tiles %lld", hb[101] - hb[100], hb[102] - hb[101], hb[103] - hb[102], hb[104]);
+      fprintf(stderr, "\n");
+    }
   } else {
     // Software pipeline over chunks of the slot list: while chunk c's table scatter (bound by the L2 atomic units, it keeps
     // its rate with 4 CTAs per SM) runs on the side stream, chunk c+1's MLP backward (bound by its tcgen05 layer chain, half
@@ -959,8 +1033,8 @@ static int run_bwd_tc(const AcnPoints* pts, const AcnPairs* pairs, const AcnNgpE
     const int hash_gx = (num_sms_cached() * 4 + g->levels - 1) / g->levels;
     for (int c = 0; c < n_chunks; ++c) {
       const int lo = c * chunk_tiles, hi = (c == n_chunks - 1) ? tiles : (c + 1) * chunk_tiles;
-      k_ngp_mlp_bwd_tc<2><<<G, 256, BWD_SMEM, st>>>(make_src(pts), pairs->point, pairs->weight, pairs->seg, Mcap, tab, enc, ld, d_out, d_enc,
-                                                    partial + (int64_t)c * G * P_FLOATS, gmax, lo, hi);
+      k_ngp_mlp_bwd_tc<2><<<G, 256 + 32, BWD_SMEM, st>>>(make_src(pts), pairs->point, pairs->weight, pairs->seg, Mcap, tab, enc, ld, d_out, d_enc,
+                                                    partial + (int64_t)c * G * P_FLOATS, gmax, lo, hi, nullptr);
       ACN_LAUNCH_CHECK();
       ACN_CUDA(cudaEventRecord(ev[c], st));
       ACN_CUDA(cudaStreamWaitEvent(side, ev[c], 0));

@@ -27,6 +27,15 @@ __device__ __forceinline__ uint64_t smem_desc(uint32_t saddr, uint32_t lbo_bytes
   return d;
 }
 
+// Same descriptor from an address in 16-byte units: shared memory is < 256 KB, so the address field cannot overflow its
+// 14 bits and base16 + constant folds into ONE uniform add per descriptor (the single issuing thread is the critical
+// path of the backward kernel: 16 SASS instructions per MMA with smem_desc(), 8 with this form).
+__device__ __forceinline__ uint64_t smem_desc16(uint32_t addr16, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint32_t lo = addr16 + ((lbo_bytes >> 4) << 16);
+  uint32_t hi = (sbo_bytes >> 4) | (1u << 14);
+  return ((uint64_t)hi << 32) | lo;
+}
+
 enum : uint32_t { F16 = 0, BF16 = 1 };
 enum : uint32_t { K_MAJOR = 0, MN_MAJOR = 1 };
 
@@ -81,6 +90,9 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
 // named barrier over `nthreads` threads (a warpgroup-sized pipeline inside a larger CTA)
 __device__ __forceinline__ void bar_sync(int id, int nthreads) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory"); }
 
+// producer side of a named barrier: counts this warp in and does not wait (the consumer warp uses bar_sync on the same id)
+__device__ __forceinline__ void bar_arrive(int id, int nthreads) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(nthreads) : "memory"); }
+
 // ---- TMEM ----------------------------------------------------------------------------------
 // One full warp allocates `ncols` (power of two >= 32) columns; the base address lands in *slot (shared).
 __device__ __forceinline__ void tmem_alloc(uint32_t* slot, uint32_t ncols) {
@@ -132,6 +144,28 @@ __device__ __forceinline__ uint32_t pack_h2(float a, float b) {
 __device__ __forceinline__ uint32_t pack_bf2(float a, float b) {
   __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
   return *reinterpret_cast<uint32_t*>(&h);
+}
+// fp32 pair -> packed fp16 in ONE F2FP instruction: round-to-nearest, saturate to +-65504 (no inf), optional fused ReLU.
+// The epilogues are issue-bound (8192 elements per 128 x 64 layer tile), so instructions per element are what counts.
+__device__ __forceinline__ uint32_t pack_h2_sat(float lo, float hi) {
+  uint32_t r;
+  asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+__device__ __forceinline__ uint32_t pack_h2_relu_sat(float lo, float hi) {
+  uint32_t r;
+  asm("cvt.rn.relu.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+// ReLU backward on packed halves: g where the stored activation h is > 0, else 0 (HSET2.BF + HMUL2)
+__device__ __forceinline__ uint32_t h2_gate(uint32_t g, uint32_t h) {
+  uint32_t m, z;
+  asm("set.gt.f16x2.f16x2 %0, %1, %2;" : "=r"(m) : "r"(h), "r"(0u));
+  asm("mul.rn.f16x2 %0, %1, %2;" : "=r"(z) : "r"(g), "r"(m));
+  return z;
+}
+__device__ __forceinline__ void ld_chunk(uint32_t saddr, uint32_t (&w)[4]) {
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]) : "r"(saddr) : "memory");
 }
 __device__ __forceinline__ void st_chunk(uint32_t saddr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
   asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(saddr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
