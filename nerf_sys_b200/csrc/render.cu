@@ -253,26 +253,89 @@ __global__ void __launch_bounds__(256) k_bg_fwd(const float* __restrict__ d, int
   }
 }
 
-__global__ void __launch_bounds__(256) k_bg_bwd(const float* __restrict__ d_rgb, int64_t N, const float* __restrict__ w1,
-                                                const float* __restrict__ sv, int64_t ld, float* __restrict__ ws) {
+// Backward of the whole head in one kernel + a fixed-order reduce (was 5 launches, 54 us for 8192 rays).
+// A CTA takes 128-ray tiles: thread = ray builds dz1 (3) and dz0 (32) and parks them with sh (16) and h (32) in shared
+// memory (rows padded to 129 floats: conflict-free when a warp reads different rows at one ray); then thread = output
+// accumulates its <= 6 of the 643 gradient entries over the tile's rays.  Per-CTA partials, summed in CTA order.
+constexpr int BG_NOUT = 512 + 32 + 96 + 3;  // dW0 (32,16) | db0 (32) | dW1 (3,32) | db1 (3)
+constexpr int BG_PSTRIDE = 648;
+constexpr int BG_TILE = 128, BG_PAD = 129;
+constexpr int BG_MAX_CTAS = 592;
+
+__global__ void __launch_bounds__(BG_TILE) k_bg_bwd_fused(const float* __restrict__ d_rgb, int64_t N, const float* __restrict__ w1,
+                                                          const float* __restrict__ sv, int64_t ld, float* __restrict__ partial) {
   __shared__ float s_w1[3 * 32];
-  if (threadIdx.x < 96) s_w1[threadIdx.x] = __ldg(w1 + threadIdx.x);
-  __syncthreads();
-  for (int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r < N; r += (int64_t)gridDim.x * blockDim.x) {
+  __shared__ float s_a[35][BG_PAD];  // rows 0..31 dz0, 32..34 dz1
+  __shared__ float s_b[49][BG_PAD];  // rows 0..15 sh, 16..47 h, 48 ones
+  const int t = threadIdx.x;
+  if (t < 96) s_w1[t] = __ldg(w1 + t);
+  s_b[48][t] = 1.f;
+  // output o of this thread: A row ra[k], B row rb[k]
+  int ra[6], rb[6];
+#pragma unroll
+  for (int k = 0; k < 6; ++k) {
+    int o = t + k * BG_TILE;
+    if (o < 512) { ra[k] = o >> 4; rb[k] = o & 15; }
+    else if (o < 544) { ra[k] = o - 512; rb[k] = 48; }
+    else if (o < 640) { ra[k] = 32 + (o - 544) / 32; rb[k] = 16 + (o - 544) % 32; }
+    else if (o < BG_NOUT) { ra[k] = 32 + (o - 640); rb[k] = 48; }
+    else { ra[k] = 0; rb[k] = 48; }
+  }
+  float acc[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  const int64_t tiles = (N + BG_TILE - 1) / BG_TILE;
+  for (int64_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+    const int64_t r = tile * BG_TILE + t;
+    const bool ok = r < N;
+    __syncthreads();  // previous tile's readers are done (and s_w1 / ones are in place on the first pass)
     float dz[3];
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
-      float o = sv[(int64_t)(BG_R_RGB + c) * ld + r];
-      dz[c] = __ldg(d_rgb + r * 3 + c) * o * (1.f - o);
-      ws[(int64_t)(BG_R_DZ1 + c) * ld + r] = dz[c];
+      float o = ok ? sv[(int64_t)(BG_R_RGB + c) * ld + r] : 0.f;
+      dz[c] = ok ? __ldg(d_rgb + r * 3 + c) * o * (1.f - o) : 0.f;
+      s_a[32 + c][t] = dz[c];
     }
-#pragma unroll 4
+#pragma unroll 8
     for (int j = 0; j < 32; ++j) {
-      float h = sv[(int64_t)(BG_R_H + j) * ld + r];
+      float h = ok ? sv[(int64_t)(BG_R_H + j) * ld + r] : 0.f;
       float v = s_w1[j] * dz[0] + s_w1[32 + j] * dz[1] + s_w1[64 + j] * dz[2];
-      ws[(int64_t)(BG_R_DZ0 + j) * ld + r] = (h > 0.f) ? v : 0.f;
+      s_a[j][t] = (h > 0.f) ? v : 0.f;
+      s_b[16 + j][t] = h;
+    }
+#pragma unroll
+    for (int i = 0; i < 16; ++i) s_b[i][t] = ok ? sv[(int64_t)(BG_R_SH + i) * ld + r] : 0.f;
+    __syncthreads();
+#pragma unroll 4
+    for (int q = 0; q < BG_TILE; ++q) {
+#pragma unroll
+      for (int k = 0; k < 6; ++k) acc[k] = fmaf(s_a[ra[k]][q], s_b[rb[k]][q], acc[k]);
     }
   }
+  float* out = partial + (int64_t)blockIdx.x * BG_PSTRIDE;
+#pragma unroll
+  for (int k = 0; k < 6; ++k) {
+    int o = t + k * BG_TILE;
+    if (o < BG_NOUT) out[o] = acc[k];
+  }
+}
+
+__global__ void __launch_bounds__(128) k_bg_bwd_reduce(const float* __restrict__ partial, int G, float* __restrict__ g_w0, float* __restrict__ g_b0,
+                                                       float* __restrict__ g_w1, float* __restrict__ g_b1) {
+  const int o = blockIdx.x * blockDim.x + threadIdx.x;
+  if (o >= BG_NOUT) return;
+  float acc = 0.f;
+  int x = 0;
+  for (; x + 8 <= G; x += 8) {  // eight loads in flight, added in CTA order (deterministic)
+    float v[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) v[u] = partial[(int64_t)(x + u) * BG_PSTRIDE + o];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) acc += v[u];
+  }
+  for (; x < G; ++x) acc += partial[(int64_t)x * BG_PSTRIDE + o];
+  if (o < 512) { if (g_w0) g_w0[o] = acc; }
+  else if (o < 544) { if (g_b0) g_b0[o - 512] = acc; }
+  else if (o < 640) { if (g_w1) g_w1[o - 544] = acc; }
+  else { if (g_b1) g_b1[o - 640] = acc; }
 }
 
 // ---------------------------------------------------------------------------------------
@@ -377,7 +440,10 @@ int acn_composite_bwd(const float* rgb_sigma, const float* t, const float* bg, i
 }
 
 int64_t acn_bg_save_bytes(int64_t N) { return sizeof(float) * BG_R_SAVE * r128(N); }
-int64_t acn_bg_bwd_ws_bytes(int64_t N) { return sizeof(float) * (BG_R_WS * r128(N) + wgrad_partial_floats(1)); }
+int64_t acn_bg_bwd_ws_bytes(int64_t N) {
+  (void)N;
+  return sizeof(float) * (int64_t)BG_MAX_CTAS * BG_PSTRIDE;
+}
 
 int acn_bg_forward(const float* d, int64_t stride, int64_t N, const float* w0, const float* b0, const float* w1, const float* b1,
                    float* rgb, void* save, void* stream) {
@@ -397,25 +463,13 @@ int acn_bg_backward(const float* d_rgb, int64_t N, const float* w0, const float*
   int64_t ld = r128(N);
   const float* sv = reinterpret_cast<const float*>(save);
   float* w = reinterpret_cast<float*>(ws);
-  if (N > 0) {
-    k_bg_bwd<<<persistent_grid((N + 255) / 256, 4), 256, 0, st>>>(d_rgb, N, w1, sv, ld, w);
-    ACN_LAUNCH_CHECK();
-  }
-  float* partial = w + (int64_t)BG_R_WS * ld;
-  {
-    float* dW[1] = {g_w1};
-    float* db[1] = {g_b1};
-    WgradJob job{w + (int64_t)BG_R_DZ1 * ld, sv + (int64_t)BG_R_H * ld, 3, 32, ld};
-    int rc = wgrad_launch(job, nullptr, 1, N, dW, db, partial, st);
-    if (rc) return rc;
-  }
-  {
-    float* dW[1] = {g_w0};
-    float* db[1] = {g_b0};
-    WgradJob job{w + (int64_t)BG_R_DZ0 * ld, sv + (int64_t)BG_R_SH * ld, 32, 16, ld};
-    int rc = wgrad_launch(job, nullptr, 1, N, dW, db, partial, st);
-    if (rc) return rc;
-  }
+  int G = (int)((N + BG_TILE - 1) / BG_TILE);
+  if (G > BG_MAX_CTAS) G = BG_MAX_CTAS;
+  if (G < 1) G = 1;  // N == 0: one CTA writes a zero partial, the gradients come out zero
+  k_bg_bwd_fused<<<G, BG_TILE, 0, st>>>(d_rgb, N, w1, sv, ld, w);
+  ACN_LAUNCH_CHECK();
+  k_bg_bwd_reduce<<<(BG_NOUT + 127) / 128, 128, 0, st>>>(w, G, g_w0, g_b0, g_w1, g_b1);
+  ACN_LAUNCH_CHECK();
   return ACN_OK;
 }
 

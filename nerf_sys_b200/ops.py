@@ -744,7 +744,7 @@ class BgFn(torch.autograd.Function):
         with torch.cuda.device(w0.device), _timed("bg_bwd"):
             check(L.acn_bg_backward(_ptr(d_rgb), ctx.N, _ptr(w0), _ptr(w1), _ptr(ctx.save), _ptr(g[0]), _ptr(g[1]), _ptr(g[2]),
                                     _ptr(g[3]), _ptr(ws), _stream()), "acn_bg_backward")
-        _count(5)
+        _count(2)
         ctx.save = None
         return (None, None, None, *g)
 
