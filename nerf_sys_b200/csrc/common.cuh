@@ -49,6 +49,23 @@ static inline int persistent_grid(int64_t work_items, int per_sm) {
 static inline cudaStream_t as_stream(void* s) { return reinterpret_cast<cudaStream_t>(s); }
 
 // ---- device-side pieces shared by several kernels -------------------------
+// A read-only load the compiler must issue HERE.  __ldg() is an invariant load that LLVM may sink to its first use, which
+// silently turns a software prefetch (issue now, consume one tile later) into a load-then-stall.
+__device__ __forceinline__ float ldg_now(const float* p) {
+  float v;
+  asm volatile("ld.global.nc.f32 %0, [%1];" : "=f"(v) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ int ldg_now(const int* p) {
+  int v;
+  asm volatile("ld.global.nc.s32 %0, [%1];" : "=r"(v) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ float4 ldg_now(const float4* p) {
+  float4 v;
+  asm volatile("ld.global.nc.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+  return v;
+}
 // No-return reductions with an explicit .global state space.  atomicAdd() on a pointer the compiler cannot prove global
 // (e.g. one picked from a kernel-parameter array by a runtime index) compiles to the generic ATOM.E form, which waits for
 // the round trip through L2: measured 2x slower than REDG for the table-gradient scatter (profiles/r1_v5_red_microbench.txt).
@@ -79,6 +96,13 @@ static inline PointSrc make_src(const AcnPoints* p) {
   return s;
 }
 
+// ray index of point p.  A 64-bit division is a ~500-cycle emulated subroutine on the GPU; point ids fit 32 bits in
+// every launch the host layer makes (chunked below 2^31), so the unsigned 32-bit form is taken whenever it is exact.
+__device__ __forceinline__ int64_t ray_of(int64_t p, int S) {
+  if ((uint64_t)p <= 0xffffffffull) return (int64_t)((uint32_t)p / (uint32_t)S);
+  return p / S;
+}
+
 // xyz of point p.  Implicit form: o + d*t with a separate multiply and add
 // (ray_rendering.py:317) - no FMA contraction, so positions are bit-identical.
 __device__ __forceinline__ void load_xyz(const PointSrc& s, int64_t p, float& x, float& y, float& z) {
@@ -88,7 +112,7 @@ __device__ __forceinline__ void load_xyz(const PointSrc& s, int64_t p, float& x,
     y = __ldg(q + 1);
     z = __ldg(q + 2);
   } else {
-    int64_t r = p / s.S;
+    int64_t r = ray_of(p, s.S);
     const float4* rr = reinterpret_cast<const float4*>(s.rays + r * 8);
     float4 a = __ldg(rr), b = __ldg(rr + 1);
     float tv = __ldg(s.t + p);
@@ -105,7 +129,7 @@ __device__ __forceinline__ void load_dir(const PointSrc& s, int64_t p, float& x,
     y = __ldg(q + 1);
     z = __ldg(q + 2);
   } else {
-    int64_t r = p / s.S;
+    int64_t r = ray_of(p, s.S);
     const float4* rr = reinterpret_cast<const float4*>(s.rays + r * 8);
     float4 a = __ldg(rr), b = __ldg(rr + 1);
     x = a.w;

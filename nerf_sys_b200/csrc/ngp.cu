@@ -84,20 +84,25 @@ struct GradTables {
 // Table-gradient scatter, grid.y = level (a CTA wave works on one 8 MiB slab of the gradient table, which stays L2-resident).
 // Coarse levels (agg.s[l] > 0: cells wider than the spacing of consecutive samples) go through the warp-aggregated
 // scatter; the reductions are REDG (explicit .global, see red_add in common.cuh).
-struct AggSteps {
-  int8_t s[ACN_MAX_LEVELS];
-};
+// 4 bits per level in one 64-bit kernel parameter (a small array indexed by blockIdx.y made nvcc copy the parameter block
+// to local memory in every thread: 32 KB of local stores per CTA, behind the REDs in the same LSU queue)
+using AggSteps = unsigned long long;
+// (the fused expert path is specialised on L = 16, see check_common)
 
 __global__ void __launch_bounds__(256) k_ngp_hash_bwd(PointSrc src, const int32_t* __restrict__ pair_point, const int32_t* __restrict__ seg,
                                                       int64_t M_ident, ExpertTable tab, GridParams g, const float* __restrict__ denc, int64_t ld,
                                                       GradTables gts, int64_t m_lo, int64_t m_hi, AggSteps agg) {
   __shared__ int s_seg[ACN_MAX_EXPERTS + 1];
+  __shared__ float2* s_gt[ACN_MAX_EXPERTS];
   if (threadIdx.x <= tab.E) s_seg[threadIdx.x] = seg ? seg[threadIdx.x] : (threadIdx.x == 0 ? 0 : (int)M_ident);
+#pragma unroll
+  for (int k = 0; k < ACN_MAX_EXPERTS; ++k)  // static parameter offsets: a runtime index would put the block in local memory
+    if (threadIdx.x == 32 + k) s_gt[k] = reinterpret_cast<float2*>(gts.t[k]);
   __syncthreads();
   int64_t M = seg ? s_seg[tab.E] : M_ident;
   const int l = blockIdx.y;
   const uint32_t mask = (1u << g.log2_T) - 1u, base = (uint32_t)l << g.log2_T;
-  const int steps = agg.s[l];
+  const int steps = (int)((agg >> (4 * l)) & 15ull);
   const uint32_t lane_key = 0xffffffffu - (threadIdx.x & 31u);
   if (m_hi < M) M = m_hi;
   for (int64_t mb = m_lo + blockIdx.x * (int64_t)blockDim.x; mb < M; mb += (int64_t)gridDim.x * blockDim.x) {  // CTA-uniform
@@ -105,7 +110,7 @@ __global__ void __launch_bounds__(256) k_ngp_hash_bwd(PointSrc src, const int32_
     const bool in_range = m < M;
     const int64_t p = in_range ? (pair_point ? (int64_t)pair_point[m] : m) : -1;
     const int e = (seg && in_range) ? find_expert(s_seg, tab.E, m) : 0;
-    float2* gt = reinterpret_cast<float2*>(gts.t[e]);
+    float2* gt = s_gt[e];
     const bool live = p >= 0 && gt != nullptr;
     Cell c{0u, 0u, 0u, 0.f, 0.f, 0.f};
     float2 gv = make_float2(0.f, 0.f);
@@ -468,10 +473,11 @@ int launch_hash_bwd_range(const AcnPoints* pts, const AcnPairs* pairs, const Acn
   int64_t span = (m_hi < Mcap ? m_hi : Mcap) - m_lo;
   // aggregation depth per level: cells of a coarse level are wider than the spacing of consecutive samples, so runs of
   // 2..8 lanes share a cell (measured at C2: 661 -> 494 us from REDG alone, -> ~410 us with the aggregation)
-  AggSteps agg;
-  for (int l = 0; l < ACN_MAX_LEVELS; ++l) {
+  AggSteps agg = 0;
+  for (int l = 0; l < g->levels && l < 16; ++l) {
     int r = g->res[l];
-    agg.s[l] = (g->interp != 2 && l < g->levels && r < 512) ? (r <= 20 ? 3 : r <= 40 ? 2 : r <= 80 ? 1 : 0) : 0;
+    unsigned long long st_l = (g->interp != 2 && r < 512) ? (r <= 20 ? 3 : r <= 40 ? 2 : r <= 80 ? 1 : 0) : 0;
+    agg |= st_l << (4 * l);
   }
   dim3 hg(grid_x > 0 ? grid_x : persistent_grid((span + 255) / 256, 4), g->levels);
   k_ngp_hash_bwd<<<hg, 256, 0, st>>>(make_src(pts), pairs->point, pairs->seg, Mcap, tab, make_grid(g), d_enc, h_round_ld(Mcap), gts, m_lo, m_hi,

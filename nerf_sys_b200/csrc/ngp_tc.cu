@@ -23,6 +23,9 @@
 
 namespace acn {
 
+#ifndef ACN_TC_PROFILE
+#define ACN_TC_PROFILE 0
+#endif
 #ifndef ACN_TC_G_BF16
 #define ACN_TC_G_BF16 0  // mixed fp16 x bf16 operands in one kind::f16 MMA raise an illegal-instruction fault on sm_100a (measured)
 #endif
@@ -69,29 +72,44 @@ __device__ __forceinline__ float bval(const AcnNgpExpert& ex, int L, int o) {
   }
 }
 
-__device__ __forceinline__ void load_layer_tc(uint8_t* dst, const AcnNgpExpert& ex, int L, int nrows, int in_pad, int tid, int nthr) {
+// Layer, row count and padded width are template parameters (the layer switch and the divisions fold away) and the loop is
+// unrolled four deep, so a thread has four weight loads in flight: the run-time form walked 35 dependent global loads
+// per thread, 21 k cycles (11 us) at the top of every fused MLP kernel.
+template <int L, int NROWS, int IN_PAD>
+__device__ __forceinline__ void load_layer_tc(uint8_t* dst, const AcnNgpExpert& ex, int tid, int nthr) {
   __half* d = reinterpret_cast<__half*>(dst);
-  int total = nrows * (in_pad + 16);
+  constexpr int total = NROWS * (IN_PAD + 16);
+#pragma unroll 4
   for (int e = tid; e < total; e += nthr) {
-    int c = e / (nrows * 8), rem = e - c * nrows * 8;
+    int c = e / (NROWS * 8), rem = e - c * NROWS * 8;
     int o = rem >> 3, j = rem & 7;
     int k = c * 8 + j - 8;
     float v;
     if (c == 0)
       v = (j == 0) ? bval(ex, L, o) : 0.f;
     else
-      v = (k < in_pad) ? wval(ex, L, o, k) : 0.f;
+      v = (k < IN_PAD) ? wval(ex, L, o, k) : 0.f;
     d[e] = __float2half_rn(v);
   }
 }
 
+// expert e of the parameter block, by value, through static offsets (a runtime index makes nvcc copy the whole 1.3 KB block
+// to every thread's local memory)
+__device__ __forceinline__ AcnNgpExpert pick_expert(const ExpertTableTc& tab, int e) {
+  AcnNgpExpert ex = tab.ex[0];
+#pragma unroll
+  for (int k = 1; k < ACN_MAX_EXPERTS; ++k)
+    if (k == e) ex = tab.ex[k];
+  return ex;
+}
+
 __device__ __forceinline__ void load_weights_tc(uint8_t* sw, const AcnNgpExpert& ex, int tid, int nthr) {
-  load_layer_tc(sw + OW0, ex, 0, 64, 32, tid, nthr);
-  load_layer_tc(sw + OW1, ex, 1, 64, 64, tid, nthr);
-  load_layer_tc(sw + OWH, ex, 2, 16, 64, tid, nthr);
-  load_layer_tc(sw + OW3, ex, 3, 64, 32, tid, nthr);
-  load_layer_tc(sw + OW4, ex, 4, 64, 64, tid, nthr);
-  load_layer_tc(sw + OW5, ex, 5, 16, 64, tid, nthr);
+  load_layer_tc<0, 64, 32>(sw + OW0, ex, tid, nthr);
+  load_layer_tc<1, 64, 64>(sw + OW1, ex, tid, nthr);
+  load_layer_tc<2, 16, 64>(sw + OWH, ex, tid, nthr);
+  load_layer_tc<3, 64, 32>(sw + OW3, ex, tid, nthr);
+  load_layer_tc<4, 64, 64>(sw + OW4, ex, tid, nthr);
+  load_layer_tc<5, 16, 64>(sw + OW5, ex, tid, nthr);
 }
 
 // ---- CTA -> (expert, tile range) ------------------------------------------------------------
@@ -279,7 +297,7 @@ __global__ void __launch_bounds__(FWD_THREADS, 1)
   const CtaPart part = s_part;
   const uint32_t sw = smem_u32(smem), abuf = sw + W_BYTES + q * ABUF;
   const uint32_t sw16 = sw >> 4, abuf16 = sw16 + (W_BYTES + q * ABUF) / 16;  // smem base is 128-byte aligned
-  if (part.e >= 0) load_weights_tc(smem, tab.ex[part.e], tid, FWD_THREADS);
+  if (part.e >= 0) load_weights_tc(smem, pick_expert(tab, part.e), tid, FWD_THREADS);
   store_ones_chunk(abuf, r, 0);
   store_zero_chunk(abuf, r, 9);
   fence_async_smem();
@@ -432,20 +450,21 @@ static_assert(T_A5 + 72 <= 512, "TMEM budget");
 constexpr int P_A0 = 0, P_A1 = P_A0 + 64 * 40, P_AH = P_A1 + 64 * 72, P_A3 = P_AH + 16 * 72, P_A4 = P_A3 + 64 * 40, P_A5 = P_A4 + 64 * 72;
 constexpr int P_FLOATS = P_A5 + 16 * 72;
 
-// dump rows [0, 16*nq) of an M=64 accumulator (N columns) to `dst` (row-major, N floats per row)
+// dump rows [0, 16*nq) of an M=64 accumulator (N columns) to `dst` (row-major, N floats per row).  Rows 16w..16w+15 sit in
+// lanes 32w..32w+15, which the warps w, w+4, w+8, .. may all read: they split the 8-column chunks between them.
 template <int N>
-__device__ __forceinline__ void dump_acc(uint32_t tbase, uint32_t col, int nq, float* __restrict__ dst, int tid, bool valid, float inv_s) {
-  const int w = tid >> 5, l = tid & 31;
-  if (tid >= 128 || w >= nq) return;  // warp-uniform
+__device__ __forceinline__ void dump_acc(uint32_t tbase, uint32_t col, int nq, float* __restrict__ dst, int tid, int nparts, bool valid, float inv_s) {
+  const int w = (tid >> 5) & 3, part = tid >> 7, l = tid & 31;
+  if (part >= nparts || w >= nq) return;  // warp-uniform
   float v[8];
 #pragma unroll 1
-  for (int c = 0; c < N; c += 8) {
+  for (int c = 8 * part; c < N; c += 8 * nparts) {
     tmem_ld8(tbase + col + c + ((uint32_t)w << 21), v);
     tmem_ld_wait();
     if (l < 16) {
-      float* d = dst + (16 * w + l) * N + c;
-#pragma unroll
-      for (int i = 0; i < 8; ++i) d[i] = valid ? v[i] * inv_s : 0.f;
+      float4* d = reinterpret_cast<float4*>(dst + (16 * w + l) * N + c);
+      d[0] = valid ? make_float4(v[0] * inv_s, v[1] * inv_s, v[2] * inv_s, v[3] * inv_s) : make_float4(0.f, 0.f, 0.f, 0.f);
+      d[1] = valid ? make_float4(v[4] * inv_s, v[5] * inv_s, v[6] * inv_s, v[7] * inv_s) : make_float4(0.f, 0.f, 0.f, 0.f);
     }
   }
 }
@@ -463,10 +482,19 @@ __global__ void __launch_bounds__(128 * NQ + 32, NQ == 2 ? 2 : 1)  // NQ = 2: at
     k_ngp_mlp_bwd_tc(PointSrc src, const int32_t* __restrict__ pair_point, const float* __restrict__ pair_w, const int32_t* __restrict__ seg,
                      int64_t M_ident, ExpertTableTc tab, const float* __restrict__ enc, int64_t ld, const float* __restrict__ d_out,
                      float* __restrict__ d_enc, float* __restrict__ partial, const float* __restrict__ gmax, int tile_lo, int tile_hi,
-                     long long* dbg) {
+                     long long* dbg, int dbg_tid) {
+  // ACN_TC_PROFILE (compile-time, off in the product build): clock64 stamps of one thread of CTA 3 on its sixth tile, four
+  // per chain step, plus whole-kernel phase marks; this is how the issue-bound steps and the slow prologue were found.
+#if ACN_TC_PROFILE
   int dbg_i = 0; bool dbg_on = false;
   if (dbg && threadIdx.x == 0 && blockIdx.x == 3) dbg[100] = clock64();
 #define DBG_STAMP() do { if (dbg_on && dbg_i < 120) dbg[dbg_i++] = clock64(); } while (0)
+#define DBG_MARK(i) do { if (dbg && threadIdx.x == 0 && blockIdx.x == 3) dbg[i] = clock64(); } while (0)
+#else
+  (void)dbg; (void)dbg_tid;
+#define DBG_STAMP() ((void)0)
+#define DBG_MARK(i) ((void)0)
+#endif
   constexpr int PASSES = 4 / NQ;  // 16-column passes per thread in a 64-column epilogue
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ __align__(8) uint64_t s_bar;
@@ -493,7 +521,7 @@ __global__ void __launch_bounds__(128 * NQ + 32, NQ == 2 ? 2 : 1)  // NQ = 2: at
   const uint32_t sb = smem_u32(smem);
   constexpr int NEPI = 128 * NQ;          // epilogue threads
   const bool issuer = tid >= NEPI;        // warp NEPI/32
-  if (part.e >= 0) load_weights_tc(smem, tab.ex[part.e], tid, NEPI + 32);
+  if (part.e >= 0) load_weights_tc(smem, pick_expert(tab, part.e), tid, NEPI + 32);
   if (!issuer) {
     constexpr uint32_t bufs[6] = {B_ENC, B_H0, B_H1, B_CIN, B_C0, B_C1};
     constexpr int zc[6] = {5, 9, 9, 5, 9, 9};
@@ -515,7 +543,7 @@ __global__ void __launch_bounds__(128 * NQ + 32, NQ == 2 ? 2 : 1)  // NQ = 2: at
   fence_before();
   __syncthreads();
   fence_after();
-  if (dbg && threadIdx.x == 0 && blockIdx.x == 3) dbg[101] = clock64();
+  DBG_MARK(101);
   const uint32_t tbase = s_tmem;
   const uint32_t tD = tbase + T_D;
   const uint32_t trow0 = tD + ((uint32_t)((tid >> 5) & 3) << 21);  // column 0 of this thread's row
@@ -615,15 +643,23 @@ __global__ void __launch_bounds__(128 * NQ + 32, NQ == 2 ? 2 : 1)  // NQ = 2: at
     auto prefetch = [&](int tile) {
       const int64_t m_ = (int64_t)tile * ROWS + r;
       const bool ok_ = tile < part.tile1 && m_ < M;
+      if (ok_) {
 #pragma unroll
-      for (int i = 0; i < FE; ++i) xn[i] = ok_ ? __ldg(enc + (int64_t)(FE * q + i) * ld + m_) : 0.f;
-      pn = ok_ ? (pair_point ? (int64_t)__ldg(pair_point + m_) : m_) : -1;
+        for (int i = 0; i < FE; ++i) xn[i] = ldg_now(enc + (int64_t)(FE * q + i) * ld + m_);
+        pn = pair_point ? (int64_t)ldg_now(pair_point + m_) : m_;
+      } else {
+#pragma unroll
+        for (int i = 0; i < FE; ++i) xn[i] = 0.f;
+        pn = -1;
+      }
     };
     prefetch(part.tile0);
     for (int tile = part.tile0; tile < part.tile1; ++tile) {
       const int64_t m = (int64_t)tile * ROWS + r;
       const int64_t p = pn;
-      dbg_on = dbg && tid == 0 && blockIdx.x == 3 && tile == part.tile0 + 5;
+#if ACN_TC_PROFILE
+      dbg_on = dbg && tid == dbg_tid && blockIdx.x == 3 && tile == part.tile0 + 5;
+#endif
       DBG_STAMP();
       float v[16];
       float4 dy = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -640,7 +676,7 @@ __global__ void __launch_bounds__(128 * NQ + 32, NQ == 2 ? 2 : 1)  // NQ = 2: at
         store_h<8>(sb + B_ENC, r, 1 + PASSES * q + s_, x);
       }
       if (q == 0 && p >= 0) {
-        dy = __ldg(reinterpret_cast<const float4*>(d_out + p * 4));
+        dy = ldg_now(reinterpret_cast<const float4*>(d_out + p * 4));
         if (pair_point) {
           float w = __ldg(pair_w + m);
           dy.x *= w; dy.y *= w; dy.z *= w; dy.w *= w;
@@ -726,21 +762,21 @@ __global__ void __launch_bounds__(128 * NQ + 32, NQ == 2 ? 2 : 1)  // NQ = 2: at
 #undef TC_STEP3
 #undef EPI_RELU
 #undef EPI_MASK
-  if (dbg && threadIdx.x == 0 && blockIdx.x == 3) { dbg[102] = clock64(); dbg[104] = part.tile1 - part.tile0; }
+  DBG_MARK(102);
   fence_before();
   __syncthreads();
   fence_after();
   {
     float* dst = partial + (int64_t)blockIdx.x * P_FLOATS;
     const bool valid = acc != 0;
-    dump_acc<40>(tbase, T_A0, 4, dst + P_A0, tid, valid, inv_s);
-    dump_acc<72>(tbase, T_A1, 4, dst + P_A1, tid, valid, inv_s);
-    dump_acc<72>(tbase, T_AH, 1, dst + P_AH, tid, valid, inv_s);
-    dump_acc<40>(tbase, T_A3, 4, dst + P_A3, tid, valid, inv_s);
-    dump_acc<72>(tbase, T_A4, 4, dst + P_A4, tid, valid, inv_s);
-    dump_acc<72>(tbase, T_A5, 1, dst + P_A5, tid, valid, inv_s);
+    dump_acc<40>(tbase, T_A0, 4, dst + P_A0, tid, NQ, valid, inv_s);
+    dump_acc<72>(tbase, T_A1, 4, dst + P_A1, tid, NQ, valid, inv_s);
+    dump_acc<72>(tbase, T_AH, 1, dst + P_AH, tid, NQ, valid, inv_s);
+    dump_acc<40>(tbase, T_A3, 4, dst + P_A3, tid, NQ, valid, inv_s);
+    dump_acc<72>(tbase, T_A4, 4, dst + P_A4, tid, NQ, valid, inv_s);
+    dump_acc<72>(tbase, T_A5, 1, dst + P_A5, tid, NQ, valid, inv_s);
   }
-  if (dbg && threadIdx.x == 0 && blockIdx.x == 3) dbg[103] = clock64();
+  DBG_MARK(103);
   fence_before();
   __syncthreads();
   if (tid < 32) tmem_dealloc(tbase, 512);
@@ -1011,22 +1047,31 @@ static int run_bwd_tc(const AcnPoints* pts, const AcnPairs* pairs, const AcnNgpE
   const int chunk_tiles = (tiles + n_chunks - 1) / n_chunks;
   static thread_local cudaEvent_t ev[TC_MAX_CHUNKS + 2];  // fork / per-chunk / join markers (never used for timing)
   static thread_local int ev_dev = -1;
-  static long long* dbgbuf = nullptr;
-  if (getenv("ACN_TC_DBG") && !dbgbuf) { cudaMalloc(&dbgbuf, 128 * 8); cudaMemset(dbgbuf, 0, 128 * 8); }
+  long long* dbgbuf = nullptr;
+  int dbg_tid = 0;
+#if ACN_TC_PROFILE
+  static long long* s_dbg = nullptr;
+  if (getenv("ACN_TC_DBG")) {
+    if (!s_dbg) { cudaMalloc(&s_dbg, 128 * 8); cudaMemset(s_dbg, 0, 128 * 8); }
+    dbgbuf = s_dbg;
+    dbg_tid = atoi(getenv("ACN_TC_DBG"));
+  }
+#endif
   if (!side) {  // the kernel has the SM to itself
     ACN_REQUIRE(n_chunks == 1, "%s: chunks need a side stream", who);
     k_ngp_mlp_bwd_tc<4><<<G, 512 + 32, BWD_SMEM, st>>>(make_src(pts), pairs->point, pairs->weight, pairs->seg, Mcap, tab, enc, ld, d_out, d_enc,
-                                                  partial, gmax, 0, tiles, dbgbuf);
+                                                  partial, gmax, 0, tiles, dbgbuf, dbg_tid);
     ACN_LAUNCH_CHECK();
+#if ACN_TC_PROFILE
     if (dbgbuf) {
       cudaStreamSynchronize(st);
       long long hb[128];
       cudaMemcpy(hb, dbgbuf, sizeof(hb), cudaMemcpyDeviceToHost);
       fprintf(stderr, "TCDBG");
-      for (int i = 0; i < 50; ++i) fprintf(stderr, " %lld", hb[i] - hb[0]);
-      fprintf(stderr, "\nTCKERN setup %lld loop %lld dump %lld tiles %lld", hb[101] - hb[100], hb[102] - hb[101], hb[103] - hb[102], hb[104]);
-      fprintf(stderr, "\n");
+      for (int i = 0; i < 50; ++i) fprintf(stderr, " %lld", hb[i] - hb[100]);
+      fprintf(stderr, "\nTCKERN setup %lld loop %lld dump %lld\n", hb[101] - hb[100], hb[102] - hb[101], hb[103] - hb[102]);
     }
+#endif
   } else {
     // Software pipeline over chunks of the slot list: while chunk c's table scatter (bound by the L2 atomic units, it keeps
     // its rate with 4 CTAs per SM) runs on the side stream, chunk c+1's MLP backward (bound by its tcgen05 layer chain, half
@@ -1043,7 +1088,7 @@ static int run_bwd_tc(const AcnPoints* pts, const AcnPairs* pairs, const AcnNgpE
     for (int c = 0; c < n_chunks; ++c) {
       const int lo = c * chunk_tiles, hi = (c == n_chunks - 1) ? tiles : (c + 1) * chunk_tiles;
       k_ngp_mlp_bwd_tc<2><<<G, 256 + 32, BWD_SMEM, st>>>(make_src(pts), pairs->point, pairs->weight, pairs->seg, Mcap, tab, enc, ld, d_out, d_enc,
-                                                    partial + (int64_t)c * G * P_FLOATS, gmax, lo, hi, nullptr);
+                                                    partial + (int64_t)c * G * P_FLOATS, gmax, lo, hi, nullptr, 0);
       ACN_LAUNCH_CHECK();
       ACN_CUDA(cudaEventRecord(ev[c], st));
       ACN_CUDA(cudaStreamWaitEvent(side, ev[c], 0));

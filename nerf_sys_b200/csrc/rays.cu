@@ -153,7 +153,7 @@ __global__ void __launch_bounds__(256) k_strat_t(const float* __restrict__ rays,
                                                  const float* __restrict__ u, float* __restrict__ t) {
   int64_t total = N * S;
   for (int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; p < total; p += (int64_t)gridDim.x * blockDim.x) {
-    int64_t r = p / S;
+    int64_t r = ray_of(p, S);
     int s = (int)(p - r * S);
     float near = __ldg(rays + r * 8 + 6), far = __ldg(rays + r * 8 + 7);
     float ta = __ldg(tau + s);

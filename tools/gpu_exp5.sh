@@ -1,6 +1,6 @@
 mkdir -p gpurun_out
-ACN_TC_DBG=1 timeout 300 python bench.py --steps 3 --warmup 3 --no-cpu-baseline --no-render --no-graph > gpurun_out/dbg.json 2> gpurun_out/dbg.err
-grep TCDBG gpurun_out/dbg.err | tail -2
+
+
 timeout 900 python -m pytest tests -m gpu -q -x > gpurun_out/gpu_all.log 2>&1; echo "gpu tests rc=$?"; tail -5 gpurun_out/gpu_all.log
 timeout 300 python bench.py --steps 20 --warmup 3 --no-cpu-baseline > gpurun_out/b.json 2> gpurun_out/b.err || tail -3 gpurun_out/b.err
 python - <<PY
