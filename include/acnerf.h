@@ -312,6 +312,23 @@ int acn_adam_multi(const AcnAdamTensor* tensors_host, int count, float beta1, fl
                    int32_t* steps_dev, const float* sumsq_dev, float max_norm, const float* grad_scale_dev,
                    float* coef_dev, int write_coef, void* stream);
 
+/* ---- (e): expert-parallel dispatch / combine around the sample all-to-all -
+ * New design (the reference is single-GPU); replaces, across GPUs, the per-expert
+ * nonzero / index_select / index_add_ loop of models/inr/meta_container.py:305-337.
+ * acn_a2a_pack: compacts a routed pair list (drops the -1 padding) into send rows
+ *   rows6 (M,6) = [xyz, dir] built from the implicit point form, grouped by expert
+ *   (= grouped by destination rank under block placement); out_point/out_weight (M,)
+ *   are the point id and routing weight of each row, counts (K+1,) the rows per expert
+ *   (counts[K] = M), offs (K+1,) their exclusive prefix.  Buffers are sized for
+ *   pairs->Mcap rows by the caller.
+ * acn_a2a_combine: out[point[j]] += weight[j] * y[j] for returned [rgb,sigma] rows
+ *   (out (P,4), caller zeroes);  acn_a2a_combine_bwd: d_y[j] = weight[j] * d_out[point[j]]. */
+int acn_a2a_pack(const AcnPoints* pts, const AcnPairs* pairs, int K, float* rows6, int32_t* out_point,
+                 float* out_weight, int32_t* counts, int32_t* offs, void* stream);
+int acn_a2a_combine(const float* y, const int32_t* point, const float* weight, int64_t M, float* out, void* stream);
+int acn_a2a_combine_bwd(const float* d_out, const int32_t* point, const float* weight, int64_t M, float* d_y,
+                        void* stream);
+
 #if defined(__GNUC__)
 #pragma GCC visibility pop
 #endif

@@ -108,6 +108,9 @@ SIGNATURES = {
     "acn_sumsq_accum": (C.c_int, [vp, i64, vp, vp]),
     "acn_sumsq_multi": (C.c_int, [P(AcnAdamTensor), C.c_int, vp, vp]),
     "acn_adam_multi": (C.c_int, [P(AcnAdamTensor), C.c_int, f32, f32, f32, vp, vp, f32, vp, vp, C.c_int, vp]),
+    "acn_a2a_pack": (C.c_int, [P(AcnPoints), P(AcnPairs), C.c_int, vp, vp, vp, vp, vp, vp]),
+    "acn_a2a_combine": (C.c_int, [vp, vp, vp, i64, vp, vp]),
+    "acn_a2a_combine_bwd": (C.c_int, [vp, vp, vp, i64, vp, vp]),
 }
 
 _lock = threading.Lock()

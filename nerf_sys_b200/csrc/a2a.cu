@@ -1,0 +1,139 @@
+// Expert-parallel dispatch / combine around the sample all-to-all (new design, the reference is single-GPU:
+// its per-expert nonzero / index_select / index_add_ loop is models/inr/meta_container.py:305-337).
+//
+//   k_a2a_count   : valid pairs per expert of the routed pair list (groups are stable: valid slots first, -1 padding last),
+//                   found by a binary search per expert; also the exclusive offsets of the groups in the send buffer.
+//   k_a2a_pack    : compacts the pair list (drops the padding) and builds the send rows [xyz, dir] straight from the
+//                   implicit point form (rays, t) - the (N*S, 6) tensor is never materialised.  Rows are grouped by
+//                   expert, and experts are placed on ranks in contiguous blocks, so the buffer is already grouped by
+//                   destination rank: it is the input of ONE all_to_all_single.
+//   k_a2a_combine : out[point[j]] += weight[j] * y[j] for the returned [rgb, sigma] rows (REDG.128 per pair).
+//   k_a2a_combine_bwd : d_y[j] = weight[j] * d_out[point[j]] (the rows that travel back to the owners).
+// All HBM-bound streaming kernels: 28 B out per routed pair for the dispatch, 16 B + one RED.128 for the combine.
+#include "common.cuh"
+
+namespace acn {
+
+// counts[e] (e < K), counts[K] = total; offs[e] = exclusive prefix.  One warp per expert, K <= ACN_MAX_EXPERTS.
+__global__ void __launch_bounds__(32 * ACN_MAX_EXPERTS) k_a2a_count(const int32_t* __restrict__ point, const int32_t* __restrict__ seg, int K,
+                                                                    int64_t Mcap, int32_t* __restrict__ counts, int32_t* __restrict__ offs) {
+  __shared__ int s_cnt[ACN_MAX_EXPERTS];
+  const int e = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (e < K && lane == 0) {
+    int64_t lo = seg[e], hi = seg[e + 1];
+    if (hi > Mcap) hi = Mcap;
+    if (lo > hi) lo = hi;
+    const int64_t base = lo;
+    while (lo < hi) {  // first slot with point < 0
+      int64_t mid = (lo + hi) >> 1;
+      if (__ldg(point + mid) >= 0)
+        lo = mid + 1;
+      else
+        hi = mid;
+    }
+    s_cnt[e] = (int)(lo - base);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int run = 0;
+    for (int k = 0; k < K; ++k) {
+      offs[k] = run;
+      counts[k] = s_cnt[k];
+      run += s_cnt[k];
+    }
+    counts[K] = run;
+    offs[K] = run;
+  }
+}
+
+__global__ void __launch_bounds__(256) k_a2a_pack(PointSrc src, const int32_t* __restrict__ point, const float* __restrict__ weight,
+                                                  const int32_t* __restrict__ seg, int K, int64_t Mcap, const int32_t* __restrict__ offs,
+                                                  float* __restrict__ rows6, int32_t* __restrict__ out_point, float* __restrict__ out_weight) {
+  __shared__ int s_seg[ACN_MAX_EXPERTS + 1], s_off[ACN_MAX_EXPERTS + 1];
+  if (threadIdx.x <= K) {
+    s_seg[threadIdx.x] = seg[threadIdx.x];
+    s_off[threadIdx.x] = offs[threadIdx.x];
+  }
+  __syncthreads();
+  int64_t M = s_seg[K];
+  if (M > Mcap) M = Mcap;
+  for (int64_t m = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; m < M; m += (int64_t)gridDim.x * blockDim.x) {
+    const int p = __ldg(point + m);
+    if (p < 0) continue;
+    int e = 0;
+    for (int k = 1; k < K; ++k)
+      if (m >= s_seg[k]) e = k;
+    const int64_t j = (int64_t)s_off[e] + (m - s_seg[e]);
+    float x, y, z, dx, dy, dz;
+    load_xyz(src, p, x, y, z);
+    load_dir(src, p, dx, dy, dz);
+    float2* r = reinterpret_cast<float2*>(rows6 + j * 6);
+    r[0] = make_float2(x, y);
+    r[1] = make_float2(z, dx);
+    r[2] = make_float2(dy, dz);
+    out_point[j] = p;
+    out_weight[j] = __ldg(weight + m);
+  }
+}
+
+__global__ void __launch_bounds__(256) k_a2a_combine(const float4* __restrict__ y, const int32_t* __restrict__ point, const float* __restrict__ weight,
+                                                     int64_t M, float4* __restrict__ out) {
+  for (int64_t j = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; j < M; j += (int64_t)gridDim.x * blockDim.x) {
+    const float w = __ldg(weight + j);
+    const float4 v = __ldg(y + j);
+    red_add(out + __ldg(point + j), make_float4(v.x * w, v.y * w, v.z * w, v.w * w));
+  }
+}
+
+__global__ void __launch_bounds__(256) k_a2a_combine_bwd(const float4* __restrict__ d_out, const int32_t* __restrict__ point,
+                                                         const float* __restrict__ weight, int64_t M, float4* __restrict__ d_y) {
+  for (int64_t j = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; j < M; j += (int64_t)gridDim.x * blockDim.x) {
+    const float w = __ldg(weight + j);
+    const float4 g = __ldg(d_out + __ldg(point + j));
+    d_y[j] = make_float4(g.x * w, g.y * w, g.z * w, g.w * w);
+  }
+}
+
+}  // namespace acn
+
+using namespace acn;
+
+extern "C" {
+
+int acn_a2a_pack(const AcnPoints* pts, const AcnPairs* pairs, int K, float* rows6, int32_t* out_point, float* out_weight, int32_t* counts,
+                 int32_t* offs, void* stream) {
+  ACN_REQUIRE(pts && pairs && rows6 && out_point && out_weight && counts && offs, "acn_a2a_pack: NULL argument");
+  ACN_REQUIRE(K >= 1 && K <= ACN_MAX_EXPERTS, "acn_a2a_pack: K must be in [1,%d]", ACN_MAX_EXPERTS);
+  ACN_REQUIRE(pairs->point && pairs->weight && pairs->seg, "acn_a2a_pack: needs a routed pair list (not the identity list)");
+  ACN_REQUIRE(pts->x6 || (pts->rays && pts->t && pts->S >= 1), "acn_a2a_pack: points need x6 or (rays,t,S)");
+  ACN_REQUIRE(pts->P < ((int64_t)1 << 31), "acn_a2a_pack: chunk the point set below 2^31");
+  cudaStream_t st = as_stream(stream);
+  k_a2a_count<<<1, 32 * ACN_MAX_EXPERTS, 0, st>>>(pairs->point, pairs->seg, K, pairs->Mcap, counts, offs);
+  ACN_LAUNCH_CHECK();
+  if (pairs->Mcap > 0) {
+    k_a2a_pack<<<persistent_grid((pairs->Mcap + 255) / 256, 8), 256, 0, st>>>(make_src(pts), pairs->point, pairs->weight, pairs->seg, K, pairs->Mcap,
+                                                                             offs, rows6, out_point, out_weight);
+    ACN_LAUNCH_CHECK();
+  }
+  return ACN_OK;
+}
+
+int acn_a2a_combine(const float* y, const int32_t* point, const float* weight, int64_t M, float* out, void* stream) {
+  ACN_REQUIRE(M >= 0 && out && (M == 0 || (y && point && weight)), "acn_a2a_combine: bad arguments");
+  if (M == 0) return ACN_OK;
+  k_a2a_combine<<<persistent_grid((M + 255) / 256, 8), 256, 0, as_stream(stream)>>>(reinterpret_cast<const float4*>(y), point, weight, M,
+                                                                                   reinterpret_cast<float4*>(out));
+  ACN_LAUNCH_CHECK();
+  return ACN_OK;
+}
+
+int acn_a2a_combine_bwd(const float* d_out, const int32_t* point, const float* weight, int64_t M, float* d_y, void* stream) {
+  ACN_REQUIRE(M >= 0 && (M == 0 || (d_out && point && weight && d_y)), "acn_a2a_combine_bwd: bad arguments");
+  if (M == 0) return ACN_OK;
+  k_a2a_combine_bwd<<<persistent_grid((M + 255) / 256, 8), 256, 0, as_stream(stream)>>>(reinterpret_cast<const float4*>(d_out), point, weight, M,
+                                                                                       reinterpret_cast<float4*>(d_y));
+  ACN_LAUNCH_CHECK();
+  return ACN_OK;
+}
+
+}  // extern "C"

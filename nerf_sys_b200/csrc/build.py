@@ -31,6 +31,7 @@ SOURCES = {
     "dense_tc.cu": [],
     "render.cu": [],
     "optim.cu": [],
+    "a2a.cu": ["-fmad=false"],
 }
 
 

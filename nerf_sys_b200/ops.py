@@ -343,6 +343,64 @@ def route_pack(pts: PointSet, centroids_host: Sequence[float], K: int, margin: f
 
 
 # --------------------------------------------------------------------------
+# (e) expert-parallel dispatch / combine around the sample all-to-all
+# --------------------------------------------------------------------------
+def a2a_pack(pts: PointSet, pairs: PairList, K: int):
+    """Compacts a routed pair list into all-to-all send rows (meta_container.py:305-313 across GPUs): returns
+    rows6 (M,6) [xyz,dir] grouped by expert, point (M,) int32, weight (M,), counts (K host ints).  One
+    4*(K+1)-byte device->host read (the reference reads K nonzero() sizes)."""
+    if pairs.identity:
+        raise ValueError("a2a_pack needs a routed pair list")
+    dev = pts.device
+    cap = pairs.M
+    rows = torch.empty(cap, 6, device=dev, dtype=torch.float32)
+    point = torch.empty(cap, device=dev, dtype=torch.int32)
+    weight = torch.empty(cap, device=dev, dtype=torch.float32)
+    counts = torch.empty(K + 1, device=dev, dtype=torch.int32)
+    offs = torch.empty(K + 1, device=dev, dtype=torch.int32)
+    cp, cq = pts.c(), pairs.c()
+    with torch.cuda.device(dev), _timed("a2a_pack"):
+        check(lib().acn_a2a_pack(C.byref(cp), C.byref(cq), K, _ptr(rows), _ptr(point), _ptr(weight), _ptr(counts), _ptr(offs),
+                                 _stream()), "acn_a2a_pack")
+    _count(2)
+    ch = counts.tolist()
+    M = ch[K]
+    return rows[:M], point[:M], weight[:M], ch[:K]
+
+
+class A2aCombineFn(torch.autograd.Function):
+    """out[point[j]] += weight[j] * y[j] (meta_container.py:322-337); backward d_y[j] = weight[j] * d_out[point[j]]."""
+
+    @staticmethod
+    def forward(ctx, y: Tensor, point: Tensor, weight: Tensor, P: int):
+        yy = _f32(y.detach(), "y")
+        M = yy.shape[0]
+        if yy.dim() != 2 or yy.shape[1] != 4 or point.numel() != M or weight.numel() != M:
+            raise ValueError("a2a_combine: y must be (M,4) with M point ids and weights")
+        pt, wt = _need(point, "point", torch.int32), _f32(weight, "weight")
+        out = torch.zeros(P, 4, device=yy.device, dtype=torch.float32)
+        with torch.cuda.device(yy.device), _timed("a2a_combine"):
+            check(lib().acn_a2a_combine(_ptr(yy), _ptr(pt), _ptr(wt), M, _ptr(out), _stream()), "acn_a2a_combine")
+        _count(1)
+        ctx.save_for_backward(pt, wt)
+        return out
+
+    @staticmethod
+    def backward(ctx, d_out):
+        pt, wt = ctx.saved_tensors
+        g = _f32(d_out, "d_out")
+        d_y = torch.empty(pt.numel(), 4, device=g.device, dtype=torch.float32)
+        with torch.cuda.device(g.device), _timed("a2a_combine_bwd"):
+            check(lib().acn_a2a_combine_bwd(_ptr(g), _ptr(pt), _ptr(wt), pt.numel(), _ptr(d_y), _stream()), "acn_a2a_combine_bwd")
+        _count(1)
+        return d_y, None, None, None
+
+
+def a2a_combine(y: Tensor, point: Tensor, weight: Tensor, P: int) -> Tensor:
+    return A2aCombineFn.apply(y, point, weight, int(P))
+
+
+# --------------------------------------------------------------------------
 # a9-a11 stand-alone encoders
 # --------------------------------------------------------------------------
 def hashgrid_indices(x01: Tensor, g: AcnGridDesc) -> Tensor:

@@ -132,30 +132,31 @@ def exchange_counts(counts: Sequence[int], group=None) -> List[List[int]]:
     return table  # type: ignore[return-value]
 
 
-def expert_parallel_apply(x: Tensor, sel_point: Tensor, sel_weight: Tensor, counts: Sequence[int], P: int,
-                          expert_fn: Callable[[Tensor, List[int], List[Tensor]], Tensor], group=None, out_dim: int = 4) -> Tensor:
+def expert_parallel_apply(rows: Tensor, counts: Sequence[int], expert_fn: Callable[[Tensor, List[int], List[Tensor]], Tensor],
+                          combine: Callable[[Tensor], Tensor], group=None) -> Tensor:
     """Soft-routed container forward with experts sharded over ranks (meta_container.py:305-321 semantics).
 
-    x          (P, D) this rank's sample points (xyz + direction)
-    sel_point  (M,) int64 point index of every routed (point, expert) pair, GROUPED BY EXPERT 0..K-1
-    sel_weight (M,) routing weight of the pair
-    counts     K host ints: pairs per expert (sum = M)
+    rows       (M, D) this rank's routed samples (xyz + direction), one row per (point, expert) pair, GROUPED BY
+               EXPERT 0..K-1 (on the GPU: `ops.a2a_pack`, built straight from rays and t)
+    counts     K host ints: rows per expert (sum = M)
     expert_fn(rows (R, D), local_experts, index) -> (R, out_dim): evaluates this rank's experts; ``index[j]`` holds the
                rows of ``rows`` that belong to ``local_experts[j]`` (every row belongs to exactly one).
-    Returns out (P, out_dim) = sum over the pairs of a point of weight * expert(point), differentiable w.r.t. the
-    parameters expert_fn uses (gradients reach the owning rank through the reversed all-to-all)."""
+    combine(y (M, out_dim)) -> out (P, out_dim): blends the returned rows into the points with the routing weights
+               (on the GPU: `ops.a2a_combine`).
+    The result is differentiable w.r.t. the parameters expert_fn uses (gradients reach the owning rank through the
+    reversed all-to-all)."""
     world, rank = _world(group)
     K = len(counts)
     owner = expert_owner(K, world)
     mine = [e for e in range(K) if owner[e] == rank]
-    if sel_point.numel() != sum(counts):
-        raise ValueError(f"sel_point has {sel_point.numel()} pairs but counts sum to {sum(counts)}")
-    rows = x.index_select(0, sel_point)
+    if rows.shape[0] != sum(counts):
+        raise ValueError(f"{rows.shape[0]} routed rows but counts sum to {sum(counts)}")
+    dev = rows.device
     if world == 1:
         bounds = [0]
         for c in counts:
             bounds.append(bounds[-1] + int(c))
-        index = [torch.arange(bounds[e], bounds[e + 1], device=x.device) for e in range(K)]
+        index = [torch.arange(bounds[e], bounds[e + 1], device=dev) for e in range(K)]
         y = expert_fn(rows, list(range(K)), index)
     else:
         table = exchange_counts(counts, group)
@@ -168,16 +169,15 @@ def expert_parallel_apply(x: Tensor, sel_point: Tensor, sel_weight: Tensor, coun
             for j, e in enumerate(mine):
                 n = table[s][e]
                 if n:
-                    index[j].append(torch.arange(off, off + n, device=x.device))
+                    index[j].append(torch.arange(off, off + n, device=dev))
                 off += n
-        index = [torch.cat(ix) if ix else torch.empty(0, dtype=torch.long, device=x.device) for ix in index]
+        index = [torch.cat(ix) if ix else torch.empty(0, dtype=torch.long, device=dev) for ix in index]
         y_owner = expert_fn(got, mine, index)
         if torch.is_grad_enabled() and not y_owner.requires_grad:
             # every rank must take part in the backward exchange even if its own experts are frozen (config 4)
-            y_owner = y_owner + torch.zeros(1, device=x.device, dtype=y_owner.dtype, requires_grad=True)
+            y_owner = y_owner + torch.zeros(1, device=dev, dtype=y_owner.dtype, requires_grad=True)
         y = _AllToAll.apply(y_owner, recv, send, group)
-    out = x.new_zeros(P, out_dim)
-    return out.index_add(0, sel_point, y * sel_weight.unsqueeze(1))
+    return combine(y)
 
 
 def container_evaluate_ep(model, pts, params=None, group=None) -> Tensor:
@@ -190,16 +190,9 @@ def container_evaluate_ep(model, pts, params=None, group=None) -> Tensor:
     K = len(model.submodules)
     with torch.no_grad():
         pairs = ops.route_pack(pts, model.centroids_host(), K, model.boundary_margin, model.cluster_2d)
-        valid = pairs.point >= 0
-        csum = torch.cumsum(valid.to(torch.int32), 0)
-        seg = pairs.seg.to(torch.long)
-        ends = torch.where(seg[1:] > 0, csum[(seg[1:] - 1).clamp_min(0)], torch.zeros_like(seg[1:], dtype=csum.dtype))
-        ends = ends.tolist()  # the one host read of the step (the reference reads K nonzero() sizes, meta_container.py:309)
-        counts = [int(ends[0])] + [int(ends[e] - ends[e - 1]) for e in range(1, K)]
-        sel = torch.nonzero(valid).squeeze(1)
-        sel_point = pairs.point.index_select(0, sel).to(torch.long)
-        sel_weight = pairs.weight.index_select(0, sel)
-        x6 = pts.x6 if pts.x6 is not None else ops.sample_points(pts.rays, pts.t)
+        # send rows [xyz, dir] built from (rays, t), padding dropped, grouped by expert = by destination rank;
+        # counts: the one host read of the step (the reference reads K nonzero() sizes, meta_container.py:309)
+        rows6, sel_point, sel_weight, counts = ops.a2a_pack(pts, pairs, K)
     spec_all = model.expert_spec()
 
     def expert_fn(rows: Tensor, local: List[int], index: List[Tensor]) -> Tensor:
@@ -223,4 +216,4 @@ def container_evaluate_ep(model, pts, params=None, group=None) -> Tensor:
             mlp.extend(model.submodules[e].mlp_tensors(model._sub_params(params, e)))
         return ops.ngp_experts(ops.PointSet(x6=rows.contiguous()), pl, spec, tables, mlp)
 
-    return expert_parallel_apply(x6, sel_point, sel_weight, counts, pts.P, expert_fn, group)
+    return expert_parallel_apply(rows6, counts, expert_fn, lambda y: ops.a2a_combine(y, sel_point, sel_weight, pts.P), group)

@@ -168,6 +168,41 @@ def test_route_pack_is_a_stable_partition():
                     assert (weight[seg[k]:seg[k] + live.numel()] == 1).all()
 
 
+def test_a2a_pack_and_combine_match_the_reference_loop():
+    """Dispatch rows / blend of meta_container.py:305-337 as the all-to-all sees them: rows grouped by expert in
+    nonzero() order (exact: positions are rebuilt with the same mul-then-add), combine == index_add_ of w*y."""
+    from nerf_sys_b200 import ops
+    aabb, cent, _ = O.grid_scene(2, 4)
+    for N, S, margin in ((1, 1, 1.05), (37, 16, 1.05), (300, 96, 1.6), (256, 64, 1.0)):
+        rays = O.aerial_rays(N, aabb, seed=N)
+        g = torch.Generator().manual_seed(N)
+        t = O.stratified_t(rays[:, 6], rays[:, 7], S, u=torch.rand(N, S, generator=g))
+        x6 = O.sample_points(rays, t).reshape(-1, 6)
+        ps = ops.PointSet(rays=rays.to(DEV), t=t.to(DEV))
+        pairs = ops.route_pack(ps, cent.reshape(-1).tolist(), 8, margin, True)
+        rows, point, weight, counts = ops.a2a_pack(ps, pairs, 8)
+        wd, hd = O.routing(x6[:, :3], cent, margin, True, direct=True)
+        exp_rows, exp_point, exp_w = [], [], []
+        for k in range(8):
+            sel = ((wd[:, k] > 0) if wd is not None else (hd == k)).nonzero().squeeze(1)
+            assert counts[k] == sel.numel()
+            exp_rows.append(x6[sel]); exp_point.append(sel)
+            exp_w.append(wd[sel, k] if wd is not None else torch.ones(sel.numel()))
+        exp_rows, exp_point, exp_w = torch.cat(exp_rows), torch.cat(exp_point), torch.cat(exp_w)
+        assert torch.equal(point.cpu().long(), exp_point)
+        assert torch.equal(rows.cpu(), exp_rows), "send rows are bit-exact copies of the sample points"
+        close(weight, exp_w, 2e-7, "pair weights")
+        M, P = exp_point.numel(), N * S
+        y = torch.randn(M, 4, generator=g)
+        yd = y.to(DEV).requires_grad_(True)
+        out = ops.a2a_combine(yd, point, weight, P)
+        ref = torch.zeros(P, 4).index_add_(0, exp_point, y * weight.cpu().unsqueeze(1))
+        close(out, ref, 1e-6, "combine")
+        cot = torch.randn(P, 4, generator=g)
+        (out * cot.to(DEV)).sum().backward()
+        assert torch.equal(yd.grad.cpu(), cot[exp_point] * weight.cpu().unsqueeze(1)), "combine backward is one multiply"
+
+
 # ----------------------------------------------------------------------------- a9-a11
 def test_hash_indices_bit_exact_and_encoders_golden():
     from nerf_sys_b200 import ops

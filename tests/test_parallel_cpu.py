@@ -104,7 +104,8 @@ def _ep_worker(rank, world, frozen):
             y = y.index_add(0, ix, torch.tanh(rows[ix] @ Ws[e]))
         return y
 
-    out = PL.expert_parallel_apply(x, sel_point, sel_w, counts, P, expert_fn)
+    out = PL.expert_parallel_apply(x.index_select(0, sel_point), counts, expert_fn,
+                                   lambda y: x.new_zeros(P, 4).index_add(0, sel_point, y * sel_w.unsqueeze(1)))
     ref_W = [w.clone().requires_grad_(True) for w in _make_weights()]
     ref = _dense(x, sel_point, sel_w, counts, ref_W)
     assert torch.allclose(out, ref, atol=1e-6), (out - ref).abs().max()
@@ -143,7 +144,8 @@ def test_expert_parallel_single_process_path():
             y = y.index_add(0, ix, torch.tanh(rows[ix] @ Ws[e]))
         return y
 
-    out = PL.expert_parallel_apply(x, sel_point, sel_w, counts, 200, expert_fn)
+    out = PL.expert_parallel_apply(x.index_select(0, sel_point), counts, expert_fn,
+                                   lambda y: x.new_zeros(200, 4).index_add(0, sel_point, y * sel_w.unsqueeze(1)))
     assert torch.allclose(out, _dense(x, sel_point, sel_w, counts, Ws), atol=1e-6)
 
 
