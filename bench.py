@@ -222,6 +222,55 @@ def render_c5(device, world, barrier, max_over_ranks, frames=4):
                       "frame all-gathered"}
 
 
+def train_c3(device, rank, world, barrier, max_over_ranks, steps=10, warmup=3):
+    """Config 3: the 8-expert container (soft routing, margin 1.05) trained on 8192 aerial rays per GPU x 96 samples: full-container
+    forward + backward + global clip + Adam (the runtime_adapt step, runtime_adapt.py:249-268).  world > 1: experts sharded in blocks
+    over the ranks, every routed sample travels to its expert's owner and back (one all-to-all each way, and again in the backward
+    pass), background-head gradients all-reduced, clip norm all-reduced."""
+    from nerf_sys_b200 import parallel as PL
+    from nerf_sys_b200.nerfs.losses import compute_mse_loss
+    from nerf_sys_b200.optim import FusedAdam
+    from oracle import acnerf_oracle as O  # scene constants / synthetic rays only
+    model, aabb = build_c5(device)
+    model.train()
+    if world > 1:
+        model.set_expert_parallel(True)
+    groups, shared = PL.owned_param_groups(model)
+    lrs = {"encoding": 1e-2, "sigma": 2e-3, "color": 2e-3, "background": 1e-3}
+    opt = FusedAdam([{"params": g["params"], "lr": lrs[n]} for n, g in groups.items()], max_grad_norm=1.0).shard_grad_norm(None, shared)
+    nb = 4
+    g = torch.Generator().manual_seed(900 + rank)
+    rays = [O.aerial_rays(N_RAYS, aabb, seed=1000 + 16 * rank + b).to(device) for b in range(nb)]
+    gts = [torch.rand(N_RAYS, 3, generator=g).to(device) for _ in range(nb)]
+
+    def step(i):
+        opt.zero_grad(set_to_none=True)
+        loss = compute_mse_loss(P, model, {"rays": rays[i % nb], "rgbs": gts[i % nb]})
+        (loss / world).backward()  # the step's loss is the mean over the world x 8192 rays of all ranks
+        PL.allreduce_shared_grads(shared, average=False)
+        opt.step()
+        return loss
+
+    for i in range(max(warmup, 3)):
+        step(i)
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(steps):
+        loss = step(i)
+    e1.record()
+    barrier()
+    ms = max_over_ranks(e0.elapsed_time(e1))
+    out = {"value": world * N_RAYS * steps / (ms / 1e3), "unit": "rays/s", "ms_per_step": ms / steps, "loss": float(loss.item()),
+           "config": f"config[2]: 8 experts (2^20-row tables), {N_RAYS} aerial rays/GPU x {S_TRAIN} samples, soft routing, fwd+bwd+clip+Adam, "
+                     + ("all 8 experts on one GPU" if world == 1 else
+                        f"experts sharded {8 // world if 8 % world == 0 else '~' + str(8 / world)} per GPU over {world} GPUs, NCCL sample all-to-all "
+                        "(dispatch 24 B/row, combine 16 B/row, reversed in backward), eager launches")}
+    del model, opt
+    torch.cuda.empty_cache()
+    return out
+
+
 class P:  # the argparse namespace fields compute_mse_loss reads (common/args.py)
     ray_samples, chunk_points, color_space = S_TRAIN, 4456448, "identity"
 
@@ -309,6 +358,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-render", action="store_true")
+    ap.add_argument("--no-c3", action="store_true", help="skip the 8-expert container training measurement (config[2])")
     ap.add_argument("--no-graph", action="store_true", help="drive every step from Python instead of replaying a CUDA graph")
     ap.add_argument("--bwd-chunks", type=int, default=1, help="chunks of the pipelined backward (1 = MLP backward, then table scatter)")
     ap.add_argument("--mlp-math", default="f16tc", choices=["f16tc", "fp32"],
@@ -450,6 +500,9 @@ def main():
     c5 = None
     if not args.no_render:
         c5 = render_c5(dev, world, barrier, max_over_ranks)
+    c3 = None
+    if not args.no_c3:
+        c3 = train_c3(dev, rank, world, barrier, max_over_ranks)
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -475,7 +528,7 @@ def main():
                                             "collective": "none" if world == 1 else "nccl all-reduce of 643 bg-head grads"},
             "clocks": clk, "e2e": {"value": world * N_RAYS * K / (ms_e2e / 1e3), "unit": "rays/s", "h2d_bytes_per_step": bytes_in,
                                    "d2h_bytes_per_step": 4, "ms_per_step": ms_e2e / K},
-            "gpu_launches": launches, "roofline": roofline, "kernels": kern, "render": render, "render_c5": c5, "cpu_baseline": cpu,
+            "gpu_launches": launches, "roofline": roofline, "kernels": kern, "render": render, "render_c5": c5, "train_c3": c3, "cpu_baseline": cpu,
             "final_loss": final_loss}))
     if world > 1:
         # Leave without tearing NCCL down: the captured graph still references the communicator's kernels and

@@ -10,6 +10,8 @@
 //   k_a2a_combine : out[point[j]] += weight[j] * y[j] for the returned [rgb, sigma] rows (REDG.128 per pair).
 //   k_a2a_combine_bwd : d_y[j] = weight[j] * d_out[point[j]] (the rows that travel back to the owners).
 // All HBM-bound streaming kernels: 28 B out per routed pair for the dispatch, 16 B + one RED.128 for the combine.
+#include <string.h>
+
 #include "common.cuh"
 
 namespace acn {
@@ -94,6 +96,90 @@ __global__ void __launch_bounds__(256) k_a2a_combine_bwd(const float4* __restric
   }
 }
 
+// ---- the same three steps with the rows living in the OWNER's memory (NVLink peer mappings) ---------------------
+// route.base[e] is the owner's buffer as mapped into this process (or a local buffer when this rank owns e) and
+// route.row0[e] the first row of this rank's block of expert e in it.  Pair j of the compact list belongs to expert
+// e = max{k : offs[k] <= j} and is row route.row0[e] + (j - offs[e]) there.  Stores and loads are 8- and 16-byte
+// vectors of consecutive rows across a warp: full 32-byte sectors on the NVLink path.
+struct RouteDev {
+  void* base[ACN_MAX_EXPERTS];
+  int64_t row0[ACN_MAX_EXPERTS];
+};
+
+__device__ __forceinline__ int expert_of(const int* s_off, int K, int64_t j) {
+  int e = 0;
+  for (int k = 1; k < K; ++k)
+    if (j >= s_off[k]) e = k;
+  return e;
+}
+
+__global__ void __launch_bounds__(256) k_a2a_push_rows(PointSrc src, const int32_t* __restrict__ point, const float* __restrict__ weight,
+                                                       const int32_t* __restrict__ seg, int K, int64_t Mcap, const int32_t* __restrict__ offs,
+                                                       RouteDev route, int32_t* __restrict__ out_point, float* __restrict__ out_weight) {
+  __shared__ int s_seg[ACN_MAX_EXPERTS + 1], s_off[ACN_MAX_EXPERTS + 1];
+  if (threadIdx.x <= K) {
+    s_seg[threadIdx.x] = seg[threadIdx.x];
+    s_off[threadIdx.x] = offs[threadIdx.x];
+  }
+  __syncthreads();
+  int64_t M = s_seg[K];
+  if (M > Mcap) M = Mcap;
+  for (int64_t m = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; m < M; m += (int64_t)gridDim.x * blockDim.x) {
+    const int p = __ldg(point + m);
+    if (p < 0) continue;
+    int e = 0;
+    for (int k = 1; k < K; ++k)
+      if (m >= s_seg[k]) e = k;
+    const int64_t i = m - s_seg[e];
+    float x, y, z, dx, dy, dz;
+    load_xyz(src, p, x, y, z);
+    load_dir(src, p, dx, dy, dz);
+    float2* r = reinterpret_cast<float2*>(static_cast<float*>(route.base[e]) + (route.row0[e] + i) * 6);
+    r[0] = make_float2(x, y);
+    r[1] = make_float2(z, dx);
+    r[2] = make_float2(dy, dz);
+    const int64_t j = (int64_t)s_off[e] + i;
+    out_point[j] = p;
+    out_weight[j] = __ldg(weight + m);
+  }
+}
+
+__global__ void __launch_bounds__(256) k_a2a_pull_combine(RouteDev route, const int32_t* __restrict__ point, const float* __restrict__ weight,
+                                                          const int32_t* __restrict__ offs, int K, int64_t M, float4* __restrict__ out) {
+  __shared__ int s_off[ACN_MAX_EXPERTS + 1];
+  if (threadIdx.x <= K) s_off[threadIdx.x] = offs[threadIdx.x];
+  __syncthreads();
+  for (int64_t j = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; j < M; j += (int64_t)gridDim.x * blockDim.x) {
+    const int e = expert_of(s_off, K, j);
+    const float4 v = __ldcg(static_cast<const float4*>(route.base[e]) + route.row0[e] + (j - s_off[e]));  // L2-coherent: a peer wrote it
+    const float w = __ldg(weight + j);
+    red_add(out + __ldg(point + j), make_float4(v.x * w, v.y * w, v.z * w, v.w * w));
+  }
+}
+
+__global__ void __launch_bounds__(256) k_a2a_push_grad(const float4* __restrict__ d_out, const int32_t* __restrict__ point,
+                                                       const float* __restrict__ weight, const int32_t* __restrict__ offs, int K, int64_t M,
+                                                       RouteDev route) {
+  __shared__ int s_off[ACN_MAX_EXPERTS + 1];
+  if (threadIdx.x <= K) s_off[threadIdx.x] = offs[threadIdx.x];
+  __syncthreads();
+  for (int64_t j = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; j < M; j += (int64_t)gridDim.x * blockDim.x) {
+    const int e = expert_of(s_off, K, j);
+    const float w = __ldg(weight + j);
+    const float4 g = __ldg(d_out + __ldg(point + j));
+    *(static_cast<float4*>(route.base[e]) + route.row0[e] + (j - s_off[e])) = make_float4(g.x * w, g.y * w, g.z * w, g.w * w);
+  }
+}
+
+static inline bool make_route(const AcnA2aRoute* r, int K, RouteDev& d) {
+  for (int e = 0; e < ACN_MAX_EXPERTS; ++e) {
+    d.base[e] = e < K ? r->base[e] : nullptr;
+    d.row0[e] = e < K ? r->row0[e] : 0;
+    if (e < K && (!d.base[e] || d.row0[e] < 0)) return false;
+  }
+  return true;
+}
+
 }  // namespace acn
 
 using namespace acn;
@@ -133,6 +219,92 @@ int acn_a2a_combine_bwd(const float* d_out, const int32_t* point, const float* w
   k_a2a_combine_bwd<<<persistent_grid((M + 255) / 256, 8), 256, 0, as_stream(stream)>>>(reinterpret_cast<const float4*>(d_out), point, weight, M,
                                                                                        reinterpret_cast<float4*>(d_y));
   ACN_LAUNCH_CHECK();
+  return ACN_OK;
+}
+
+int acn_a2a_count(const AcnPairs* pairs, int K, int32_t* counts, int32_t* offs, void* stream) {
+  ACN_REQUIRE(pairs && counts && offs, "acn_a2a_count: NULL argument");
+  ACN_REQUIRE(K >= 1 && K <= ACN_MAX_EXPERTS, "acn_a2a_count: K must be in [1,%d]", ACN_MAX_EXPERTS);
+  ACN_REQUIRE(pairs->point && pairs->seg, "acn_a2a_count: needs a routed pair list (not the identity list)");
+  k_a2a_count<<<1, 32 * ACN_MAX_EXPERTS, 0, as_stream(stream)>>>(pairs->point, pairs->seg, K, pairs->Mcap, counts, offs);
+  ACN_LAUNCH_CHECK();
+  return ACN_OK;
+}
+
+int acn_a2a_push_rows(const AcnPoints* pts, const AcnPairs* pairs, int K, const int32_t* offs, const AcnA2aRoute* route, int32_t* out_point,
+                      float* out_weight, void* stream) {
+  ACN_REQUIRE(pts && pairs && offs && route && out_point && out_weight, "acn_a2a_push_rows: NULL argument");
+  ACN_REQUIRE(K >= 1 && K <= ACN_MAX_EXPERTS, "acn_a2a_push_rows: K must be in [1,%d]", ACN_MAX_EXPERTS);
+  ACN_REQUIRE(pairs->point && pairs->weight && pairs->seg, "acn_a2a_push_rows: needs a routed pair list (not the identity list)");
+  ACN_REQUIRE(pts->x6 || (pts->rays && pts->t && pts->S >= 1), "acn_a2a_push_rows: points need x6 or (rays,t,S)");
+  ACN_REQUIRE(pts->P < ((int64_t)1 << 31), "acn_a2a_push_rows: chunk the point set below 2^31");
+  RouteDev rd;
+  ACN_REQUIRE(make_route(route, K, rd), "acn_a2a_push_rows: route has a NULL base or a negative row");
+  if (pairs->Mcap == 0) return ACN_OK;
+  k_a2a_push_rows<<<persistent_grid((pairs->Mcap + 255) / 256, 8), 256, 0, as_stream(stream)>>>(make_src(pts), pairs->point, pairs->weight, pairs->seg,
+                                                                                              K, pairs->Mcap, offs, rd, out_point, out_weight);
+  ACN_LAUNCH_CHECK();
+  return ACN_OK;
+}
+
+int acn_a2a_pull_combine(const AcnA2aRoute* route, const int32_t* point, const float* weight, const int32_t* offs, int K, int64_t M, float* out,
+                         void* stream) {
+  ACN_REQUIRE(route && offs && out && M >= 0 && (M == 0 || (point && weight)), "acn_a2a_pull_combine: bad arguments");
+  ACN_REQUIRE(K >= 1 && K <= ACN_MAX_EXPERTS, "acn_a2a_pull_combine: K must be in [1,%d]", ACN_MAX_EXPERTS);
+  RouteDev rd;
+  ACN_REQUIRE(make_route(route, K, rd), "acn_a2a_pull_combine: route has a NULL base or a negative row");
+  if (M == 0) return ACN_OK;
+  k_a2a_pull_combine<<<persistent_grid((M + 255) / 256, 8), 256, 0, as_stream(stream)>>>(rd, point, weight, offs, K, M, reinterpret_cast<float4*>(out));
+  ACN_LAUNCH_CHECK();
+  return ACN_OK;
+}
+
+int acn_a2a_push_grad(const float* d_out, const int32_t* point, const float* weight, const int32_t* offs, int K, int64_t M,
+                      const AcnA2aRoute* route, void* stream) {
+  ACN_REQUIRE(route && offs && M >= 0 && (M == 0 || (d_out && point && weight)), "acn_a2a_push_grad: bad arguments");
+  ACN_REQUIRE(K >= 1 && K <= ACN_MAX_EXPERTS, "acn_a2a_push_grad: K must be in [1,%d]", ACN_MAX_EXPERTS);
+  RouteDev rd;
+  ACN_REQUIRE(make_route(route, K, rd), "acn_a2a_push_grad: route has a NULL base or a negative row");
+  if (M == 0) return ACN_OK;
+  k_a2a_push_grad<<<persistent_grid((M + 255) / 256, 8), 256, 0, as_stream(stream)>>>(reinterpret_cast<const float4*>(d_out), point, weight, offs, K, M,
+                                                                                     rd);
+  ACN_LAUNCH_CHECK();
+  return ACN_OK;
+}
+
+/* ---- exchange slabs: memory one rank allocates and its peers map over NVLink (CUDA IPC, one process per GPU) ---- */
+int acn_p2p_alloc(int64_t bytes, void** ptr, void* handle64) {
+  ACN_REQUIRE(bytes > 0 && ptr && handle64, "acn_p2p_alloc: bad arguments");
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "handle size");
+  void* p = nullptr;
+  ACN_CUDA(cudaMalloc(&p, (size_t)bytes));
+  cudaIpcMemHandle_t h;
+  cudaError_t e = cudaIpcGetMemHandle(&h, p);
+  if (e != cudaSuccess) {
+    cudaFree(p);
+    set_error("acn_p2p_alloc: cudaIpcGetMemHandle: %s", cudaGetErrorString(e));
+    return ACN_ECUDA;
+  }
+  memcpy(handle64, &h, 64);
+  *ptr = p;
+  return ACN_OK;
+}
+
+int acn_p2p_free(void* ptr) {
+  if (ptr) ACN_CUDA(cudaFree(ptr));
+  return ACN_OK;
+}
+
+int acn_p2p_open(const void* handle64, void** ptr) {
+  ACN_REQUIRE(handle64 && ptr, "acn_p2p_open: bad arguments");
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle64, 64);
+  ACN_CUDA(cudaIpcOpenMemHandle(ptr, h, cudaIpcMemLazyEnablePeerAccess));
+  return ACN_OK;
+}
+
+int acn_p2p_close(void* ptr) {
+  if (ptr) ACN_CUDA(cudaIpcCloseMemHandle(ptr));
   return ACN_OK;
 }
 

@@ -58,6 +58,16 @@ class MetaContainer(MetaModule):
             self.bg_mlp = nn.Sequential(nn.Linear(self.bg_dir_enc.out_dim, self.bg_hidden_dim, bias=True), nn.ReLU(),
                                         nn.Linear(self.bg_hidden_dim, 3, bias=True), nn.Sigmoid())
         self._cent_host = None
+        self._ep = None  # (process group or None for the default group) when the experts are sharded over ranks
+
+    # ---- expert parallelism (new: the reference is single-GPU) ----------
+    def set_expert_parallel(self, enabled: bool = True, group=None) -> "MetaContainer":
+        """Shard the experts over the ranks of ``group`` (block placement, parallel.expert_owner): `evaluate` /
+        `forward` then route locally, ship every routed sample to its expert's owner with one all-to-all, evaluate
+        there and ship [rgb, sigma] back.  Every rank keeps the full state_dict; only the owner's copy of an expert
+        is evaluated, receives gradients and needs optimiser state (parallel.owned_param_groups)."""
+        object.__setattr__(self, "_ep", (group,) if enabled else None)
+        return self
 
     # ---- host copy of the centroids (they travel in the kernel-parameter block) ----
     def centroids_host(self) -> List[float]:
@@ -88,6 +98,10 @@ class MetaContainer(MetaModule):
             return self.submodules[active_module].evaluate(pts, self._sub_params(params, active_module))
         for sub in self.submodules:
             sub._require_fused()
+        if self._ep is not None:
+            from ... import parallel
+            if parallel._world(self._ep[0])[0] > 1:
+                return parallel.container_evaluate_ep(self, pts, params=params, group=self._ep[0])
         if K == 1 and self.boundary_margin > 1.0:
             # a single centroid always gets weight 1: skip the pack, keep the fused launch
             return self.submodules[0].evaluate(pts, self._sub_params(params, 0))

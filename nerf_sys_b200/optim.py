@@ -10,6 +10,7 @@ from __future__ import annotations
 from typing import Optional
 
 import torch
+import torch.distributed as dist
 
 import ctypes as C
 
@@ -30,6 +31,15 @@ class FusedAdam(torch.optim.Optimizer):
         self.max_grad_norm = max_grad_norm
         self._steps_dev = None
         self._index = {}
+        self._shard = None
+
+    def shard_grad_norm(self, group, shared_params) -> "FusedAdam":
+        """Expert parallelism: this optimiser holds one rank's experts plus the replicated ``shared_params``.  The clip
+        of runtime_adapt.py:265 is over the norm of ALL parameters, so the sum of squares of the sharded tensors is
+        all-reduced over ``group`` and the replicated ones (identical on every rank after their gradient all-reduce)
+        are counted once."""
+        self._shard = (group, {id(p) for p in shared_params})
+        return self
 
     # ---- device-side bookkeeping -------------------------------------------------------------
     def _ensure(self, dev):
@@ -111,6 +121,18 @@ class FusedAdam(torch.optim.Optimizer):
                     for arr, n in chunks:
                         check(L.acn_sumsq_multi(arr, n, self._acc.data_ptr(), stream), "acn_sumsq_multi")
                 ops._count(len(chunks) + 1)
+                if self._shard is not None and dist.is_initialized() and dist.get_world_size(self._shard[0]) > 1:
+                    sh = [d for d in descs if id(d[0]) in self._shard[1]]
+                    rep = torch.zeros_like(self._acc)
+                    if sh:
+                        arr = (AcnAdamTensor * len(sh))()
+                        for i, (p, g, st, lr, wd) in enumerate(sh):
+                            arr[i].param, arr[i].grad, arr[i].n = p.data_ptr(), g.data_ptr(), p.numel()
+                        check(L.acn_sumsq_multi(arr, len(sh), rep.data_ptr(), stream), "acn_sumsq_multi")
+                        ops._count(1)
+                    part = self._acc - rep
+                    dist.all_reduce(part, group=self._shard[0])
+                    self._acc.copy_(part + rep)
             with ops._timed("adam"):
                 for ci, (arr, n) in enumerate(chunks):
                     check(L.acn_adam_multi(arr, n, float(b1), float(b2), eps, self._steps_dev.data_ptr(),

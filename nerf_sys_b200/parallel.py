@@ -217,3 +217,27 @@ def container_evaluate_ep(model, pts, params=None, group=None) -> Tensor:
         return ops.ngp_experts(ops.PointSet(x6=rows.contiguous()), pl, spec, tables, mlp)
 
     return expert_parallel_apply(rows6, counts, expert_fn, lambda y: ops.a2a_combine(y, sel_point, sel_weight, pts.P), group)
+
+
+def owned_param_groups(model, group=None):
+    """`MetaContainer.get_param_groups()` restricted to what this rank trains under expert parallelism: its own
+    experts' tensors plus the replicated background head (whose gradients `allreduce_shared_grads` averages).
+    Returns (groups, shared_params)."""
+    world, rank = _world(group)
+    owner = expert_owner(len(model.submodules), world)
+    enc, sig, col = [], [], []
+    for e, sub in enumerate(model.submodules):
+        if owner[e] != rank:
+            continue
+        g = sub.get_param_groups()
+        enc.extend(g["encoding"]["params"])
+        sig.extend(g["sigma"]["params"])
+        col.extend(g["color"]["params"])
+    shared = []
+    if getattr(model, "use_bg_nerf", False):
+        shared = list(model.bg_dir_enc.parameters()) + list(model.bg_mlp.parameters())
+    groups = {}
+    for name, ps in (("encoding", enc), ("sigma", sig), ("color", col), ("background", shared)):
+        if ps:
+            groups[name] = {"params": ps}
+    return groups, shared

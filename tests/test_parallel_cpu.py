@@ -177,3 +177,37 @@ def _render_worker(rank, world):
 @pytest.mark.parametrize("world", [2, 3])
 def test_ray_sharded_frame_and_shared_grad_allreduce(world):
     _spawn(_render_worker, world)
+
+
+def test_owned_param_groups_partition_experts_and_keep_the_shared_head():
+    """Expert parallelism: a rank optimises its own experts plus the replicated background head (world 1 = everything)."""
+    from types import SimpleNamespace
+    import torch.nn as nn
+
+    class Sub(nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.t, self.s, self.c = nn.Parameter(torch.zeros(4, 2)), nn.Parameter(torch.zeros(3)), nn.Parameter(torch.zeros(2))
+
+        def get_param_groups(self):
+            return {"encoding": {"params": [self.t]}, "sigma": {"params": [self.s]}, "color": {"params": [self.c]}}
+
+    subs = [Sub() for _ in range(8)]
+    model = SimpleNamespace(submodules=subs, use_bg_nerf=True, bg_dir_enc=nn.Identity(), bg_mlp=nn.Linear(16, 3))
+    groups, shared = PL.owned_param_groups(model)
+    assert len(groups["encoding"]["params"]) == 8 and len(shared) == 2 and groups["background"]["params"] == shared
+    import nerf_sys_b200.parallel as mod
+    real = mod._world
+    try:
+        for world in (2, 3, 8):
+            seen = []
+            for rank in range(world):
+                mod._world = lambda group, w=world, r=rank: (w, r)
+                g, sh = PL.owned_param_groups(model)
+                lo, hi = PL.shard_range(8, world, rank)
+                assert [id(p) for p in g["encoding"]["params"]] == [id(subs[e].t) for e in range(lo, hi)]
+                assert len(g["sigma"]["params"]) == hi - lo == len(g["color"]["params"]) and len(sh) == 2
+                seen += g["encoding"]["params"]
+            assert len(seen) == 8, "every expert is trained by exactly one rank"
+    finally:
+        mod._world = real
