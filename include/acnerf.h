@@ -329,6 +329,34 @@ int acn_a2a_combine(const float* y, const int32_t* point, const float* weight, i
 int acn_a2a_combine_bwd(const float* d_out, const int32_t* point, const float* weight, int64_t M, float* d_y,
                         void* stream);
 
+/* The same exchange with the rows living in the OWNER's memory, written / read by the kernels themselves over
+ * NVLink peer mappings instead of travelling through a collective.  AcnA2aRoute: base[e] = the buffer of expert e's
+ * owner as mapped into this process (a local pointer when this rank owns e), row0[e] = first row of this rank's block
+ * of expert e in it; pair j of the compact list (expert e = max{k: offs[k] <= j}) is row row0[e] + j - offs[e].
+ *   acn_a2a_count        counts (K+1,), offs (K+1,) of a routed pair list (first half of acn_a2a_pack)
+ *   acn_a2a_push_rows    writes the [xyz,dir] rows (24 B) into the owners' row buffers; out_point/out_weight as acn_a2a_pack
+ *   acn_a2a_pull_combine out[point[j]] += weight[j] * y_owner[row]   (16-byte loads from the owners' result buffers)
+ *   acn_a2a_push_grad    d_y_owner[row] = weight[j] * d_out[point[j]] (16-byte stores into the owners' gradient buffers)
+ * Ordering between ranks (rows landed before the owner evaluates, results complete before they are pulled, buffers free
+ * before they are rewritten) is the caller's: a stream-ordered barrier between the phases. */
+typedef struct AcnA2aRoute {
+  void* base[ACN_MAX_EXPERTS];
+  int64_t row0[ACN_MAX_EXPERTS];
+} AcnA2aRoute;
+int acn_a2a_count(const AcnPairs* pairs, int K, int32_t* counts, int32_t* offs, void* stream);
+int acn_a2a_push_rows(const AcnPoints* pts, const AcnPairs* pairs, int K, const int32_t* offs, const AcnA2aRoute* route,
+                      int32_t* out_point, float* out_weight, void* stream);
+int acn_a2a_pull_combine(const AcnA2aRoute* route, const int32_t* point, const float* weight, const int32_t* offs, int K,
+                         int64_t M, float* out, void* stream);
+int acn_a2a_push_grad(const float* d_out, const int32_t* point, const float* weight, const int32_t* offs, int K, int64_t M,
+                      const AcnA2aRoute* route, void* stream);
+/* Exchange slabs (one process per GPU, CUDA IPC): acn_p2p_alloc = cudaMalloc + a 64-byte handle the peers pass to
+ * acn_p2p_open (maps the slab with peer access); the host layer owns both and releases them with _close / _free. */
+int acn_p2p_alloc(int64_t bytes, void** ptr, void* handle64);
+int acn_p2p_free(void* ptr);
+int acn_p2p_open(const void* handle64, void** ptr);
+int acn_p2p_close(void* ptr);
+
 #if defined(__GNUC__)
 #pragma GCC visibility pop
 #endif

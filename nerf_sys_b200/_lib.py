@@ -47,6 +47,10 @@ class AcnAdamTensor(C.Structure):
                 ("step_index", i32), ("reserved", i32)]
 
 
+class AcnA2aRoute(C.Structure):
+    _fields_ = [("base", vp * ACN_MAX_EXPERTS), ("row0", i64 * ACN_MAX_EXPERTS)]
+
+
 ACN_ADAM_MAX_TENSORS = 64
 P = C.POINTER
 fp = P(f32)  # host float arrays
@@ -111,6 +115,14 @@ SIGNATURES = {
     "acn_a2a_pack": (C.c_int, [P(AcnPoints), P(AcnPairs), C.c_int, vp, vp, vp, vp, vp, vp]),
     "acn_a2a_combine": (C.c_int, [vp, vp, vp, i64, vp, vp]),
     "acn_a2a_combine_bwd": (C.c_int, [vp, vp, vp, i64, vp, vp]),
+    "acn_a2a_count": (C.c_int, [P(AcnPairs), C.c_int, vp, vp, vp]),
+    "acn_a2a_push_rows": (C.c_int, [P(AcnPoints), P(AcnPairs), C.c_int, vp, P(AcnA2aRoute), vp, vp, vp]),
+    "acn_a2a_pull_combine": (C.c_int, [P(AcnA2aRoute), vp, vp, vp, C.c_int, i64, vp, vp]),
+    "acn_a2a_push_grad": (C.c_int, [vp, vp, vp, vp, C.c_int, i64, P(AcnA2aRoute), vp]),
+    "acn_p2p_alloc": (C.c_int, [i64, P(C.c_void_p), vp]),
+    "acn_p2p_free": (C.c_int, [vp]),
+    "acn_p2p_open": (C.c_int, [vp, P(C.c_void_p)]),
+    "acn_p2p_close": (C.c_int, [vp]),
 }
 
 _lock = threading.Lock()

@@ -61,12 +61,14 @@ class MetaContainer(MetaModule):
         self._ep = None  # (process group or None for the default group) when the experts are sharded over ranks
 
     # ---- expert parallelism (new: the reference is single-GPU) ----------
-    def set_expert_parallel(self, enabled: bool = True, group=None) -> "MetaContainer":
+    def set_expert_parallel(self, enabled: bool = True, group=None, exchange=None) -> "MetaContainer":
         """Shard the experts over the ranks of ``group`` (block placement, parallel.expert_owner): `evaluate` /
         `forward` then route locally, ship every routed sample to its expert's owner with one all-to-all, evaluate
         there and ship [rgb, sigma] back.  Every rank keeps the full state_dict; only the owner's copy of an expert
-        is evaluated, receives gradients and needs optimiser state (parallel.owned_param_groups)."""
-        object.__setattr__(self, "_ep", (group,) if enabled else None)
+        is evaluated, receives gradients and needs optimiser state (parallel.owned_param_groups).  With
+        ``exchange`` (a parallel.PeerExchange) the samples and results move through NVLink peer memory inside the
+        pack / combine kernels instead of NCCL all-to-alls."""
+        object.__setattr__(self, "_ep", (group, exchange) if enabled else None)
         return self
 
     # ---- host copy of the centroids (they travel in the kernel-parameter block) ----
@@ -100,6 +102,8 @@ class MetaContainer(MetaModule):
             sub._require_fused()
         if self._ep is not None:
             from ... import parallel
+            if self._ep[1] is not None:
+                return parallel.container_evaluate_p2p(self, pts, self._ep[1], params=params)
             if parallel._world(self._ep[0])[0] > 1:
                 return parallel.container_evaluate_ep(self, pts, params=params, group=self._ep[0])
         if K == 1 and self.boundary_margin > 1.0:

@@ -12,7 +12,7 @@ from typing import List, Optional, Sequence, Tuple
 import torch
 
 from . import _lib
-from ._lib import (ACN_MAX_EXPERTS, ACN_NGP_LAYERS, ACN_TILE, AcnGridDesc, AcnNgpExpert, AcnNgpExpertGrads, AcnPairs,
+from ._lib import (ACN_MAX_EXPERTS, ACN_NGP_LAYERS, ACN_TILE, AcnA2aRoute, AcnGridDesc, AcnNgpExpert, AcnNgpExpertGrads, AcnPairs,
                    AcnPoints, check, host_floats, lib)
 
 Tensor = torch.Tensor
@@ -366,6 +366,57 @@ def a2a_pack(pts: PointSet, pairs: PairList, K: int):
     ch = counts.tolist()
     M = ch[K]
     return rows[:M], point[:M], weight[:M], ch[:K]
+
+
+def a2a_count(pairs: PairList, K: int) -> Tuple[Tensor, Tensor]:
+    """Device-side (counts (K+1,), offs (K+1,)) of a routed pair list; counts[K] = offs[K] = live pairs."""
+    dev = pairs.point.device
+    counts = torch.empty(K + 1, device=dev, dtype=torch.int32)
+    offs = torch.empty(K + 1, device=dev, dtype=torch.int32)
+    cq = pairs.c()
+    with torch.cuda.device(dev):
+        check(lib().acn_a2a_count(C.byref(cq), K, _ptr(counts), _ptr(offs), _stream()), "acn_a2a_count")
+    _count(1)
+    return counts, offs
+
+
+def make_route(bases: Sequence[int], row0: Sequence[int]) -> AcnA2aRoute:
+    r = AcnA2aRoute()
+    for e, (b, o) in enumerate(zip(bases, row0)):
+        r.base[e], r.row0[e] = int(b), int(o)
+    return r
+
+
+def a2a_push_rows(pts: PointSet, pairs: PairList, K: int, offs: Tensor, route: AcnA2aRoute, M: int) -> Tuple[Tensor, Tensor]:
+    """Writes the [xyz,dir] rows of the live pairs into their experts' owners (route); returns the compact
+    (point (M,) int32, weight (M,)) of the pairs for the combine."""
+    dev = pts.device
+    point = torch.empty(M, device=dev, dtype=torch.int32)
+    weight = torch.empty(M, device=dev, dtype=torch.float32)
+    cp, cq = pts.c(), pairs.c()
+    with torch.cuda.device(dev), _timed("a2a_push_rows"):
+        check(lib().acn_a2a_push_rows(C.byref(cp), C.byref(cq), K, _ptr(offs), C.byref(route), _ptr(point), _ptr(weight), _stream()),
+              "acn_a2a_push_rows")
+    _count(1)
+    return point, weight
+
+
+def a2a_pull_combine(route: AcnA2aRoute, point: Tensor, weight: Tensor, offs: Tensor, K: int, P: int) -> Tensor:
+    dev = point.device
+    out = torch.zeros(P, 4, device=dev, dtype=torch.float32)
+    with torch.cuda.device(dev), _timed("a2a_pull_combine"):
+        check(lib().acn_a2a_pull_combine(C.byref(route), _ptr(point), _ptr(weight), _ptr(offs), K, point.numel(), _ptr(out), _stream()),
+              "acn_a2a_pull_combine")
+    _count(1)
+    return out
+
+
+def a2a_push_grad(d_out: Tensor, point: Tensor, weight: Tensor, offs: Tensor, K: int, route: AcnA2aRoute) -> None:
+    g = _f32(d_out, "d_out")
+    with torch.cuda.device(g.device), _timed("a2a_push_grad"):
+        check(lib().acn_a2a_push_grad(_ptr(g), _ptr(point), _ptr(weight), _ptr(offs), K, point.numel(), C.byref(route), _stream()),
+              "acn_a2a_push_grad")
+    _count(1)
 
 
 class A2aCombineFn(torch.autograd.Function):

@@ -180,6 +180,21 @@ def expert_parallel_apply(rows: Tensor, counts: Sequence[int], expert_fn: Callab
     return combine(y)
 
 
+def _evaluate_local(model, params, rows: Tensor, local: List[int], point: Tensor, segs: List[int]) -> Tensor:
+    """This rank's experts ``local`` over received rows: ``point`` (segs[-1],) int32 lists, expert by expert (each group
+    padded to 128 slots with -1), the rows of ``rows`` (R,6) that belong to it.  One fused launch per direction."""
+    from . import ops
+    spec_all = model.expert_spec()
+    dev = rows.device
+    pl = ops.PairList(segs[-1], point, torch.ones(segs[-1], device=dev), torch.tensor(segs, dtype=torch.int32, device=dev), segs)
+    spec = ops.ExpertSpec(spec_all.grid, [spec_all.box_min[e] for e in local], [spec_all.extent[e] for e in local])
+    tables = [model.submodules[e].xyz_encoder.hash_table for e in local]
+    mlp: List[Tensor] = []
+    for e in local:
+        mlp.extend(model.submodules[e].mlp_tensors(model._sub_params(params, e)))
+    return ops.ngp_experts(ops.PointSet(x6=rows), pl, spec, tables, mlp)
+
+
 def container_evaluate_ep(model, pts, params=None, group=None) -> Tensor:
     """MetaContainer.forward over a point set with the experts sharded across ``group`` (block placement,
     `expert_owner`): route on this rank, ship every routed sample to its expert's owner, evaluate there with the
@@ -193,7 +208,6 @@ def container_evaluate_ep(model, pts, params=None, group=None) -> Tensor:
         # send rows [xyz, dir] built from (rays, t), padding dropped, grouped by expert = by destination rank;
         # counts: the one host read of the step (the reference reads K nonzero() sizes, meta_container.py:309)
         rows6, sel_point, sel_weight, counts = ops.a2a_pack(pts, pairs, K)
-    spec_all = model.expert_spec()
 
     def expert_fn(rows: Tensor, local: List[int], index: List[Tensor]) -> Tensor:
         R = rows.shape[0]
@@ -207,14 +221,7 @@ def container_evaluate_ep(model, pts, params=None, group=None) -> Tensor:
             if pad:
                 point.append(torch.full((pad,), -1, dtype=torch.int32, device=rows.device))
             segs.append(segs[-1] + n + pad)
-        point_t = torch.cat(point)
-        pl = ops.PairList(segs[-1], point_t, torch.ones(segs[-1], device=rows.device), torch.tensor(segs, dtype=torch.int32, device=rows.device), segs)
-        spec = ops.ExpertSpec(spec_all.grid, [spec_all.box_min[e] for e in local], [spec_all.extent[e] for e in local])
-        tables = [model.submodules[e].xyz_encoder.hash_table for e in local]
-        mlp: List[Tensor] = []
-        for e in local:
-            mlp.extend(model.submodules[e].mlp_tensors(model._sub_params(params, e)))
-        return ops.ngp_experts(ops.PointSet(x6=rows.contiguous()), pl, spec, tables, mlp)
+        return _evaluate_local(model, params, rows.contiguous(), local, torch.cat(point), segs)
 
     return expert_parallel_apply(rows6, counts, expert_fn, lambda y: ops.a2a_combine(y, sel_point, sel_weight, pts.P), group)
 
@@ -241,3 +248,154 @@ def owned_param_groups(model, group=None):
         if ps:
             groups[name] = {"params": ps}
     return groups, shared
+
+
+# ---------------------------------------------------------------------------------------------
+# the same exchange through NVLink peer memory: the kernels write / read the owner's buffers themselves
+# ---------------------------------------------------------------------------------------------
+class _Slab:
+    """A raw device allocation exposed through __cuda_array_interface__ so torch can view it without owning it."""
+
+    def __init__(self, ptr: int, n_floats: int):
+        self.__cuda_array_interface__ = {"shape": (n_floats,), "typestr": "<f4", "data": (ptr, False), "version": 2}
+
+
+class PeerExchange:
+    """One exchange slab per rank, mapped by every peer (CUDA IPC over NVLink / NVSwitch), holding up to ``rows_cap``
+    received rows: rows (cap,6) | y (cap,4) | g (cap,4).  Senders write sample rows and result gradients straight into
+    the owner's slab and read the owner's [rgb,sigma] rows out of it (csrc/a2a.cu); no collective carries data.
+    Ordering between the phases is a stream-ordered barrier (a one-element NCCL all-reduce)."""
+
+    ROW_FLOATS = (6, 4, 4)
+
+    def __init__(self, rows_cap: int, group=None, device=None):
+        import ctypes as C
+        from ._lib import check, lib
+        self.group = group
+        self.world, self.rank = _world(group)
+        self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        self.cap = int(rows_cap)
+        self._lib = lib()
+        n_floats = self.cap * sum(self.ROW_FLOATS)
+        ptr, handle = C.c_void_p(), C.create_string_buffer(64)
+        with torch.cuda.device(self.device):
+            check(self._lib.acn_p2p_alloc(n_floats * 4, C.byref(ptr), handle), "acn_p2p_alloc")
+        self._ptr = int(ptr.value)
+        self._opened: List[int] = []
+        handles: List[Optional[bytes]] = [None] * self.world
+        if self.world > 1:
+            dist.all_gather_object(handles, handle.raw, group=group)
+        self.peer = [0] * self.world  # slab base of every rank as mapped into this process
+        for r in range(self.world):
+            if r == self.rank:
+                self.peer[r] = self._ptr
+                continue
+            q = C.c_void_p()
+            with torch.cuda.device(self.device):
+                check(self._lib.acn_p2p_open(C.c_char_p(handles[r]), C.byref(q)), "acn_p2p_open")
+            self.peer[r] = int(q.value)
+            self._opened.append(int(q.value))
+        flat = torch.as_tensor(_Slab(self._ptr, n_floats), device=self.device)
+        o1, o2 = self.cap * 6, self.cap * 10
+        self.rows, self.y, self.g = flat[:o1].view(self.cap, 6), flat[o1:o2].view(self.cap, 4), flat[o2:].view(self.cap, 4)
+        self._byte_off = {"rows": 0, "y": o1 * 4, "g": o2 * 4}
+        self._flag = torch.zeros(1, device=self.device)
+        self.barrier()
+
+    def base(self, kind: str, r: int) -> int:
+        return self.peer[r] + self._byte_off[kind]
+
+    def barrier(self) -> None:
+        """Every rank's earlier work on its stream (including stores into peers) is complete before any rank's later work."""
+        if self.world > 1:
+            dist.all_reduce(self._flag, group=self.group)
+
+    def close(self) -> None:
+        if self._lib is None:
+            return
+        torch.cuda.synchronize(self.device)
+        self.barrier()
+        torch.cuda.synchronize(self.device)
+        self.rows = self.y = self.g = None
+        for q in self._opened:
+            self._lib.acn_p2p_close(q)
+        self._lib.acn_p2p_free(self._ptr)
+        self._lib = None
+
+
+class _PeerCombine(torch.autograd.Function):
+    """forward: publish this rank's results in its slab, barrier, pull the rows of this rank's pairs from their owners and
+    blend (out[point] += w*y).  backward: push w*d_out[point] into the owners' gradient rows, barrier, hand this rank's
+    gradient rows to the expert backward."""
+
+    @staticmethod
+    def forward(ctx, y_owner: Tensor, ex: PeerExchange, route_y, route_g, sel_point: Tensor, sel_weight: Tensor, offs: Tensor, K: int, P: int):
+        from . import ops
+        R = y_owner.shape[0]
+        if R:
+            ex.y[:R].copy_(y_owner.detach())
+            ex.g[:R].zero_()  # padding rows of the gradient block stay zero (peers only write live rows, after this barrier)
+        ex.barrier()
+        out = ops.a2a_pull_combine(route_y, sel_point, sel_weight, offs, K, P)
+        ctx.ex, ctx.route_g, ctx.K, ctx.R = ex, route_g, K, R
+        ctx.save_for_backward(sel_point, sel_weight, offs)
+        return out
+
+    @staticmethod
+    def backward(ctx, d_out):
+        from . import ops
+        sel_point, sel_weight, offs = ctx.saved_tensors
+        ops.a2a_push_grad(d_out, sel_point, sel_weight, offs, ctx.K, ctx.route_g)
+        ctx.ex.barrier()
+        return ctx.ex.g[:ctx.R], None, None, None, None, None, None, None, None
+
+
+def container_evaluate_p2p(model, pts, ex: PeerExchange, params=None) -> Tensor:
+    """`container_evaluate_ep` with the data path in our own kernels: the routed samples of expert e are written by the
+    routing rank directly into the slab of e's owner (24 B rows over NVLink), the owner evaluates its experts in place,
+    and the routing rank pulls the [rgb,sigma] rows it needs (16 B) while blending.  Layout of an owner's slab: its
+    experts in order, each expert's block = the sub-blocks of source ranks 0..world-1, blocks padded to 128 rows: an
+    expert's rows are contiguous, so the received rows need no regrouping.  Per call: one (K+1)-int all-gather (the
+    only host read) and two barriers; the backward pass adds one push and one barrier."""
+    from . import ops
+    world, rank = ex.world, ex.rank
+    K = len(model.submodules)
+    owner = expert_owner(K, world)
+    mine = [e for e in range(K) if owner[e] == rank]
+    dev = pts.device
+    with torch.no_grad():
+        pairs = ops.route_pack(pts, model.centroids_host(), K, model.boundary_margin, model.cluster_2d)
+        counts, offs = ops.a2a_count(pairs, K)
+        if world > 1:
+            table_dev = torch.empty(world, K + 1, device=dev, dtype=torch.int32)
+            # also the step's opening barrier: nobody writes into a slab before its owner is done with the previous step
+            dist.all_gather_into_tensor(table_dev, counts, group=ex.group)
+        else:
+            table_dev = counts.view(1, K + 1)
+        table = table_dev.tolist()  # the one host read of the step
+        M = table[rank][K]
+        start, tot, used = [0] * K, [0] * K, [0] * world
+        for e in range(K):
+            tot[e] = sum(table[s][e] for s in range(world))
+            start[e] = used[owner[e]]
+            used[owner[e]] += (tot[e] + ops.ACN_TILE - 1) // ops.ACN_TILE * ops.ACN_TILE
+        if max(used) > ex.cap:
+            raise RuntimeError(f"PeerExchange capacity {ex.cap} rows is too small for {max(used)} received rows")
+        row0 = [start[e] + sum(table[s][e] for s in range(rank)) for e in range(K)]
+        route = {k: ops.make_route([ex.base(k, owner[e]) for e in range(K)], row0) for k in ("rows", "y", "g")}
+        sel_point, sel_weight = ops.a2a_push_rows(pts, pairs, K, offs, route["rows"], M)
+        ex.barrier()
+        R = used[rank]
+        point = torch.arange(R, device=dev, dtype=torch.int32)
+        segs = [0]
+        for e in mine:
+            segs.append(start[e] + (tot[e] + ops.ACN_TILE - 1) // ops.ACN_TILE * ops.ACN_TILE)
+            point[start[e] + tot[e]:segs[-1]] = -1
+    if R and mine:
+        y_owner = _evaluate_local(model, params, ex.rows[:R], mine, point, segs)
+    else:
+        y_owner = torch.zeros(R, 4, device=dev)
+    if torch.is_grad_enabled() and not y_owner.requires_grad:
+        # every rank takes part in the backward exchange even if its own experts are frozen (config 4)
+        y_owner = y_owner + torch.zeros(1, device=dev, requires_grad=True)
+    return _PeerCombine.apply(y_owner, ex, route["y"], route["g"], sel_point, sel_weight, offs, K, pts.P)

@@ -474,6 +474,37 @@ def test_config3_eight_experts_soft_routing_vs_oracle():
     assert n_checked >= 8 * 15
 
 
+def test_peer_exchange_path_matches_the_fused_container_on_one_gpu():
+    """The peer-memory exchange kernels (push rows / pull-combine / push grad, csrc/a2a.cu) with every slab local
+    (world 1): same outputs and gradients as the single-launch container, fp32 mode."""
+    from nerf_sys_b200 import ops, parallel as PL
+    m, st, cfg, mins, aabb = _big_scene(8, 2, 4, 14)
+    m.train()
+    N, S = 640, 48
+    rays = O.aerial_rays(N, aabb, seed=21).to(DEV)
+    g = torch.Generator().manual_seed(8)
+    u, cot = torch.rand(N, S, generator=g).to(DEV), torch.randn(N * S, 4, generator=g).to(DEV)
+    pts = ops.PointSet(rays=rays, t=ops.stratified_t(rays, S, u))
+    y_ref = m.evaluate(pts)
+    (y_ref * cot).sum().backward()
+    g_ref = {n: p.grad.clone() for n, p in m.named_parameters() if p.grad is not None}
+    m.zero_grad(set_to_none=True)
+    ex = PL.PeerExchange(rows_cap=2 * N * S + 8 * 128)
+    try:
+        m.set_expert_parallel(True, exchange=ex)
+        for _ in range(2):  # second pass: the slab is reused
+            m.zero_grad(set_to_none=True)
+            y = m.evaluate(pts)
+            (y * cot).sum().backward()
+        close(y, y_ref, 1e-6, "peer-exchange container output")
+        for n, ref in g_ref.items():
+            got = dict(m.named_parameters())[n].grad
+            assert ((got - ref).norm() / ref.norm().clamp_min(1e-30)).item() < 1e-5, n
+    finally:
+        m.set_expert_parallel(False)
+        ex.close()
+
+
 def test_config4_untouched_experts_stay_frozen():
     """C4: a batch whose samples fall in experts {2,5} only leaves the other six without gradients."""
     from nerf_sys_b200 import ops

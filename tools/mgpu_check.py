@@ -22,7 +22,8 @@ torch.cuda.set_device(local)
 dev = torch.device("cuda", local)
 dist.init_process_group("nccl", device_id=dev)
 ok = True
-for mode in ("fp32", "f16tc"):
+ex = PL.PeerExchange(rows_cap=2 * 1024 * 32 * world + 8 * 128)
+for mode, path in (("fp32", "nccl"), ("f16tc", "nccl"), ("fp32", "p2p"), ("f16tc", "p2p")):
     ops.set_mlp_math(mode)
     m, st, cfg, mins, aabb = _big_scene(8, 2, 4, 14)
     m = m.to(dev).train()
@@ -40,7 +41,7 @@ for mode in ("fp32", "f16tc"):
     for v in g_ref.values():  # an expert's gradient is the sum of every rank's contribution
         dist.all_reduce(v)
     m.zero_grad(set_to_none=True)
-    y = PL.container_evaluate_ep(m, pts)
+    y = PL.container_evaluate_ep(m, pts) if path == "nccl" else PL.container_evaluate_p2p(m, pts, ex)
     (y * cot).sum().backward()
     tol = 1e-5 if mode == "fp32" else 2e-3
     err = (y - y_ref).abs().max().item()
@@ -62,7 +63,7 @@ for mode in ("fp32", "f16tc"):
     good = stats[0].item() <= tol and stats[1].item() <= gtol
     ok = ok and good
     if rank == 0:
-        print(f"[{mode}] expert-parallel a2a, world {world}: out max-abs err {stats[0].item():.2e} (tol {tol}), "
+        print(f"[{mode}] expert-parallel a2a ({path}), world {world}: out max-abs err {stats[0].item():.2e} (tol {tol}), "
               f"owner-gradient rel-L2 {stats[1].item():.2e} (tol {gtol}) -> {'ok' if good else 'MISMATCH'}", flush=True)
 
 # ray-sharded render
@@ -79,6 +80,7 @@ good = e <= 1e-6
 ok = ok and good
 if rank == 0:
     print(f"ray-sharded render {W}x{H}, world {world}: max-abs err vs single-GPU frame {e:.2e} -> {'ok' if good else 'MISMATCH'}", flush=True)
+ex.close()
 dist.barrier()
 dist.destroy_process_group()
 sys.exit(0 if ok else 1)
