@@ -225,49 +225,65 @@ def render_c5(device, world, barrier, max_over_ranks, frames=4):
 def train_c3(device, rank, world, barrier, max_over_ranks, steps=10, warmup=3):
     """Config 3: the 8-expert container (soft routing, margin 1.05) trained on 8192 aerial rays per GPU x 96 samples: full-container
     forward + backward + global clip + Adam (the runtime_adapt step, runtime_adapt.py:249-268).  world > 1: experts sharded in blocks
-    over the ranks, every routed sample travels to its expert's owner and back (one all-to-all each way, and again in the backward
-    pass), background-head gradients all-reduced, clip norm all-reduced."""
+    over the ranks; every routed sample travels to its expert's owner and its [rgb,sigma] back (and the gradient rows in the backward
+    pass) - measured twice: through NVLink peer memory inside the pack/combine kernels (the product path) and through NCCL
+    all-to-alls; background-head gradients and the clip norm are all-reduced."""
     from nerf_sys_b200 import parallel as PL
     from nerf_sys_b200.nerfs.losses import compute_mse_loss
     from nerf_sys_b200.optim import FusedAdam
     from oracle import acnerf_oracle as O  # scene constants / synthetic rays only
-    model, aabb = build_c5(device)
-    model.train()
-    if world > 1:
-        model.set_expert_parallel(True)
-    groups, shared = PL.owned_param_groups(model)
-    lrs = {"encoding": 1e-2, "sigma": 2e-3, "color": 2e-3, "background": 1e-3}
-    opt = FusedAdam([{"params": g["params"], "lr": lrs[n]} for n, g in groups.items()], max_grad_norm=1.0).shard_grad_norm(None, shared)
     nb = 4
-    g = torch.Generator().manual_seed(900 + rank)
-    rays = [O.aerial_rays(N_RAYS, aabb, seed=1000 + 16 * rank + b).to(device) for b in range(nb)]
-    gts = [torch.rand(N_RAYS, 3, generator=g).to(device) for _ in range(nb)]
+    lrs = {"encoding": 1e-2, "sigma": 2e-3, "color": 2e-3, "background": 1e-3}
 
-    def step(i):
-        opt.zero_grad(set_to_none=True)
-        loss = compute_mse_loss(P, model, {"rays": rays[i % nb], "rgbs": gts[i % nb]})
-        (loss / world).backward()  # the step's loss is the mean over the world x 8192 rays of all ranks
-        PL.allreduce_shared_grads(shared, average=False)
-        opt.step()
-        return loss
+    def run(path):
+        model, aabb = build_c5(device)
+        model.train()
+        ex = None
+        if world > 1:
+            if path == "p2p":
+                ex = PL.PeerExchange(rows_cap=2 * N_RAYS * S_TRAIN * world + 16 * 128)
+            model.set_expert_parallel(True, exchange=ex)
+        groups, shared = PL.owned_param_groups(model)
+        opt = FusedAdam([{"params": gr["params"], "lr": lrs[n]} for n, gr in groups.items()], max_grad_norm=1.0).shard_grad_norm(None, shared)
+        rays = [O.aerial_rays(N_RAYS, aabb, seed=1000 + 16 * rank + b).to(device) for b in range(nb)]
+        g = torch.Generator().manual_seed(900 + rank)
+        gts = [torch.rand(N_RAYS, 3, generator=g).to(device) for _ in range(nb)]
 
-    for i in range(max(warmup, 3)):
-        step(i)
-    barrier()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for i in range(steps):
-        loss = step(i)
-    e1.record()
-    barrier()
-    ms = max_over_ranks(e0.elapsed_time(e1))
-    out = {"value": world * N_RAYS * steps / (ms / 1e3), "unit": "rays/s", "ms_per_step": ms / steps, "loss": float(loss.item()),
+        def step(i):
+            opt.zero_grad(set_to_none=True)
+            loss = compute_mse_loss(P, model, {"rays": rays[i % nb], "rgbs": gts[i % nb]})
+            (loss / world).backward()  # the step's loss is the mean over the world x 8192 rays of all ranks
+            PL.allreduce_shared_grads(shared, average=False)
+            opt.step()
+            return loss
+
+        for i in range(max(warmup, 3)):
+            step(i)
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(steps):
+            loss = step(i)
+        e1.record()
+        barrier()
+        ms = max_over_ranks(e0.elapsed_time(e1))
+        lv = float(loss.item())
+        if ex is not None:
+            model.set_expert_parallel(False)
+            ex.close()
+        del model, opt
+        torch.cuda.empty_cache()
+        return ms, lv
+
+    ms, lv = run("p2p")
+    out = {"value": world * N_RAYS * steps / (ms / 1e3), "unit": "rays/s", "ms_per_step": ms / steps, "loss": lv,
            "config": f"config[2]: 8 experts (2^20-row tables), {N_RAYS} aerial rays/GPU x {S_TRAIN} samples, soft routing, fwd+bwd+clip+Adam, "
                      + ("all 8 experts on one GPU" if world == 1 else
-                        f"experts sharded {8 // world if 8 % world == 0 else '~' + str(8 / world)} per GPU over {world} GPUs, NCCL sample all-to-all "
-                        "(dispatch 24 B/row, combine 16 B/row, reversed in backward), eager launches")}
-    del model, opt
-    torch.cuda.empty_cache()
+                        f"experts sharded {8 / world:g} per GPU over {world} GPUs; sample rows (24 B), results (16 B) and gradient rows (16 B) "
+                        "written / read in the owner's memory over NVLink by the pack and combine kernels, eager launches")}
+    if world > 1:
+        ms2, lv2 = run("nccl")
+        out["nccl_all_to_all"] = {"value": world * N_RAYS * steps / (ms2 / 1e3), "unit": "rays/s", "ms_per_step": ms2 / steps, "loss": lv2}
     return out
 
 
