@@ -23,75 +23,100 @@ struct RouteCfg {
 
 // Returns the membership mask; w[k] = routing weight (0 when not a member).
 // Hard routing (margin <= 1): mask has the single argmin bit, w = 1.
+// KT = experts rounded up to a power of two (loops are unrolled to KT with no per-k "k < K" test: the centroids of the
+// padding experts sit at +inf, so their distance is +inf and they are never the nearest, never members and add an exact 0
+// to the weight sum); D3 = distances over (x,y,z) instead of (y,z).
+template <int KT, bool D3>
 __device__ __forceinline__ uint32_t route_point(const RouteCfg& cfg, float x, float y, float z, float* w, int* hard) {
-  float dist[ACN_MAX_EXPERTS];
+  // squared distances, in the operation order the distance itself uses
+  float sq[KT];
+  float smin = INFINITY;
+#pragma unroll
+  for (int k = 0; k < KT; ++k) {
+    float dy = y - cfg.c[k][1], dz = z - cfg.c[k][2];
+    float s;
+    if (D3) {
+      float dx = x - cfg.c[k][0];
+      s = dx * dx + dy * dy;
+      s = s + dz * dz;
+    } else {
+      s = dy * dy + dz * dz;
+    }
+    sq[k] = s;
+    smin = fminf(smin, s);
+  }
+  // Fast path (19 of 20 samples): exactly one centroid inside the membership band.  The band is the membership test in the
+  // squared domain widened by 2e-5 (1e-5 in distance), two orders of magnitude above the rounding of sqrt and of
+  // margin*min, so a centroid outside it fails the exact test d_k <= margin*d_min too; the lone member's exact weight is
+  // (1/d)/max(1/d, 1e-6) = 1 for 1e-6 < d < 1e6.  Everything else (two candidates, a tie, a sample on a centroid,
+  // non-finite positions of invalid rays) takes the exact arithmetic below, so the integer decisions stay bit-exact
+  // (tests/test_gpu_parity.py).
+  {
+    const float m2 = cfg.margin > 1.0f ? cfg.margin * cfg.margin : 1.0f;
+    const float band = m2 * smin * 1.00002f;
+    int ncand = 0, c = 0;
+#pragma unroll
+    for (int k = 0; k < KT; ++k) {
+      const bool in = sq[k] <= band;
+      ncand += in ? 1 : 0;
+      c = in ? k : c;
+    }
+    if (ncand == 1 && smin > 1e-11f && smin < 1e11f) {
+#pragma unroll
+      for (int k = 0; k < KT; ++k) w[k] = (k == c) ? 1.0f : 0.0f;
+      if (hard) *hard = c;
+      return 1u << c;
+    }
+  }
+  // exact path, branch-free over the KT centroids
+  float dist[KT];
   float mind = INFINITY;
   int amin = 0;
 #pragma unroll
-  for (int k = 0; k < ACN_MAX_EXPERTS; ++k) {
-    if (k < cfg.K) {
-      float dy = y - cfg.c[k][1], dz = z - cfg.c[k][2];
-      float s;
-      if (cfg.dims == 3) {
-        float dx = x - cfg.c[k][0];
-        s = dx * dx + dy * dy;
-        s = s + dz * dz;
-      } else {
-        s = dy * dy + dz * dz;
-      }
-      float d = sqrtf(s);
-      if (cfg.margin > 1.0f) d = fmaxf(d, 1e-6f);
-      dist[k] = d;
-      if (d < mind) {  // strict: first index wins ties, as torch.argmin / min
-        mind = d;
-        amin = k;
-      }
-    } else {
-      dist[k] = INFINITY;
-    }
+  for (int k = 0; k < KT; ++k) {
+    float d = sqrtf(sq[k]);
+    if (cfg.margin > 1.0f) d = fmaxf(d, 1e-6f);
+    dist[k] = d;
+    const bool lt = d < mind;  // strict: first index wins ties, as torch.argmin / min
+    mind = lt ? d : mind;
+    amin = lt ? k : amin;
   }
   if (hard) *hard = amin;
-  uint32_t mask = 0;
   if (!(cfg.margin > 1.0f)) {
 #pragma unroll
-    for (int k = 0; k < ACN_MAX_EXPERTS; ++k) w[k] = (k == amin) ? 1.0f : 0.0f;
+    for (int k = 0; k < KT; ++k) w[k] = (k == amin) ? 1.0f : 0.0f;
     return 1u << amin;
   }
-  float thr = cfg.margin * mind;
+  const float thr = cfg.margin * mind;
   float sum = 0.f;
 #pragma unroll
-  for (int k = 0; k < ACN_MAX_EXPERTS; ++k) {
-    float inv = 0.f;
-    if (k < cfg.K) {
-      inv = 1.0f / dist[k];
-      bool in = dist[k] <= thr;
-      inv = in ? inv : 0.f;
-      sum = sum + inv;
-      // membership is "weight > 0" (meta_container.py:308)
-    }
-    w[k] = inv;
+  for (int k = 0; k < KT; ++k) {
+    float inv = 1.0f / dist[k];
+    inv = (dist[k] <= thr) ? inv : 0.f;
+    sum = sum + inv;
+    w[k] = inv;  // membership is "weight > 0" (meta_container.py:308)
   }
-  float den = fmaxf(sum, 1e-6f);
+  const float den = fmaxf(sum, 1e-6f);
+  uint32_t mask = 0;
 #pragma unroll
-  for (int k = 0; k < ACN_MAX_EXPERTS; ++k) {
-    if (k < cfg.K) {
-      w[k] = w[k] / den;
-      if (w[k] > 0.f) mask |= 1u << k;
-    }
+  for (int k = 0; k < KT; ++k) {
+    w[k] = w[k] / den;
+    mask |= (w[k] > 0.f) ? (1u << k) : 0u;
   }
   return mask;
 }
 
+template <int KT, bool D3>
 __global__ void __launch_bounds__(RT) k_routing(PointSrc src, int64_t P, RouteCfg cfg, float* __restrict__ weights,
                                                 int64_t* __restrict__ hard) {
   for (int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; p < P; p += (int64_t)gridDim.x * blockDim.x) {
-    float x, y, z, w[ACN_MAX_EXPERTS];
+    float x, y, z, w[KT];
     int h;
     load_xyz(src, p, x, y, z);
-    route_point(cfg, x, y, z, w, &h);
+    route_point<KT, D3>(cfg, x, y, z, w, &h);
     if (cfg.margin > 1.0f) {
 #pragma unroll
-      for (int k = 0; k < ACN_MAX_EXPERTS; ++k)
+      for (int k = 0; k < KT; ++k)
         if (k < cfg.K) weights[p * cfg.K + k] = w[k];
     } else {
       hard[p] = h;
@@ -99,7 +124,111 @@ __global__ void __launch_bounds__(RT) k_routing(PointSrc src, int64_t P, RouteCf
   }
 }
 
+// ---- the same decisions for a whole warp (the pack kernels) -----------------------------------------------------
+// Lanes are consecutive samples of a ray, so 4 of 5 warps hold a sample or two inside a membership band while the other
+// lanes take the fast path; run per thread, the exact arithmetic then executes with ~2 of 32 lanes active (measured:
+// 81 % of the warps, 2.3 active lanes, two thirds of the kernel's instructions).  Here every lane first classifies its own
+// sample (squared distances, candidate count), then the warp works through its "exact" samples together: 32/KT samples per
+// pass, ONE (sample, centroid) pair per lane - one sqrt, one reciprocal, one division per lane - with the weight sum
+// accumulated in ascending centroid order by a shuffle chain, i.e. the same operations in the same order as route_point().
+template <int KT, bool D3>
+__device__ __forceinline__ uint32_t route_warp(const RouteCfg& cfg, bool valid, float x, float y, float z, float* w) {
+  constexpr uint32_t FULL = 0xffffffffu;
+  constexpr int PPP = 32 / KT;  // samples per pass
+  const int lane = threadIdx.x & 31, g = lane / KT, k = lane % KT;
+  const bool soft = cfg.margin > 1.0f;
+  float sq[KT];
+  float smin = INFINITY;
+#pragma unroll
+  for (int kk = 0; kk < KT; ++kk) {
+    float dy = y - cfg.c[kk][1], dz = z - cfg.c[kk][2];
+    float s;
+    if (D3) {
+      float dx = x - cfg.c[kk][0];
+      s = dx * dx + dy * dy;
+      s = s + dz * dz;
+    } else {
+      s = dy * dy + dz * dz;
+    }
+    sq[kk] = s;
+    smin = fminf(smin, s);
+  }
+  const float band = (soft ? cfg.margin * cfg.margin : 1.0f) * smin * 1.00002f;
+  int ncand = 0, c = 0;
+#pragma unroll
+  for (int kk = 0; kk < KT; ++kk) {
+    const bool in = sq[kk] <= band;
+    ncand += in ? 1 : 0;
+    c = in ? kk : c;
+  }
+  const bool fast = ncand == 1 && smin > 1e-11f && smin < 1e11f;  // see route_point()
+  uint32_t mask = (valid && fast) ? (1u << c) : 0u;
+#pragma unroll
+  for (int kk = 0; kk < KT; ++kk) w[kk] = (fast && kk == c) ? 1.0f : 0.0f;
+  uint32_t slow = __ballot_sync(FULL, valid && !fast);
+  while (slow) {  // warp-uniform
+    // this pass takes the first PPP exact samples; group g of KT lanes works for the g-th of them
+    uint32_t rem = slow;
+    int src = -1;
+#pragma unroll
+    for (int i = 0; i < PPP; ++i) {
+      const int l = rem ? (__ffs(rem) - 1) : -1;
+      src = (i == g) ? l : src;
+      rem = rem ? (rem & (rem - 1)) : 0u;
+    }
+    const uint32_t taken = slow & ~rem;
+    slow = rem;
+    const bool active = src >= 0;
+    const int from = active ? src : 0;
+    float v = INFINITY;
+#pragma unroll
+    for (int kk = 0; kk < KT; ++kk) {
+      const float t = __shfl_sync(FULL, sq[kk], from);
+      v = (kk == k) ? t : v;
+    }
+    float d = sqrtf(v);
+    if (soft) d = fmaxf(d, 1e-6f);
+    if (!active) d = INFINITY;
+    float mind = d;  // min over the group; NaN never wins, as with the strict "d < min" chain
+#pragma unroll
+    for (int o = KT / 2; o > 0; o >>= 1) mind = fminf(mind, __shfl_xor_sync(FULL, mind, o));
+    const uint32_t gmask = (KT == 32) ? FULL : ((1u << KT) - 1u);
+    const int gshift = g * KT;
+    float wv;
+    bool member;
+    if (!soft) {
+      // first index that reaches the minimum (torch.argmin); index 0 when no distance is below +inf
+      const uint32_t hit = (__ballot_sync(FULL, active && d == mind && mind < INFINITY) >> gshift) & gmask;
+      const int amin = hit ? (__ffs(hit) - 1) : 0;
+      member = active && k == amin;
+      wv = member ? 1.0f : 0.0f;
+    } else {
+      const float thr = cfg.margin * mind;
+      float inv = 1.0f / d;
+      inv = (d <= thr) ? inv : 0.f;
+      float sum = 0.f;
+#pragma unroll
+      for (int kk = 0; kk < KT; ++kk) sum = sum + __shfl_sync(FULL, inv, gshift + kk);  // ascending centroid order
+      const float den = fmaxf(sum, 1e-6f);
+      wv = inv / den;
+      member = active && wv > 0.f;  // membership is "weight > 0" (meta_container.py:308)
+    }
+    const uint32_t bal = __ballot_sync(FULL, member);
+    // hand the results to the lanes that own the samples of this pass
+    const bool mine = (taken >> lane) & 1u;
+    const int my_g = __popc(taken & ((1u << lane) - 1u));
+    if (mine) mask = (bal >> (my_g * KT)) & gmask;
+#pragma unroll
+    for (int kk = 0; kk < KT; ++kk) {
+      const float t = __shfl_sync(FULL, wv, (mine ? my_g * KT : 0) + kk);
+      if (mine) w[kk] = t;
+    }
+  }
+  return mask;
+}
+
 // ---- pass 1: per-block, per-expert member counts: counts[k*nb + b] ------------
+template <int KT, bool D3>
 __global__ void __launch_bounds__(RT) k_route_count(PointSrc src, int64_t P, RouteCfg cfg, int nb, int32_t* __restrict__ counts) {
   __shared__ int cnt[ACN_MAX_EXPERTS];
   for (int b = blockIdx.x; b < nb; b += gridDim.x) {
@@ -108,13 +237,11 @@ __global__ void __launch_bounds__(RT) k_route_count(PointSrc src, int64_t P, Rou
 #pragma unroll
     for (int j = 0; j < RPT; ++j) {
       int64_t p = (int64_t)b * RB + j * RT + threadIdx.x;
-      uint32_t mask = 0;
-      if (p < P) {
-        float x, y, z, w[ACN_MAX_EXPERTS];
-        load_xyz(src, p, x, y, z);
-        mask = route_point(cfg, x, y, z, w, nullptr);
-      }
-      for (int k = 0; k < cfg.K; ++k) {
+      float x = 0.f, y = 0.f, z = 0.f, w[KT];
+      if (p < P) load_xyz(src, p, x, y, z);
+      const uint32_t mask = route_warp<KT, D3>(cfg, p < P, x, y, z, w);
+#pragma unroll
+      for (int k = 0; k < KT; ++k) {
         unsigned bal = __ballot_sync(0xffffffffu, (mask >> k) & 1u);
         if ((threadIdx.x & 31) == 0 && bal) atomicAdd(&cnt[k], __popc(bal));
       }
@@ -125,46 +252,45 @@ __global__ void __launch_bounds__(RT) k_route_count(PointSrc src, int64_t P, Rou
   }
 }
 
-// ---- pass 2: exclusive scan over blocks per expert (in place) + tile-aligned segments
-__global__ void __launch_bounds__(1024) k_route_scan(int32_t* __restrict__ counts, int nb, int K, int32_t* __restrict__ seg) {
+// ---- pass 2: exclusive scan over blocks, one CTA per expert (in place); totals[k] -> tile-aligned segments
+__global__ void __launch_bounds__(1024) k_route_scan(int32_t* __restrict__ counts, int nb, int32_t* __restrict__ totals) {
   __shared__ int warp_sum[32];
   __shared__ int carry;
-  __shared__ int totals[ACN_MAX_EXPERTS];
-  int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  for (int k = 0; k < K; ++k) {
-    if (threadIdx.x == 0) carry = 0;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, k = blockIdx.x;
+  if (threadIdx.x == 0) carry = 0;
+  __syncthreads();
+  for (int base = 0; base < nb; base += 1024) {
+    int i = base + threadIdx.x;
+    int v = (i < nb) ? counts[(int64_t)k * nb + i] : 0;
+    int inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      int n = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += n;
+    }
+    if (lane == 31) warp_sum[warp] = inc;
     __syncthreads();
-    for (int base = 0; base < nb; base += 1024) {
-      int i = base + threadIdx.x;
-      int v = (i < nb) ? counts[(int64_t)k * nb + i] : 0;
-      int inc = v;
+    if (warp == 0) {
+      int ws = warp_sum[lane];
+      int winc = ws;
 #pragma unroll
       for (int o = 1; o < 32; o <<= 1) {
-        int n = __shfl_up_sync(0xffffffffu, inc, o);
-        if (lane >= o) inc += n;
+        int n = __shfl_up_sync(0xffffffffu, winc, o);
+        if (lane >= o) winc += n;
       }
-      if (lane == 31) warp_sum[warp] = inc;
-      __syncthreads();
-      if (warp == 0) {
-        int ws = warp_sum[lane];
-        int winc = ws;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-          int n = __shfl_up_sync(0xffffffffu, winc, o);
-          if (lane >= o) winc += n;
-        }
-        warp_sum[lane] = winc - ws;  // exclusive
-      }
-      __syncthreads();
-      int excl = carry + warp_sum[warp] + inc - v;
-      if (i < nb) counts[(int64_t)k * nb + i] = excl;
-      __syncthreads();
-      if (threadIdx.x == 1023) carry = excl + v;
-      __syncthreads();
+      warp_sum[lane] = winc - ws;  // exclusive
     }
-    if (threadIdx.x == 0) totals[k] = carry;
+    __syncthreads();
+    int excl = carry + warp_sum[warp] + inc - v;
+    if (i < nb) counts[(int64_t)k * nb + i] = excl;
+    __syncthreads();
+    if (threadIdx.x == 1023) carry = excl + v;
     __syncthreads();
   }
+  if (threadIdx.x == 0) totals[k] = carry;
+}
+
+__global__ void k_route_seg(const int32_t* __restrict__ totals, int K, int32_t* __restrict__ seg) {
   if (threadIdx.x == 0) {
     int s = 0;
     seg[0] = 0;
@@ -176,6 +302,7 @@ __global__ void __launch_bounds__(1024) k_route_scan(int32_t* __restrict__ count
 }
 
 // ---- pass 3: stable write of (point, weight) pairs into each expert's segment ----
+template <int KT, bool D3>
 __global__ void __launch_bounds__(RT) k_route_write(PointSrc src, int64_t P, RouteCfg cfg, int nb, const int32_t* __restrict__ base,
                                                     const int32_t* __restrict__ seg, int32_t* __restrict__ pair_point,
                                                     float* __restrict__ pair_w, int64_t Mcap) {
@@ -188,26 +315,19 @@ __global__ void __launch_bounds__(RT) k_route_write(PointSrc src, int64_t P, Rou
 #pragma unroll 1
     for (int j = 0; j < RPT; ++j) {
       int64_t p = (int64_t)b * RB + j * RT + threadIdx.x;
-      uint32_t mask = 0;
-      float w[ACN_MAX_EXPERTS];
-      if (p < P) {
-        float x, y, z;
-        load_xyz(src, p, x, y, z);
-        mask = route_point(cfg, x, y, z, w, nullptr);
-      }
-      unsigned bals[ACN_MAX_EXPERTS];
+      float x = 0.f, y = 0.f, z = 0.f, w[KT];
+      if (p < P) load_xyz(src, p, x, y, z);
+      const uint32_t mask = route_warp<KT, D3>(cfg, p < P, x, y, z, w);
+      unsigned bals[KT];
 #pragma unroll
-      for (int k = 0; k < ACN_MAX_EXPERTS; ++k) {
-        bals[k] = 0;
-        if (k < cfg.K) {
-          bals[k] = __ballot_sync(0xffffffffu, (mask >> k) & 1u);
-          if (lane == 0) wcnt[k][warp] = __popc(bals[k]);
-        }
+      for (int k = 0; k < KT; ++k) {
+        bals[k] = __ballot_sync(0xffffffffu, (mask >> k) & 1u);
+        if (lane == 0) wcnt[k][warp] = __popc(bals[k]);
       }
       __syncthreads();
 #pragma unroll
-      for (int k = 0; k < ACN_MAX_EXPERTS; ++k) {
-        if (k < cfg.K && ((mask >> k) & 1u)) {
+      for (int k = 0; k < KT; ++k) {
+        if ((mask >> k) & 1u) {
           int off = run[k];
           for (int ww = 0; ww < warp; ++ww) off += wcnt[k][ww];
           off += __popc(bals[k] & ((1u << lane) - 1u));
@@ -228,12 +348,32 @@ __global__ void __launch_bounds__(RT) k_route_write(PointSrc src, int64_t P, Rou
   }
 }
 
+// kernel<KT, D3> with KT = K rounded up to 2, 4, 8 or 16
+#define ROUTE_LAUNCH_D(KT, c2d, kernel, grid, st, ...)                   \
+  do {                                                                   \
+    if (c2d)                                                             \
+      kernel<KT, false><<<grid, RT, 0, st>>>(__VA_ARGS__);               \
+    else                                                                 \
+      kernel<KT, true><<<grid, RT, 0, st>>>(__VA_ARGS__);                \
+  } while (0)
+#define ROUTE_DISPATCH(K, c2d, kernel, grid, st, ...)                    \
+  do {                                                                   \
+    if ((K) <= 2)                                                        \
+      ROUTE_LAUNCH_D(2, c2d, kernel, grid, st, __VA_ARGS__);             \
+    else if ((K) <= 4)                                                   \
+      ROUTE_LAUNCH_D(4, c2d, kernel, grid, st, __VA_ARGS__);             \
+    else if ((K) <= 8)                                                   \
+      ROUTE_LAUNCH_D(8, c2d, kernel, grid, st, __VA_ARGS__);             \
+    else                                                                 \
+      ROUTE_LAUNCH_D(16, c2d, kernel, grid, st, __VA_ARGS__);            \
+  } while (0)
+
 static int fill_cfg(RouteCfg& cfg, const float* centroids_host, int K, float margin, int cluster_2d) {
   cfg.K = K;
   cfg.margin = margin;
   cfg.dims = cluster_2d ? 2 : 3;
   for (int k = 0; k < ACN_MAX_EXPERTS; ++k)
-    for (int a = 0; a < 3; ++a) cfg.c[k][a] = (k < K) ? centroids_host[k * 3 + a] : 0.f;
+    for (int a = 0; a < 3; ++a) cfg.c[k][a] = (k < K) ? centroids_host[k * 3 + a] : INFINITY;  // padding experts: distance +inf
   return 0;
 }
 
@@ -250,7 +390,7 @@ int acn_routing(const AcnPoints* pts, const float* centroids_host, int K, float 
   if (pts->P == 0) return ACN_OK;
   RouteCfg cfg;
   fill_cfg(cfg, centroids_host, K, margin, cluster_2d);
-  k_routing<<<persistent_grid((pts->P + RT - 1) / RT, 8), RT, 0, as_stream(stream)>>>(make_src(pts), pts->P, cfg, weights, hard);
+  ROUTE_DISPATCH(K, cluster_2d, k_routing, persistent_grid((pts->P + RT - 1) / RT, 8), as_stream(stream), make_src(pts), pts->P, cfg, weights, hard);
   ACN_LAUNCH_CHECK();
   return ACN_OK;
 }
@@ -279,13 +419,16 @@ int acn_route_pack(const AcnPoints* pts, const float* centroids_host, int K, flo
   ACN_CUDA(cudaMemsetAsync(pair_point, 0xFF, sizeof(int32_t) * Mcap, st));
   ACN_CUDA(cudaMemsetAsync(pair_weight, 0, sizeof(float) * Mcap, st));
   if (nb > 0) {
-    k_route_count<<<persistent_grid(nb, 8), RT, 0, st>>>(make_src(pts), P, cfg, nb, counts);
+    ROUTE_DISPATCH(K, cluster_2d, k_route_count, persistent_grid(nb, 8), st, make_src(pts), P, cfg, nb, counts);
     ACN_LAUNCH_CHECK();
   }
-  k_route_scan<<<1, 1024, 0, st>>>(counts, nb, K, seg);
+  int32_t* totals = counts + (int64_t)nb * K;  // the 64 spare ints of the workspace
+  k_route_scan<<<K, 1024, 0, st>>>(counts, nb, totals);
+  ACN_LAUNCH_CHECK();
+  k_route_seg<<<1, 32, 0, st>>>(totals, K, seg);
   ACN_LAUNCH_CHECK();
   if (nb > 0) {
-    k_route_write<<<persistent_grid(nb, 8), RT, 0, st>>>(make_src(pts), P, cfg, nb, counts, seg, pair_point, pair_weight, Mcap);
+    ROUTE_DISPATCH(K, cluster_2d, k_route_write, persistent_grid(nb, 8), st, make_src(pts), P, cfg, nb, counts, seg, pair_point, pair_weight, Mcap);
     ACN_LAUNCH_CHECK();
   }
   return ACN_OK;

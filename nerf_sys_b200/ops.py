@@ -223,7 +223,7 @@ def raygen(H: int, W: int, fx, fy, cx, cy, center_pixels: bool, c2w: Tensor, aab
            row0: int = 0, rows: Optional[int] = None) -> Tensor:
     rows = H - row0 if rows is None else rows
     out = torch.empty(rows * W, 8, device=device, dtype=torch.float32)
-    with torch.cuda.device(out.device):
+    with torch.cuda.device(out.device), _timed("raygen"):
         check(lib().acn_raygen(H, W, row0, rows, fx, fy, cx, cy, int(bool(center_pixels)), _c2w_host(c2w), _aabb_host(aabb),
                                float(near), float(far), _ptr(out), _stream()), "acn_raygen")
     _count(1)
@@ -331,8 +331,9 @@ def route_pack(pts: PointSet, centroids_host: Sequence[float], K: int, margin: f
         while True:
             point = torch.empty(cap, device=dev, dtype=torch.int32)
             weight = torch.empty(cap, device=dev, dtype=torch.float32)
-            check(L.acn_route_pack(C.byref(cp), ch, K, float(margin), int(cluster_2d), _ptr(point), _ptr(weight), _ptr(seg), cap,
-                                   _ptr(ws), _stream()), "acn_route_pack")
+            with _timed("route_pack"):
+                check(L.acn_route_pack(C.byref(cp), ch, K, float(margin), int(cluster_2d), _ptr(point), _ptr(weight), _ptr(seg), cap,
+                                       _ptr(ws), _stream()), "acn_route_pack")
             _count(3)
             seg_host = seg.tolist()
             if seg_host[K] <= cap:
