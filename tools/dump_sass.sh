@@ -26,6 +26,10 @@ dump ngp.o 14k_ngp_hash_fwd k_ngp_hash_fwd
 dump ngp.o 14k_ngp_hash_bwd k_ngp_hash_bwd
 dump render.o 15k_composite_fwd k_composite_fwd
 dump render.o 15k_composite_bwd k_composite_bwd
-dump routing.o 13k_route_write k_route_write
+dump routing.o "13k_route_writeILi8ELb0" k_route_write
+dump routing.o "13k_route_countILi8ELb0" k_route_count
+dump a2a.o 15k_a2a_push_rows k_a2a_push_rows
+dump a2a.o 18k_a2a_pull_combine k_a2a_pull_combine
+dump a2a.o 15k_a2a_push_grad k_a2a_push_grad
 dump optim.o 12k_adam_multi k_adam_multi
 } | tee $out/CENSUS.txt
