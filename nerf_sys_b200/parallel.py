@@ -350,6 +350,21 @@ class _PeerCombine(torch.autograd.Function):
         return ctx.ex.g[:ctx.R], None, None, None, None, None, None, None, None
 
 
+def peer_layout(table: Sequence[Sequence[int]], owner: Sequence[int], rank: int, tile: int = 128):
+    """Row layout of the owners' slabs for one exchange.  table[s][e] = routed samples rank s holds for expert e.
+    An owner's slab holds its experts in order, each expert's block = the sub-blocks of source ranks 0..world-1 back to
+    back, blocks padded to ``tile`` rows.  Returns (start[e] first row of e's block in its owner's slab, tot[e] rows of e
+    over all sources, used[r] rows of rank r's slab, row0[e] first row of THIS rank's sub-block of e)."""
+    world, K = len(table), len(owner)
+    start, tot, used = [0] * K, [0] * K, [0] * world
+    for e in range(K):
+        tot[e] = sum(int(table[s][e]) for s in range(world))
+        start[e] = used[owner[e]]
+        used[owner[e]] += (tot[e] + tile - 1) // tile * tile
+    row0 = [start[e] + sum(int(table[s][e]) for s in range(rank)) for e in range(K)]
+    return start, tot, used, row0
+
+
 def container_evaluate_p2p(model, pts, ex: PeerExchange, params=None) -> Tensor:
     """`container_evaluate_ep` with the data path in our own kernels: the routed samples of expert e are written by the
     routing rank directly into the slab of e's owner (24 B rows over NVLink), the owner evaluates its experts in place,
@@ -374,14 +389,9 @@ def container_evaluate_p2p(model, pts, ex: PeerExchange, params=None) -> Tensor:
             table_dev = counts.view(1, K + 1)
         table = table_dev.tolist()  # the one host read of the step
         M = table[rank][K]
-        start, tot, used = [0] * K, [0] * K, [0] * world
-        for e in range(K):
-            tot[e] = sum(table[s][e] for s in range(world))
-            start[e] = used[owner[e]]
-            used[owner[e]] += (tot[e] + ops.ACN_TILE - 1) // ops.ACN_TILE * ops.ACN_TILE
+        start, tot, used, row0 = peer_layout(table, owner, rank, ops.ACN_TILE)
         if max(used) > ex.cap:
             raise RuntimeError(f"PeerExchange capacity {ex.cap} rows is too small for {max(used)} received rows")
-        row0 = [start[e] + sum(table[s][e] for s in range(rank)) for e in range(K)]
         route = {k: ops.make_route([ex.base(k, owner[e]) for e in range(K)], row0) for k in ("rows", "y", "g")}
         sel_point, sel_weight = ops.a2a_push_rows(pts, pairs, K, offs, route["rows"], M)
         ex.barrier()

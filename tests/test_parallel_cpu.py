@@ -211,3 +211,33 @@ def test_owned_param_groups_partition_experts_and_keep_the_shared_head():
             assert len(seen) == 8, "every expert is trained by exactly one rank"
     finally:
         mod._world = real
+
+
+def test_peer_layout_tiles_every_slab_without_overlap():
+    """Peer-memory exchange: every (source, expert) sub-block lands in its owner's slab exactly once, expert blocks are
+    contiguous, start on tile boundaries and appear in expert order; empty experts and ragged counts included."""
+    g = torch.Generator().manual_seed(5)
+    for world in (1, 2, 3, 8):
+        K = 8
+        owner = PL.expert_owner(K, world)
+        table = torch.randint(0, 700, (world, K), generator=g)
+        table[:, 3] = 0          # an expert nobody routes to
+        table[0, 5] = 0          # a source with nothing for expert 5
+        table = table.tolist()
+        cover = {r: [] for r in range(world)}
+        for rank in range(world):
+            start, tot, used, row0 = PL.peer_layout(table, owner, rank, 128)
+            for e in range(K):
+                assert tot[e] == sum(table[s][e] for s in range(world)) and start[e] % 128 == 0
+                assert start[e] <= row0[e] and row0[e] + table[rank][e] <= start[e] + tot[e]
+                cover[owner[e]].append((row0[e], row0[e] + table[rank][e], e))
+        for r in range(world):
+            spans = sorted(x for x in cover[r] if x[1] > x[0])
+            for a, b in zip(spans, spans[1:]):
+                assert a[1] <= b[0], "sub-blocks must not overlap"
+                assert a[2] <= b[2], "experts appear in order"
+            mine = [e for e in range(K) if owner[e] == r]
+            assert used[r] == sum((tot[e] + 127) // 128 * 128 for e in mine)
+            for e in mine:  # the sources tile the expert's block exactly
+                rows = sum(b - a for a, b, ee in spans if ee == e)
+                assert rows == tot[e]
