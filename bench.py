@@ -245,6 +245,7 @@ def train_c3(device, rank, world, barrier, max_over_ranks, steps=10, warmup=3):
             model.set_expert_parallel(True, exchange=ex)
         groups, shared = PL.owned_param_groups(model)
         opt = FusedAdam([{"params": gr["params"], "lr": lrs[n]} for n, gr in groups.items()], max_grad_norm=1.0).shard_grad_norm(None, shared)
+        reducer = PL.SharedGradReducer(shared, average=False)
         rays = [O.aerial_rays(N_RAYS, aabb, seed=1000 + 16 * rank + b).to(device) for b in range(nb)]
         g = torch.Generator().manual_seed(900 + rank)
         gts = [torch.rand(N_RAYS, 3, generator=g).to(device) for _ in range(nb)]
@@ -253,7 +254,7 @@ def train_c3(device, rank, world, barrier, max_over_ranks, steps=10, warmup=3):
             opt.zero_grad(set_to_none=True)
             loss = compute_mse_loss(P, model, {"rays": rays[i % nb], "rgbs": gts[i % nb]})
             (loss / world).backward()  # the step's loss is the mean over the world x 8192 rays of all ranks
-            PL.allreduce_shared_grads(shared, average=False)
+            reducer.wait()
             opt.step()
             return loss
 
@@ -268,6 +269,7 @@ def train_c3(device, rank, world, barrier, max_over_ranks, steps=10, warmup=3):
         barrier()
         ms = max_over_ranks(e0.elapsed_time(e1))
         lv = float(loss.item())
+        reducer.remove()
         if ex is not None:
             model.set_expert_parallel(False)
             ex.close()
@@ -306,12 +308,15 @@ def allreduce_bg(model, world):
         o += g.numel()
 
 
-def train_step(model, opt, rays, rgbs, world):
+def train_step(model, opt, rays, rgbs, world, reducer=None):
     from nerf_sys_b200.nerfs.losses import compute_mse_loss
     opt.zero_grad(set_to_none=True)
     loss = compute_mse_loss(P, model, {"rays": rays, "rgbs": rgbs})
     loss.backward()
-    allreduce_bg(model, world)
+    if reducer is not None:
+        reducer.wait()
+    else:
+        allreduce_bg(model, world)
     opt.step()
     return loss
 
@@ -418,17 +423,20 @@ def main():
         return t.item()
 
     from nerf_sys_b200.nerfs.losses import compute_mse_loss
+    from nerf_sys_b200 import parallel as PL
+    # shared background head: its gradients are all-reduced (mean) on a side stream underneath the expert backward
+    reducer = PL.SharedGradReducer(list(model.bg_mlp.parameters())) if world > 1 else None
     use_graph = not args.no_graph
     if use_graph:
         from nerf_sys_b200.engine import GraphedTrainStep
         gstep = GraphedTrainStep(opt, lambda r, c: compute_mse_loss(P, model, {"rays": r, "rgbs": c}), (pool[0], rgbs[0]), warmup=W,
-                                 post_backward=lambda: allreduce_bg(model, world))
+                                 post_backward=(reducer.wait if reducer is not None else None))
 
         def step(r, c):
             return gstep(r, c)
     else:
         def step(r, c):
-            return train_step(model, opt, r, c, world)
+            return train_step(model, opt, r, c, world, reducer)
 
     # ---- resident-input arm ------------------------------------------------------------
     for i in range(W):
@@ -464,7 +472,7 @@ def main():
     ops.set_bwd_chunks(1)  # unpipelined, so that the MLP backward and the table scatter are timed one at a time
     timing = ops.kernel_timing(True)
     for i in range(K):
-        train_step(model, opt, pool[(W + i) % nb], rgbs[(W + i) % nb], world)
+        train_step(model, opt, pool[(W + i) % nb], rgbs[(W + i) % nb], world, reducer)
     barrier()
     ops.kernel_timing(False)
     ops.set_bwd_chunks(args.bwd_chunks)
@@ -541,7 +549,7 @@ def main():
                                             "kernel_timing": "separate eager pass of the same K steps, CUDA-event pair per C-ABI call, backward unpipelined",
                                             "backward": (f"{args.bwd_chunks}-chunk software pipeline: table scatter of chunk c on a side stream beside the "
                                                          "MLP backward of chunk c+1") if args.bwd_chunks > 1 else "MLP backward, then table scatter",
-                                            "collective": "none" if world == 1 else "nccl all-reduce of 643 bg-head grads"},
+                                            "collective": "none" if world == 1 else "nccl all-reduce of 643 bg-head grads on a side stream under the expert backward"},
             "clocks": clk, "e2e": {"value": world * N_RAYS * K / (ms_e2e / 1e3), "unit": "rays/s", "h2d_bytes_per_step": bytes_in,
                                    "d2h_bytes_per_step": 4, "ms_per_step": ms_e2e / K},
             "gpu_launches": launches, "roofline": roofline, "kernels": kern, "render": render, "render_c5": c5, "train_c3": c3, "cpu_baseline": cpu,

@@ -333,7 +333,8 @@ int acn_a2a_combine_bwd(const float* d_out, const int32_t* point, const float* w
  * NVLink peer mappings instead of travelling through a collective.  AcnA2aRoute: base[e] = the buffer of expert e's
  * owner as mapped into this process (a local pointer when this rank owns e), row0[e] = first row of this rank's block
  * of expert e in it; pair j of the compact list (expert e = max{k: offs[k] <= j}) is row row0[e] + j - offs[e].
- *   acn_a2a_count        counts (K+1,), offs (K+1,) of a routed pair list (first half of acn_a2a_pack)
+ *   acn_a2a_count        counts (K+1,), offs (K+1,) of a routed pair list (first half of acn_a2a_pack); counts[K] = -1
+ *                        when seg[K] > pairs->Mcap, i.e. the list was truncated at its speculative capacity
  *   acn_a2a_push_rows    writes the [xyz,dir] rows (24 B) into the owners' row buffers; out_point/out_weight as acn_a2a_pack
  *   acn_a2a_pull_combine out[point[j]] += weight[j] * y_owner[row]   (16-byte loads from the owners' result buffers)
  *   acn_a2a_push_grad    d_y_owner[row] = weight[j] * d_out[point[j]] (16-byte stores into the owners' gradient buffers)

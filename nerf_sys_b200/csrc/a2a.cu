@@ -43,7 +43,7 @@ __global__ void __launch_bounds__(32 * ACN_MAX_EXPERTS) k_a2a_count(const int32_
       counts[k] = s_cnt[k];
       run += s_cnt[k];
     }
-    counts[K] = run;
+    counts[K] = ((int64_t)seg[K] > Mcap) ? -1 : run;  // -1: the pair list was truncated at its capacity
     offs[K] = run;
   }
 }

@@ -315,9 +315,11 @@ def routing(pts: PointSet, centroids_host: Sequence[float], K: int, margin: floa
     return None, hard
 
 
-def route_pack(pts: PointSet, centroids_host: Sequence[float], K: int, margin: float, cluster_2d: bool) -> PairList:
+def route_pack(pts: PointSet, centroids_host: Sequence[float], K: int, margin: float, cluster_2d: bool, sync: bool = True) -> PairList:
     """Routing + stable pack by expert.  One 4*(K+1)-byte device->host read fixes the exact
-    pair count (the reference syncs K times through nonzero(), meta_container.py:309)."""
+    pair count (the reference syncs K times through nonzero(), meta_container.py:309).
+    ``sync=False`` skips that read: the list keeps its speculative capacity (``seg_host`` is None, the kernels take the
+    segment table from the device) and the CALLER must check ``seg[K] <= pairs.M`` once it reads the counts."""
     if K > ACN_MAX_EXPERTS:
         raise ValueError(f"at most {ACN_MAX_EXPERTS} experts per routing call (got {K})")
     L = lib()
@@ -334,7 +336,9 @@ def route_pack(pts: PointSet, centroids_host: Sequence[float], K: int, margin: f
             with _timed("route_pack"):
                 check(L.acn_route_pack(C.byref(cp), ch, K, float(margin), int(cluster_2d), _ptr(point), _ptr(weight), _ptr(seg), cap,
                                        _ptr(ws), _stream()), "acn_route_pack")
-            _count(3)
+            _count(6)
+            if not sync:
+                return PairList(cap, point, weight, seg, None)
             seg_host = seg.tolist()
             if seg_host[K] <= cap:
                 break

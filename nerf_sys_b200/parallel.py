@@ -73,6 +73,47 @@ def allreduce_shared_grads(params: Sequence[Tensor], group=None, average: bool =
         o += g.numel()
 
 
+class SharedGradReducer:
+    """`allreduce_shared_grads` started from inside the backward pass.  The background head's gradients are complete
+    right after the compositing backward - before the expert MLP backward and the table scatter, which are 60 % of a
+    step - so their all-reduce runs on a side stream underneath those kernels; ``wait()`` joins it in front of the
+    optimiser.  Works under CUDA-graph capture (the side stream forks from and re-joins the capturing stream)."""
+
+    def __init__(self, params: Sequence[Tensor], group=None, average: bool = True):
+        self.params = [p for p in params if p.requires_grad]
+        self.group, self.average = group, average
+        self._ready = 0
+        self._launched = False
+        self._stream = torch.cuda.Stream(self.params[0].device) if self.params and self.params[0].is_cuda else None
+        self._hooks = [p.register_post_accumulate_grad_hook(self._on_grad) for p in self.params]
+
+    def _on_grad(self, _p) -> None:
+        self._ready += 1
+        if self._ready < len(self.params) or _world(self.group)[0] == 1:
+            return
+        self._launched = True
+        if self._stream is None:
+            allreduce_shared_grads(self.params, self.group, self.average)
+            return
+        self._stream.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(self._stream):
+            allreduce_shared_grads(self.params, self.group, self.average)
+
+    def wait(self) -> None:
+        """Call between backward() and optimizer.step()."""
+        if self._launched:
+            if self._stream is not None:
+                torch.cuda.current_stream().wait_stream(self._stream)
+        else:  # some parameter got no gradient this step: reduce what there is, in line
+            allreduce_shared_grads(self.params, self.group, self.average)
+        self._ready, self._launched = 0, False
+
+    def remove(self) -> None:
+        for h in self._hooks:
+            h.remove()
+        self._hooks = []
+
+
 # ---------------------------------------------------------------------------------------------
 # ray-sharded full-frame render
 # ---------------------------------------------------------------------------------------------
@@ -379,7 +420,8 @@ def container_evaluate_p2p(model, pts, ex: PeerExchange, params=None) -> Tensor:
     mine = [e for e in range(K) if owner[e] == rank]
     dev = pts.device
     with torch.no_grad():
-        pairs = ops.route_pack(pts, model.centroids_host(), K, model.boundary_margin, model.cluster_2d)
+        # no host read here: the pair list keeps its speculative capacity and is checked with the counts below
+        pairs = ops.route_pack(pts, model.centroids_host(), K, model.boundary_margin, model.cluster_2d, sync=False)
         counts, offs = ops.a2a_count(pairs, K)
         if world > 1:
             table_dev = torch.empty(world, K + 1, device=dev, dtype=torch.int32)
@@ -388,6 +430,9 @@ def container_evaluate_p2p(model, pts, ex: PeerExchange, params=None) -> Tensor:
         else:
             table_dev = counts.view(1, K + 1)
         table = table_dev.tolist()  # the one host read of the step
+        if any(row[K] < 0 for row in table):  # seen identically by every rank: all of them raise
+            raise RuntimeError(f"routing produced more (sample, expert) pairs than the speculative capacity {pairs.M} of the pair "
+                               f"list on some rank (margin {model.boundary_margin}): raise acn_route_pack_capacity")
         M = table[rank][K]
         start, tot, used, row0 = peer_layout(table, owner, rank, ops.ACN_TILE)
         if max(used) > ex.cap:

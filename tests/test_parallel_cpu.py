@@ -171,6 +171,16 @@ def _render_worker(rank, world):
     PL.allreduce_shared_grads(ps)
     mean = sum(range(1, world + 1)) / world
     assert torch.allclose(ps[0].grad, torch.full((3, 2), mean)) and torch.allclose(ps[1].grad, torch.arange(5.0) * mean)
+    # the same reduction started from inside backward() as soon as the shared gradients exist
+    qs = [torch.ones(3, 2, requires_grad=True), torch.ones(5, requires_grad=True)]
+    red = PL.SharedGradReducer(qs)
+    for _ in range(2):
+        for q in qs:
+            q.grad = None
+        ((qs[0].sum() + (qs[1] * torch.arange(5.0)).sum()) * (rank + 1)).backward()
+        red.wait()
+        assert torch.allclose(qs[0].grad, torch.full((3, 2), mean)) and torch.allclose(qs[1].grad, torch.arange(5.0) * mean)
+    red.remove()
     assert ps[2].grad is None
 
 
