@@ -353,10 +353,19 @@ int acn_a2a_push_grad(const float* d_out, const int32_t* point, const float* wei
                       const AcnA2aRoute* route, void* stream);
 /* Exchange slabs (one process per GPU, CUDA IPC): acn_p2p_alloc = cudaMalloc + a 64-byte handle the peers pass to
  * acn_p2p_open (maps the slab with peer access); the host layer owns both and releases them with _close / _free. */
-int acn_p2p_alloc(int64_t bytes, void** ptr, void* handle64);
+#define ACN_MAX_PEERS 16
+#define ACN_P2P_SYNC_BYTES 4096 /* head of every slab: int32 flag[16] | status | pad to 32 ints | table[16][ACN_MAX_EXPERTS+1] */
+int acn_p2p_alloc(int64_t bytes, void** ptr, void* handle64); /* the first ACN_P2P_SYNC_BYTES are zeroed */
 int acn_p2p_free(void* ptr);
 int acn_p2p_open(const void* handle64, void** ptr);
 int acn_p2p_close(void* ptr);
+/* Barrier number `epoch` (1,2,..., the same sequence on every rank) between the `world` ranks whose slabs are
+ * sync_bases_host[0..world-1] (as mapped into this process), stream-ordered: the peer stores of this rank's earlier
+ * kernels are visible to a rank once that rank's barrier kernel has returned.  With counts != NULL the rank first writes
+ * its n_counts ints into row `rank` of every slab's table, i.e. an all-gather rides on the barrier.  A peer that does not
+ * arrive within ~4 s sets the status word (int 16 of the sync area) to 1 instead of hanging the GPU. */
+int acn_p2p_barrier(void* const* sync_bases_host, int world, int rank, int32_t epoch, const int32_t* counts, int n_counts,
+                    void* stream);
 
 #if defined(__GNUC__)
 #pragma GCC visibility pop

@@ -52,6 +52,8 @@ class AcnA2aRoute(C.Structure):
 
 
 ACN_ADAM_MAX_TENSORS = 64
+ACN_MAX_PEERS = 16
+ACN_P2P_SYNC_BYTES = 4096
 P = C.POINTER
 fp = P(f32)  # host float arrays
 
@@ -123,6 +125,7 @@ SIGNATURES = {
     "acn_p2p_free": (C.c_int, [vp]),
     "acn_p2p_open": (C.c_int, [vp, P(C.c_void_p)]),
     "acn_p2p_close": (C.c_int, [vp]),
+    "acn_p2p_barrier": (C.c_int, [P(C.c_void_p), C.c_int, C.c_int, i32, vp, C.c_int, vp]),
 }
 
 _lock = threading.Lock()

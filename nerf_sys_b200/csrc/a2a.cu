@@ -171,6 +171,49 @@ __global__ void __launch_bounds__(256) k_a2a_push_grad(const float4* __restrict_
   }
 }
 
+// ---- device-side barrier (and count exchange) between the ranks of one box -------------------------------------
+// Every slab starts with a sync area of ACN_P2P_SYNC_BYTES: int32 flag[16] | status | pad to 32 ints | table[16][17].
+// Barrier number `epoch` (1, 2, ... the same sequence on every rank): rank r stores epoch into flag[r] of EVERY rank's
+// slab (st.release.sys after a system fence, so the peer stores of this rank's earlier kernels are visible to whoever
+// acquires the flag), then waits until all flags of its OWN slab have reached epoch (ld.acquire.sys).  With `counts`, the
+// rank first writes its (n_counts) routed-sample counts into row `rank` of every slab's table: one launch replaces an
+// all-gather plus a barrier.  The wait is bounded (~4 s); on expiry status is set to 1 and the host raises at its next read.
+struct PeerSync {
+  int32_t* base[ACN_MAX_PEERS];
+};
+
+__device__ __forceinline__ void st_release_sys(int32_t* p, int32_t v) {
+  asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ int32_t ld_acquire_sys(const int32_t* p) {
+  int32_t v;
+  asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
+__global__ void __launch_bounds__(32) k_p2p_barrier(PeerSync peers, int world, int rank, int32_t epoch, const int32_t* __restrict__ counts,
+                                                    int n_counts) {
+  const int t = threadIdx.x;
+  if (counts != nullptr && t < world) {
+    int32_t* row = peers.base[t] + 32 + rank * (ACN_MAX_EXPERTS + 1);
+    for (int i = 0; i < n_counts; ++i) row[i] = counts[i];
+  }
+  __threadfence_system();
+  __syncwarp();
+  if (t < world) st_release_sys(peers.base[t] + rank, epoch);
+  if (t < world) {
+    const int32_t* mine = peers.base[rank] + t;
+    const long long t0 = clock64();
+    while (ld_acquire_sys(mine) - epoch < 0) {
+      if (clock64() - t0 > 8000000000ll) {  // ~4 s at 2 GHz: a peer never arrived
+        atomicExch(peers.base[rank] + 16, 1);
+        break;
+      }
+    }
+  }
+  __syncwarp();
+}
+
 static inline bool make_route(const AcnA2aRoute* r, int K, RouteDev& d) {
   for (int e = 0; e < ACN_MAX_EXPERTS; ++e) {
     d.base[e] = e < K ? r->base[e] : nullptr;
@@ -278,8 +321,14 @@ int acn_p2p_alloc(int64_t bytes, void** ptr, void* handle64) {
   static_assert(sizeof(cudaIpcMemHandle_t) == 64, "handle size");
   void* p = nullptr;
   ACN_CUDA(cudaMalloc(&p, (size_t)bytes));
+  cudaError_t e = cudaMemset(p, 0, (size_t)(bytes < ACN_P2P_SYNC_BYTES ? bytes : ACN_P2P_SYNC_BYTES));
+  if (e != cudaSuccess) {
+    cudaFree(p);
+    set_error("acn_p2p_alloc: cudaMemset: %s", cudaGetErrorString(e));
+    return ACN_ECUDA;
+  }
   cudaIpcMemHandle_t h;
-  cudaError_t e = cudaIpcGetMemHandle(&h, p);
+  e = cudaIpcGetMemHandle(&h, p);
   if (e != cudaSuccess) {
     cudaFree(p);
     set_error("acn_p2p_alloc: cudaIpcGetMemHandle: %s", cudaGetErrorString(e));
@@ -305,6 +354,19 @@ int acn_p2p_open(const void* handle64, void** ptr) {
 
 int acn_p2p_close(void* ptr) {
   if (ptr) ACN_CUDA(cudaIpcCloseMemHandle(ptr));
+  return ACN_OK;
+}
+
+int acn_p2p_barrier(void* const* sync_bases_host, int world, int rank, int32_t epoch, const int32_t* counts, int n_counts, void* stream) {
+  ACN_REQUIRE(sync_bases_host && world >= 1 && world <= ACN_MAX_PEERS && rank >= 0 && rank < world, "acn_p2p_barrier: bad world / rank");
+  ACN_REQUIRE(n_counts >= 0 && n_counts <= ACN_MAX_EXPERTS + 1 && (n_counts == 0 || counts), "acn_p2p_barrier: bad counts");
+  PeerSync ps;
+  for (int r = 0; r < ACN_MAX_PEERS; ++r) {
+    ps.base[r] = r < world ? static_cast<int32_t*>(sync_bases_host[r]) : nullptr;
+    ACN_REQUIRE(r >= world || ps.base[r], "acn_p2p_barrier: NULL slab for rank %d", r);
+  }
+  k_p2p_barrier<<<1, 32, 0, as_stream(stream)>>>(ps, world, rank, epoch, n_counts ? counts : nullptr, n_counts);
+  ACN_LAUNCH_CHECK();
   return ACN_OK;
 }
 

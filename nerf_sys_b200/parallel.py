@@ -303,21 +303,25 @@ class _Slab:
 
 class PeerExchange:
     """One exchange slab per rank, mapped by every peer (CUDA IPC over NVLink / NVSwitch), holding up to ``rows_cap``
-    received rows: rows (cap,6) | y (cap,4) | g (cap,4).  Senders write sample rows and result gradients straight into
-    the owner's slab and read the owner's [rgb,sigma] rows out of it (csrc/a2a.cu); no collective carries data.
-    Ordering between the phases is a stream-ordered barrier (a one-element NCCL all-reduce)."""
+    received rows: sync area | rows (cap,6) | y (cap,4) | g (cap,4).  Senders write sample rows and result gradients
+    straight into the owner's slab and read the owner's [rgb,sigma] rows out of it (csrc/a2a.cu); no collective carries
+    data.  Ordering between the phases is `barrier()`: one 32-thread kernel per rank that raises this rank's flag in every
+    slab and waits for every flag in its own (release / acquire at system scope), stream-ordered like any other launch."""
 
     ROW_FLOATS = (6, 4, 4)
 
     def __init__(self, rows_cap: int, group=None, device=None):
         import ctypes as C
-        from ._lib import check, lib
+        from ._lib import ACN_MAX_PEERS, ACN_P2P_SYNC_BYTES, check, lib
         self.group = group
         self.world, self.rank = _world(group)
+        if self.world > ACN_MAX_PEERS:
+            raise ValueError(f"PeerExchange spans one box: at most {ACN_MAX_PEERS} ranks")
         self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
         self.cap = int(rows_cap)
-        self._lib = lib()
-        n_floats = self.cap * sum(self.ROW_FLOATS)
+        self._lib, self._check, self._C = lib(), check, C
+        head = ACN_P2P_SYNC_BYTES // 4
+        n_floats = head + self.cap * sum(self.ROW_FLOATS)
         ptr, handle = C.c_void_p(), C.create_string_buffer(64)
         with torch.cuda.device(self.device):
             check(self._lib.acn_p2p_alloc(n_floats * 4, C.byref(ptr), handle), "acn_p2p_alloc")
@@ -336,28 +340,50 @@ class PeerExchange:
                 check(self._lib.acn_p2p_open(C.c_char_p(handles[r]), C.byref(q)), "acn_p2p_open")
             self.peer[r] = int(q.value)
             self._opened.append(int(q.value))
+        self._bases = (C.c_void_p * self.world)(*self.peer)
         flat = torch.as_tensor(_Slab(self._ptr, n_floats), device=self.device)
-        o1, o2 = self.cap * 6, self.cap * 10
-        self.rows, self.y, self.g = flat[:o1].view(self.cap, 6), flat[o1:o2].view(self.cap, 4), flat[o2:].view(self.cap, 4)
-        self._byte_off = {"rows": 0, "y": o1 * 4, "g": o2 * 4}
-        self._flag = torch.zeros(1, device=self.device)
+        self.sync = flat[:head].view(torch.int32)  # flag[16] | status | pad | table[16][ACN_MAX_EXPERTS+1] at int 32
+        o0 = head
+        o1, o2 = o0 + self.cap * 6, o0 + self.cap * 10
+        self.rows, self.y, self.g = flat[o0:o1].view(self.cap, 6), flat[o1:o2].view(self.cap, 4), flat[o2:].view(self.cap, 4)
+        self._byte_off = {"rows": o0 * 4, "y": o1 * 4, "g": o2 * 4}
+        self._epoch = 0
+        if self.world > 1:
+            dist.barrier(group=group)  # every slab is mapped (and its sync area zeroed) before the first flag is written
         self.barrier()
 
     def base(self, kind: str, r: int) -> int:
         return self.peer[r] + self._byte_off[kind]
 
-    def barrier(self) -> None:
-        """Every rank's earlier work on its stream (including stores into peers) is complete before any rank's later work."""
-        if self.world > 1:
-            dist.all_reduce(self._flag, group=self.group)
+    def barrier(self, counts: Optional[Tensor] = None) -> None:
+        """Every rank's earlier work on its stream (including stores into peers) is complete and visible before any rank's
+        later work.  With ``counts`` (int32, <= 17 entries) the ranks also exchange them: afterwards ``table()`` holds
+        every rank's row."""
+        C = self._C
+        self._epoch += 1
+        n = 0 if counts is None else int(counts.numel())
+        with torch.cuda.device(self.device):
+            self._check(self._lib.acn_p2p_barrier(self._bases, self.world, self.rank, self._epoch,
+                                                  None if counts is None else C.c_void_p(counts.data_ptr()), n,
+                                                  C.c_void_p(torch.cuda.current_stream().cuda_stream)), "acn_p2p_barrier")
+
+    def table(self, n: int) -> List[List[int]]:
+        """Host copy of the exchanged counts, one row of ``n`` ints per rank (the step's one device->host read); raises if
+        a barrier timed out."""
+        from ._lib import ACN_MAX_EXPERTS
+        w = ACN_MAX_EXPERTS + 1
+        host = self.sync[16:32 + self.world * w].tolist()
+        if host[0] != 0:
+            raise RuntimeError("PeerExchange: a rank did not reach a barrier within its time limit")
+        return [host[16 + r * w:16 + r * w + n] for r in range(self.world)]
 
     def close(self) -> None:
         if self._lib is None:
             return
         torch.cuda.synchronize(self.device)
-        self.barrier()
-        torch.cuda.synchronize(self.device)
-        self.rows = self.y = self.g = None
+        if self.world > 1:
+            dist.barrier(group=self.group)
+        self.rows = self.y = self.g = self.sync = None
         for q in self._opened:
             self._lib.acn_p2p_close(q)
         self._lib.acn_p2p_free(self._ptr)
@@ -411,8 +437,9 @@ def container_evaluate_p2p(model, pts, ex: PeerExchange, params=None) -> Tensor:
     routing rank directly into the slab of e's owner (24 B rows over NVLink), the owner evaluates its experts in place,
     and the routing rank pulls the [rgb,sigma] rows it needs (16 B) while blending.  Layout of an owner's slab: its
     experts in order, each expert's block = the sub-blocks of source ranks 0..world-1, blocks padded to 128 rows: an
-    expert's rows are contiguous, so the received rows need no regrouping.  Per call: one (K+1)-int all-gather (the
-    only host read) and two barriers; the backward pass adds one push and one barrier."""
+    expert's rows are contiguous, so the received rows need no regrouping.  Per call: three barrier kernels (the
+    first one carries the (K+1) routed-sample counts of every rank: the only host read); the backward pass adds one push
+    and one barrier.  No NCCL call on the path."""
     from . import ops
     world, rank = ex.world, ex.rank
     K = len(model.submodules)
@@ -423,13 +450,10 @@ def container_evaluate_p2p(model, pts, ex: PeerExchange, params=None) -> Tensor:
         # no host read here: the pair list keeps its speculative capacity and is checked with the counts below
         pairs = ops.route_pack(pts, model.centroids_host(), K, model.boundary_margin, model.cluster_2d, sync=False)
         counts, offs = ops.a2a_count(pairs, K)
-        if world > 1:
-            table_dev = torch.empty(world, K + 1, device=dev, dtype=torch.int32)
-            # also the step's opening barrier: nobody writes into a slab before its owner is done with the previous step
-            dist.all_gather_into_tensor(table_dev, counts, group=ex.group)
-        else:
-            table_dev = counts.view(1, K + 1)
-        table = table_dev.tolist()  # the one host read of the step
+        # counts travel with the step's opening barrier: nobody writes into a slab before its owner is done with the
+        # previous step, and every rank ends up with the whole table
+        ex.barrier(counts)
+        table = ex.table(K + 1)  # the one host read of the step
         if any(row[K] < 0 for row in table):  # seen identically by every rank: all of them raise
             raise RuntimeError(f"routing produced more (sample, expert) pairs than the speculative capacity {pairs.M} of the pair "
                                f"list on some rank (margin {model.boundary_margin}): raise acn_route_pack_capacity")
