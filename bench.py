@@ -245,7 +245,6 @@ def train_c3(device, rank, world, barrier, max_over_ranks, steps=10, warmup=3):
             model.set_expert_parallel(True, exchange=ex)
         groups, shared = PL.owned_param_groups(model)
         opt = FusedAdam([{"params": gr["params"], "lr": lrs[n]} for n, gr in groups.items()], max_grad_norm=1.0).shard_grad_norm(None, shared)
-        reducer = PL.SharedGradReducer(shared, average=False)
         rays = [O.aerial_rays(N_RAYS, aabb, seed=1000 + 16 * rank + b).to(device) for b in range(nb)]
         g = torch.Generator().manual_seed(900 + rank)
         gts = [torch.rand(N_RAYS, 3, generator=g).to(device) for _ in range(nb)]
@@ -254,7 +253,7 @@ def train_c3(device, rank, world, barrier, max_over_ranks, steps=10, warmup=3):
             opt.zero_grad(set_to_none=True)
             loss = compute_mse_loss(P, model, {"rays": rays[i % nb], "rgbs": gts[i % nb]})
             (loss / world).backward()  # the step's loss is the mean over the world x 8192 rays of all ranks
-            reducer.wait()
+            PL.allreduce_shared_grads(shared, average=False)  # eager step: enqueued while the table scatter runs
             opt.step()
             return loss
 
@@ -269,7 +268,6 @@ def train_c3(device, rank, world, barrier, max_over_ranks, steps=10, warmup=3):
         barrier()
         ms = max_over_ranks(e0.elapsed_time(e1))
         lv = float(loss.item())
-        reducer.remove()
         if ex is not None:
             model.set_expert_parallel(False)
             ex.close()

@@ -221,13 +221,15 @@ def expert_parallel_apply(rows: Tensor, counts: Sequence[int], expert_fn: Callab
     return combine(y)
 
 
-def _evaluate_local(model, params, rows: Tensor, local: List[int], point: Tensor, segs: List[int]) -> Tensor:
+def _evaluate_local(model, params, rows: Tensor, local: List[int], point: Tensor, segs: List[int], seg_dev: Optional[Tensor] = None) -> Tensor:
     """This rank's experts ``local`` over received rows: ``point`` (segs[-1],) int32 lists, expert by expert (each group
     padded to 128 slots with -1), the rows of ``rows`` (R,6) that belong to it.  One fused launch per direction."""
     from . import ops
     spec_all = model.expert_spec()
     dev = rows.device
-    pl = ops.PairList(segs[-1], point, torch.ones(segs[-1], device=dev), torch.tensor(segs, dtype=torch.int32, device=dev), segs)
+    if seg_dev is None:
+        seg_dev = torch.tensor(segs, dtype=torch.int32, device=dev)
+    pl = ops.PairList(segs[-1], point, torch.ones(segs[-1], device=dev), seg_dev, segs)
     spec = ops.ExpertSpec(spec_all.grid, [spec_all.box_min[e] for e in local], [spec_all.extent[e] for e in local])
     tables = [model.submodules[e].xyz_encoder.hash_table for e in local]
     mlp: List[Tensor] = []
@@ -348,6 +350,7 @@ class PeerExchange:
         self.rows, self.y, self.g = flat[o0:o1].view(self.cap, 6), flat[o1:o2].view(self.cap, 4), flat[o2:].view(self.cap, 4)
         self._byte_off = {"rows": o0 * 4, "y": o1 * 4, "g": o2 * 4}
         self._epoch = 0
+        self._seg_pin = torch.empty(32, dtype=torch.int32).pin_memory()
         if self.world > 1:
             dist.barrier(group=group)  # every slab is mapped (and its sync area zeroed) before the first flag is written
         self.barrier()
@@ -471,7 +474,11 @@ def container_evaluate_p2p(model, pts, ex: PeerExchange, params=None) -> Tensor:
             segs.append(start[e] + (tot[e] + ops.ACN_TILE - 1) // ops.ACN_TILE * ops.ACN_TILE)
             point[start[e] + tot[e]:segs[-1]] = -1
     if R and mine:
-        y_owner = _evaluate_local(model, params, ex.rows[:R], mine, point, segs)
+        # segment table through a pinned staging buffer: a pageable host->device copy would drain the stream (and with it
+        # wait for every peer to reach the barrier above) before the expert kernels could even be enqueued
+        ex._seg_pin[:len(segs)] = torch.tensor(segs, dtype=torch.int32)
+        seg_dev = ex._seg_pin[:len(segs)].to(dev, non_blocking=True)
+        y_owner = _evaluate_local(model, params, ex.rows[:R], mine, point, segs, seg_dev)
     else:
         y_owner = torch.zeros(R, 4, device=dev)
     if torch.is_grad_enabled() and not y_owner.requires_grad:
