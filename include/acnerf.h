@@ -67,6 +67,8 @@ typedef struct AcnPoints {
   const float* t;    /* (N,S) */
   int32_t S;
   int64_t P;         /* number of points */
+  const float* t_T;  /* optional (S,N) copy of t (NULL = absent): read instead of t, coalesced, when consecutive slots
+                        are the same sample of adjacent rays (acn_route_pack_order, sample_major) */
 } AcnPoints;
 
 /* Routed (point, expert) pairs, grouped by expert, each group padded to a
@@ -148,6 +150,14 @@ int64_t acn_route_pack_ws_bytes(int64_t P, int K);
 int acn_route_pack(const AcnPoints* pts, const float* centroids_host, int K, float margin, int cluster_2d,
                    int32_t* pair_point, float* pair_weight, int32_t* seg, int64_t Mcap, void* ws,
                    void* stream);
+/* Same, with the enumeration order chosen: sample_major = 1 (implicit points only) lists each expert's members in
+ * (sample, ray) order instead of point order, so that consecutive slots are the same sample of adjacent rays - for the
+ * rays of an image block, neighbouring pixels that share grid cells on most levels.  Point ids, weights and the
+ * membership are unchanged; only the order inside a segment differs (a renderer's choice: every later kernel is
+ * order-agnostic). */
+int acn_route_pack_order(const AcnPoints* pts, const float* centroids_host, int K, float margin, int cluster_2d,
+                         int32_t* pair_point, float* pair_weight, int32_t* seg, int64_t Mcap, void* ws,
+                         int sample_major, void* stream);
 
 /* ---- a8-a11: encoders ---------------------------------------------------- */
 /* models/encodings.py:331-358: table row ids of the 8 corners, idx (P,L,8) int32,

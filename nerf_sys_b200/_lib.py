@@ -27,7 +27,7 @@ class AcnGridDesc(C.Structure):
 
 
 class AcnPoints(C.Structure):
-    _fields_ = [("x6", vp), ("rays", vp), ("t", vp), ("S", i32), ("P", i64)]
+    _fields_ = [("x6", vp), ("rays", vp), ("t", vp), ("S", i32), ("P", i64), ("t_T", vp)]
 
 
 class AcnPairs(C.Structure):
@@ -74,6 +74,7 @@ SIGNATURES = {
     "acn_route_pack_capacity": (i64, [i64, C.c_int]),
     "acn_route_pack_ws_bytes": (i64, [i64, C.c_int]),
     "acn_route_pack": (C.c_int, [P(AcnPoints), fp, C.c_int, f32, C.c_int, vp, vp, vp, i64, vp, vp]),
+    "acn_route_pack_order": (C.c_int, [P(AcnPoints), fp, C.c_int, f32, C.c_int, vp, vp, vp, i64, vp, C.c_int, vp]),
     "acn_hashgrid_indices": (C.c_int, [vp, i64, P(AcnGridDesc), vp, vp]),
     "acn_hashgrid_fwd": (C.c_int, [vp, i64, vp, P(AcnGridDesc), vp, vp]),
     "acn_hashgrid_bwd": (C.c_int, [vp, i64, vp, P(AcnGridDesc), vp, vp]),

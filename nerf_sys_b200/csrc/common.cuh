@@ -85,6 +85,8 @@ struct PointSrc {
   const float* rays;
   const float* t;
   int S;
+  const float* tT;  // optional (S, n_rays) copy of t
+  uint32_t n_rays;
 };
 
 static inline PointSrc make_src(const AcnPoints* p) {
@@ -93,6 +95,8 @@ static inline PointSrc make_src(const AcnPoints* p) {
   s.rays = p->rays;
   s.t = p->t;
   s.S = p->S;
+  s.tT = p->x6 ? nullptr : p->t_T;
+  s.n_rays = (p->S > 0) ? (uint32_t)(p->P / p->S) : 0u;
   return s;
 }
 
@@ -115,7 +119,7 @@ __device__ __forceinline__ void load_xyz(const PointSrc& s, int64_t p, float& x,
     int64_t r = ray_of(p, s.S);
     const float4* rr = reinterpret_cast<const float4*>(s.rays + r * 8);
     float4 a = __ldg(rr), b = __ldg(rr + 1);
-    float tv = __ldg(s.t + p);
+    float tv = s.tT ? __ldg(s.tT + (p - r * s.S) * (int64_t)s.n_rays + r) : __ldg(s.t + p);
     x = __fadd_rn(a.x, __fmul_rn(a.w, tv));
     y = __fadd_rn(a.y, __fmul_rn(b.x, tv));
     z = __fadd_rn(a.z, __fmul_rn(b.y, tv));

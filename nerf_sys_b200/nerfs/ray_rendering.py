@@ -63,7 +63,7 @@ def stratified_t_vals(near: Tensor, far: Tensor, ray_samples: int, randomized: b
 
 def render_rays_stratified(model, rays: Tensor, ray_samples: int, params=None, active_module: Optional[int] = None,
                            bg_color_default: str = "white", chunk: int = 1_000_000, sigma_scale=1.0, u: Optional[Tensor] = None,
-                           **kwargs):
+                           coherent: bool = False, **kwargs):
     """Stratified renderer: rgb (N,3), depth (N,), weights (N,S), acc (N,).
 
     ``chunk`` is accepted for signature compatibility; nothing is staged per point, so there is
@@ -75,7 +75,7 @@ def render_rays_stratified(model, rays: Tensor, ray_samples: int, params=None, a
         if model.training and u is None:
             u = torch.rand(N, S, device=rays.device, dtype=torch.float32)
         t_vals = ops.stratified_t(rays, S, u if model.training else None)
-    pts = ops.PointSet(rays=rays, t=t_vals)
+    pts = ops.PointSet(rays=rays, t=t_vals, coherent=coherent)  # coherent: rays are a block of image rows (render_image)
     # as in the reference (:323-326): with active_module the expert is called directly and `params`
     # holds EXPERT-level keys (meta_core.extract_module_params); otherwise container-level keys
     model_eff = model.submodules[active_module] if active_module is not None else model
@@ -114,7 +114,7 @@ def render_image(model, *, H: int, W: int, fx: float, fy: float, cx: float, cy: 
         rows = min(rows_per_chunk, R1 - r0)
         rays = ops.raygen(H, W, fx, fy, cx, cy, center_pixels, c2w, aabb, device, row0=r0, rows=rows)
         c, d, _, a = render_rays(model, rays, ray_samples=ray_samples, params=params, active_module=active_module,
-                                 bg_color_default=bg_color_default, chunk=chunk_points)
+                                 bg_color_default=bg_color_default, chunk=chunk_points, coherent=True)
         sl = slice((r0 - R0) * W, (r0 - R0 + rows) * W)
         rgb[sl], depth[sl], acc[sl] = c, d, a
     if row_range is not None:

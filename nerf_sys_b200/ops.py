@@ -150,7 +150,10 @@ def grid_desc(levels: int, log2_T: int, interp: str, res: Sequence[int], feature
 class PointSet:
     """Sample points: explicit (P,6) rows, or implicit (rays (N,8), t (N,S))."""
 
-    def __init__(self, x6: Optional[Tensor] = None, rays: Optional[Tensor] = None, t: Optional[Tensor] = None):
+    def __init__(self, x6: Optional[Tensor] = None, rays: Optional[Tensor] = None, t: Optional[Tensor] = None, coherent: bool = False):
+        # coherent: consecutive rays are neighbouring pixels of an image block (a renderer's hint; lets the pack list the
+        # samples in (sample, ray) order so that the lanes of the gather kernels share grid cells)
+        self.coherent = bool(coherent) and x6 is None
         if x6 is not None:
             self.x6 = _f32(x6, "x6")
             self.rays = self.t = None
@@ -161,11 +164,14 @@ class PointSet:
             self.rays, self.t = _f32(rays, "rays"), _f32(t, "t")
             self.S, self.P = int(self.t.shape[1]), int(self.t.numel())
             self.device = self.rays.device
+        # (S,N) copy of t for the sample-major slot order: adjacent lanes read adjacent floats
+        self.tT = self.t.t().contiguous() if self.coherent else None
 
     def c(self) -> AcnPoints:
         p = AcnPoints()
         p.x6, p.rays, p.t = _ptr(self.x6), _ptr(self.rays), _ptr(self.t)
         p.S, p.P = self.S, self.P
+        p.t_T = _ptr(self.tT)
         return p
 
 
@@ -315,9 +321,11 @@ def routing(pts: PointSet, centroids_host: Sequence[float], K: int, margin: floa
     return None, hard
 
 
-def route_pack(pts: PointSet, centroids_host: Sequence[float], K: int, margin: float, cluster_2d: bool, sync: bool = True) -> PairList:
+def route_pack(pts: PointSet, centroids_host: Sequence[float], K: int, margin: float, cluster_2d: bool, sync: bool = True,
+               sample_major: bool = False) -> PairList:
     """Routing + stable pack by expert.  One 4*(K+1)-byte device->host read fixes the exact
     pair count (the reference syncs K times through nonzero(), meta_container.py:309).
+    ``sample_major`` lists each expert's members in (sample, ray) order (acn_route_pack_order).
     ``sync=False`` skips that read: the list keeps its speculative capacity (``seg_host`` is None, the kernels take the
     segment table from the device) and the CALLER must check ``seg[K] <= pairs.M`` once it reads the counts."""
     if K > ACN_MAX_EXPERTS:
@@ -334,8 +342,8 @@ def route_pack(pts: PointSet, centroids_host: Sequence[float], K: int, margin: f
             point = torch.empty(cap, device=dev, dtype=torch.int32)
             weight = torch.empty(cap, device=dev, dtype=torch.float32)
             with _timed("route_pack"):
-                check(L.acn_route_pack(C.byref(cp), ch, K, float(margin), int(cluster_2d), _ptr(point), _ptr(weight), _ptr(seg), cap,
-                                       _ptr(ws), _stream()), "acn_route_pack")
+                check(L.acn_route_pack_order(C.byref(cp), ch, K, float(margin), int(cluster_2d), _ptr(point), _ptr(weight), _ptr(seg), cap,
+                                             _ptr(ws), int(bool(sample_major)), _stream()), "acn_route_pack_order")
             _count(6)
             if not sync:
                 return PairList(cap, point, weight, seg, None)

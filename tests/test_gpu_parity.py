@@ -168,6 +168,39 @@ def test_route_pack_is_a_stable_partition():
                     assert (weight[seg[k]:seg[k] + live.numel()] == 1).all()
 
 
+def test_route_pack_sample_major_is_the_same_partition_in_render_order():
+    """acn_route_pack_order(sample_major=1): same members and weights per expert as the natural order, listed in
+    (sample, ray) order; and a frame rendered through it equals the frame rendered in point order."""
+    from nerf_sys_b200 import ops
+    from nerf_sys_b200.nerfs.ray_rendering import render_rays
+    aabb, cent, _ = O.grid_scene(2, 4)
+    for N, S, K in ((5, 3, 8), (333, 17, 8), (1000, 64, 8), (257, 33, 1)):
+        rays = O.aerial_rays(N, aabb, seed=N).to(DEV)
+        t = ops.stratified_t(rays, S, None)
+        ps = ops.PointSet(rays=rays, t=t)
+        ch = cent.reshape(-1).tolist()[:3 * K]
+        a = ops.route_pack(ps, ch, K, 1.05, True)
+        b = ops.route_pack(ps, ch, K, 1.05, True, sample_major=True)
+        assert a.seg_host == b.seg_host
+        for k in range(K):
+            pa, wa = a.point[a.seg_host[k]:a.seg_host[k + 1]].cpu(), a.weight[a.seg_host[k]:a.seg_host[k + 1]].cpu()
+            pb, wb = b.point[b.seg_host[k]:b.seg_host[k + 1]].cpu(), b.weight[b.seg_host[k]:b.seg_host[k + 1]].cpu()
+            la, lb = pa >= 0, pb >= 0
+            assert la.sum() == lb.sum() and (lb[: int(lb.sum())]).all(), "live slots first, padding last"
+            order = torch.argsort(pb[lb])
+            assert torch.equal(pb[lb][order], pa[la]) and torch.equal(wb[lb][order], wa[la])
+            key = (pb[lb] % S).long() * N + (pb[lb] // S).long()  # (sample, ray) order
+            assert torch.equal(key, torch.sort(key).values)
+    m, st, cfg, mins, aabb = _big_scene(8, 2, 4, 14)
+    m.eval()
+    rays = O.aerial_rays(2000, aabb, seed=4).to(DEV)
+    with torch.no_grad():
+        ref = render_rays(m, rays, ray_samples=48)
+        got = render_rays(m, rays, ray_samples=48, coherent=True)
+    for x, y, name in zip(got, ref, ("rgb", "depth", "weights", "acc")):
+        close(x, y, 1e-6, f"coherent render {name}")
+
+
 def test_a2a_pack_and_combine_match_the_reference_loop():
     """Dispatch rows / blend of meta_container.py:305-337 as the all-to-all sees them: rows grouped by expert in
     nonzero() order (exact: positions are rebuilt with the same mul-then-add), combine == index_add_ of w*y."""
