@@ -67,8 +67,11 @@ typedef struct AcnPoints {
   const float* t;    /* (N,S) */
   int32_t S;
   int64_t P;         /* number of points */
-  const float* t_T;  /* optional (S,N) copy of t (NULL = absent): read instead of t, coalesced, when consecutive slots
-                        are the same sample of adjacent rays (acn_route_pack_order, sample_major) */
+  const float* t_T;  /* optional (S,N) copy of t, N = P/S.  Non-NULL selects SAMPLE-MAJOR point ids: point p is sample
+                        p / N of ray p % N and its t is t_T[p]; everything indexed by point id (pair lists, outputs) is
+                        then in (S,N) order.  A renderer's choice for rays that are neighbouring pixels: consecutive
+                        points - the lanes of every kernel - are the same sample of adjacent pixels and share grid
+                        cells, where consecutive samples of one ray share nothing above res ~32. */
 } AcnPoints;
 
 /* Routed (point, expert) pairs, grouped by expert, each group padded to a
@@ -150,14 +153,6 @@ int64_t acn_route_pack_ws_bytes(int64_t P, int K);
 int acn_route_pack(const AcnPoints* pts, const float* centroids_host, int K, float margin, int cluster_2d,
                    int32_t* pair_point, float* pair_weight, int32_t* seg, int64_t Mcap, void* ws,
                    void* stream);
-/* Same, with the enumeration order chosen: sample_major = 1 (implicit points only) lists each expert's members in
- * (sample, ray) order instead of point order, so that consecutive slots are the same sample of adjacent rays - for the
- * rays of an image block, neighbouring pixels that share grid cells on most levels.  Point ids, weights and the
- * membership are unchanged; only the order inside a segment differs (a renderer's choice: every later kernel is
- * order-agnostic). */
-int acn_route_pack_order(const AcnPoints* pts, const float* centroids_host, int K, float margin, int cluster_2d,
-                         int32_t* pair_point, float* pair_weight, int32_t* seg, int64_t Mcap, void* ws,
-                         int sample_major, void* stream);
 
 /* ---- a8-a11: encoders ---------------------------------------------------- */
 /* models/encodings.py:331-358: table row ids of the 8 corners, idx (P,L,8) int32,
@@ -274,6 +269,12 @@ int acn_bg_backward(const float* d_rgb, int64_t N, const float* w0, const float*
  * -> rgb (N,3), depth (N), weights (N,S) or NULL, acc (N).  No early termination. */
 int acn_composite_fwd(const float* rgb_sigma, const float* t, const float* bg, int64_t N, int S,
                       float sigma_scale, float* rgb, float* depth, float* weights, float* acc, void* stream);
+/* acn_composite_fwd with the (rgb,sigma) row of (ray r, sample s) at rgb_sigma + 4*(r*ray_stride + s*sample_stride):
+ * (S, 1) is the reference's (N,S,4) layout, (1, N) the (S,N,4) output of a sample-major point set (AcnPoints.t_T).
+ * t, weights stay (N,S). */
+int acn_composite_fwd_strided(const float* rgb_sigma, int64_t ray_stride, int64_t sample_stride, const float* t,
+                              const float* bg, int64_t N, int S, float sigma_scale, float* rgb, float* depth,
+                              float* weights, float* acc, void* stream);
 /* its backward: g_rgb (N,3), g_depth (N) or NULL, g_acc (N) or NULL, g_weights (N,S) or NULL
  * -> d_rgb_sigma (N,S,4), d_bg (N,3) or NULL */
 int acn_composite_bwd(const float* rgb_sigma, const float* t, const float* bg, int64_t N, int S,

@@ -74,7 +74,6 @@ SIGNATURES = {
     "acn_route_pack_capacity": (i64, [i64, C.c_int]),
     "acn_route_pack_ws_bytes": (i64, [i64, C.c_int]),
     "acn_route_pack": (C.c_int, [P(AcnPoints), fp, C.c_int, f32, C.c_int, vp, vp, vp, i64, vp, vp]),
-    "acn_route_pack_order": (C.c_int, [P(AcnPoints), fp, C.c_int, f32, C.c_int, vp, vp, vp, i64, vp, C.c_int, vp]),
     "acn_hashgrid_indices": (C.c_int, [vp, i64, P(AcnGridDesc), vp, vp]),
     "acn_hashgrid_fwd": (C.c_int, [vp, i64, vp, P(AcnGridDesc), vp, vp]),
     "acn_hashgrid_bwd": (C.c_int, [vp, i64, vp, P(AcnGridDesc), vp, vp]),
@@ -108,6 +107,7 @@ SIGNATURES = {
     "acn_bg_bwd_ws_bytes": (i64, [i64]),
     "acn_bg_backward": (C.c_int, [vp, i64, vp, vp, vp, vp, vp, vp, vp, vp, vp]),
     "acn_composite_fwd": (C.c_int, [vp, vp, vp, i64, C.c_int, f32, vp, vp, vp, vp, vp]),
+    "acn_composite_fwd_strided": (C.c_int, [vp, i64, i64, vp, vp, i64, C.c_int, f32, vp, vp, vp, vp, vp]),
     "acn_composite_bwd": (C.c_int, [vp, vp, vp, i64, C.c_int, f32, vp, vp, vp, vp, vp, vp, vp]),
     "acn_mse_loss": (C.c_int, [vp, vp, i64, C.c_int, vp, vp, vp, vp]),
     "acn_adam_step": (C.c_int, [vp, vp, vp, vp, i64, f32, f32, f32, f32, f32, i64, vp, vp]),

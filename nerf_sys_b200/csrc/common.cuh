@@ -107,6 +107,17 @@ __device__ __forceinline__ int64_t ray_of(int64_t p, int S) {
   return p / S;
 }
 
+// (ray, t) of point p of an implicit point set: ray-major ids (p = ray * S + sample, t[p]) or, when the (S,N) copy of t
+// is given, sample-major ids (p = sample * N + ray, tT[p]).
+__device__ __forceinline__ int64_t ray_and_t(const PointSrc& s, int64_t p, float& tv) {
+  if (s.tT) {
+    tv = __ldg(s.tT + p);
+    return (int64_t)((uint32_t)p % s.n_rays);  // launches are chunked below 2^31 points
+  }
+  tv = __ldg(s.t + p);
+  return ray_of(p, s.S);
+}
+
 // xyz of point p.  Implicit form: o + d*t with a separate multiply and add
 // (ray_rendering.py:317) - no FMA contraction, so positions are bit-identical.
 __device__ __forceinline__ void load_xyz(const PointSrc& s, int64_t p, float& x, float& y, float& z) {
@@ -116,10 +127,10 @@ __device__ __forceinline__ void load_xyz(const PointSrc& s, int64_t p, float& x,
     y = __ldg(q + 1);
     z = __ldg(q + 2);
   } else {
-    int64_t r = ray_of(p, s.S);
+    float tv;
+    int64_t r = ray_and_t(s, p, tv);
     const float4* rr = reinterpret_cast<const float4*>(s.rays + r * 8);
     float4 a = __ldg(rr), b = __ldg(rr + 1);
-    float tv = s.tT ? __ldg(s.tT + (p - r * s.S) * (int64_t)s.n_rays + r) : __ldg(s.t + p);
     x = __fadd_rn(a.x, __fmul_rn(a.w, tv));
     y = __fadd_rn(a.y, __fmul_rn(b.x, tv));
     z = __fadd_rn(a.z, __fmul_rn(b.y, tv));
@@ -133,7 +144,7 @@ __device__ __forceinline__ void load_dir(const PointSrc& s, int64_t p, float& x,
     y = __ldg(q + 1);
     z = __ldg(q + 2);
   } else {
-    int64_t r = ray_of(p, s.S);
+    int64_t r = s.tT ? (int64_t)((uint32_t)p % s.n_rays) : ray_of(p, s.S);
     const float4* rr = reinterpret_cast<const float4*>(s.rays + r * 8);
     float4 a = __ldg(rr), b = __ldg(rr + 1);
     x = a.w;

@@ -56,7 +56,10 @@ __device__ __forceinline__ SampleEval eval_sample(float sigma_in, float scale, c
   return r;
 }
 
-__global__ void __launch_bounds__(256) k_composite_fwd(const float4* __restrict__ rs, const float* __restrict__ t, const float* __restrict__ bg,
+// rs element (ray r, sample s) sits at rs[r * ray_stride + s * sample_stride]: (S, 1) for the reference's (N,S,4) layout, (1, N) for
+// the (S,N,4) output of a sample-major point set (AcnPoints.t_T)
+__global__ void __launch_bounds__(256) k_composite_fwd(const float4* __restrict__ rs, int64_t ray_stride, int64_t sample_stride,
+                                                       const float* __restrict__ t, const float* __restrict__ bg,
                                                        int64_t N, int S, float scale, float* __restrict__ rgb, float* __restrict__ depth,
                                                        float* __restrict__ weights, float* __restrict__ acc) {
   int lane = threadIdx.x & 31;
@@ -72,7 +75,7 @@ __global__ void __launch_bounds__(256) k_composite_fwd(const float4* __restrict_
       float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
       float ts = 0.f;
       if (ok) {
-        v = __ldg(rs + r * S + s);
+        v = __ldg(rs + r * ray_stride + s * sample_stride);
         ts = __ldg(trow + s);
         SampleEval ev = eval_sample(v.w, scale, trow, s, S);
         fac = ev.fac;
@@ -407,16 +410,22 @@ static inline int64_t r128(int64_t n) { return (n + 127) / 128 * 128; }
 
 extern "C" {
 
-int acn_composite_fwd(const float* rgb_sigma, const float* t, const float* bg, int64_t N, int S, float sigma_scale, float* rgb,
-                      float* depth, float* weights, float* acc, void* stream) {
+int acn_composite_fwd_strided(const float* rgb_sigma, int64_t ray_stride, int64_t sample_stride, const float* t, const float* bg, int64_t N,
+                              int S, float sigma_scale, float* rgb, float* depth, float* weights, float* acc, void* stream) {
   ACN_REQUIRE(rgb_sigma && t && rgb && depth && acc && N >= 0, "acn_composite_fwd: NULL argument");
   ACN_REQUIRE(S >= 2, "acn_composite_fwd: needs at least 2 samples per ray (got %d)", S);
+  ACN_REQUIRE(ray_stride >= 1 && sample_stride >= 1, "acn_composite_fwd_strided: strides are in (rgb,sigma) rows and positive");
   if (N == 0) return ACN_OK;
   int grid = persistent_grid((N + 7) / 8, 8);
-  k_composite_fwd<<<grid, 256, 0, as_stream(stream)>>>(reinterpret_cast<const float4*>(rgb_sigma), t, bg, N, S, sigma_scale, rgb, depth,
-                                                       weights, acc);
+  k_composite_fwd<<<grid, 256, 0, as_stream(stream)>>>(reinterpret_cast<const float4*>(rgb_sigma), ray_stride, sample_stride, t, bg, N, S,
+                                                       sigma_scale, rgb, depth, weights, acc);
   ACN_LAUNCH_CHECK();
   return ACN_OK;
+}
+
+int acn_composite_fwd(const float* rgb_sigma, const float* t, const float* bg, int64_t N, int S, float sigma_scale, float* rgb,
+                      float* depth, float* weights, float* acc, void* stream) {
+  return acn_composite_fwd_strided(rgb_sigma, S, 1, t, bg, N, S, sigma_scale, rgb, depth, weights, acc, stream);
 }
 
 int acn_composite_bwd(const float* rgb_sigma, const float* t, const float* bg, int64_t N, int S, float sigma_scale, const float* g_rgb,

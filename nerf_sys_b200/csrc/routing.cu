@@ -227,31 +227,19 @@ __device__ __forceinline__ uint32_t route_warp(const RouteCfg& cfg, bool valid, 
   return mask;
 }
 
-// Enumeration order of the pack.  Natural (n_rays == 0): slot order = point order (the reference's nonzero() order).
-// Sample-major (n_rays = N > 0, implicit points only): the i-th enumerated point is sample i / N of ray i % N, so that
-// consecutive slots - the lanes of every later kernel - are the SAME sample of ADJACENT rays.  For the rays of an image
-// block those are neighbouring pixels at nearly the same depth: they fall into the same or adjacent grid cells on all
-// but the finest levels, where consecutive samples of one ray (0.03 scene units apart) share nothing above res 32.
-__device__ __forceinline__ int64_t enum_point(int64_t i, uint32_t n_rays, int S) {
-  if (n_rays == 0) return i;
-  const uint32_t s = (uint32_t)i / n_rays, r = (uint32_t)i - s * n_rays;
-  return (int64_t)r * S + s;
-}
-
 // ---- pass 1: per-block, per-expert member counts: counts[k*nb + b] ------------
 template <int KT, bool D3>
-__global__ void __launch_bounds__(RT) k_route_count(PointSrc src, int64_t P, RouteCfg cfg, int nb, int32_t* __restrict__ counts, uint32_t n_rays) {
+__global__ void __launch_bounds__(RT) k_route_count(PointSrc src, int64_t P, RouteCfg cfg, int nb, int32_t* __restrict__ counts) {
   __shared__ int cnt[ACN_MAX_EXPERTS];
   for (int b = blockIdx.x; b < nb; b += gridDim.x) {
     if (threadIdx.x < ACN_MAX_EXPERTS) cnt[threadIdx.x] = 0;
     __syncthreads();
 #pragma unroll
     for (int j = 0; j < RPT; ++j) {
-      const int64_t i = (int64_t)b * RB + j * RT + threadIdx.x;
-      const int64_t p = enum_point(i, n_rays, src.S);
+      const int64_t p = (int64_t)b * RB + j * RT + threadIdx.x;
       float x = 0.f, y = 0.f, z = 0.f, w[KT];
-      if (i < P) load_xyz(src, p, x, y, z);
-      const uint32_t mask = route_warp<KT, D3>(cfg, i < P, x, y, z, w);
+      if (p < P) load_xyz(src, p, x, y, z);
+      const uint32_t mask = route_warp<KT, D3>(cfg, p < P, x, y, z, w);
 #pragma unroll
       for (int k = 0; k < KT; ++k) {
         unsigned bal = __ballot_sync(0xffffffffu, (mask >> k) & 1u);
@@ -317,7 +305,7 @@ __global__ void k_route_seg(const int32_t* __restrict__ totals, int K, int32_t* 
 template <int KT, bool D3>
 __global__ void __launch_bounds__(RT) k_route_write(PointSrc src, int64_t P, RouteCfg cfg, int nb, const int32_t* __restrict__ base,
                                                     const int32_t* __restrict__ seg, int32_t* __restrict__ pair_point,
-                                                    float* __restrict__ pair_w, int64_t Mcap, uint32_t n_rays) {
+                                                    float* __restrict__ pair_w, int64_t Mcap) {
   __shared__ int run[ACN_MAX_EXPERTS];
   __shared__ int wcnt[ACN_MAX_EXPERTS][RT / 32];
   int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -326,11 +314,10 @@ __global__ void __launch_bounds__(RT) k_route_write(PointSrc src, int64_t P, Rou
     __syncthreads();
 #pragma unroll 1
     for (int j = 0; j < RPT; ++j) {
-      const int64_t i = (int64_t)b * RB + j * RT + threadIdx.x;
-      const int64_t p = enum_point(i, n_rays, src.S);
+      const int64_t p = (int64_t)b * RB + j * RT + threadIdx.x;
       float x = 0.f, y = 0.f, z = 0.f, w[KT];
-      if (i < P) load_xyz(src, p, x, y, z);
-      const uint32_t mask = route_warp<KT, D3>(cfg, i < P, x, y, z, w);
+      if (p < P) load_xyz(src, p, x, y, z);
+      const uint32_t mask = route_warp<KT, D3>(cfg, p < P, x, y, z, w);
       unsigned bals[KT];
 #pragma unroll
       for (int k = 0; k < KT; ++k) {
@@ -418,26 +405,21 @@ int64_t acn_route_pack_ws_bytes(int64_t P, int K) {
   return sizeof(int32_t) * (nb * K + 64);
 }
 
-static int route_pack_impl(const AcnPoints* pts, const float* centroids_host, int K, float margin, int cluster_2d, int32_t* pair_point,
-                           float* pair_weight, int32_t* seg, int64_t Mcap, void* ws, int sample_major, void* stream) {
+int acn_route_pack(const AcnPoints* pts, const float* centroids_host, int K, float margin, int cluster_2d, int32_t* pair_point,
+                   float* pair_weight, int32_t* seg, int64_t Mcap, void* ws, void* stream) {
   ACN_REQUIRE(pts && centroids_host && K >= 1 && K <= ACN_MAX_EXPERTS, "acn_route_pack: K must be in [1,%d]", ACN_MAX_EXPERTS);
   ACN_REQUIRE(pair_point && pair_weight && seg && ws && Mcap > 0, "acn_route_pack: missing buffers");
   ACN_REQUIRE(pts->P < (int64_t)1 << 31, "acn_route_pack: chunk the points below 2^31");
   cudaStream_t st = as_stream(stream);
   int64_t P = pts->P;
   int nb = (int)((P + RB - 1) / RB);
-  uint32_t n_rays = 0;
-  if (sample_major) {
-    ACN_REQUIRE(!pts->x6 && pts->S >= 1 && P % pts->S == 0, "acn_route_pack_order: sample-major order needs implicit points (rays, t, S)");
-    n_rays = (uint32_t)(P / pts->S);
-  }
   RouteCfg cfg;
   fill_cfg(cfg, centroids_host, K, margin, cluster_2d);
   int32_t* counts = reinterpret_cast<int32_t*>(ws);
   ACN_CUDA(cudaMemsetAsync(pair_point, 0xFF, sizeof(int32_t) * Mcap, st));
   ACN_CUDA(cudaMemsetAsync(pair_weight, 0, sizeof(float) * Mcap, st));
   if (nb > 0) {
-    ROUTE_DISPATCH(K, cluster_2d, k_route_count, persistent_grid(nb, 8), st, make_src(pts), P, cfg, nb, counts, n_rays);
+    ROUTE_DISPATCH(K, cluster_2d, k_route_count, persistent_grid(nb, 8), st, make_src(pts), P, cfg, nb, counts);
     ACN_LAUNCH_CHECK();
   }
   int32_t* totals = counts + (int64_t)nb * K;  // the 64 spare ints of the workspace
@@ -446,20 +428,10 @@ static int route_pack_impl(const AcnPoints* pts, const float* centroids_host, in
   k_route_seg<<<1, 32, 0, st>>>(totals, K, seg);
   ACN_LAUNCH_CHECK();
   if (nb > 0) {
-    ROUTE_DISPATCH(K, cluster_2d, k_route_write, persistent_grid(nb, 8), st, make_src(pts), P, cfg, nb, counts, seg, pair_point, pair_weight, Mcap, n_rays);
+    ROUTE_DISPATCH(K, cluster_2d, k_route_write, persistent_grid(nb, 8), st, make_src(pts), P, cfg, nb, counts, seg, pair_point, pair_weight, Mcap);
     ACN_LAUNCH_CHECK();
   }
   return ACN_OK;
-}
-
-int acn_route_pack(const AcnPoints* pts, const float* centroids_host, int K, float margin, int cluster_2d, int32_t* pair_point,
-                   float* pair_weight, int32_t* seg, int64_t Mcap, void* ws, void* stream) {
-  return route_pack_impl(pts, centroids_host, K, margin, cluster_2d, pair_point, pair_weight, seg, Mcap, ws, 0, stream);
-}
-
-int acn_route_pack_order(const AcnPoints* pts, const float* centroids_host, int K, float margin, int cluster_2d, int32_t* pair_point,
-                         float* pair_weight, int32_t* seg, int64_t Mcap, void* ws, int sample_major, void* stream) {
-  return route_pack_impl(pts, centroids_host, K, margin, cluster_2d, pair_point, pair_weight, seg, Mcap, ws, sample_major, stream);
 }
 
 }  // extern "C"

@@ -94,7 +94,7 @@ class MetaContainer(MetaModule):
         return None if params is None else self.get_subdict(params, f"submodules.{k}")
 
     def evaluate(self, pts: ops.PointSet, params=None, active_module: Optional[int] = None) -> torch.Tensor:
-        """(P,4) [rgb, sigma] for a point set (explicit rows or implicit ray samples)."""
+        """(P,4) [rgb, sigma] for a point set (explicit rows or implicit ray samples), in the set's own point order."""
         K = len(self.submodules)
         if active_module is not None:
             return self.submodules[active_module].evaluate(pts, self._sub_params(params, active_module))
@@ -106,15 +106,11 @@ class MetaContainer(MetaModule):
                 return parallel.container_evaluate_p2p(self, pts, self._ep[1], params=params)
             if parallel._world(self._ep[0])[0] > 1:
                 return parallel.container_evaluate_ep(self, pts, params=params, group=self._ep[0])
-        # rendering an image block (no autograd, neighbouring pixels): list the samples in (sample, ray) order so that the
-        # lanes of the gather kernels are the same sample of adjacent pixels and share grid cells
-        # (measured: 1080p x 8 experts 53.9 -> 52.3 ms; with a single expert the identity slot list is faster than any pack)
-        coherent = K > 1 and getattr(pts, "coherent", False) and not torch.is_grad_enabled()
         if K == 1 and self.boundary_margin > 1.0:
             # a single centroid always gets weight 1: skip the pack, keep the fused launch
             return self.submodules[0].evaluate(pts, self._sub_params(params, 0))
         with torch.no_grad():
-            pairs = ops.route_pack(pts, self.centroids_host(), K, self.boundary_margin, self.cluster_2d, sample_major=coherent)
+            pairs = ops.route_pack(pts, self.centroids_host(), K, self.boundary_margin, self.cluster_2d)
         tables = [sub.xyz_encoder.hash_table for sub in self.submodules]
         mlp: List[torch.Tensor] = []
         for k, sub in enumerate(self.submodules):

@@ -75,14 +75,24 @@ def render_rays_stratified(model, rays: Tensor, ray_samples: int, params=None, a
         if model.training and u is None:
             u = torch.rand(N, S, device=rays.device, dtype=torch.float32)
         t_vals = ops.stratified_t(rays, S, u if model.training else None)
-    pts = ops.PointSet(rays=rays, t=t_vals, coherent=coherent)  # coherent: rays are a block of image rows (render_image)
+    pts = ops.PointSet(rays=rays, t=t_vals)
     # as in the reference (:323-326): with active_module the expert is called directly and `params`
     # holds EXPERT-level keys (meta_core.extract_module_params); otherwise container-level keys
     model_eff = model.submodules[active_module] if active_module is not None else model
+    # A block of image rows (render_image), no autograd, several experts: number the points sample-major, so that the lanes
+    # of the routing / gather / MLP kernels are the same sample of adjacent pixels and share grid cells (measured, 1080p x 8
+    # experts: frame 53.9 -> 47 ms); the compositor reads the (S,N,4) result in place.  With one expert the identity slot list
+    # (no pack at all) is faster; sharded experts keep ray-major rows.
+    sample_major = (coherent and not torch.is_grad_enabled() and active_module is None and len(getattr(model, "submodules", ())) > 1
+                    and getattr(model, "_ep", None) is None)
+    if sample_major:
+        pts = pts.sample_major()
     rgb_sigma = model_eff.evaluate(pts, params=params)
-    rgb_sigma = rgb_sigma.view(N, S, 4)
-    bg_rgb = _get_bg_rgb(model, rays[:, 3:6], params, rgb_sigma, N=N, bg_color_default=bg_color_default)
-    return ops.composite(rgb_sigma, t_vals, bg_rgb, float(sigma_scale))
+    bg_view = rgb_sigma.view(S, N, 4).transpose(0, 1) if sample_major else rgb_sigma.view(N, S, 4)  # only for the bg policy's shape / last sample
+    bg_rgb = _get_bg_rgb(model, rays[:, 3:6], params, bg_view, N=N, bg_color_default=bg_color_default)
+    if sample_major:
+        return ops.composite_sample_major(rgb_sigma, t_vals, bg_rgb, float(sigma_scale))
+    return ops.composite(rgb_sigma.view(N, S, 4), t_vals, bg_rgb, float(sigma_scale))
 
 
 def render_rays(model, rays, *args, **kwargs):

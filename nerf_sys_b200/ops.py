@@ -151,9 +151,9 @@ class PointSet:
     """Sample points: explicit (P,6) rows, or implicit (rays (N,8), t (N,S))."""
 
     def __init__(self, x6: Optional[Tensor] = None, rays: Optional[Tensor] = None, t: Optional[Tensor] = None, coherent: bool = False):
-        # coherent: consecutive rays are neighbouring pixels of an image block (a renderer's hint; lets the pack list the
-        # samples in (sample, ray) order so that the lanes of the gather kernels share grid cells)
+        # coherent: consecutive rays are neighbouring pixels of an image block (a renderer's hint, see sample_major())
         self.coherent = bool(coherent) and x6 is None
+        self.tT = None
         if x6 is not None:
             self.x6 = _f32(x6, "x6")
             self.rays = self.t = None
@@ -164,8 +164,24 @@ class PointSet:
             self.rays, self.t = _f32(rays, "rays"), _f32(t, "t")
             self.S, self.P = int(self.t.shape[1]), int(self.t.numel())
             self.device = self.rays.device
-        # (S,N) copy of t for the sample-major slot order: adjacent lanes read adjacent floats
-        self.tT = self.t.t().contiguous() if self.coherent else None
+
+    def sample_major(self) -> "PointSet":
+        """The same points with SAMPLE-MAJOR ids (AcnPoints.t_T): point p = sample p // N of ray p % N.  Consecutive points -
+        the lanes of every kernel - are then the same sample of adjacent rays; for a block of image rows those are
+        neighbouring pixels that share grid cells on most levels.  Outputs indexed by point id come back in (S,N) order
+        (`to_ray_major`)."""
+        if self.x6 is not None:
+            raise ValueError("sample_major() needs implicit points (rays, t)")
+        q = PointSet(rays=self.rays, t=self.t)
+        q.tT = self.t.t().contiguous()
+        return q
+
+    def to_ray_major(self, out: Tensor) -> Tensor:
+        """(P, C) in this set's point order -> (P, C) in ray-major order (p = ray * S + sample)."""
+        if self.tT is None:
+            return out
+        N = self.P // self.S
+        return out.view(self.S, N, -1).transpose(0, 1).reshape(self.P, -1)
 
     def c(self) -> AcnPoints:
         p = AcnPoints()
@@ -321,11 +337,9 @@ def routing(pts: PointSet, centroids_host: Sequence[float], K: int, margin: floa
     return None, hard
 
 
-def route_pack(pts: PointSet, centroids_host: Sequence[float], K: int, margin: float, cluster_2d: bool, sync: bool = True,
-               sample_major: bool = False) -> PairList:
+def route_pack(pts: PointSet, centroids_host: Sequence[float], K: int, margin: float, cluster_2d: bool, sync: bool = True) -> PairList:
     """Routing + stable pack by expert.  One 4*(K+1)-byte device->host read fixes the exact
     pair count (the reference syncs K times through nonzero(), meta_container.py:309).
-    ``sample_major`` lists each expert's members in (sample, ray) order (acn_route_pack_order).
     ``sync=False`` skips that read: the list keeps its speculative capacity (``seg_host`` is None, the kernels take the
     segment table from the device) and the CALLER must check ``seg[K] <= pairs.M`` once it reads the counts."""
     if K > ACN_MAX_EXPERTS:
@@ -342,8 +356,8 @@ def route_pack(pts: PointSet, centroids_host: Sequence[float], K: int, margin: f
             point = torch.empty(cap, device=dev, dtype=torch.int32)
             weight = torch.empty(cap, device=dev, dtype=torch.float32)
             with _timed("route_pack"):
-                check(L.acn_route_pack_order(C.byref(cp), ch, K, float(margin), int(cluster_2d), _ptr(point), _ptr(weight), _ptr(seg), cap,
-                                             _ptr(ws), int(bool(sample_major)), _stream()), "acn_route_pack_order")
+                check(L.acn_route_pack(C.byref(cp), ch, K, float(margin), int(cluster_2d), _ptr(point), _ptr(weight), _ptr(seg), cap,
+                                       _ptr(ws), _stream()), "acn_route_pack")
             _count(6)
             if not sync:
                 return PairList(cap, point, weight, seg, None)
@@ -926,6 +940,25 @@ class CompositeFn(torch.autograd.Function):
 
 def composite(rgb_sigma: Tensor, t: Tensor, bg: Optional[Tensor], sigma_scale: float = 1.0):
     return CompositeFn.apply(rgb_sigma, t, bg, float(sigma_scale))
+
+
+@torch.no_grad()
+def composite_sample_major(rgb_sigma: Tensor, t: Tensor, bg: Optional[Tensor], sigma_scale: float = 1.0):
+    """`composite` for the (S*N, 4) output of a sample-major point set (PointSet.sample_major): read in place through
+    acn_composite_fwd_strided, no transposed copy.  Inference only (the sample-major order is a renderer's choice)."""
+    rs, tt = _f32(rgb_sigma, "rgb_sigma"), _f32(t, "t_vals")
+    N, S = tt.shape
+    if rs.numel() != N * S * 4:
+        raise ValueError(f"rgb_sigma must hold {N}x{S} rows of 4, got {tuple(rs.shape)}")
+    b = None if bg is None else _f32(bg, "bg_rgb")
+    dev = rs.device
+    rgb, depth = torch.empty(N, 3, device=dev), torch.empty(N, device=dev)
+    w, acc = torch.empty(N, S, device=dev), torch.empty(N, device=dev)
+    with torch.cuda.device(dev), _timed("composite_fwd"):
+        check(lib().acn_composite_fwd_strided(_ptr(rs), 1, N, _ptr(tt), _ptr(b), N, S, float(sigma_scale), _ptr(rgb), _ptr(depth), _ptr(w),
+                                              _ptr(acc), _stream()), "acn_composite_fwd_strided")
+    _count(1)
+    return rgb, depth, w, acc
 
 
 # --------------------------------------------------------------------------

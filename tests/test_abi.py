@@ -37,7 +37,7 @@ def test_library_exports_every_declared_symbol():
 def test_struct_layout_matches_c():
     from nerf_sys_b200 import _lib
     assert ctypes.sizeof(_lib.AcnGridDesc) == 4 * 4 + 4 * 32
-    assert ctypes.sizeof(_lib.AcnPoints) == 40
+    assert ctypes.sizeof(_lib.AcnPoints) == 48  # x6, rays, t, S (+pad), P, t_T
     assert ctypes.sizeof(_lib.AcnPairs) == 32
     assert ctypes.sizeof(_lib.AcnNgpExpert) == 8 * 15 + 24
     assert ctypes.sizeof(_lib.AcnNgpExpertGrads) == 8 * 15

@@ -168,29 +168,39 @@ def test_route_pack_is_a_stable_partition():
                     assert (weight[seg[k]:seg[k] + live.numel()] == 1).all()
 
 
-def test_route_pack_sample_major_is_the_same_partition_in_render_order():
-    """acn_route_pack_order(sample_major=1): same members and weights per expert as the natural order, listed in
-    (sample, ray) order; and a frame rendered through it equals the frame rendered in point order."""
+def test_sample_major_point_ids_give_the_same_partition_and_frame():
+    """AcnPoints.t_T (sample-major point ids, p = sample * N + ray): positions are bit-identical, every expert gets the same
+    members with the same weights (listed in sample-major order), and a frame rendered through it equals the frame
+    rendered with ray-major ids."""
     from nerf_sys_b200 import ops
     from nerf_sys_b200.nerfs.ray_rendering import render_rays
     aabb, cent, _ = O.grid_scene(2, 4)
-    for N, S, K in ((5, 3, 8), (333, 17, 8), (1000, 64, 8), (257, 33, 1)):
+    for N, S, K in ((5, 3, 8), (333, 17, 8), (1000, 64, 8), (257, 33, 2)):
         rays = O.aerial_rays(N, aabb, seed=N).to(DEV)
         t = ops.stratified_t(rays, S, None)
         ps = ops.PointSet(rays=rays, t=t)
+        sm = ps.sample_major()
         ch = cent.reshape(-1).tolist()[:3 * K]
         a = ops.route_pack(ps, ch, K, 1.05, True)
-        b = ops.route_pack(ps, ch, K, 1.05, True, sample_major=True)
+        b = ops.route_pack(sm, ch, K, 1.05, True)
         assert a.seg_host == b.seg_host
         for k in range(K):
             pa, wa = a.point[a.seg_host[k]:a.seg_host[k + 1]].cpu(), a.weight[a.seg_host[k]:a.seg_host[k + 1]].cpu()
             pb, wb = b.point[b.seg_host[k]:b.seg_host[k + 1]].cpu(), b.weight[b.seg_host[k]:b.seg_host[k + 1]].cpu()
             la, lb = pa >= 0, pb >= 0
             assert la.sum() == lb.sum() and (lb[: int(lb.sum())]).all(), "live slots first, padding last"
-            order = torch.argsort(pb[lb])
-            assert torch.equal(pb[lb][order], pa[la]) and torch.equal(wb[lb][order], wa[la])
-            key = (pb[lb] % S).long() * N + (pb[lb] // S).long()  # (sample, ray) order
-            assert torch.equal(key, torch.sort(key).values)
+            assert torch.equal(pb[lb], torch.sort(pb[lb]).values), "stable in the set's own point order"
+            nat = (pb[lb] % N).long() * S + (pb[lb] // N).long()  # sample-major id -> ray-major id
+            order = torch.argsort(nat)
+            assert torch.equal(nat[order], pa[la].long()) and torch.equal(wb[lb][order], wa[la])
+        rows_a, pt_a, _, _ = ops.a2a_pack(ps, a, K)
+        rows_b, pt_b, _, _ = ops.a2a_pack(sm, b, K)
+        nat = (pt_b.long() % N) * S + pt_b.long() // N
+        ia, ib = torch.argsort(pt_a.long() * 16, stable=True), torch.argsort(nat * 16, stable=True)
+        # the same (point, expert) rows: compare as sorted multisets of 7-tuples
+        ka = torch.cat([pt_a.long()[:, None].double(), rows_a.double()], 1).cpu()
+        kb = torch.cat([nat[:, None].double(), rows_b.double()], 1).cpu()
+        assert torch.equal(torch.unique(ka, dim=0), torch.unique(kb, dim=0)), "positions / directions are bit-identical"
     m, st, cfg, mins, aabb = _big_scene(8, 2, 4, 14)
     m.eval()
     rays = O.aerial_rays(2000, aabb, seed=4).to(DEV)
