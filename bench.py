@@ -51,7 +51,7 @@ def peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
         d = json.load(open(p))
-        return {"hbm": d["hbm_gbs"], "tensor": d["bf16_tflops_sustained"], "src": "MEASURED_PEAKS.json (sustained bf16)"}
+        return {"hbm": d["hbm_gbs"], "tensor": d["bf16_tflops_sustained"], "src": "MEASURED_PEAKS.json (hbm_gbs copy bandwidth; bf16_tflops_sustained for tensor-bound kernels)"}
     return {"hbm": 6650.0, "tensor": 1400.0, "src": "fallback (B200_PROFILING.md)"}
 
 
