@@ -79,12 +79,11 @@ def render_rays_stratified(model, rays: Tensor, ray_samples: int, params=None, a
     # as in the reference (:323-326): with active_module the expert is called directly and `params`
     # holds EXPERT-level keys (meta_core.extract_module_params); otherwise container-level keys
     model_eff = model.submodules[active_module] if active_module is not None else model
-    # A block of image rows (render_image), no autograd, several experts: number the points sample-major, so that the lanes
-    # of the routing / gather / MLP kernels are the same sample of adjacent pixels and share grid cells (measured, 1080p x 8
-    # experts: frame 53.9 -> 47 ms); the compositor reads the (S,N,4) result in place.  With one expert the identity slot list
-    # (no pack at all) is faster; sharded experts keep ray-major rows.
-    sample_major = (coherent and not torch.is_grad_enabled() and active_module is None and len(getattr(model, "submodules", ())) > 1
-                    and getattr(model, "_ep", None) is None)
+    # A block of image rows (render_image), no autograd: number the points sample-major, so that the lanes of the routing /
+    # gather / MLP kernels are the same sample of adjacent pixels and share grid cells (measured, 1080p x 8 experts: frame
+    # 53.9 -> 48 ms); the compositor reads the (S,N,4) result in place.  Every kernel is order-agnostic (a single expert's
+    # identity slot list simply becomes sample-major too); sharded experts keep ray-major rows.
+    sample_major = coherent and not torch.is_grad_enabled() and getattr(model, "_ep", None) is None
     if sample_major:
         pts = pts.sample_major()
     rgb_sigma = model_eff.evaluate(pts, params=params)

@@ -201,14 +201,19 @@ def test_sample_major_point_ids_give_the_same_partition_and_frame():
         ka = torch.cat([pt_a.long()[:, None].double(), rows_a.double()], 1).cpu()
         kb = torch.cat([nat[:, None].double(), rows_b.double()], 1).cpu()
         assert torch.equal(torch.unique(ka, dim=0), torch.unique(kb, dim=0)), "positions / directions are bit-identical"
-    m, st, cfg, mins, aabb = _big_scene(8, 2, 4, 14)
-    m.eval()
-    rays = O.aerial_rays(2000, aabb, seed=4).to(DEV)
-    with torch.no_grad():
-        ref = render_rays(m, rays, ray_samples=48)
-        got = render_rays(m, rays, ray_samples=48, coherent=True)
-    for x, y, name in zip(got, ref, ("rgb", "depth", "weights", "acc")):
-        close(x, y, 1e-6, f"coherent render {name}")
+    for K, gy, gz in ((8, 2, 4), (1, 1, 1)):  # routed slot list / a single expert's identity slot list
+        m, st, cfg, mins, aabb = _big_scene(K, gy, gz, 14)
+        m.eval()
+        rays = O.aerial_rays(2000, aabb, seed=4).to(DEV)
+        for mode, tol in (("fp32", 1e-6), ("f16tc", 1e-6)):  # the same arithmetic on the same points, in another order
+            with ops.mlp_math(mode), torch.no_grad():
+                ref = render_rays(m, rays, ray_samples=48)
+                got = render_rays(m, rays, ray_samples=48, coherent=True)
+                one = render_rays(m, rays, ray_samples=48, coherent=True, active_module=0) if K == 1 else None
+            for x, y, name in zip(got, ref, ("rgb", "depth", "weights", "acc")):
+                close(x, y, tol, f"coherent render {name} (K={K}, {mode})")
+            if one is not None:
+                close(one[0], ref[0], tol, "coherent render through active_module")
 
 
 def test_a2a_pack_and_combine_match_the_reference_loop():
