@@ -109,8 +109,12 @@ class MetaContainer(MetaModule):
         if K == 1 and self.boundary_margin > 1.0:
             # a single centroid always gets weight 1: skip the pack, keep the fused launch
             return self.submodules[0].evaluate(pts, self._sub_params(params, 0))
+        # a renderer that verifies the capacity once per frame (render_image) lets the pack skip its host read
+        defer = getattr(pts, "route_checks", None) is not None and not torch.is_grad_enabled()
         with torch.no_grad():
-            pairs = ops.route_pack(pts, self.centroids_host(), K, self.boundary_margin, self.cluster_2d)
+            pairs = ops.route_pack(pts, self.centroids_host(), K, self.boundary_margin, self.cluster_2d, sync=not defer)
+        if defer:
+            pts.route_checks.append((pairs.seg, pairs.M))
         tables = [sub.xyz_encoder.hash_table for sub in self.submodules]
         mlp: List[torch.Tensor] = []
         for k, sub in enumerate(self.submodules):

@@ -63,7 +63,7 @@ def stratified_t_vals(near: Tensor, far: Tensor, ray_samples: int, randomized: b
 
 def render_rays_stratified(model, rays: Tensor, ray_samples: int, params=None, active_module: Optional[int] = None,
                            bg_color_default: str = "white", chunk: int = 1_000_000, sigma_scale=1.0, u: Optional[Tensor] = None,
-                           coherent: bool = False, **kwargs):
+                           coherent: bool = False, route_checks: Optional[list] = None, **kwargs):
     """Stratified renderer: rgb (N,3), depth (N,), weights (N,S), acc (N,).
 
     ``chunk`` is accepted for signature compatibility; nothing is staged per point, so there is
@@ -76,6 +76,7 @@ def render_rays_stratified(model, rays: Tensor, ray_samples: int, params=None, a
             u = torch.rand(N, S, device=rays.device, dtype=torch.float32)
         t_vals = ops.stratified_t(rays, S, u if model.training else None)
     pts = ops.PointSet(rays=rays, t=t_vals)
+    pts.route_checks = route_checks  # render_image verifies the routing capacity once per frame instead of once per block
     # as in the reference (:323-326): with active_module the expert is called directly and `params`
     # holds EXPERT-level keys (meta_core.extract_module_params); otherwise container-level keys
     model_eff = model.submodules[active_module] if active_module is not None else model
@@ -119,13 +120,19 @@ def render_image(model, *, H: int, W: int, fx: float, fy: float, cx: float, cy: 
     rgb = torch.empty(n_rows * W, 3, device=device)
     depth = torch.empty(n_rows * W, device=device)
     acc = torch.empty(n_rows * W, device=device)
-    for r0 in range(R0, R1, rows_per_chunk):
-        rows = min(rows_per_chunk, R1 - r0)
-        rays = ops.raygen(H, W, fx, fy, cx, cy, center_pixels, c2w, aabb, device, row0=r0, rows=rows)
-        c, d, _, a = render_rays(model, rays, ray_samples=ray_samples, params=params, active_module=active_module,
-                                 bg_color_default=bg_color_default, chunk=chunk_points, coherent=True)
-        sl = slice((r0 - R0) * W, (r0 - R0 + rows) * W)
-        rgb[sl], depth[sl], acc[sl] = c, d, a
+    # First pass: no host read inside the frame (the routing of every block keeps its speculative capacity and the whole
+    # frame is verified with one read at the end); in the rare overflow (a very wide boundary margin) the frame is redone
+    # with the per-block read that sizes the lists exactly.
+    for checks in ([], None):
+        for r0 in range(R0, R1, rows_per_chunk):
+            rows = min(rows_per_chunk, R1 - r0)
+            rays = ops.raygen(H, W, fx, fy, cx, cy, center_pixels, c2w, aabb, device, row0=r0, rows=rows)
+            c, d, _, a = render_rays(model, rays, ray_samples=ray_samples, params=params, active_module=active_module,
+                                     bg_color_default=bg_color_default, chunk=chunk_points, coherent=True, route_checks=checks)
+            sl = slice((r0 - R0) * W, (r0 - R0 + rows) * W)
+            rgb[sl], depth[sl], acc[sl] = c, d, a
+        if checks is None or ops.route_capacity_ok(checks):
+            break
     if row_range is not None:
         return rgb.clamp_(0, 1), depth, acc
     return rgb.view(H, W, 3).clamp_(0, 1), depth.view(-1), acc.view(-1)

@@ -154,6 +154,8 @@ class PointSet:
         # coherent: consecutive rays are neighbouring pixels of an image block (a renderer's hint, see sample_major())
         self.coherent = bool(coherent) and x6 is None
         self.tT = None
+        # a renderer's list of (seg, capacity) to verify later: lets the container route without its host read (no_grad only)
+        self.route_checks: Optional[list] = None
         if x6 is not None:
             self.x6 = _f32(x6, "x6")
             self.rays = self.t = None
@@ -174,6 +176,7 @@ class PointSet:
             raise ValueError("sample_major() needs implicit points (rays, t)")
         q = PointSet(rays=self.rays, t=self.t)
         q.tT = self.t.t().contiguous()
+        q.route_checks = self.route_checks
         return q
 
     def to_ray_major(self, out: Tensor) -> Tensor:
@@ -367,6 +370,14 @@ def route_pack(pts: PointSet, centroids_host: Sequence[float], K: int, margin: f
             cap = seg_host[K]
     M = seg_host[K]
     return PairList(M, point[:M], weight[:M], seg, seg_host)
+
+
+def route_capacity_ok(checks: Sequence[Tuple[Tensor, int]]) -> bool:
+    """One device->host read for a whole frame: did every deferred route_pack(sync=False) fit its speculative capacity?"""
+    if not checks:
+        return True
+    used = torch.stack([seg[-1] for seg, _ in checks]).tolist()
+    return all(u <= cap for u, (_, cap) in zip(used, checks))
 
 
 # --------------------------------------------------------------------------
