@@ -55,7 +55,7 @@ __device__ __forceinline__ int find_expert(const int* s_seg, int E, int64_t m) {
 __global__ void __launch_bounds__(256) k_ngp_hash_fwd(PointSrc src, const int32_t* __restrict__ pair_point, const int32_t* __restrict__ seg,
                                                       int64_t M_ident, ExpertTable tab, GridParams g, float* __restrict__ enc, int64_t ld) {
   __shared__ int s_seg[ACN_MAX_EXPERTS + 1];
-  if (threadIdx.x <= tab.E) s_seg[threadIdx.x] = seg ? seg[threadIdx.x] : (threadIdx.x == 0 ? 0 : (int)M_ident);
+  if (threadIdx.x <= tab.E) s_seg[threadIdx.x] = seg ? min(seg[threadIdx.x], (int)M_ident) : (threadIdx.x == 0 ? 0 : (int)M_ident);  // never past the capacity
   __syncthreads();
   int64_t M = seg ? s_seg[tab.E] : M_ident;
   int l = blockIdx.y;
@@ -94,7 +94,7 @@ __global__ void __launch_bounds__(256) k_ngp_hash_bwd(PointSrc src, const int32_
                                                       GradTables gts, int64_t m_lo, int64_t m_hi, AggSteps agg) {
   __shared__ int s_seg[ACN_MAX_EXPERTS + 1];
   __shared__ float2* s_gt[ACN_MAX_EXPERTS];
-  if (threadIdx.x <= tab.E) s_seg[threadIdx.x] = seg ? seg[threadIdx.x] : (threadIdx.x == 0 ? 0 : (int)M_ident);
+  if (threadIdx.x <= tab.E) s_seg[threadIdx.x] = seg ? min(seg[threadIdx.x], (int)M_ident) : (threadIdx.x == 0 ? 0 : (int)M_ident);  // never past the capacity
 #pragma unroll
   for (int k = 0; k < ACN_MAX_EXPERTS; ++k)  // static parameter offsets: a runtime index would put the block in local memory
     if (threadIdx.x == 32 + k) s_gt[k] = reinterpret_cast<float2*>(gts.t[k]);
@@ -232,7 +232,7 @@ __global__ void __launch_bounds__(NT) k_ngp_mlp_fwd(PointSrc src, const int32_t*
   float* sw = smem;
   float* act = smem + W_FLOATS;
   int* s_seg = reinterpret_cast<int*>(act + ACT_FLOATS);
-  if (threadIdx.x <= tab.E) s_seg[threadIdx.x] = seg ? seg[threadIdx.x] : (threadIdx.x == 0 ? 0 : (int)M_ident);
+  if (threadIdx.x <= tab.E) s_seg[threadIdx.x] = seg ? min(seg[threadIdx.x], (int)M_ident) : (threadIdx.x == 0 ? 0 : (int)M_ident);  // never past the capacity
   __syncthreads();
   int64_t M = seg ? s_seg[tab.E] : M_ident;
   TileIter it = my_tiles((M + NT - 1) / NT);
@@ -347,7 +347,7 @@ __global__ void __launch_bounds__(NT) k_ngp_mlp_bwd(const int32_t* __restrict__ 
   float* sw = smem;
   float* act = smem + W_FLOATS;
   int* s_seg = reinterpret_cast<int*>(act + ACT_FLOATS);
-  if (threadIdx.x <= tab.E) s_seg[threadIdx.x] = seg ? seg[threadIdx.x] : (threadIdx.x == 0 ? 0 : (int)M_ident);
+  if (threadIdx.x <= tab.E) s_seg[threadIdx.x] = seg ? min(seg[threadIdx.x], (int)M_ident) : (threadIdx.x == 0 ? 0 : (int)M_ident);  // never past the capacity
   __syncthreads();
   int64_t M = seg ? s_seg[tab.E] : M_ident;
   int64_t Mld = round_ld(M);

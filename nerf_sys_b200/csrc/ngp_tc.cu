@@ -284,7 +284,8 @@ __global__ void __launch_bounds__(FWD_THREADS, 1)
   __shared__ CtaPart s_part;
   const int tid = threadIdx.x, q = tid >> 7;
   const uint32_t r = tid & 127;
-  if (tid <= tab.E) s_seg[tid] = seg ? seg[tid] : (tid == 0 ? 0 : round_up128(M_ident));
+  // a pair list truncated at its speculative capacity (route_pack without the host read) is consumed up to its last whole tile
+  if (tid <= tab.E) s_seg[tid] = seg ? min(seg[tid], (int)(M_ident / ROWS) * (int)ROWS) : (tid == 0 ? 0 : round_up128(M_ident));
   __syncthreads();
   const int64_t M = seg ? (int64_t)s_seg[tab.E] : M_ident;
   if (tid == 0) {

@@ -449,6 +449,34 @@ def _big_scene(K, gy, gz, log2_T, seed=0, table_std=0.1):
     return m.to(DEV), st, cfg, [b[0] for b in boxes], aabb
 
 
+def test_render_image_frame_equals_block_renders_and_survives_a_routing_overflow():
+    """render_image routes every block without a host read and verifies the capacity once per frame; with a margin wide
+    enough to overflow the speculative capacity (every sample a member of several experts) it must redo the frame with
+    exact sizes and still return the same pixels as block-by-block rendering in ray-major order."""
+    from nerf_sys_b200 import ops
+    from nerf_sys_b200.nerfs.ray_rendering import render_image, render_rays
+    from nerf_sys_b200.nerfs.scene_box import SceneBox
+    m, st, cfg, mins, aabb = _big_scene(8, 2, 4, 14)
+    m.eval()
+    H, W = 54, 96
+    c2w = O.ring_pose(3, 20, radius=0.9)
+    sb = SceneBox(aabb.to(DEV))
+    for margin in (1.05, 2.5):
+        m.boundary_margin = margin
+        rgb, depth, acc = render_image(m, H=H, W=W, fx=80.0, fy=80.0, cx=W / 2, cy=H / 2, c2w=c2w, scene_box=sb, ray_samples=32,
+                                       rows_per_chunk=20)
+        rays = ops.raygen(H, W, 80.0, 80.0, W / 2, H / 2, True, c2w, aabb.to(DEV), DEV)
+        with torch.no_grad():
+            c, d, _, a = render_rays(m, rays, ray_samples=32)
+        if margin > 2:  # the scenario really overflows the speculative capacity
+            t = ops.stratified_t(rays, 32, None)
+            pairs = ops.route_pack(ops.PointSet(rays=rays, t=t), m.centroids_host(), 8, margin, True)
+            assert pairs.M > 1.25 * rays.shape[0] * 32 + 8 * 128
+        close(rgb.view(-1, 3), c.clamp(0, 1), 2e-6, f"frame rgb, margin {margin}")
+        close(depth, d, 2e-6, "frame depth")
+        close(acc, a, 2e-6, "frame acc")
+
+
 def test_config2_single_expert_full_table_vs_oracle():
     """C2 shape (K=1, T=2^20, S=96) on 2048 rays: forward and every gradient vs the CPU oracle."""
     from nerf_sys_b200 import ops
