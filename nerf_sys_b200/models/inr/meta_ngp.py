@@ -85,17 +85,20 @@ class MetaNGP(MetaModule):
 
     def _apply(self, fn, *a, **k):
         self._box_host = None
+        object.__setattr__(self, "_mlp_cache", None)
         return super()._apply(fn, *a, **k)
 
     def mlp_tensors(self, params: Optional[Dict[str, Tensor]] = None) -> List[Tensor]:
         """The 14 MLP tensors in ABI order, each taken from ``params`` when present (fast weights)."""
-        own = dict(self.meta_named_parameters())
-        out = []
-        for key in ops.NGP_LAYER_KEYS:
-            for leaf in ("weight", "bias"):
-                n = f"{key}.{leaf}"
-                out.append(params[n] if (params is not None and n in params) else own[n])
-        return out
+        own = getattr(self, "_mlp_cache", None)
+        first = f"{ops.NGP_LAYER_KEYS[0]}.weight"
+        if own is None or own[0][1] is not self.get_parameter(first):  # walking the module tree costs ~0.1 ms per expert per call
+            named = dict(self.meta_named_parameters())
+            own = [(f"{key}.{leaf}", named[f"{key}.{leaf}"]) for key in ops.NGP_LAYER_KEYS for leaf in ("weight", "bias")]
+            object.__setattr__(self, "_mlp_cache", own)
+        if params is None:
+            return [p for _, p in own]
+        return [params[n] if n in params else p for n, p in own]
 
     def expert_spec(self) -> ops.ExpertSpec:
         mn, ext = self.box_host()

@@ -104,7 +104,27 @@ class _timed:
 
 
 def _stream() -> C.c_void_p:
-    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    """The current stream of the current device (raw handle; the Python Stream object costs ~10 us per call)."""
+    return C.c_void_p(torch._C._cuda_getCurrentRawStream(torch._C._cuda_getDevice()))
+
+
+class _NoGuard:
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        return False
+
+
+_no_guard = _NoGuard()
+
+
+def _on(dev):
+    """Device guard for a launch: nothing when `dev` is already current (the one-process-per-GPU case)."""
+    idx = dev.index if isinstance(dev, torch.device) else int(dev)
+    if idx is None or idx == torch._C._cuda_getDevice():
+        return _no_guard
+    return torch.cuda.device(idx)
 
 
 def _ptr(t: Optional[Tensor]):
@@ -216,7 +236,7 @@ class PairList:
 # --------------------------------------------------------------------------
 def ray_directions(H: int, W: int, fx: float, fy: float, cx: float, cy: float, center_pixels: bool, device) -> Tensor:
     out = torch.empty(H, W, 3, device=device, dtype=torch.float32)
-    with torch.cuda.device(out.device):
+    with _on(out.device):
         check(lib().acn_ray_directions(H, W, fx, fy, cx, cy, int(bool(center_pixels)), _ptr(out), _stream()), "acn_ray_directions")
     _count(1)
     return out
@@ -237,7 +257,7 @@ def get_rays(dirs: Tensor, c2w: Tensor, aabb: Optional[Tensor], near: Optional[f
              max_bound: float = 1e10, invalid_value: float = 1e10) -> Tensor:
     d = _f32(dirs, "directions").reshape(-1, 3)
     out = torch.empty(d.shape[0], 8, device=d.device, dtype=torch.float32)
-    with torch.cuda.device(d.device):
+    with _on(d.device):
         check(lib().acn_get_rays(_ptr(d), d.shape[0], _c2w_host(c2w), _aabb_host(aabb), float(near or 0.0), float(far or 0.0),
                                  float(max_bound), float(invalid_value), _ptr(out), _stream()), "acn_get_rays")
     _count(1)
@@ -248,7 +268,7 @@ def raygen(H: int, W: int, fx, fy, cx, cy, center_pixels: bool, c2w: Tensor, aab
            row0: int = 0, rows: Optional[int] = None) -> Tensor:
     rows = H - row0 if rows is None else rows
     out = torch.empty(rows * W, 8, device=device, dtype=torch.float32)
-    with torch.cuda.device(out.device), _timed("raygen"):
+    with _on(out.device), _timed("raygen"):
         check(lib().acn_raygen(H, W, row0, rows, fx, fy, cx, cy, int(bool(center_pixels)), _c2w_host(c2w), _aabb_host(aabb),
                                float(near), float(far), _ptr(out), _stream()), "acn_raygen")
     _count(1)
@@ -259,7 +279,7 @@ def ray_aabb(o: Tensor, d: Tensor, aabb: Tensor, max_bound: float = 1e10, invali
     o, d = _f32(o, "origins"), _f32(d, "directions")
     n = o.shape[0]
     tn, tf = torch.empty(n, device=o.device), torch.empty(n, device=o.device)
-    with torch.cuda.device(o.device):
+    with _on(o.device):
         check(lib().acn_ray_aabb(_ptr(o), _ptr(d), n, _aabb_host(aabb), float(max_bound), float(invalid_value), _ptr(tn), _ptr(tf),
                                  _stream()), "acn_ray_aabb")
     _count(1)
@@ -270,7 +290,7 @@ def clamp_near_far(rays: Tensor, override, eps: float = 1e-6, invalid_value: flo
     r = _f32(rays, "rays")
     n = r.shape[0]
     valid = torch.empty(n, device=r.device, dtype=torch.uint8)
-    with torch.cuda.device(r.device):
+    with _on(r.device):
         if override is None:
             check(lib().acn_clamp_near_far(_ptr(r), n, 1, 0, 0.0, 0, 0.0, float(eps), float(invalid_value), None, _ptr(valid),
                                            _stream()), "acn_clamp_near_far")
@@ -304,7 +324,7 @@ def stratified_t(rays: Tensor, S: int, u: Optional[Tensor]) -> Tensor:
         u = _f32(u, "u")
         if tuple(u.shape) != (N, S):
             raise ValueError(f"u must be ({N},{S}), got {tuple(u.shape)}")
-    with torch.cuda.device(r.device), _timed("stratified_t"):
+    with _on(r.device), _timed("stratified_t"):
         check(lib().acn_stratified_t(_ptr(r), N, S, _ptr(_tau(S, r.device)), _ptr(u), _ptr(t), _stream()), "acn_stratified_t")
     _count(1)
     return t
@@ -314,7 +334,7 @@ def sample_points(rays: Tensor, t: Tensor) -> Tensor:
     r, tt = _f32(rays, "rays"), _f32(t, "t")
     N, S = tt.shape
     x6 = torch.empty(N * S, 6, device=r.device, dtype=torch.float32)
-    with torch.cuda.device(r.device):
+    with _on(r.device):
         check(lib().acn_sample_points(_ptr(r), _ptr(tt), N, S, _ptr(x6), _stream()), "acn_sample_points")
     _count(1)
     return x6
@@ -328,7 +348,7 @@ def routing(pts: PointSet, centroids_host: Sequence[float], K: int, margin: floa
         raise ValueError(f"at most {ACN_MAX_EXPERTS} experts per routing call (got {K})")
     ch = host_floats(centroids_host)
     cp = pts.c()
-    with torch.cuda.device(pts.device):
+    with _on(pts.device):
         if margin > 1.0:
             w = torch.empty(pts.P, K, device=pts.device, dtype=torch.float32)
             check(lib().acn_routing(C.byref(cp), ch, K, float(margin), int(cluster_2d), _ptr(w), None, _stream()), "acn_routing")
@@ -351,7 +371,7 @@ def route_pack(pts: PointSet, centroids_host: Sequence[float], K: int, margin: f
     ch = host_floats(centroids_host)
     cp = pts.c()
     dev = pts.device
-    with torch.cuda.device(dev):
+    with _on(dev):
         cap = int(L.acn_route_pack_capacity(pts.P, K))
         ws = torch.empty(int(L.acn_route_pack_ws_bytes(pts.P, K)) // 4 + 1, device=dev, dtype=torch.int32)
         seg = torch.empty(K + 1, device=dev, dtype=torch.int32)
@@ -397,7 +417,7 @@ def a2a_pack(pts: PointSet, pairs: PairList, K: int):
     counts = torch.empty(K + 1, device=dev, dtype=torch.int32)
     offs = torch.empty(K + 1, device=dev, dtype=torch.int32)
     cp, cq = pts.c(), pairs.c()
-    with torch.cuda.device(dev), _timed("a2a_pack"):
+    with _on(dev), _timed("a2a_pack"):
         check(lib().acn_a2a_pack(C.byref(cp), C.byref(cq), K, _ptr(rows), _ptr(point), _ptr(weight), _ptr(counts), _ptr(offs),
                                  _stream()), "acn_a2a_pack")
     _count(2)
@@ -412,7 +432,7 @@ def a2a_count(pairs: PairList, K: int) -> Tuple[Tensor, Tensor]:
     counts = torch.empty(K + 1, device=dev, dtype=torch.int32)
     offs = torch.empty(K + 1, device=dev, dtype=torch.int32)
     cq = pairs.c()
-    with torch.cuda.device(dev):
+    with _on(dev):
         check(lib().acn_a2a_count(C.byref(cq), K, _ptr(counts), _ptr(offs), _stream()), "acn_a2a_count")
     _count(1)
     return counts, offs
@@ -432,7 +452,7 @@ def a2a_push_rows(pts: PointSet, pairs: PairList, K: int, offs: Tensor, route: A
     point = torch.empty(M, device=dev, dtype=torch.int32)
     weight = torch.empty(M, device=dev, dtype=torch.float32)
     cp, cq = pts.c(), pairs.c()
-    with torch.cuda.device(dev), _timed("a2a_push_rows"):
+    with _on(dev), _timed("a2a_push_rows"):
         check(lib().acn_a2a_push_rows(C.byref(cp), C.byref(cq), K, _ptr(offs), C.byref(route), _ptr(point), _ptr(weight), _stream()),
               "acn_a2a_push_rows")
     _count(1)
@@ -442,7 +462,7 @@ def a2a_push_rows(pts: PointSet, pairs: PairList, K: int, offs: Tensor, route: A
 def a2a_pull_combine(route: AcnA2aRoute, point: Tensor, weight: Tensor, offs: Tensor, K: int, P: int) -> Tensor:
     dev = point.device
     out = torch.zeros(P, 4, device=dev, dtype=torch.float32)
-    with torch.cuda.device(dev), _timed("a2a_pull_combine"):
+    with _on(dev), _timed("a2a_pull_combine"):
         check(lib().acn_a2a_pull_combine(C.byref(route), _ptr(point), _ptr(weight), _ptr(offs), K, point.numel(), _ptr(out), _stream()),
               "acn_a2a_pull_combine")
     _count(1)
@@ -451,7 +471,7 @@ def a2a_pull_combine(route: AcnA2aRoute, point: Tensor, weight: Tensor, offs: Te
 
 def a2a_push_grad(d_out: Tensor, point: Tensor, weight: Tensor, offs: Tensor, K: int, route: AcnA2aRoute) -> None:
     g = _f32(d_out, "d_out")
-    with torch.cuda.device(g.device), _timed("a2a_push_grad"):
+    with _on(g.device), _timed("a2a_push_grad"):
         check(lib().acn_a2a_push_grad(_ptr(g), _ptr(point), _ptr(weight), _ptr(offs), K, point.numel(), C.byref(route), _stream()),
               "acn_a2a_push_grad")
     _count(1)
@@ -468,7 +488,7 @@ class A2aCombineFn(torch.autograd.Function):
             raise ValueError("a2a_combine: y must be (M,4) with M point ids and weights")
         pt, wt = _need(point, "point", torch.int32), _f32(weight, "weight")
         out = torch.zeros(P, 4, device=yy.device, dtype=torch.float32)
-        with torch.cuda.device(yy.device), _timed("a2a_combine"):
+        with _on(yy.device), _timed("a2a_combine"):
             check(lib().acn_a2a_combine(_ptr(yy), _ptr(pt), _ptr(wt), M, _ptr(out), _stream()), "acn_a2a_combine")
         _count(1)
         ctx.save_for_backward(pt, wt)
@@ -479,7 +499,7 @@ class A2aCombineFn(torch.autograd.Function):
         pt, wt = ctx.saved_tensors
         g = _f32(d_out, "d_out")
         d_y = torch.empty(pt.numel(), 4, device=g.device, dtype=torch.float32)
-        with torch.cuda.device(g.device), _timed("a2a_combine_bwd"):
+        with _on(g.device), _timed("a2a_combine_bwd"):
             check(lib().acn_a2a_combine_bwd(_ptr(g), _ptr(pt), _ptr(wt), pt.numel(), _ptr(d_y), _stream()), "acn_a2a_combine_bwd")
         _count(1)
         return d_y, None, None, None
@@ -495,7 +515,7 @@ def a2a_combine(y: Tensor, point: Tensor, weight: Tensor, P: int) -> Tensor:
 def hashgrid_indices(x01: Tensor, g: AcnGridDesc) -> Tensor:
     x = _need(x01, "x01")
     idx = torch.empty(x.shape[0], g.levels, 8, device=x.device, dtype=torch.int32)
-    with torch.cuda.device(x.device):
+    with _on(x.device):
         check(lib().acn_hashgrid_indices(_ptr(x), x.shape[0], C.byref(g), _ptr(idx), _stream()), "acn_hashgrid_indices")
     _count(1)
     return idx
@@ -509,7 +529,7 @@ class HashGridFn(torch.autograd.Function):
         x = _need(x01.detach().reshape(-1, 3), "x01")
         tb = _need(table.detach(), "hash_table")
         y = torch.empty(x.shape[0], g.levels * g.features, device=x.device, dtype=torch.float32)
-        with torch.cuda.device(x.device):
+        with _on(x.device):
             check(lib().acn_hashgrid_fwd(_ptr(x), x.shape[0], _ptr(tb), C.byref(g), _ptr(y), _stream()), "acn_hashgrid_fwd")
         _count(1)
         ctx.g, ctx.shape = g, table.shape
@@ -522,7 +542,7 @@ class HashGridFn(torch.autograd.Function):
         g = ctx.g
         dy = _f32(dy, "dy").reshape(x.shape[0], -1)
         grad = torch.zeros(ctx.shape, device=x.device, dtype=torch.float32)
-        with torch.cuda.device(x.device):
+        with _on(x.device):
             check(lib().acn_hashgrid_bwd(_ptr(x), x.shape[0], _ptr(dy), C.byref(g), _ptr(grad), _stream()), "acn_hashgrid_bwd")
         _count(1)
         return None, grad, None
@@ -531,7 +551,7 @@ class HashGridFn(torch.autograd.Function):
 def sh16(d: Tensor) -> Tensor:
     x = _f32(d, "d").reshape(-1, 3)
     out = torch.empty(x.shape[0], 16, device=x.device, dtype=torch.float32)
-    with torch.cuda.device(x.device):
+    with _on(x.device):
         check(lib().acn_sh16(_ptr(x), x.shape[0], _ptr(out), _stream()), "acn_sh16")
     _count(1)
     return out.reshape(*d.shape[:-1], 16)
@@ -541,7 +561,7 @@ def freq_encode(x: Tensor, n_freq: int, include_input: bool = True) -> Tensor:
     xx = _f32(x, "x").reshape(-1, 3)
     width = (3 if include_input else 0) + 6 * n_freq
     out = torch.empty(xx.shape[0], width, device=xx.device, dtype=torch.float32)
-    with torch.cuda.device(xx.device):
+    with _on(xx.device):
         check(lib().acn_freq_encode(_ptr(xx), xx.shape[0], int(n_freq), int(include_input), _ptr(out), _stream()), "acn_freq_encode")
     _count(1)
     return out.reshape(*x.shape[:-1], width)
@@ -605,7 +625,7 @@ class NgpEncodeFn(torch.autograd.Function):
         enc = torch.empty(32, ld, device=pts.device, dtype=torch.float32)
         ex = _expert_array(spec, tb, None)
         cp, cq = pts.c(), pairs.c()
-        with torch.cuda.device(pts.device), _timed("hash_fwd"):
+        with _on(pts.device), _timed("hash_fwd"):
             check(L.acn_ngp_encode_fwd(C.byref(cp), C.byref(cq), ex, spec.E, C.byref(spec.grid), _ptr(enc), _stream()),
                   "acn_ngp_encode_fwd")
         _count(1)
@@ -630,7 +650,7 @@ class NgpEncodeFn(torch.autograd.Function):
                 outs.append(None)
         ex = _expert_array(spec, tb, None)
         cp, cq = pts.c(), pairs.c()
-        with torch.cuda.device(pts.device), _timed("hash_bwd"):
+        with _on(pts.device), _timed("hash_bwd"):
             check(L.acn_ngp_encode_bwd(C.byref(cp), C.byref(cq), ex, spec.E, C.byref(spec.grid), _ptr(d_enc), grads, _stream()),
                   "acn_ngp_encode_bwd")
         _count(1)
@@ -661,7 +681,7 @@ class NgpMlpFn(torch.autograd.Function):
             save = torch.empty(int(L.acn_ngp_save_bytes(pairs.M)) // 4, device=dev, dtype=torch.float32)
         ex = _expert_array(spec, None, ws)
         cp, cq = pts.c(), pairs.c()
-        with torch.cuda.device(dev), _timed("mlp_fwd"):
+        with _on(dev), _timed("mlp_fwd"):
             if tc:
                 check(L.acn_ngp_mlp_fwd_tc(C.byref(cp), C.byref(cq), ex, spec.E, _ptr(enc_c), _ptr(out), _stream()), "acn_ngp_mlp_fwd_tc")
             else:
@@ -703,13 +723,13 @@ class NgpMlpFn(torch.autograd.Function):
         if ctx.tc:
             wsb = torch.empty(int(L.acn_ngp_bwd_tc_ws_bytes()) // 4, device=dev, dtype=torch.float32)
             cp = pts.c()
-            with torch.cuda.device(dev), _timed("mlp_bwd"):
+            with _on(dev), _timed("mlp_bwd"):
                 check(L.acn_ngp_mlp_bwd_tc(C.byref(cp), C.byref(cq), ex, spec.E, _ptr(enc), _ptr(d_out), grads, _ptr(d_enc), _ptr(wsb),
                                            _stream()), "acn_ngp_mlp_bwd_tc")
             _count(3)
         else:
             wsb = torch.empty(int(L.acn_ngp_bwd_ws_bytes(pairs.M, spec.E)) // 4, device=dev, dtype=torch.float32)
-            with torch.cuda.device(dev), _timed("mlp_bwd"):
+            with _on(dev), _timed("mlp_bwd"):
                 check(L.acn_ngp_mlp_bwd(C.byref(cq), ex, spec.E, _ptr(enc), _ptr(d_out), _ptr(ctx.save), grads, _ptr(d_enc), _ptr(wsb),
                                         _stream()), "acn_ngp_mlp_bwd")
             _count(1 + 14)
@@ -726,7 +746,7 @@ def tc_selftest(X: Tensor, Y: Tensor, G: Tensor, mixed: bool):
     D1 = torch.empty(128, 64, device=X.device)
     D2 = torch.empty(64, 64, device=X.device)
     D3 = torch.empty(128, 64, device=X.device)
-    with torch.cuda.device(X.device):
+    with _on(X.device):
         check(L.acn_tc_selftest(_ptr(X), _ptr(Y), _ptr(G), int(bool(mixed)), _ptr(D1), _ptr(D2), _ptr(D3), _stream()), "acn_tc_selftest")
     _count(1)
     return D1, D2, D3
@@ -775,7 +795,7 @@ class NgpExpertsTcFn(torch.autograd.Function):
         out = torch.empty(pts.P, 4, device=dev, dtype=torch.float32) if pairs.identity else torch.zeros(pts.P, 4, device=dev,
                                                                                                         dtype=torch.float32)
         cp, cq = pts.c(), pairs.c()
-        with torch.cuda.device(dev):
+        with _on(dev):
             with _timed("hash_fwd"):
                 check(L.acn_ngp_encode_fwd(C.byref(cp), C.byref(cq), _expert_array(spec, tb, None), E, C.byref(spec.grid), _ptr(enc), _stream()),
                       "acn_ngp_encode_fwd")
@@ -825,7 +845,7 @@ class NgpExpertsTcFn(torch.autograd.Function):
         d_enc = torch.empty_like(enc)
         ex = _expert_array(spec, tb, ws)
         cp, cq = pts.c(), pairs.c()
-        with torch.cuda.device(dev):
+        with _on(dev):
             if want_table and _bwd_chunks > 1:
                 wsb = torch.empty(int(L.acn_ngp_bwd_tc_pipelined_ws_bytes(_bwd_chunks)) // 4, device=dev, dtype=torch.float32)
                 side = _side_stream(dev)
@@ -871,7 +891,7 @@ class BgFn(torch.autograd.Function):
         need_grad = any(ctx.needs_input_grad)
         rgb = torch.empty(N, 3, device=dd.device, dtype=torch.float32)
         save = torch.empty(int(L.acn_bg_save_bytes(N)) // 4, device=dd.device, dtype=torch.float32) if need_grad else None
-        with torch.cuda.device(dd.device), _timed("bg_fwd"):
+        with _on(dd.device), _timed("bg_fwd"):
             check(L.acn_bg_forward(_ptr(dd), stride, N, _ptr(p[0]), _ptr(p[1]), _ptr(p[2]), _ptr(p[3]), _ptr(rgb), _ptr(save),
                                    _stream()), "acn_bg_forward")
         _count(1)
@@ -888,7 +908,7 @@ class BgFn(torch.autograd.Function):
         d_rgb = _f32(d_rgb, "d_rgb")
         g = [torch.empty_like(t) for t in (w0, b0, w1, b1)]
         ws = torch.empty(int(L.acn_bg_bwd_ws_bytes(ctx.N)) // 4, device=w0.device, dtype=torch.float32)
-        with torch.cuda.device(w0.device), _timed("bg_bwd"):
+        with _on(w0.device), _timed("bg_bwd"):
             check(L.acn_bg_backward(_ptr(d_rgb), ctx.N, _ptr(w0), _ptr(w1), _ptr(ctx.save), _ptr(g[0]), _ptr(g[1]), _ptr(g[2]),
                                     _ptr(g[3]), _ptr(ws), _stream()), "acn_bg_backward")
         _count(2)
@@ -922,7 +942,7 @@ class CompositeFn(torch.autograd.Function):
         dev = rs.device
         rgb, depth = torch.empty(N, 3, device=dev), torch.empty(N, device=dev)
         w, acc = torch.empty(N, S, device=dev), torch.empty(N, device=dev)
-        with torch.cuda.device(dev), _timed("composite_fwd"):
+        with _on(dev), _timed("composite_fwd"):
             check(lib().acn_composite_fwd(_ptr(rs), _ptr(tt), _ptr(b), N, S, float(sigma_scale), _ptr(rgb), _ptr(depth), _ptr(w),
                                           _ptr(acc), _stream()), "acn_composite_fwd")
         _count(1)
@@ -942,7 +962,7 @@ class CompositeFn(torch.autograd.Function):
         g_w = None if g_w is None else _f32(g_w, "g_weights")
         d_rs = torch.empty_like(rs)
         d_bg = torch.empty_like(b) if (b is not None and ctx.needs_input_grad[2]) else None
-        with torch.cuda.device(dev), _timed("composite_bwd"):
+        with _on(dev), _timed("composite_bwd"):
             check(lib().acn_composite_bwd(_ptr(rs), _ptr(tt), _ptr(b), N, S, ctx.scale, _ptr(g_rgb), _ptr(g_depth), _ptr(g_acc),
                                           _ptr(g_w), _ptr(d_rs), _ptr(d_bg), _stream()), "acn_composite_bwd")
         _count(1)
@@ -965,7 +985,7 @@ def composite_sample_major(rgb_sigma: Tensor, t: Tensor, bg: Optional[Tensor], s
     dev = rs.device
     rgb, depth = torch.empty(N, 3, device=dev), torch.empty(N, device=dev)
     w, acc = torch.empty(N, S, device=dev), torch.empty(N, device=dev)
-    with torch.cuda.device(dev), _timed("composite_fwd"):
+    with _on(dev), _timed("composite_fwd"):
         check(lib().acn_composite_fwd_strided(_ptr(rs), 1, N, _ptr(tt), _ptr(b), N, S, float(sigma_scale), _ptr(rgb), _ptr(depth), _ptr(w),
                                               _ptr(acc), _stream()), "acn_composite_fwd_strided")
     _count(1)
@@ -983,7 +1003,7 @@ class MseFn(torch.autograd.Function):
         loss = torch.empty(1, device=p.device)
         d_pred = torch.empty_like(p)
         ws = torch.empty(2048, device=p.device)
-        with torch.cuda.device(p.device), _timed("mse_loss"):
+        with _on(p.device), _timed("mse_loss"):
             check(lib().acn_mse_loss(_ptr(p), _ptr(g), N, int(space), _ptr(loss), _ptr(d_pred), _ptr(ws), _stream()), "acn_mse_loss")
         _count(2)
         ctx.save_for_backward(d_pred)
@@ -1004,7 +1024,7 @@ def adam_step(param: Tensor, grad: Tensor, exp_avg: Tensor, exp_avg_sq: Tensor, 
     for t, n in ((param, "param"), (grad, "grad"), (exp_avg, "exp_avg"), (exp_avg_sq, "exp_avg_sq")):
         if not (t.is_cuda and t.dtype == torch.float32 and t.is_contiguous()):
             raise RuntimeError(f"adam_step: {n} must be a contiguous CUDA fp32 tensor")
-    with torch.cuda.device(param.device), _timed("adam"):
+    with _on(param.device), _timed("adam"):
         check(lib().acn_adam_step(_ptr(param), _ptr(grad), _ptr(exp_avg), _ptr(exp_avg_sq), param.numel(), lr, beta1, beta2, eps,
                                   weight_decay, int(step), _ptr(grad_scale), _stream()), "acn_adam_step")
     _count(1)
@@ -1013,7 +1033,7 @@ def adam_step(param: Tensor, grad: Tensor, exp_avg: Tensor, exp_avg_sq: Tensor, 
 def sgd_axpy(w: Tensor, g: Tensor, lr: float) -> Tensor:
     ww, gg = _need(w.detach(), "w"), _need(g.detach(), "g")
     out = torch.empty_like(ww)
-    with torch.cuda.device(ww.device):
+    with _on(ww.device):
         check(lib().acn_sgd_axpy(_ptr(ww), _ptr(gg), float(lr), ww.numel(), _ptr(out), _stream()), "acn_sgd_axpy")
     _count(1)
     return out
@@ -1021,6 +1041,6 @@ def sgd_axpy(w: Tensor, g: Tensor, lr: float) -> Tensor:
 
 def sumsq_accum(x: Tensor, acc: Tensor):
     xx = _need(x.detach(), "x")
-    with torch.cuda.device(xx.device), _timed("sumsq"):
+    with _on(xx.device), _timed("sumsq"):
         check(lib().acn_sumsq_accum(_ptr(xx), xx.numel(), _ptr(acc), _stream()), "acn_sumsq_accum")
     _count(1)

@@ -104,15 +104,26 @@ class FusedAdam(torch.optim.Optimizer):
         stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
         b1, b2 = self.param_groups[0]["betas"]
         eps = float(self.param_groups[0]["eps"])
-        chunks = []
-        for c0 in range(0, len(descs), ACN_ADAM_MAX_TENSORS):
-            part = descs[c0:c0 + ACN_ADAM_MAX_TENSORS]
-            arr = (AcnAdamTensor * len(part))()
-            for i, (p, g, st, lr, wd) in enumerate(part):
-                arr[i].param, arr[i].grad = p.data_ptr(), g.data_ptr()
-                arr[i].exp_avg, arr[i].exp_avg_sq = st["exp_avg"].data_ptr(), st["exp_avg_sq"].data_ptr()
-                arr[i].n, arr[i].lr, arr[i].weight_decay, arr[i].step_index = p.numel(), lr, wd, self._index[id(p)]
-            chunks.append((arr, len(part)))
+        # descriptor arrays are rebuilt only when the set of live tensors (or their storage) changes; otherwise just the
+        # gradient pointers and learning rates are refreshed (eager steps are host-bound: ~64 tensors x 9 fields per step)
+        key = tuple((id(p), p.data_ptr(), st["exp_avg"].data_ptr()) for p, _, st, _, _ in descs)
+        if getattr(self, "_arr_key", None) != key:
+            chunks = []
+            for c0 in range(0, len(descs), ACN_ADAM_MAX_TENSORS):
+                part = descs[c0:c0 + ACN_ADAM_MAX_TENSORS]
+                arr = (AcnAdamTensor * len(part))()
+                for i, (p, g, st, lr, wd) in enumerate(part):
+                    arr[i].param = p.data_ptr()
+                    arr[i].exp_avg, arr[i].exp_avg_sq = st["exp_avg"].data_ptr(), st["exp_avg_sq"].data_ptr()
+                    arr[i].n, arr[i].weight_decay, arr[i].step_index = p.numel(), wd, self._index[id(p)]
+                chunks.append((arr, len(part)))
+            self._arr_key, self._arr_chunks = key, chunks
+        chunks = self._arr_chunks
+        for ci, (arr, n) in enumerate(chunks):
+            base = ci * ACN_ADAM_MAX_TENSORS
+            for i in range(n):
+                d = descs[base + i]
+                arr[i].grad, arr[i].lr, arr[i].weight_decay = d[1].data_ptr(), d[3], d[4]
         clip = self.max_grad_norm is not None
         with torch.cuda.device(dev):
             if clip:
