@@ -38,7 +38,8 @@ class FusedAdam(torch.optim.Optimizer):
         of runtime_adapt.py:265 is over the norm of ALL parameters, so the sum of squares of the sharded tensors is
         all-reduced over ``group`` and the replicated ones (identical on every rank after their gradient all-reduce)
         are counted once."""
-        self._shard = (group, {id(p) for p in shared_params})
+        world = dist.get_world_size(group) if (dist.is_available() and dist.is_initialized()) else 1
+        self._shard = (group, {id(p) for p in shared_params}, world)
         return self
 
     # ---- device-side bookkeeping -------------------------------------------------------------
@@ -132,7 +133,7 @@ class FusedAdam(torch.optim.Optimizer):
                     for arr, n in chunks:
                         check(L.acn_sumsq_multi(arr, n, self._acc.data_ptr(), stream), "acn_sumsq_multi")
                 ops._count(len(chunks) + 1)
-                if self._shard is not None and dist.is_initialized() and dist.get_world_size(self._shard[0]) > 1:
+                if self._shard is not None and self._shard[2] > 1:
                     sh = [d for d in descs if id(d[0]) in self._shard[1]]
                     rep = torch.zeros_like(self._acc)
                     if sh:

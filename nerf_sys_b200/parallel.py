@@ -55,9 +55,11 @@ def _world(group) -> Tuple[int, int]:
 # ---------------------------------------------------------------------------------------------
 # shared parameters
 # ---------------------------------------------------------------------------------------------
-def allreduce_shared_grads(params: Sequence[Tensor], group=None, average: bool = True) -> None:
-    """One flat all-reduce over the gradients of replicated parameters (the background head: 643 floats)."""
-    world, _ = _world(group)
+def allreduce_shared_grads(params: Sequence[Tensor], group=None, average: bool = True, world: Optional[int] = None) -> None:
+    """One flat all-reduce over the gradients of replicated parameters (the background head: 643 floats).
+    ``world``: the group size when the caller already knows it (the c10d queries cost tens of microseconds per step)."""
+    if world is None:
+        world, _ = _world(group)
     if world == 1:
         return
     gs = [p.grad for p in params if p.grad is not None]
@@ -84,20 +86,21 @@ class SharedGradReducer:
         self.group, self.average = group, average
         self._ready = 0
         self._launched = False
+        self._world = _world(group)[0]
         self._stream = torch.cuda.Stream(self.params[0].device) if self.params and self.params[0].is_cuda else None
         self._hooks = [p.register_post_accumulate_grad_hook(self._on_grad) for p in self.params]
 
     def _on_grad(self, _p) -> None:
         self._ready += 1
-        if self._ready < len(self.params) or _world(self.group)[0] == 1:
+        if self._ready < len(self.params) or self._world == 1:
             return
         self._launched = True
         if self._stream is None:
-            allreduce_shared_grads(self.params, self.group, self.average)
+            allreduce_shared_grads(self.params, self.group, self.average, self._world)
             return
         self._stream.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(self._stream):
-            allreduce_shared_grads(self.params, self.group, self.average)
+            allreduce_shared_grads(self.params, self.group, self.average, self._world)
 
     def wait(self) -> None:
         """Call between backward() and optimizer.step()."""
@@ -105,7 +108,7 @@ class SharedGradReducer:
             if self._stream is not None:
                 torch.cuda.current_stream().wait_stream(self._stream)
         else:  # some parameter got no gradient this step: reduce what there is, in line
-            allreduce_shared_grads(self.params, self.group, self.average)
+            allreduce_shared_grads(self.params, self.group, self.average, self._world)
         self._ready, self._launched = 0, False
 
     def remove(self) -> None:
