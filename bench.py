@@ -463,9 +463,11 @@ def main():
     barrier()
     e0.record()
     for i in range(K):
-        r = pool_h[(W + i) % nb].to(dev, non_blocking=True)
-        c = rgbs_h[(W + i) % nb].to(dev, non_blocking=True)
-        loss_h[i:i + 1].copy_(step(r, c).detach().reshape(1), non_blocking=True)
+        if use_graph:  # pinned host batch straight into the captured step's input buffers (one H2D copy per tensor)
+            l = gstep(pool_h[(W + i) % nb], rgbs_h[(W + i) % nb])
+        else:
+            l = step(pool_h[(W + i) % nb].to(dev, non_blocking=True), rgbs_h[(W + i) % nb].to(dev, non_blocking=True))
+        loss_h[i:i + 1].copy_(l.detach().reshape(1), non_blocking=True)
         evs[i].record()
         if i > 0:
             evs[i - 1].synchronize()
