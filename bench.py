@@ -287,6 +287,59 @@ def train_c3(device, rank, world, barrier, max_over_ranks, steps=10, warmup=3):
     return out
 
 
+def adapt_c4(device, steps=10, warmup=3):
+    """Config 4 (one GPU): incremental adaptation of the 8-expert container on a new aerial batch whose samples fall in experts
+    {2, 5} only (nadir rays over those two tiles); the other six experts get no gradient, so their parameters and Adam state are not
+    touched (asserted bit-unchanged) and the step costs two experts' worth of scatter and optimiser traffic."""
+    from nerf_sys_b200.nerfs.losses import compute_mse_loss
+    from nerf_sys_b200.optim import build_optimizer
+    model, aabb = build_c5(device)
+    model.train()
+    opt = build_optimizer(model, max_grad_norm=1.0)
+    cent = model.centroids.detach().cpu()
+    g = torch.Generator().manual_seed(77)
+    nb, batches = 4, []
+    for b in range(nb):
+        rays = torch.zeros(N_RAYS, 8)
+        for i, k in enumerate((2, 5)):
+            sl = slice(i * N_RAYS // 2, (i + 1) * N_RAYS // 2)
+            rays[sl, 0] = float(aabb[0, 0]) + 0.01
+            rays[sl, 1:3] = cent[k, 1:3] + (torch.rand(N_RAYS // 2, 2, generator=g) - 0.5) * 0.3
+            rays[sl, 3] = 1.0  # straight down: the YZ position (the routing key) never changes along the ray
+            rays[sl, 6], rays[sl, 7] = 0.0, float(aabb[1, 0] - aabb[0, 0]) - 0.02
+        batches.append((rays.to(device), torch.rand(N_RAYS, 3, generator=g).to(device)))
+    frozen = {n: p.detach().clone() for n, p in model.named_parameters() if n.startswith("submodules.") and int(n.split(".")[1]) not in (2, 5)}
+
+    def step(i):
+        opt.zero_grad(set_to_none=True)
+        loss = compute_mse_loss(P, model, {"rays": batches[i % nb][0], "rgbs": batches[i % nb][1]})
+        loss.backward()
+        opt.step()
+        return loss
+
+    for i in range(max(warmup, 3)):
+        step(i)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(steps):
+        loss = step(i)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    named = dict(model.named_parameters())
+    unchanged = all(torch.equal(v, named[n].detach()) for n, v in frozen.items())
+    no_state = all(len(opt.state.get(named[n], {})) == 0 for n in frozen)
+    assert unchanged and no_state, "experts outside {2,5} must stay bit-unchanged, without optimiser state"
+    out = {"value": N_RAYS * steps / (ms / 1e3), "unit": "rays/s", "ms_per_step": ms / steps, "loss": float(loss.item()),
+           "frozen_experts_bit_unchanged": bool(unchanged and no_state),
+           "config": f"config[3]: 8-expert container, {N_RAYS} nadir rays x {S_TRAIN} samples over the tiles of experts 2 and 5, fwd+bwd+clip+Adam; "
+                     "six experts receive no gradient and no optimiser step"}
+    del model, opt
+    torch.cuda.empty_cache()
+    return out
+
+
 class P:  # the argparse namespace fields compute_mse_loss reads (common/args.py)
     ray_samples, chunk_points, color_space = S_TRAIN, 4456448, "identity"
 
@@ -540,6 +593,7 @@ def main():
     c3 = None
     if not args.no_c3:
         c3 = train_c3(dev, rank, world, barrier, max_over_ranks)
+    c4 = adapt_c4(dev) if (world == 1 and not args.no_c3) else None
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -566,7 +620,7 @@ def main():
             "clocks": clk, "e2e": {"value": world * N_RAYS * K / (ms_e2e / 1e3), "unit": "rays/s", "h2d_bytes_per_step": bytes_in,
                                    "d2h_bytes_per_step": 4, "ms_per_step": ms_e2e / K,
                                    "note": "loss of step i-1 read on the host while step i runs; all K losses read inside the timed region"},
-            "gpu_launches": launches, "roofline": roofline, "kernels": kern, "render": render, "render_c5": c5, "train_c3": c3, "cpu_baseline": cpu,
+            "gpu_launches": launches, "roofline": roofline, "kernels": kern, "render": render, "render_c5": c5, "train_c3": c3, "adapt_c4": c4, "cpu_baseline": cpu,
             "final_loss": final_loss}))
     if world > 1:
         # Leave without tearing NCCL down: the captured graph still references the communicator's kernels and
