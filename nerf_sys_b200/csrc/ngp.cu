@@ -72,8 +72,9 @@ __global__ void __launch_bounds__(256) k_ngp_hash_fwd(PointSrc src, const int32_
                          to_unit(z, ex.box_min[2], ex.extent[2]), g.res[l], g.interp);
       v = level_encode(reinterpret_cast<const float2*>(ex.table), c, mask, base, g.interp);
     }
-    enc[(int64_t)(2 * l) * ld + m] = v.x;
-    enc[(int64_t)(2 * l + 1) * ld + m] = v.y;
+    // streaming stores: the encoding is read once by the next kernel and must not push the table slabs out of L2
+    __stcs(enc + (int64_t)(2 * l) * ld + m, v.x);
+    __stcs(enc + (int64_t)(2 * l + 1) * ld + m, v.y);
   }
 }
 
