@@ -587,13 +587,18 @@ def main():
                   "ms_per_frame": rms / nv}
         model.train()
 
-    c5 = None
-    if not args.no_render:
-        c5 = render_c5(dev, world, barrier, max_over_ranks)
-    c3 = None
-    if not args.no_c3:
-        c3 = train_c3(dev, rank, world, barrier, max_over_ranks)
-    c4 = adapt_c4(dev) if (world == 1 and not args.no_c3) else None
+    # secondary measurements: a failure here is recorded in its own field and must not cost the headline line (every rank runs
+    # the same code, so an exception is raised on all of them alike)
+    def guarded(fn, *a):
+        try:
+            return fn(*a)
+        except Exception as e:  # noqa: BLE001
+            torch.cuda.synchronize()
+            return {"error": f"{type(e).__name__}: {e}"[:300]}
+
+    c5 = guarded(render_c5, dev, world, barrier, max_over_ranks) if not args.no_render else None
+    c3 = guarded(train_c3, dev, rank, world, barrier, max_over_ranks) if not args.no_c3 else None
+    c4 = guarded(adapt_c4, dev) if (world == 1 and not args.no_c3) else None
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
