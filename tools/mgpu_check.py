@@ -66,6 +66,54 @@ for mode, path in (("fp32", "nccl"), ("f16tc", "nccl"), ("fp32", "p2p"), ("f16tc
         print(f"[{mode}] expert-parallel a2a ({path}), world {world}: out max-abs err {stats[0].item():.2e} (tol {tol}), "
               f"owner-gradient rel-L2 {stats[1].item():.2e} (tol {gtol}) -> {'ok' if good else 'MISMATCH'}", flush=True)
 
+# one expert-parallel optimisation step == the same step on one GPU over the concatenated batch: loss, the global clip
+# coefficient (sharded sum of squares all-reduced, replicated head counted once) and the owner's updated parameters
+from nerf_sys_b200.optim import FusedAdam, build_optimizer  # noqa: E402
+ops.set_mlp_math("fp32")
+N, S = 512, 32
+rays = O.aerial_rays(N, aabb, seed=70 + rank).to(dev)
+g = torch.Generator().manual_seed(17 + rank)
+u, gt = torch.rand(N, S, generator=g).to(dev), torch.rand(N, 3, generator=g).to(dev)
+all_rays, all_u, all_gt = [torch.empty(world * N, *x.shape[1:], device=dev) for x in (rays, u, gt)]
+for dst, src in ((all_rays, rays), (all_u, u), (all_gt, gt)):
+    dist.all_gather_into_tensor(dst, src.contiguous())
+ref_m = _big_scene(8, 2, 4, 14)[0].to(dev).train()
+ref_opt = build_optimizer(ref_m, max_grad_norm=0.05)  # small enough that the clip is active
+rgb, *_ = render_rays(ref_m, all_rays, ray_samples=S, u=all_u)
+ref_loss = ops.mse_loss(rgb, all_gt)
+ref_loss.backward()
+ref_opt.step()
+ep_m = _big_scene(8, 2, 4, 14)[0].to(dev).train()
+ep_m.set_expert_parallel(True, exchange=ex)
+groups, shared = PL.owned_param_groups(ep_m)
+lrs = {"encoding": 1e-2, "sigma": 2e-3, "color": 2e-3, "background": 1e-3}
+ep_opt = FusedAdam([{"params": gr["params"], "lr": lrs[n]} for n, gr in groups.items()], max_grad_norm=0.05).shard_grad_norm(None, shared)
+rgb, *_ = render_rays(ep_m, rays, ray_samples=S, u=u)
+loss = ops.mse_loss(rgb, gt)
+(loss / world).backward()
+PL.allreduce_shared_grads(shared, average=False, world=world)
+ep_opt.step()
+mean_loss = loss.detach().clone()
+dist.all_reduce(mean_loss)
+mean_loss /= world
+owner = PL.expert_owner(8, world)
+ref_p = dict(ref_m.named_parameters())
+perr = 0.0
+for n, p in ep_m.named_parameters():
+    mine = (n.startswith("submodules.") and owner[int(n.split(".")[1])] == rank) or n.startswith("bg_mlp")
+    if mine:
+        perr = max(perr, (p.detach() - ref_p[n].detach()).abs().max().item())
+stats = torch.tensor([abs(mean_loss.item() - ref_loss.item()), abs(ep_opt._coef.item() - ref_opt._coef.item()) / ref_opt._coef.item(), perr],
+                     device=dev)
+dist.all_reduce(stats, op=dist.ReduceOp.MAX)
+good = stats[0].item() <= 1e-6 and stats[1].item() <= 1e-4 and ref_opt._coef.item() < 0.999 and stats[2].item() <= 2e-4
+ok = ok and good
+if rank == 0:
+    print(f"expert-parallel optimisation step, world {world}: loss diff {stats[0].item():.1e}, clip coefficient {ep_opt._coef.item():.6f} vs "
+          f"{ref_opt._coef.item():.6f} (rel {stats[1].item():.1e}), owner parameters max-abs diff {stats[2].item():.1e} -> {'ok' if good else 'MISMATCH'}",
+          flush=True)
+ep_m.set_expert_parallel(False)
+
 # ray-sharded render
 ops.set_mlp_math("f16tc")
 m, st, cfg, mins, aabb = _big_scene(8, 2, 4, 14)
