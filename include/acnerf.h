@@ -275,6 +275,10 @@ int acn_composite_fwd(const float* rgb_sigma, const float* t, const float* bg, i
 int acn_composite_fwd_strided(const float* rgb_sigma, int64_t ray_stride, int64_t sample_stride, const float* t,
                               const float* bg, int64_t N, int S, float sigma_scale, float* rgb, float* depth,
                               float* weights, float* acc, void* stream);
+/* The same for a sample-major point set: rgb_sigma_T (S,N,4), t_T (S,N) -> rgb (N,3), depth (N), weights_T (S,N) or NULL, acc (N);
+ * one thread per ray, sequential transmittance product (the order torch.cumprod uses), fully coalesced rows. */
+int acn_composite_fwd_sm(const float* rgb_sigma_T, const float* t_T, const float* bg, int64_t N, int S, float sigma_scale,
+                         float* rgb, float* depth, float* weights_T, float* acc, void* stream);
 /* its backward: g_rgb (N,3), g_depth (N) or NULL, g_acc (N) or NULL, g_weights (N,S) or NULL
  * -> d_rgb_sigma (N,S,4), d_bg (N,3) or NULL */
 int acn_composite_bwd(const float* rgb_sigma, const float* t, const float* bg, int64_t N, int S,

@@ -107,6 +107,7 @@ SIGNATURES = {
     "acn_bg_bwd_ws_bytes": (i64, [i64]),
     "acn_bg_backward": (C.c_int, [vp, i64, vp, vp, vp, vp, vp, vp, vp, vp, vp]),
     "acn_composite_fwd": (C.c_int, [vp, vp, vp, i64, C.c_int, f32, vp, vp, vp, vp, vp]),
+    "acn_composite_fwd_sm": (C.c_int, [vp, vp, vp, i64, C.c_int, f32, vp, vp, vp, vp, vp]),
     "acn_composite_fwd_strided": (C.c_int, [vp, i64, i64, vp, vp, i64, C.c_int, f32, vp, vp, vp, vp, vp]),
     "acn_composite_bwd": (C.c_int, [vp, vp, vp, i64, C.c_int, f32, vp, vp, vp, vp, vp, vp, vp]),
     "acn_mse_loss": (C.c_int, [vp, vp, i64, C.c_int, vp, vp, vp, vp]),

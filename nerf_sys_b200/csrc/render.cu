@@ -117,6 +117,50 @@ __global__ void __launch_bounds__(256) k_composite_fwd(const float4* __restrict_
   }
 }
 
+// The same compositing for the (S,N) layouts of a sample-major point set (AcnPoints.t_T): one THREAD per ray walks its S samples
+// front to back, so a warp reads 32 adjacent rays of one sample - full 512-byte rows of rs, 128-byte rows of t - and the
+// transmittance is the sequential product the reference's cumprod forms.  No shuffles; 2 M rays of a frame fill the machine.
+__global__ void __launch_bounds__(256) k_composite_fwd_sm(const float4* __restrict__ rs, const float* __restrict__ tT, const float* __restrict__ bg,
+                                                          int64_t N, int S, float scale, float* __restrict__ rgb, float* __restrict__ depth,
+                                                          float* __restrict__ wT, float* __restrict__ acc) {
+  for (int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r < N; r += (int64_t)gridDim.x * blockDim.x) {
+    float T = 1.f, sr = 0.f, sg = 0.f, sb = 0.f, sd = 0.f, sa = 0.f;
+    float t_cur = __ldg(tT + r), t_next = __ldg(tT + N + r), d_prev = 0.f;
+    for (int s = 0; s < S; ++s) {
+      const float4 v = __ldg(rs + (int64_t)s * N + r);
+      const float d = (s < S - 1) ? __fsub_rn(t_next, t_cur) : d_prev;  // the last sample repeats the previous distance
+      float sig = fmaxf(v.w, 0.f);
+      if (scale != 1.0f) sig = sig * scale;
+      const float delta = fmaxf(d, 1e-4f);
+      const float e = expf(-(sig * delta));
+      const float alpha = fminf(fmaxf(__fsub_rn(1.0f, e), 0.f), ALPHA_MAX);
+      const float fac = __fadd_rn(__fsub_rn(1.0f, alpha), 1e-10f);
+      const float w = alpha * T;
+      T = T * fac;
+      if (wT) wT[(int64_t)s * N + r] = w;
+      sr += w * fminf(fmaxf(v.x, 0.f), 1.f);
+      sg += w * fminf(fmaxf(v.y, 0.f), 1.f);
+      sb += w * fminf(fmaxf(v.z, 0.f), 1.f);
+      sd += w * t_cur;
+      sa += w;
+      d_prev = d;
+      t_cur = t_next;
+      if (s + 2 < S) t_next = __ldg(tT + (int64_t)(s + 2) * N + r);
+    }
+    if (bg) {
+      const float k = 1.0f - sa;
+      sr += k * __ldg(bg + r * 3);
+      sg += k * __ldg(bg + r * 3 + 1);
+      sb += k * __ldg(bg + r * 3 + 2);
+    }
+    rgb[r * 3] = sr;
+    rgb[r * 3 + 1] = sg;
+    rgb[r * 3 + 2] = sb;
+    depth[r] = sd;
+    acc[r] = sa;
+  }
+}
+
 // CH = chunks of 32 samples held in registers (S <= 32*CH)
 template <int CH>
 __global__ void __launch_bounds__(256) k_composite_bwd(const float4* __restrict__ rs, const float* __restrict__ t, const float* __restrict__ bg,
@@ -419,6 +463,17 @@ int acn_composite_fwd_strided(const float* rgb_sigma, int64_t ray_stride, int64_
   int grid = persistent_grid((N + 7) / 8, 8);
   k_composite_fwd<<<grid, 256, 0, as_stream(stream)>>>(reinterpret_cast<const float4*>(rgb_sigma), ray_stride, sample_stride, t, bg, N, S,
                                                        sigma_scale, rgb, depth, weights, acc);
+  ACN_LAUNCH_CHECK();
+  return ACN_OK;
+}
+
+int acn_composite_fwd_sm(const float* rgb_sigma_T, const float* t_T, const float* bg, int64_t N, int S, float sigma_scale, float* rgb,
+                         float* depth, float* weights_T, float* acc, void* stream) {
+  ACN_REQUIRE(rgb_sigma_T && t_T && rgb && depth && acc && N >= 0, "acn_composite_fwd_sm: NULL argument");
+  ACN_REQUIRE(S >= 2, "acn_composite_fwd_sm: needs at least 2 samples per ray (got %d)", S);
+  if (N == 0) return ACN_OK;
+  k_composite_fwd_sm<<<persistent_grid((N + 255) / 256, 8), 256, 0, as_stream(stream)>>>(reinterpret_cast<const float4*>(rgb_sigma_T), t_T, bg, N, S,
+                                                                                        sigma_scale, rgb, depth, weights_T, acc);
   ACN_LAUNCH_CHECK();
   return ACN_OK;
 }

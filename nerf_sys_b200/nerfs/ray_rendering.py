@@ -91,7 +91,7 @@ def render_rays_stratified(model, rays: Tensor, ray_samples: int, params=None, a
     bg_view = rgb_sigma.view(S, N, 4).transpose(0, 1) if sample_major else rgb_sigma.view(N, S, 4)  # only for the bg policy's shape / last sample
     bg_rgb = _get_bg_rgb(model, rays[:, 3:6], params, bg_view, N=N, bg_color_default=bg_color_default)
     if sample_major:
-        return ops.composite_sample_major(rgb_sigma, t_vals, bg_rgb, float(sigma_scale))
+        return ops.composite_sample_major(rgb_sigma, pts.tT, bg_rgb, float(sigma_scale))
     return ops.composite(rgb_sigma.view(N, S, 4), t_vals, bg_rgb, float(sigma_scale))
 
 

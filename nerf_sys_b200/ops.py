@@ -974,22 +974,23 @@ def composite(rgb_sigma: Tensor, t: Tensor, bg: Optional[Tensor], sigma_scale: f
 
 
 @torch.no_grad()
-def composite_sample_major(rgb_sigma: Tensor, t: Tensor, bg: Optional[Tensor], sigma_scale: float = 1.0):
-    """`composite` for the (S*N, 4) output of a sample-major point set (PointSet.sample_major): read in place through
-    acn_composite_fwd_strided, no transposed copy.  Inference only (the sample-major order is a renderer's choice)."""
-    rs, tt = _f32(rgb_sigma, "rgb_sigma"), _f32(t, "t_vals")
-    N, S = tt.shape
+def composite_sample_major(rgb_sigma: Tensor, t_T: Tensor, bg: Optional[Tensor], sigma_scale: float = 1.0):
+    """`composite` for the (S*N, 4) output of a sample-major point set (PointSet.sample_major) and its (S,N) sample
+    distances: one thread per ray over coalesced rows (acn_composite_fwd_sm), no transposed copies.  Returns
+    rgb (N,3), depth (N,), weights (N,S) (a transposed view of the (S,N) buffer), acc (N,).  Inference only."""
+    rs, tt = _f32(rgb_sigma, "rgb_sigma"), _f32(t_T, "t_T")
+    S, N = tt.shape
     if rs.numel() != N * S * 4:
-        raise ValueError(f"rgb_sigma must hold {N}x{S} rows of 4, got {tuple(rs.shape)}")
+        raise ValueError(f"rgb_sigma must hold {S}x{N} rows of 4, got {tuple(rs.shape)}")
     b = None if bg is None else _f32(bg, "bg_rgb")
     dev = rs.device
     rgb, depth = torch.empty(N, 3, device=dev), torch.empty(N, device=dev)
-    w, acc = torch.empty(N, S, device=dev), torch.empty(N, device=dev)
+    wT, acc = torch.empty(S, N, device=dev), torch.empty(N, device=dev)
     with _on(dev), _timed("composite_fwd"):
-        check(lib().acn_composite_fwd_strided(_ptr(rs), 1, N, _ptr(tt), _ptr(b), N, S, float(sigma_scale), _ptr(rgb), _ptr(depth), _ptr(w),
-                                              _ptr(acc), _stream()), "acn_composite_fwd_strided")
+        check(lib().acn_composite_fwd_sm(_ptr(rs), _ptr(tt), _ptr(b), N, S, float(sigma_scale), _ptr(rgb), _ptr(depth), _ptr(wT),
+                                         _ptr(acc), _stream()), "acn_composite_fwd_sm")
     _count(1)
-    return rgb, depth, w, acc
+    return rgb, depth, wT.t(), acc
 
 
 # --------------------------------------------------------------------------
