@@ -79,7 +79,8 @@ typedef struct AcnPoints {
  * weight 1 (the active_module path, meta_container.py:302-304). */
 typedef struct AcnPairs {
   const int32_t* point; /* (Mcap,) point id, -1 = padding */
-  const float* weight;  /* (Mcap,) routing weight */
+  const float* weight;  /* (Mcap,) routing weight; NULL with point != NULL = every weight is 1 and no point id occurs twice
+                           (an owner's received rows under expert parallelism): results are stored, not accumulated */
   const int32_t* seg;   /* (E+1,) segment starts (multiples of ACN_TILE); seg[E] = used slots */
   int64_t Mcap;         /* capacity of the pair arrays (identity: == P) */
 } AcnPairs;
@@ -153,6 +154,11 @@ int64_t acn_route_pack_ws_bytes(int64_t P, int K);
 int acn_route_pack(const AcnPoints* pts, const float* centroids_host, int K, float margin, int cluster_2d,
                    int32_t* pair_point, float* pair_weight, int32_t* seg, int64_t Mcap, void* ws,
                    void* stream);
+
+/* Device-side reading of a segment table for steps that never read it back on the host: live[k] = (seg[k+1] > seg[k])
+ * (expert k received a sample), *status |= 1 when seg[K] > Mcap (the pair list was truncated at its speculative capacity;
+ * sticky - the host polls it every so often). */
+int acn_route_status(const int32_t* seg, int K, int64_t Mcap, int32_t* live, int32_t* status, void* stream);
 
 /* ---- a8-a11: encoders ---------------------------------------------------- */
 /* models/encodings.py:331-358: table row ids of the 8 corners, idx (P,L,8) int32,
@@ -307,9 +313,8 @@ int acn_sumsq_accum(const float* x, int64_t n, float* acc, void* stream);
 /* Multi-tensor forms: the whole parameter set in one launch each (a 15-tensor expert plus its 128 MiB table
  * otherwise costs ~40 launches per step).  Step counts live on the device (steps_dev[step_index], int32,
  * incremented by the call) so the step can be replayed from a CUDA graph; bias corrections are evaluated in
- * double like torch's.  coef = min(1, max_norm / (sqrt(*sumsq_dev) + 1e-6)) [if sumsq_dev && max_norm > 0]
- * * (*grad_scale_dev) [if given] is written to coef_dev when write_coef (first chunk of a step) and applied
- * to every gradient (clip_grad_norm_ + GradScaler.unscale_ semantics, meta_core.py:123-141, 181-190). */
+ * double like torch's.  The gradient multiplier (clip_grad_norm_ + GradScaler.unscale_ semantics, meta_core.py:123-141,
+ * 181-190) is written to coef_dev when write_coef (first chunk of a step) and applied to every gradient. */
 #define ACN_ADAM_MAX_TENSORS 64
 typedef struct AcnAdamTensor {
   float* param;
@@ -320,12 +325,20 @@ typedef struct AcnAdamTensor {
   float lr;
   float weight_decay;
   int32_t step_index;
-  int32_t reserved;
+  int32_t flags;   /* low 8 bits: liveness slot + 1 (0 = always live); ACN_ADAM_ZERO_GRAD: zero the gradient once it is read */
 } AcnAdamTensor;
-int acn_sumsq_multi(const AcnAdamTensor* tensors_host, int count, float* acc, void* stream);
+#define ACN_ADAM_ZERO_GRAD 0x100
+/* live_dev (int32, may be NULL): a tensor with liveness slot s is processed only when live_dev[s] != 0 - the device-side
+ * form of "p.grad is None -> torch.optim.Adam skips the parameter" (an expert that received no sample this step,
+ * meta_container.py:309-311), so that a step whose routing is never read back by the host can live in a CUDA graph.
+ * found_inf_dev (float, may be NULL): GradScaler's flag; != 0 skips the whole step (runtime_adapt.py:267).
+ * coef_dev (2 floats): [0] = gradient multiplier = grad_scale * min(1, max_norm / (sqrt(sumsq) * |grad_scale| + 1e-6)),
+ * i.e. the clip acts on the UNSCALED norm as scaler.unscale_ + clip_grad_norm_ do; [1] != 0 = step skipped (found_inf,
+ * or a non-finite norm). */
+int acn_sumsq_multi(const AcnAdamTensor* tensors_host, int count, const int32_t* live_dev, float* acc, void* stream);
 int acn_adam_multi(const AcnAdamTensor* tensors_host, int count, float beta1, float beta2, float eps,
                    int32_t* steps_dev, const float* sumsq_dev, float max_norm, const float* grad_scale_dev,
-                   float* coef_dev, int write_coef, void* stream);
+                   const float* found_inf_dev, const int32_t* live_dev, float* coef_dev, int write_coef, void* stream);
 
 /* ---- (e): expert-parallel dispatch / combine around the sample all-to-all -
  * New design (the reference is single-GPU); replaces, across GPUs, the per-expert
@@ -360,27 +373,52 @@ typedef struct AcnA2aRoute {
   int64_t row0[ACN_MAX_EXPERTS];
 } AcnA2aRoute;
 int acn_a2a_count(const AcnPairs* pairs, int K, int32_t* counts, int32_t* offs, void* stream);
+/* row0_dev (K int64, may be NULL) replaces route->row0 with values a kernel computed (acn_p2p_plan): no host read between
+ * routing and dispatch.  cap_rows > 0: rows at or beyond it are not written (an overflowing owner slab is reported by
+ * acn_p2p_plan's status word instead of being overrun).  M in pull_combine / push_grad is an upper bound; the live pair
+ * count is offs[K] on the device. */
 int acn_a2a_push_rows(const AcnPoints* pts, const AcnPairs* pairs, int K, const int32_t* offs, const AcnA2aRoute* route,
-                      int32_t* out_point, float* out_weight, void* stream);
-int acn_a2a_pull_combine(const AcnA2aRoute* route, const int32_t* point, const float* weight, const int32_t* offs, int K,
-                         int64_t M, float* out, void* stream);
+                      const int64_t* row0_dev, int64_t cap_rows, int32_t* out_point, float* out_weight, void* stream);
+int acn_a2a_pull_combine(const AcnA2aRoute* route, const int64_t* row0_dev, const int32_t* point, const float* weight,
+                         const int32_t* offs, int K, int64_t M, float* out, void* stream);
 int acn_a2a_push_grad(const float* d_out, const int32_t* point, const float* weight, const int32_t* offs, int K, int64_t M,
-                      const AcnA2aRoute* route, void* stream);
+                      const AcnA2aRoute* route, const int64_t* row0_dev, int64_t cap_rows, void* stream);
 /* Exchange slabs (one process per GPU, CUDA IPC): acn_p2p_alloc = cudaMalloc + a 64-byte handle the peers pass to
  * acn_p2p_open (maps the slab with peer access); the host layer owns both and releases them with _close / _free. */
 #define ACN_MAX_PEERS 16
-#define ACN_P2P_SYNC_BYTES 4096 /* head of every slab: int32 flag[16] | status | pad to 32 ints | table[16][ACN_MAX_EXPERTS+1] */
-int acn_p2p_alloc(int64_t bytes, void** ptr, void* handle64); /* the first ACN_P2P_SYNC_BYTES are zeroed */
+#define ACN_P2P_PAYLOAD_FLOATS 1024
+/* head of every slab: int32 flag[16] | status | epoch | pad to 32 ints | table[16][ACN_MAX_EXPERTS+1] | pad to 4096 B |
+ * float payload[2][16][ACN_P2P_PAYLOAD_FLOATS] (two buffers alternating with the barrier epoch) */
+#define ACN_P2P_SYNC_BYTES (4096 + 2 * ACN_MAX_PEERS * ACN_P2P_PAYLOAD_FLOATS * 4)
+int acn_p2p_alloc(int64_t bytes, void** ptr, void* handle64); /* the whole slab is zeroed */
 int acn_p2p_free(void* ptr);
 int acn_p2p_open(const void* handle64, void** ptr);
 int acn_p2p_close(void* ptr);
-/* Barrier number `epoch` (1,2,..., the same sequence on every rank) between the `world` ranks whose slabs are
- * sync_bases_host[0..world-1] (as mapped into this process), stream-ordered: the peer stores of this rank's earlier
- * kernels are visible to a rank once that rank's barrier kernel has returned.  With counts != NULL the rank first writes
- * its n_counts ints into row `rank` of every slab's table, i.e. an all-gather rides on the barrier.  A peer that does not
- * arrive within ~4 s sets the status word (int 16 of the sync area) to 1 instead of hanging the GPU. */
-int acn_p2p_barrier(void* const* sync_bases_host, int world, int rank, int32_t epoch, const int32_t* counts, int n_counts,
-                    void* stream);
+/* The next barrier between the `world` ranks whose slabs are sync_bases_host[0..world-1] (as mapped into this process),
+ * stream-ordered: the peer stores of this rank's earlier kernels are visible to a rank once that rank's barrier kernel
+ * has returned.  The barrier number lives in the rank's own slab and is advanced by the kernel, so the launch carries no
+ * per-call state and can be replayed from a CUDA graph; every rank must issue the same sequence of barriers.
+ *  counts  != NULL: the rank first writes its n_counts ints into row `rank` of every slab's table (an all-gather);
+ *  payload != NULL: the rank writes n_payload (<= ACN_P2P_PAYLOAD_FLOATS) floats into its slot of every slab, and after
+ *                   the wait every rank sums the world slots in rank order into reduced (n_payload floats) times scale:
+ *                   a deterministic small all-reduce riding on the barrier (background-head gradients, clip norms).
+ * A peer that does not arrive within timeout_s seconds sets bit 0 of the status word (int 16 of the sync area) and
+ * traps the kernel, so that nothing downstream consumes a half-written slab; the CUDA error surfaces at the host's next
+ * synchronisation. */
+int acn_p2p_barrier(void* const* sync_bases_host, int world, int rank, const int32_t* counts, int n_counts,
+                    const float* payload, int n_payload, float* reduced, float scale, float timeout_s, void* stream);
+/* Device-side layout of one exchange (parallel.peer_layout on the GPU).  Reads the count table of this rank's slab
+ * (filled by the counts barrier); owner_host[e] = rank owning expert e.  Layout of an owner's slab: its experts in
+ * order, each expert's block = the sub-blocks of source ranks 0..world-1 back to back, blocks padded to ACN_TILE rows.
+ *   row0_dev (K int64)       first row of THIS rank's sub-block of expert e in its owner's slab
+ *   seg_own (n_own+1 int32)  segment table of this rank's own experts over its slab rows
+ *   point_own (cap_rows)     row id for live rows, -1 for the padding rows of each block (an AcnPairs point list)
+ *   live_own (n_own int32)   expert received a sample from any rank
+ *   g_rows                   this rank's gradient rows (cap_rows,4): the padding rows are zeroed
+ *   status |= 2 when some owner needs more than cap_rows rows, |= 4 when a rank's pair list was truncated (sticky). */
+int acn_p2p_plan(const void* sync_base_own, int world, int rank, int K, const int32_t* owner_host, int64_t cap_rows,
+                 int64_t* row0_dev, int32_t* seg_own, int32_t* point_own, int32_t* live_own, float* g_rows,
+                 int32_t* status, void* stream);
 
 #if defined(__GNUC__)
 #pragma GCC visibility pop

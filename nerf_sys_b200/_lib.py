@@ -44,7 +44,7 @@ class AcnNgpExpertGrads(C.Structure):
 
 class AcnAdamTensor(C.Structure):
     _fields_ = [("param", vp), ("grad", vp), ("exp_avg", vp), ("exp_avg_sq", vp), ("n", i64), ("lr", f32), ("weight_decay", f32),
-                ("step_index", i32), ("reserved", i32)]
+                ("step_index", i32), ("flags", i32)]
 
 
 class AcnA2aRoute(C.Structure):
@@ -53,7 +53,9 @@ class AcnA2aRoute(C.Structure):
 
 ACN_ADAM_MAX_TENSORS = 64
 ACN_MAX_PEERS = 16
-ACN_P2P_SYNC_BYTES = 4096
+ACN_P2P_PAYLOAD_FLOATS = 1024
+ACN_P2P_SYNC_BYTES = 4096 + 2 * ACN_MAX_PEERS * ACN_P2P_PAYLOAD_FLOATS * 4
+ACN_ADAM_ZERO_GRAD = 0x100
 P = C.POINTER
 fp = P(f32)  # host float arrays
 
@@ -114,20 +116,22 @@ SIGNATURES = {
     "acn_adam_step": (C.c_int, [vp, vp, vp, vp, i64, f32, f32, f32, f32, f32, i64, vp, vp]),
     "acn_sgd_axpy": (C.c_int, [vp, vp, f32, i64, vp, vp]),
     "acn_sumsq_accum": (C.c_int, [vp, i64, vp, vp]),
-    "acn_sumsq_multi": (C.c_int, [P(AcnAdamTensor), C.c_int, vp, vp]),
-    "acn_adam_multi": (C.c_int, [P(AcnAdamTensor), C.c_int, f32, f32, f32, vp, vp, f32, vp, vp, C.c_int, vp]),
+    "acn_sumsq_multi": (C.c_int, [P(AcnAdamTensor), C.c_int, vp, vp, vp]),
+    "acn_adam_multi": (C.c_int, [P(AcnAdamTensor), C.c_int, f32, f32, f32, vp, vp, f32, vp, vp, vp, vp, C.c_int, vp]),
     "acn_a2a_pack": (C.c_int, [P(AcnPoints), P(AcnPairs), C.c_int, vp, vp, vp, vp, vp, vp]),
     "acn_a2a_combine": (C.c_int, [vp, vp, vp, i64, vp, vp]),
     "acn_a2a_combine_bwd": (C.c_int, [vp, vp, vp, i64, vp, vp]),
     "acn_a2a_count": (C.c_int, [P(AcnPairs), C.c_int, vp, vp, vp]),
-    "acn_a2a_push_rows": (C.c_int, [P(AcnPoints), P(AcnPairs), C.c_int, vp, P(AcnA2aRoute), vp, vp, vp]),
-    "acn_a2a_pull_combine": (C.c_int, [P(AcnA2aRoute), vp, vp, vp, C.c_int, i64, vp, vp]),
-    "acn_a2a_push_grad": (C.c_int, [vp, vp, vp, vp, C.c_int, i64, P(AcnA2aRoute), vp]),
+    "acn_a2a_push_rows": (C.c_int, [P(AcnPoints), P(AcnPairs), C.c_int, vp, P(AcnA2aRoute), vp, i64, vp, vp, vp]),
+    "acn_a2a_pull_combine": (C.c_int, [P(AcnA2aRoute), vp, vp, vp, vp, C.c_int, i64, vp, vp]),
+    "acn_a2a_push_grad": (C.c_int, [vp, vp, vp, vp, C.c_int, i64, P(AcnA2aRoute), vp, i64, vp]),
     "acn_p2p_alloc": (C.c_int, [i64, P(C.c_void_p), vp]),
     "acn_p2p_free": (C.c_int, [vp]),
     "acn_p2p_open": (C.c_int, [vp, P(C.c_void_p)]),
     "acn_p2p_close": (C.c_int, [vp]),
-    "acn_p2p_barrier": (C.c_int, [P(C.c_void_p), C.c_int, C.c_int, i32, vp, C.c_int, vp]),
+    "acn_p2p_barrier": (C.c_int, [P(C.c_void_p), C.c_int, C.c_int, vp, C.c_int, vp, C.c_int, vp, f32, f32, vp]),
+    "acn_p2p_plan": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, P(i32), i64, vp, vp, vp, vp, vp, vp, vp]),
+    "acn_route_status": (C.c_int, [vp, C.c_int, i64, vp, vp, vp]),
 }
 
 _lock = threading.Lock()

@@ -113,14 +113,22 @@ __device__ __forceinline__ int expert_of(const int* s_off, int K, int64_t j) {
   return e;
 }
 
+// row0 of expert e: the host's value, or the one acn_p2p_plan left on the device
+__device__ __forceinline__ void load_row0(const RouteDev& route, const int64_t* __restrict__ row0_dev, int K, int64_t* s_row0) {
+  if (threadIdx.x < ACN_MAX_EXPERTS) s_row0[threadIdx.x] = (row0_dev && (int)threadIdx.x < K) ? row0_dev[threadIdx.x] : route.row0[threadIdx.x];
+}
+
 __global__ void __launch_bounds__(256) k_a2a_push_rows(PointSrc src, const int32_t* __restrict__ point, const float* __restrict__ weight,
                                                        const int32_t* __restrict__ seg, int K, int64_t Mcap, const int32_t* __restrict__ offs,
-                                                       RouteDev route, int32_t* __restrict__ out_point, float* __restrict__ out_weight) {
+                                                       RouteDev route, const int64_t* __restrict__ row0_dev, int64_t cap_rows,
+                                                       int32_t* __restrict__ out_point, float* __restrict__ out_weight) {
   __shared__ int s_seg[ACN_MAX_EXPERTS + 1], s_off[ACN_MAX_EXPERTS + 1];
+  __shared__ int64_t s_row0[ACN_MAX_EXPERTS];
   if (threadIdx.x <= K) {
     s_seg[threadIdx.x] = seg[threadIdx.x];
     s_off[threadIdx.x] = offs[threadIdx.x];
   }
+  load_row0(route, row0_dev, K, s_row0);
   __syncthreads();
   int64_t M = s_seg[K];
   if (M > Mcap) M = Mcap;
@@ -131,27 +139,34 @@ __global__ void __launch_bounds__(256) k_a2a_push_rows(PointSrc src, const int32
     for (int k = 1; k < K; ++k)
       if (m >= s_seg[k]) e = k;
     const int64_t i = m - s_seg[e];
-    float x, y, z, dx, dy, dz;
-    load_xyz(src, p, x, y, z);
-    load_dir(src, p, dx, dy, dz);
-    float2* r = reinterpret_cast<float2*>(static_cast<float*>(route.base[e]) + (route.row0[e] + i) * 6);
-    r[0] = make_float2(x, y);
-    r[1] = make_float2(z, dx);
-    r[2] = make_float2(dy, dz);
+    const int64_t row = s_row0[e] + i;
+    if (cap_rows <= 0 || row < cap_rows) {
+      float x, y, z, dx, dy, dz;
+      load_xyz(src, p, x, y, z);
+      load_dir(src, p, dx, dy, dz);
+      float2* r = reinterpret_cast<float2*>(static_cast<float*>(route.base[e]) + row * 6);
+      r[0] = make_float2(x, y);
+      r[1] = make_float2(z, dx);
+      r[2] = make_float2(dy, dz);
+    }
     const int64_t j = (int64_t)s_off[e] + i;
     out_point[j] = p;
     out_weight[j] = __ldg(weight + m);
   }
 }
 
-__global__ void __launch_bounds__(256) k_a2a_pull_combine(RouteDev route, const int32_t* __restrict__ point, const float* __restrict__ weight,
-                                                          const int32_t* __restrict__ offs, int K, int64_t M, float4* __restrict__ out) {
+__global__ void __launch_bounds__(256) k_a2a_pull_combine(RouteDev route, const int64_t* __restrict__ row0_dev, const int32_t* __restrict__ point,
+                                                          const float* __restrict__ weight, const int32_t* __restrict__ offs, int K, int64_t M,
+                                                          float4* __restrict__ out) {
   __shared__ int s_off[ACN_MAX_EXPERTS + 1];
+  __shared__ int64_t s_row0[ACN_MAX_EXPERTS];
   if (threadIdx.x <= K) s_off[threadIdx.x] = offs[threadIdx.x];
+  load_row0(route, row0_dev, K, s_row0);
   __syncthreads();
+  if (M > s_off[K]) M = s_off[K];  // the live pair count is the device's
   for (int64_t j = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; j < M; j += (int64_t)gridDim.x * blockDim.x) {
     const int e = expert_of(s_off, K, j);
-    const float4 v = __ldcg(static_cast<const float4*>(route.base[e]) + route.row0[e] + (j - s_off[e]));  // L2-coherent: a peer wrote it
+    const float4 v = __ldcg(static_cast<const float4*>(route.base[e]) + s_row0[e] + (j - s_off[e]));  // L2-coherent: a peer wrote it
     const float w = __ldg(weight + j);
     red_add(out + __ldg(point + j), make_float4(v.x * w, v.y * w, v.z * w, v.w * w));
   }
@@ -159,25 +174,36 @@ __global__ void __launch_bounds__(256) k_a2a_pull_combine(RouteDev route, const 
 
 __global__ void __launch_bounds__(256) k_a2a_push_grad(const float4* __restrict__ d_out, const int32_t* __restrict__ point,
                                                        const float* __restrict__ weight, const int32_t* __restrict__ offs, int K, int64_t M,
-                                                       RouteDev route) {
+                                                       RouteDev route, const int64_t* __restrict__ row0_dev, int64_t cap_rows) {
   __shared__ int s_off[ACN_MAX_EXPERTS + 1];
+  __shared__ int64_t s_row0[ACN_MAX_EXPERTS];
   if (threadIdx.x <= K) s_off[threadIdx.x] = offs[threadIdx.x];
+  load_row0(route, row0_dev, K, s_row0);
   __syncthreads();
+  if (M > s_off[K]) M = s_off[K];
   for (int64_t j = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; j < M; j += (int64_t)gridDim.x * blockDim.x) {
     const int e = expert_of(s_off, K, j);
+    const int64_t row = s_row0[e] + (j - s_off[e]);
+    if (cap_rows > 0 && row >= cap_rows) continue;
     const float w = __ldg(weight + j);
     const float4 g = __ldg(d_out + __ldg(point + j));
-    *(static_cast<float4*>(route.base[e]) + route.row0[e] + (j - s_off[e])) = make_float4(g.x * w, g.y * w, g.z * w, g.w * w);
+    *(static_cast<float4*>(route.base[e]) + row) = make_float4(g.x * w, g.y * w, g.z * w, g.w * w);
   }
 }
 
-// ---- device-side barrier (and count exchange) between the ranks of one box -------------------------------------
-// Every slab starts with a sync area of ACN_P2P_SYNC_BYTES: int32 flag[16] | status | pad to 32 ints | table[16][17].
-// Barrier number `epoch` (1, 2, ... the same sequence on every rank): rank r stores epoch into flag[r] of EVERY rank's
-// slab (st.release.sys after a system fence, so the peer stores of this rank's earlier kernels are visible to whoever
-// acquires the flag), then waits until all flags of its OWN slab have reached epoch (ld.acquire.sys).  With `counts`, the
-// rank first writes its (n_counts) routed-sample counts into row `rank` of every slab's table: one launch replaces an
-// all-gather plus a barrier.  The wait is bounded (~4 s); on expiry status is set to 1 and the host raises at its next read.
+// ---- device-side barrier (count exchange, small all-reduce) between the ranks of one box --------------------------
+// Every slab starts with a sync area of ACN_P2P_SYNC_BYTES: int32 flag[16] | status | epoch | pad to 32 ints | table[16][17] |
+// pad to 4096 B | float payload[2][16][ACN_P2P_PAYLOAD_FLOATS].
+// The barrier number (1, 2, ... the same sequence on every rank) lives in the rank's OWN slab (int 17) and is advanced by
+// the kernel: a launch carries no per-call state and replays from a CUDA graph.  Rank r stores the epoch into flag[r] of
+// EVERY rank's slab (st.release.sys after a system fence, so the peer stores of this rank's earlier kernels are visible to
+// whoever acquires the flag), then waits until all flags of its OWN slab have reached it (ld.acquire.sys).
+//  counts : written into row `rank` of every slab's table first - one launch replaces an all-gather plus a barrier.
+//  payload: written into slot [epoch & 1][rank] of every slab; after the wait every rank sums the slots in rank order
+//           (bitwise identical on all ranks).  Two buffers: a rank can run at most one barrier ahead of the slowest
+//           reader, so the slot it overwrites two barriers later has been consumed.
+// The wait is bounded; on expiry the status word gets bit 0 and the kernel traps (nothing downstream may consume a
+// half-written slab).
 struct PeerSync {
   int32_t* base[ACN_MAX_PEERS];
 };
@@ -190,28 +216,135 @@ __device__ __forceinline__ int32_t ld_acquire_sys(const int32_t* p) {
   asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
+__device__ __forceinline__ float ld_relaxed_sys(const float* p) {
+  float v;
+  asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned long long global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
 
-__global__ void __launch_bounds__(32) k_p2p_barrier(PeerSync peers, int world, int rank, int32_t epoch, const int32_t* __restrict__ counts,
-                                                    int n_counts) {
+constexpr int SYNC_STATUS = 16, SYNC_EPOCH = 17, SYNC_TABLE = 32, SYNC_PAYLOAD = 1024;  // int / float offsets in the sync area
+constexpr int BARRIER_THREADS = 128;
+
+__global__ void __launch_bounds__(BARRIER_THREADS) k_p2p_barrier(PeerSync peers, int world, int rank, const int32_t* __restrict__ counts,
+                                                                 int n_counts, const float* __restrict__ payload, int n_payload,
+                                                                 float* __restrict__ reduced, float scale, unsigned long long timeout_ns) {
+  __shared__ int32_t s_epoch;
   const int t = threadIdx.x;
+  if (t == 0) {
+    int32_t* e = peers.base[rank] + SYNC_EPOCH;
+    s_epoch = *e + 1;
+    *e = s_epoch;
+  }
+  __syncthreads();
+  const int32_t epoch = s_epoch;
   if (counts != nullptr && t < world) {
-    int32_t* row = peers.base[t] + 32 + rank * (ACN_MAX_EXPERTS + 1);
+    int32_t* row = peers.base[t] + SYNC_TABLE + rank * (ACN_MAX_EXPERTS + 1);
     for (int i = 0; i < n_counts; ++i) row[i] = counts[i];
   }
+  const int slot = (epoch & 1) * ACN_MAX_PEERS * ACN_P2P_PAYLOAD_FLOATS;
+  if (payload != nullptr) {
+    for (int s = 0; s < world; ++s) {
+      float* dst = reinterpret_cast<float*>(peers.base[s]) + SYNC_PAYLOAD + slot + rank * ACN_P2P_PAYLOAD_FLOATS;
+      for (int i = t; i < n_payload; i += BARRIER_THREADS) dst[i] = payload[i];
+    }
+  }
   __threadfence_system();
-  __syncwarp();
+  __syncthreads();
   if (t < world) st_release_sys(peers.base[t] + rank, epoch);
   if (t < world) {
     const int32_t* mine = peers.base[rank] + t;
-    const long long t0 = clock64();
+    const unsigned long long t0 = global_ns();
+    unsigned spins = 0;
     while (ld_acquire_sys(mine) - epoch < 0) {
-      if (clock64() - t0 > 8000000000ll) {  // ~4 s at 2 GHz: a peer never arrived
-        atomicExch(peers.base[rank] + 16, 1);
-        break;
+      if ((++spins & 1023u) == 0u && global_ns() - t0 > timeout_ns) {  // a peer never arrived
+        atomicOr(peers.base[rank] + SYNC_STATUS, 1);
+        __threadfence_system();
+        __trap();
       }
     }
   }
-  __syncwarp();
+  __syncthreads();
+  if (payload != nullptr && reduced != nullptr) {
+    const float* src = reinterpret_cast<const float*>(peers.base[rank]) + SYNC_PAYLOAD + slot;
+    for (int i = t; i < n_payload; i += BARRIER_THREADS) {
+      float acc = 0.f;
+      for (int s = 0; s < world; ++s) acc += ld_relaxed_sys(src + s * ACN_P2P_PAYLOAD_FLOATS + i);  // rank order: same bits everywhere
+      reduced[i] = acc * scale;
+    }
+  }
+}
+
+// ---- device-side exchange layout (parallel.peer_layout on the GPU) --------------------------------------------------
+struct OwnerMap {
+  int32_t owner[ACN_MAX_EXPERTS];
+};
+
+__global__ void __launch_bounds__(256) k_p2p_plan(const int32_t* __restrict__ sync_own, int world, int rank, int K, OwnerMap om, int64_t cap_rows,
+                                                  int64_t* __restrict__ row0_dev, int32_t* __restrict__ seg_own, int32_t* __restrict__ point_own,
+                                                  int32_t* __restrict__ live_own, float4* __restrict__ g_rows, int32_t* __restrict__ status) {
+  __shared__ int s_tot[ACN_MAX_EXPERTS], s_seg[ACN_MAX_EXPERTS + 1], s_totown[ACN_MAX_EXPERTS];
+  __shared__ int s_nown;
+  if (threadIdx.x == 0) {
+    const int32_t* table = sync_own + SYNC_TABLE;
+    int used[ACN_MAX_PEERS];
+    for (int r = 0; r < ACN_MAX_PEERS; ++r) used[r] = 0;
+    int st = 0, nown = 0;
+    for (int s = 0; s < world; ++s)
+      if (table[s * (ACN_MAX_EXPERTS + 1) + K] < 0) st |= 4;
+    for (int e = 0; e < K; ++e) {
+      int tot = 0, before = 0;
+      for (int s = 0; s < world; ++s) {
+        const int c = table[s * (ACN_MAX_EXPERTS + 1) + e];
+        tot += c;
+        before += (s < rank) ? c : 0;
+      }
+      const int o = om.owner[e];
+      const int start = used[o];
+      used[o] += (tot + ACN_TILE - 1) / ACN_TILE * ACN_TILE;
+      if (blockIdx.x == 0) row0_dev[e] = (int64_t)start + before;
+      if (o == rank) {
+        s_seg[nown] = start;
+        s_totown[nown] = tot;
+        ++nown;
+      }
+      s_tot[e] = tot;
+    }
+    for (int r = 0; r < world; ++r)
+      if (used[r] > cap_rows) st |= 2;
+    int end = used[rank];
+    if (end > cap_rows) end = (int)(cap_rows / ACN_TILE * ACN_TILE);
+    s_seg[nown] = end;
+    for (int j = 0; j < nown; ++j)
+      if (s_seg[j] > end) s_seg[j] = end;
+    s_nown = nown;
+    if (blockIdx.x == 0) {
+      for (int j = 0; j <= nown; ++j) seg_own[j] = s_seg[j];
+      for (int j = 0; j < nown; ++j) live_own[j] = s_totown[j] > 0 ? 1 : 0;
+      if (st) atomicOr(status, st);
+    }
+  }
+  __syncthreads();
+  const int nown = s_nown;
+  const int end = s_seg[nown];
+  for (int m = blockIdx.x * blockDim.x + threadIdx.x; m < end; m += gridDim.x * blockDim.x) {
+    int j = 0;
+    for (int k = 1; k < nown; ++k)
+      if (m >= s_seg[k]) j = k;
+    const bool live = (m - s_seg[j]) < s_totown[j];
+    point_own[m] = live ? m : -1;
+    if (!live && g_rows) g_rows[m] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+}
+
+__global__ void k_route_status(const int32_t* __restrict__ seg, int K, int64_t Mcap, int32_t* __restrict__ live, int32_t* __restrict__ status) {
+  const int k = threadIdx.x;
+  if (k < K && live) live[k] = seg[k + 1] > seg[k] ? 1 : 0;
+  if (k == 0 && status && (int64_t)seg[K] > Mcap) atomicOr(status, 1);
 }
 
 static inline bool make_route(const AcnA2aRoute* r, int K, RouteDev& d) {
@@ -274,8 +407,8 @@ int acn_a2a_count(const AcnPairs* pairs, int K, int32_t* counts, int32_t* offs, 
   return ACN_OK;
 }
 
-int acn_a2a_push_rows(const AcnPoints* pts, const AcnPairs* pairs, int K, const int32_t* offs, const AcnA2aRoute* route, int32_t* out_point,
-                      float* out_weight, void* stream) {
+int acn_a2a_push_rows(const AcnPoints* pts, const AcnPairs* pairs, int K, const int32_t* offs, const AcnA2aRoute* route, const int64_t* row0_dev,
+                      int64_t cap_rows, int32_t* out_point, float* out_weight, void* stream) {
   ACN_REQUIRE(pts && pairs && offs && route && out_point && out_weight, "acn_a2a_push_rows: NULL argument");
   ACN_REQUIRE(K >= 1 && K <= ACN_MAX_EXPERTS, "acn_a2a_push_rows: K must be in [1,%d]", ACN_MAX_EXPERTS);
   ACN_REQUIRE(pairs->point && pairs->weight && pairs->seg, "acn_a2a_push_rows: needs a routed pair list (not the identity list)");
@@ -285,32 +418,58 @@ int acn_a2a_push_rows(const AcnPoints* pts, const AcnPairs* pairs, int K, const 
   ACN_REQUIRE(make_route(route, K, rd), "acn_a2a_push_rows: route has a NULL base or a negative row");
   if (pairs->Mcap == 0) return ACN_OK;
   k_a2a_push_rows<<<persistent_grid((pairs->Mcap + 255) / 256, 8), 256, 0, as_stream(stream)>>>(make_src(pts), pairs->point, pairs->weight, pairs->seg,
-                                                                                              K, pairs->Mcap, offs, rd, out_point, out_weight);
+                                                                                              K, pairs->Mcap, offs, rd, row0_dev, cap_rows, out_point,
+                                                                                              out_weight);
   ACN_LAUNCH_CHECK();
   return ACN_OK;
 }
 
-int acn_a2a_pull_combine(const AcnA2aRoute* route, const int32_t* point, const float* weight, const int32_t* offs, int K, int64_t M, float* out,
-                         void* stream) {
+int acn_a2a_pull_combine(const AcnA2aRoute* route, const int64_t* row0_dev, const int32_t* point, const float* weight, const int32_t* offs, int K,
+                         int64_t M, float* out, void* stream) {
   ACN_REQUIRE(route && offs && out && M >= 0 && (M == 0 || (point && weight)), "acn_a2a_pull_combine: bad arguments");
   ACN_REQUIRE(K >= 1 && K <= ACN_MAX_EXPERTS, "acn_a2a_pull_combine: K must be in [1,%d]", ACN_MAX_EXPERTS);
   RouteDev rd;
   ACN_REQUIRE(make_route(route, K, rd), "acn_a2a_pull_combine: route has a NULL base or a negative row");
   if (M == 0) return ACN_OK;
-  k_a2a_pull_combine<<<persistent_grid((M + 255) / 256, 8), 256, 0, as_stream(stream)>>>(rd, point, weight, offs, K, M, reinterpret_cast<float4*>(out));
+  k_a2a_pull_combine<<<persistent_grid((M + 255) / 256, 8), 256, 0, as_stream(stream)>>>(rd, row0_dev, point, weight, offs, K, M,
+                                                                                        reinterpret_cast<float4*>(out));
   ACN_LAUNCH_CHECK();
   return ACN_OK;
 }
 
 int acn_a2a_push_grad(const float* d_out, const int32_t* point, const float* weight, const int32_t* offs, int K, int64_t M,
-                      const AcnA2aRoute* route, void* stream) {
+                      const AcnA2aRoute* route, const int64_t* row0_dev, int64_t cap_rows, void* stream) {
   ACN_REQUIRE(route && offs && M >= 0 && (M == 0 || (d_out && point && weight)), "acn_a2a_push_grad: bad arguments");
   ACN_REQUIRE(K >= 1 && K <= ACN_MAX_EXPERTS, "acn_a2a_push_grad: K must be in [1,%d]", ACN_MAX_EXPERTS);
   RouteDev rd;
   ACN_REQUIRE(make_route(route, K, rd), "acn_a2a_push_grad: route has a NULL base or a negative row");
   if (M == 0) return ACN_OK;
   k_a2a_push_grad<<<persistent_grid((M + 255) / 256, 8), 256, 0, as_stream(stream)>>>(reinterpret_cast<const float4*>(d_out), point, weight, offs, K, M,
-                                                                                     rd);
+                                                                                     rd, row0_dev, cap_rows);
+  ACN_LAUNCH_CHECK();
+  return ACN_OK;
+}
+
+int acn_route_status(const int32_t* seg, int K, int64_t Mcap, int32_t* live, int32_t* status, void* stream) {
+  ACN_REQUIRE(seg && K >= 1 && K <= ACN_MAX_EXPERTS && (live || status), "acn_route_status: bad arguments");
+  k_route_status<<<1, 32, 0, as_stream(stream)>>>(seg, K, Mcap, live, status);
+  ACN_LAUNCH_CHECK();
+  return ACN_OK;
+}
+
+int acn_p2p_plan(const void* sync_base_own, int world, int rank, int K, const int32_t* owner_host, int64_t cap_rows, int64_t* row0_dev,
+                 int32_t* seg_own, int32_t* point_own, int32_t* live_own, float* g_rows, int32_t* status, void* stream) {
+  ACN_REQUIRE(sync_base_own && owner_host && row0_dev && seg_own && point_own && live_own && status, "acn_p2p_plan: NULL argument");
+  ACN_REQUIRE(world >= 1 && world <= ACN_MAX_PEERS && rank >= 0 && rank < world, "acn_p2p_plan: bad world / rank");
+  ACN_REQUIRE(K >= 1 && K <= ACN_MAX_EXPERTS && cap_rows >= ACN_TILE && cap_rows < ((int64_t)1 << 31), "acn_p2p_plan: bad K / capacity");
+  OwnerMap om;
+  for (int e = 0; e < ACN_MAX_EXPERTS; ++e) {
+    om.owner[e] = e < K ? owner_host[e] : 0;
+    ACN_REQUIRE(om.owner[e] >= 0 && om.owner[e] < world, "acn_p2p_plan: expert %d has owner %d outside the world", e, om.owner[e]);
+  }
+  k_p2p_plan<<<persistent_grid((cap_rows + 255) / 256, 2), 256, 0, as_stream(stream)>>>(static_cast<const int32_t*>(sync_base_own), world, rank, K, om,
+                                                                                       cap_rows, row0_dev, seg_own, point_own, live_own,
+                                                                                       reinterpret_cast<float4*>(g_rows), status);
   ACN_LAUNCH_CHECK();
   return ACN_OK;
 }
@@ -321,7 +480,7 @@ int acn_p2p_alloc(int64_t bytes, void** ptr, void* handle64) {
   static_assert(sizeof(cudaIpcMemHandle_t) == 64, "handle size");
   void* p = nullptr;
   ACN_CUDA(cudaMalloc(&p, (size_t)bytes));
-  cudaError_t e = cudaMemset(p, 0, (size_t)(bytes < ACN_P2P_SYNC_BYTES ? bytes : ACN_P2P_SYNC_BYTES));
+  cudaError_t e = cudaMemset(p, 0, (size_t)bytes);  // rows a peer never wrote are read (and ignored) by whole-tile kernels: keep them finite
   if (e != cudaSuccess) {
     cudaFree(p);
     set_error("acn_p2p_alloc: cudaMemset: %s", cudaGetErrorString(e));
@@ -357,15 +516,19 @@ int acn_p2p_close(void* ptr) {
   return ACN_OK;
 }
 
-int acn_p2p_barrier(void* const* sync_bases_host, int world, int rank, int32_t epoch, const int32_t* counts, int n_counts, void* stream) {
+int acn_p2p_barrier(void* const* sync_bases_host, int world, int rank, const int32_t* counts, int n_counts, const float* payload, int n_payload,
+                    float* reduced, float scale, float timeout_s, void* stream) {
   ACN_REQUIRE(sync_bases_host && world >= 1 && world <= ACN_MAX_PEERS && rank >= 0 && rank < world, "acn_p2p_barrier: bad world / rank");
   ACN_REQUIRE(n_counts >= 0 && n_counts <= ACN_MAX_EXPERTS + 1 && (n_counts == 0 || counts), "acn_p2p_barrier: bad counts");
+  ACN_REQUIRE(n_payload >= 0 && n_payload <= ACN_P2P_PAYLOAD_FLOATS && (n_payload == 0 || (payload && reduced)), "acn_p2p_barrier: bad payload");
   PeerSync ps;
   for (int r = 0; r < ACN_MAX_PEERS; ++r) {
     ps.base[r] = r < world ? static_cast<int32_t*>(sync_bases_host[r]) : nullptr;
     ACN_REQUIRE(r >= world || ps.base[r], "acn_p2p_barrier: NULL slab for rank %d", r);
   }
-  k_p2p_barrier<<<1, 32, 0, as_stream(stream)>>>(ps, world, rank, epoch, n_counts ? counts : nullptr, n_counts);
+  if (!(timeout_s > 0.f)) timeout_s = 120.f;
+  k_p2p_barrier<<<1, BARRIER_THREADS, 0, as_stream(stream)>>>(ps, world, rank, n_counts ? counts : nullptr, n_counts, n_payload ? payload : nullptr,
+                                                             n_payload, reduced, scale, (unsigned long long)((double)timeout_s * 1e9));
   ACN_LAUNCH_CHECK();
   return ACN_OK;
 }

@@ -323,7 +323,7 @@ __global__ void __launch_bounds__(NT) k_ngp_mlp_fwd(PointSrc src, const int32_t*
       svm[(int64_t)(R_Y + 3) * ld] = sigma;
     }
     if (p >= 0) {
-      if (pair_point) {
+      if (pair_point && pair_w) {
         float w = pair_w[m];
         float* o = out + p * 4;
         atomicAdd(o + 0, rgb[0] * w);
@@ -371,7 +371,7 @@ __global__ void __launch_bounds__(NT) k_ngp_mlp_bwd(const int32_t* __restrict__ 
     float4 dy = make_float4(0.f, 0.f, 0.f, 0.f);
     if (p >= 0) {
       dy = __ldg(reinterpret_cast<const float4*>(d_out + p * 4));
-      if (pair_point) {
+      if (pair_w) {
         float w = pair_w[m];
         dy.x *= w; dy.y *= w; dy.z *= w; dy.w *= w;
       }
@@ -449,7 +449,7 @@ static int check_common(const AcnPoints* pts, const AcnPairs* pairs, const AcnNg
   ACN_REQUIRE(g->log2_T >= 1 && g->log2_T <= 24 && g->interp >= 0 && g->interp <= 2, "%s: bad grid descriptor", who);
   ACN_REQUIRE(pts->x6 || (pts->rays && pts->t && pts->S >= 1), "%s: points need x6 or (rays,t,S)", who);
   bool ident = pairs->point == nullptr;
-  ACN_REQUIRE(ident ? (E == 1 && pairs->Mcap == pts->P) : (pairs->weight && pairs->seg), "%s: inconsistent pair list", who);
+  ACN_REQUIRE(ident ? (E == 1 && pairs->Mcap == pts->P) : (pairs->seg != nullptr), "%s: inconsistent pair list", who);
   ACN_REQUIRE(pairs->Mcap < ((int64_t)1 << 31), "%s: chunk the pair list below 2^31", who);
   return ACN_OK;
 }
@@ -535,7 +535,7 @@ int acn_ngp_mlp_fwd(const AcnPoints* pts, const AcnPairs* pairs, const AcnNgpExp
   ACN_REQUIRE(E >= 1 && E <= ACN_MAX_EXPERTS, "acn_ngp_mlp_fwd: E must be in [1,%d]", ACN_MAX_EXPERTS);
   ACN_REQUIRE(pts->x6 || (pts->rays && pts->S >= 1), "acn_ngp_mlp_fwd: points need x6 or rays");
   bool ident = pairs->point == nullptr;
-  ACN_REQUIRE(ident ? (E == 1 && pairs->Mcap == pts->P) : (pairs->weight && pairs->seg), "acn_ngp_mlp_fwd: inconsistent pair list");
+  ACN_REQUIRE(ident ? (E == 1 && pairs->Mcap == pts->P) : (pairs->seg != nullptr), "acn_ngp_mlp_fwd: inconsistent pair list");
   int64_t Mcap = pairs->Mcap;
   if (Mcap == 0) return ACN_OK;
   int rc = set_mlp_attrs();
@@ -554,7 +554,7 @@ int acn_ngp_mlp_bwd(const AcnPairs* pairs, const AcnNgpExpert* experts, int E, c
   ACN_REQUIRE(pairs && experts && enc && d_out && save && grads && d_enc && ws, "acn_ngp_mlp_bwd: NULL argument");
   ACN_REQUIRE(E >= 1 && E <= ACN_MAX_EXPERTS, "acn_ngp_mlp_bwd: E must be in [1,%d]", ACN_MAX_EXPERTS);
   bool ident = pairs->point == nullptr;
-  ACN_REQUIRE(ident ? E == 1 : (pairs->weight && pairs->seg), "acn_ngp_mlp_bwd: inconsistent pair list");
+  ACN_REQUIRE(ident ? E == 1 : (pairs->seg != nullptr), "acn_ngp_mlp_bwd: inconsistent pair list");
   int64_t Mcap = pairs->Mcap;
   if (Mcap == 0) return ACN_OK;
   int rc = set_mlp_attrs();

@@ -414,7 +414,7 @@ __global__ void __launch_bounds__(FWD_THREADS, 1)
       fence_before();  // the next tile's first MMA overwrites these columns after the bar_sync above it
       float r0 = sigmoid_f(o8[0]), r1 = sigmoid_f(o8[1]), r2 = sigmoid_f(o8[2]);
       if (p >= 0) {
-        if (pair_point) {
+        if (pair_point && pair_w) {
           float w = pair_w[m];
           float* o = out + p * 4;
           atomicAdd(o + 0, r0 * w);
@@ -678,7 +678,7 @@ __global__ void __launch_bounds__(128 * NQ + 32, NQ == 2 ? 2 : 1)  // NQ = 2: at
       }
       if (q == 0 && p >= 0) {
         dy = ldg_now(reinterpret_cast<const float4*>(d_out + p * 4));
-        if (pair_point) {
+        if (pair_w) {
           float w = __ldg(pair_w + m);
           dy.x *= w; dy.y *= w; dy.z *= w; dy.w *= w;
         }
@@ -784,7 +784,8 @@ __global__ void __launch_bounds__(128 * NQ + 32, NQ == 2 ? 2 : 1)  // NQ = 2: at
 }
 
 // max |x| over a tensor (non-negative floats order like their bit patterns; NaN sorts above inf -> scale 1)
-__global__ void __launch_bounds__(256) k_absmax(const float4* __restrict__ x, int64_t n4, float* __restrict__ out) {
+__global__ void __launch_bounds__(256) k_absmax(const float4* __restrict__ x, int64_t n4, float* __restrict__ out, const int32_t* __restrict__ bound) {
+  if (bound && n4 > (int64_t)__ldg(bound)) n4 = __ldg(bound);  // rows past the used part of an owner's slab are stale
   float m = 0.f;
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
     float4 v = __ldg(x + i);
@@ -798,7 +799,7 @@ __global__ void __launch_bounds__(256) k_absmax(const float4* __restrict__ x, in
 }
 
 int launch_absmax(const float* x, int64_t n4, float* out, cudaStream_t st) {
-  k_absmax<<<persistent_grid((n4 + 255) / 256, 4), 256, 0, st>>>(reinterpret_cast<const float4*>(x), n4, out);
+  k_absmax<<<persistent_grid((n4 + 255) / 256, 4), 256, 0, st>>>(reinterpret_cast<const float4*>(x), n4, out, nullptr);
   ACN_LAUNCH_CHECK();
   return ACN_OK;
 }
@@ -994,7 +995,7 @@ int acn_ngp_mlp_fwd_tc(const AcnPoints* pts, const AcnPairs* pairs, const AcnNgp
   ACN_REQUIRE(E >= 1 && E <= ACN_MAX_EXPERTS, "acn_ngp_mlp_fwd_tc: E must be in [1,%d]", ACN_MAX_EXPERTS);
   ACN_REQUIRE(pts->x6 || (pts->rays && pts->S >= 1), "acn_ngp_mlp_fwd_tc: points need x6 or rays");
   bool ident = pairs->point == nullptr;
-  ACN_REQUIRE(ident ? (E == 1 && pairs->Mcap == pts->P) : (pairs->weight && pairs->seg), "acn_ngp_mlp_fwd_tc: inconsistent pair list");
+  ACN_REQUIRE(ident ? (E == 1 && pairs->Mcap == pts->P) : (pairs->seg != nullptr), "acn_ngp_mlp_fwd_tc: inconsistent pair list");
   ACN_REQUIRE(pairs->Mcap < ((int64_t)1 << 31) - 128, "acn_ngp_mlp_fwd_tc: chunk the pair list below 2^31");
   int64_t Mcap = pairs->Mcap;
   if (Mcap == 0) return ACN_OK;
@@ -1020,7 +1021,7 @@ static int run_bwd_tc(const AcnPoints* pts, const AcnPairs* pairs, const AcnNgpE
   ACN_REQUIRE(E >= 1 && E <= ACN_MAX_EXPERTS, "%s: E must be in [1,%d]", who, ACN_MAX_EXPERTS);
   ACN_REQUIRE(pts->x6 || (pts->rays && pts->S >= 1), "%s: points need x6 or rays", who);
   bool ident = pairs->point == nullptr;
-  ACN_REQUIRE(ident ? (E == 1 && pairs->Mcap == pts->P) : (pairs->weight && pairs->seg), "%s: inconsistent pair list", who);
+  ACN_REQUIRE(ident ? (E == 1 && pairs->Mcap == pts->P) : (pairs->seg != nullptr), "%s: inconsistent pair list", who);
   ACN_REQUIRE(pairs->Mcap < ((int64_t)1 << 31) - 128, "%s: chunk the pair list below 2^31", who);
   ACN_REQUIRE(n_chunks >= 1 && n_chunks <= TC_MAX_CHUNKS, "%s: 1..%d chunks", who, TC_MAX_CHUNKS);
   int64_t Mcap = pairs->Mcap;
@@ -1042,7 +1043,9 @@ static int run_bwd_tc(const AcnPoints* pts, const AcnPairs* pairs, const AcnNgpE
     }
   float* gmax = partial + (int64_t)P_FLOATS * G * n_chunks;
   ACN_CUDA(cudaMemsetAsync(gmax, 0, sizeof(float), st));
-  k_absmax<<<persistent_grid((pts->P + 255) / 256, 4), 256, 0, st>>>(reinterpret_cast<const float4*>(d_out), pts->P, gmax);
+  const bool store_mode = pairs->point && !pairs->weight;  // point id == row of d_out: rows at or past seg[E] are unused
+  k_absmax<<<persistent_grid((pts->P + 255) / 256, 4), 256, 0, st>>>(reinterpret_cast<const float4*>(d_out), pts->P, gmax,
+                                                                     store_mode ? pairs->seg + E : nullptr);
   ACN_LAUNCH_CHECK();
   const int tiles = (int)(ld / ROWS);
   const int chunk_tiles = (tiles + n_chunks - 1) / n_chunks;

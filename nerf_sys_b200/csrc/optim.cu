@@ -80,9 +80,16 @@ __device__ __forceinline__ int find_tensor(const MultiDesc& d, int b) {
   return t;
 }
 
-__global__ void __launch_bounds__(256) k_sumsq_multi(const __grid_constant__ MultiDesc d, float* __restrict__ acc) {
+// AcnAdamTensor.flags: low 8 bits = liveness slot + 1 (0 = unconditional), bit 8 = write zeros over the gradient once read
+__device__ __forceinline__ bool tensor_live(const AcnAdamTensor& a, const int32_t* __restrict__ live) {
+  const int slot = a.flags & 0xff;
+  return slot == 0 || live == nullptr || __ldg(live + slot - 1) != 0;
+}
+
+__global__ void __launch_bounds__(256) k_sumsq_multi(const __grid_constant__ MultiDesc d, const int32_t* __restrict__ live, float* __restrict__ acc) {
   __shared__ float red[8];
   const int t = find_tensor(d, blockIdx.x);
+  if (!tensor_live(d.t[t], live)) return;  // block-uniform: a tensor without a gradient this step (torch: p.grad is None)
   const int nb = d.blk0[t + 1] - d.blk0[t], b = blockIdx.x - d.blk0[t];
   const float* __restrict__ x = d.t[t].grad;
   const int64_t n = d.t[t].n, n4 = n >> 2;
@@ -107,24 +114,45 @@ __global__ void __launch_bounds__(256) k_sumsq_multi(const __grid_constant__ Mul
   }
 }
 
-// steps[step_index] += 1 for every listed tensor; coef = clip coefficient * optional external gradient scale
+// coef[0] = gradient multiplier = (1/loss scale) * clip coefficient; coef[1] != 0 = skip the step (GradScaler found an
+// inf / NaN, or the gradient norm itself is not finite).  The norm is taken of the UNSCALED gradients, as the reference
+// unscales before it clips (runtime_adapt.py:261-268): norm = sqrt(sumsq) * |grad_scale|.
+// steps[step_index] += 1 for every listed live tensor unless the step is skipped.
 __global__ void k_adam_prep(const __grid_constant__ MultiDesc d, int32_t* __restrict__ steps, const float* __restrict__ sumsq, float max_norm,
-                            const float* __restrict__ grad_scale, float* __restrict__ coef, int write_coef) {
+                            const float* __restrict__ grad_scale, const float* __restrict__ found_inf, const int32_t* __restrict__ live,
+                            float* __restrict__ coef, int write_coef) {
+  __shared__ float s_skip;
   int i = threadIdx.x;
-  if (i < d.count) steps[d.t[i].step_index] += 1;
-  if (i == 0 && write_coef) {
-    float c = 1.f;
-    if (sumsq && max_norm > 0.f) c = fminf(1.f, max_norm / (sqrtf(*sumsq) + 1e-6f));  // torch.nn.utils.clip_grad_norm_
-    if (grad_scale) c *= *grad_scale;
-    *coef = c;
+  if (i == 0) {
+    if (write_coef) {
+      const float gs = grad_scale ? *grad_scale : 1.f;
+      float c = gs, skip = 0.f;
+      if (sumsq && max_norm > 0.f) {
+        const float norm = sqrtf(*sumsq) * fabsf(gs);
+        if (!(norm <= 3.0e38f)) skip = 1.f;  // inf or NaN
+        c = gs * fminf(1.f, max_norm / (norm + 1e-6f));  // torch.nn.utils.clip_grad_norm_
+      }
+      if (found_inf && *found_inf != 0.f) skip = 1.f;
+      if (!(fabsf(gs) <= 3.0e38f)) skip = 1.f;
+      coef[0] = c;
+      coef[1] = skip;
+    }
+    s_skip = coef[1];
   }
+  __syncthreads();
+  if (i < d.count && s_skip == 0.f && tensor_live(d.t[i], live)) steps[d.t[i].step_index] += 1;
 }
 
 __global__ void __launch_bounds__(256) k_adam_multi(const __grid_constant__ MultiDesc d, float beta1, float beta2, float eps,
-                                                    const int32_t* __restrict__ steps, const float* __restrict__ coef) {
+                                                    const int32_t* __restrict__ steps, const float* __restrict__ coef,
+                                                    const int32_t* __restrict__ live) {
   __shared__ AdamK sk;
   const int t = find_tensor(d, blockIdx.x);
   const AcnAdamTensor& a = d.t[t];
+  if (!tensor_live(a, live)) return;  // no gradient this step: parameter, moments and step count untouched (torch skips p.grad is None)
+  const bool skip = coef && __ldg(coef + 1) != 0.f;
+  const bool zero = (a.flags & 0x100) != 0;
+  if (skip && !zero) return;
   if (threadIdx.x == 0) {
     double step = (double)steps[a.step_index];
     double bc1 = 1.0 - pow((double)beta1, step), bc2 = 1.0 - pow((double)beta2, step);
@@ -141,11 +169,18 @@ __global__ void __launch_bounds__(256) k_adam_multi(const __grid_constant__ Mult
   const int nb = d.blk0[t + 1] - d.blk0[t], b = blockIdx.x - d.blk0[t];
   const int64_t n = a.n, n4 = n >> 2;
   float4* p4 = reinterpret_cast<float4*>(a.param);
-  const float4* g4 = reinterpret_cast<const float4*>(a.grad);
+  float4* g4 = reinterpret_cast<float4*>(const_cast<float*>(a.grad));
   float4* m4 = reinterpret_cast<float4*>(a.exp_avg);
   float4* v4 = reinterpret_cast<float4*>(a.exp_avg_sq);
+  if (skip) {  // a skipped step still hands the persistent gradient buffer back clean
+    for (int64_t i = b * 256 + threadIdx.x; i < n4; i += (int64_t)nb * 256) g4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int64_t i = (n4 << 2) + b * 256 + threadIdx.x; i < n; i += (int64_t)nb * 256) const_cast<float*>(a.grad)[i] = 0.f;
+    return;
+  }
   for (int64_t i = b * 256 + threadIdx.x; i < n4; i += (int64_t)nb * 256) {
-    float4 pa = p4[i], gb = __ldg(g4 + i), mc = m4[i], vd = v4[i];
+    float4 pa = p4[i], gb = g4[i], mc = m4[i], vd = v4[i];
+    // the gradient line was just read: writing zeros over it costs the write-back only and replaces the next step's 128 MiB memset
+    if (zero) g4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     adam_one(pa.x, gb.x, mc.x, vd.x, k, gs);
     adam_one(pa.y, gb.y, mc.y, vd.y, k, gs);
     adam_one(pa.z, gb.z, mc.z, vd.z, k, gs);
@@ -154,8 +189,11 @@ __global__ void __launch_bounds__(256) k_adam_multi(const __grid_constant__ Mult
     m4[i] = mc;
     v4[i] = vd;
   }
-  for (int64_t i = (n4 << 2) + b * 256 + threadIdx.x; i < n; i += (int64_t)nb * 256)
-    adam_one(a.param[i], a.grad[i], a.exp_avg[i], a.exp_avg_sq[i], k, gs);
+  for (int64_t i = (n4 << 2) + b * 256 + threadIdx.x; i < n; i += (int64_t)nb * 256) {
+    float g = a.grad[i];
+    if (zero) const_cast<float*>(a.grad)[i] = 0.f;
+    adam_one(a.param[i], g, a.exp_avg[i], a.exp_avg_sq[i], k, gs);
+  }
 }
 
 static int fill_multi(MultiDesc& d, const AcnAdamTensor* tensors, int count, const char* who) {
@@ -219,20 +257,20 @@ int acn_sumsq_accum(const float* x, int64_t n, float* acc, void* stream) {
   return ACN_OK;
 }
 
-int acn_sumsq_multi(const AcnAdamTensor* tensors_host, int count, float* acc, void* stream) {
+int acn_sumsq_multi(const AcnAdamTensor* tensors_host, int count, const int32_t* live_dev, float* acc, void* stream) {
   ACN_REQUIRE(acc, "acn_sumsq_multi: acc is NULL");
   MultiDesc d;
   int rc = fill_multi(d, tensors_host, count, "acn_sumsq_multi");
   if (rc) return rc;
-  k_sumsq_multi<<<d.blk0[count], 256, 0, as_stream(stream)>>>(d, acc);
+  k_sumsq_multi<<<d.blk0[count], 256, 0, as_stream(stream)>>>(d, live_dev, acc);
   ACN_LAUNCH_CHECK();
   return ACN_OK;
 }
 
 int acn_adam_multi(const AcnAdamTensor* tensors_host, int count, float beta1, float beta2, float eps, int32_t* steps_dev,
-                   const float* sumsq_dev, float max_norm, const float* grad_scale_dev, float* coef_dev, int write_coef, void* stream) {
-  ACN_REQUIRE(steps_dev, "acn_adam_multi: steps_dev is NULL");
-  ACN_REQUIRE(!write_coef || coef_dev, "acn_adam_multi: write_coef needs coef_dev");
+                   const float* sumsq_dev, float max_norm, const float* grad_scale_dev, const float* found_inf_dev,
+                   const int32_t* live_dev, float* coef_dev, int write_coef, void* stream) {
+  ACN_REQUIRE(steps_dev && coef_dev, "acn_adam_multi: steps_dev / coef_dev is NULL");
   MultiDesc d;
   int rc = fill_multi(d, tensors_host, count, "acn_adam_multi");
   if (rc) return rc;
@@ -240,9 +278,9 @@ int acn_adam_multi(const AcnAdamTensor* tensors_host, int count, float beta1, fl
     ACN_REQUIRE(tensors_host[i].param && tensors_host[i].exp_avg && tensors_host[i].exp_avg_sq && tensors_host[i].step_index >= 0,
                 "acn_adam_multi: tensor %d is incomplete", i);
   cudaStream_t st = as_stream(stream);
-  k_adam_prep<<<1, ACN_ADAM_MAX_TENSORS, 0, st>>>(d, steps_dev, sumsq_dev, max_norm, grad_scale_dev, coef_dev, write_coef);
+  k_adam_prep<<<1, ACN_ADAM_MAX_TENSORS, 0, st>>>(d, steps_dev, sumsq_dev, max_norm, grad_scale_dev, found_inf_dev, live_dev, coef_dev, write_coef);
   ACN_LAUNCH_CHECK();
-  k_adam_multi<<<d.blk0[count], 256, 0, st>>>(d, beta1, beta2, eps, steps_dev, coef_dev);
+  k_adam_multi<<<d.blk0[count], 256, 0, st>>>(d, beta1, beta2, eps, steps_dev, coef_dev, live_dev);
   ACN_LAUNCH_CHECK();
   return ACN_OK;
 }

@@ -75,7 +75,7 @@ __device__ __forceinline__ uint32_t route_point(const RouteCfg& cfg, float x, fl
 #pragma unroll
   for (int k = 0; k < KT; ++k) {
     float d = sqrtf(sq[k]);
-    if (cfg.margin > 1.0f) d = fmaxf(d, 1e-6f);
+    if (cfg.margin > 1.0f) d = (d < 1e-6f) ? 1e-6f : d;  // clamp_min that propagates NaN, as torch's does (fmaxf would return 1e-6)
     dist[k] = d;
     const bool lt = d < mind;  // strict: first index wins ties, as torch.argmin / min
     mind = lt ? d : mind;
@@ -187,7 +187,7 @@ __device__ __forceinline__ uint32_t route_warp(const RouteCfg& cfg, bool valid, 
       v = (kk == k) ? t : v;
     }
     float d = sqrtf(v);
-    if (soft) d = fmaxf(d, 1e-6f);
+    if (soft) d = (d < 1e-6f) ? 1e-6f : d;  // NaN stays NaN (torch.clamp_min): a non-finite sample is a member of no expert
     if (!active) d = INFINITY;
     float mind = d;  // min over the group; NaN never wins, as with the strict "d < min" chain
 #pragma unroll
@@ -239,7 +239,7 @@ __global__ void __launch_bounds__(RT) k_route_count(PointSrc src, int64_t P, Rou
       const int64_t p = (int64_t)b * RB + j * RT + threadIdx.x;
       float x = 0.f, y = 0.f, z = 0.f, w[KT];
       if (p < P) load_xyz(src, p, x, y, z);
-      const uint32_t mask = route_warp<KT, D3>(cfg, p < P, x, y, z, w);
+      const uint32_t mask = route_warp<KT, D3>(cfg, p < P, x, y, z, w) & ((1u << cfg.K) - 1u);  // never a padding expert
 #pragma unroll
       for (int k = 0; k < KT; ++k) {
         unsigned bal = __ballot_sync(0xffffffffu, (mask >> k) & 1u);
@@ -317,7 +317,7 @@ __global__ void __launch_bounds__(RT) k_route_write(PointSrc src, int64_t P, Rou
       const int64_t p = (int64_t)b * RB + j * RT + threadIdx.x;
       float x = 0.f, y = 0.f, z = 0.f, w[KT];
       if (p < P) load_xyz(src, p, x, y, z);
-      const uint32_t mask = route_warp<KT, D3>(cfg, p < P, x, y, z, w);
+      const uint32_t mask = route_warp<KT, D3>(cfg, p < P, x, y, z, w) & ((1u << cfg.K) - 1u);  // never a padding expert
       unsigned bals[KT];
 #pragma unroll
       for (int k = 0; k < KT; ++k) {

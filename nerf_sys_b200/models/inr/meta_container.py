@@ -59,6 +59,8 @@ class MetaContainer(MetaModule):
                                         nn.Linear(self.bg_hidden_dim, 3, bias=True), nn.Sigmoid())
         self._cent_host = None
         self._ep = None  # (process group or None for the default group) when the experts are sharded over ranks
+        self._deferred = False  # training-time routing without the host read (set_deferred_routing)
+        self._live = None       # (live flags int32 (K,), status int32 (1,)) on the parameters' device
 
     # ---- expert parallelism (new: the reference is single-GPU) ----------
     def set_expert_parallel(self, enabled: bool = True, group=None, exchange=None) -> "MetaContainer":
@@ -70,6 +72,49 @@ class MetaContainer(MetaModule):
         pack / combine kernels instead of NCCL all-to-alls."""
         object.__setattr__(self, "_ep", (group, exchange) if enabled else None)
         return self
+
+    # ---- routing without a host read (CUDA-graph capturable training steps) -------------
+    def set_deferred_routing(self, enabled: bool = True) -> "MetaContainer":
+        """Training-mode `evaluate` normally reads the (K+1)-int segment table back to size its pair lists exactly and to
+        learn which experts received samples (the reference reads K nonzero() sizes, meta_container.py:309).  Deferred:
+        the pair lists keep their speculative capacity, every expert returns gradients, and the device-side
+        ``live_flags`` tell the optimiser which experts to skip (optim.bind_expert_liveness) - the step makes no host
+        read and can be captured in a CUDA graph.  ``check_routing()`` reports a capacity overflow after the fact."""
+        object.__setattr__(self, "_deferred", bool(enabled))
+        return self
+
+    def _live_state(self):
+        dev = self.centroids.device
+        if self._live is None or self._live[0].device != dev:
+            K = len(self.submodules)
+            object.__setattr__(self, "_live", (torch.ones(K, dtype=torch.int32, device=dev), torch.zeros(1, dtype=torch.int32, device=dev)))
+        return self._live
+
+    @property
+    def live_flags(self) -> torch.Tensor:
+        """int32 (K,) on the device: expert k received a sample in the last deferred `evaluate`."""
+        return self._live_state()[0]
+
+    def live_flag_slots(self, experts=None):
+        """(flags tensor, {expert index: slot}) for optim.bind_expert_liveness; under peer-memory expert parallelism the
+        flags are the exchange's (one slot per OWNED expert, written by acn_p2p_plan)."""
+        K = len(self.submodules)
+        if self._ep is not None and self._ep[1] is not None:
+            from ... import parallel
+            ex = self._ep[1]
+            mine = [e for e, o in enumerate(parallel.expert_owner(K, ex.world)) if o == ex.rank]
+            return ex.live_own, {e: j for j, e in enumerate(mine)}
+        ks = range(K) if experts is None else experts
+        return self.live_flags, {int(k): int(k) for k in ks}
+
+    def check_routing(self) -> None:
+        """One host read: raises if a deferred routing overflowed its speculative pair capacity since the last check."""
+        if self._ep is not None and self._ep[1] is not None:
+            self._ep[1].check()
+        if self._live is not None and int(self._live[1].item()) != 0:
+            self._live[1].zero_()
+            raise RuntimeError("deferred routing produced more (sample, expert) pairs than the speculative pair-list capacity "
+                               f"(boundary_margin {self.boundary_margin}); results since the last check are truncated")
 
     # ---- host copy of the centroids (they travel in the kernel-parameter block) ----
     def centroids_host(self) -> List[float]:
@@ -111,8 +156,12 @@ class MetaContainer(MetaModule):
             return self.submodules[0].evaluate(pts, self._sub_params(params, 0))
         # a renderer that verifies the capacity once per frame (render_image) lets the pack skip its host read
         defer = getattr(pts, "route_checks", None) is not None and not torch.is_grad_enabled()
+        defer_train = self._deferred and torch.is_grad_enabled()
         with torch.no_grad():
-            pairs = ops.route_pack(pts, self.centroids_host(), K, self.boundary_margin, self.cluster_2d, sync=not defer)
+            pairs = ops.route_pack(pts, self.centroids_host(), K, self.boundary_margin, self.cluster_2d, sync=not (defer or defer_train))
+            if defer_train:
+                live, status = self._live_state()
+                ops.route_status(pairs.seg, K, pairs.M, live, status)
         if defer:
             pts.route_checks.append((pairs.seg, pairs.M))
         tables = [sub.xyz_encoder.hash_table for sub in self.submodules]
@@ -125,6 +174,31 @@ class MetaContainer(MetaModule):
         assert x.dim() == 2 and x.shape[-1] >= 6, "x must be (N,D>=6)"
         x6 = x if x.shape[-1] == 6 else x[:, :6]
         return self.evaluate(ops.PointSet(x6=x6), params=params, active_module=active_module)
+
+    def _evaluate_expert_keys(self, x6: torch.Tensor, params, active_module):
+        # with active_module the reference's density()/color() hand the expert its CONTAINER-level sub-dict
+        # (meta_container.py:170-177, 236-239), unlike render_rays, whose caller passes expert-level keys
+        if active_module is not None:
+            sub = self.submodules[active_module]
+            return sub.evaluate(ops.PointSet(x6=x6), self._sub_params(params, active_module))
+        return self.evaluate(ops.PointSet(x6=x6), params=params)
+
+    def density(self, xyz: torch.Tensor, params=None, active_module: Optional[int] = None) -> torch.Tensor:
+        """Routed density query, sigma (N,) (meta_container.py:217-273): the route -> dispatch -> combine of `forward`
+        with the sigma channel kept (soft routing blends sigma linearly with the routing weight, as `forward` does)."""
+        assert xyz.dim() == 2 and xyz.shape[-1] == 3, "xyz must be (N,3)"
+        d = torch.zeros_like(xyz, dtype=torch.float32)
+        d[:, 2] = 1.0  # the colour branch is evaluated and dropped; any unit direction does
+        out = self._evaluate_expert_keys(torch.cat([xyz.float(), d], dim=-1), params, active_module)
+        return out[:, 3].to(dtype=xyz.dtype)
+
+    def color(self, xyz: torch.Tensor, dirs: torch.Tensor, params=None, active_module: Optional[int] = None) -> torch.Tensor:
+        """Routed RGB query, (N,3) (meta_container.py:137-215): rgb_mix = sum_k w_k rgb_k."""
+        assert xyz.dim() == 2 and xyz.shape[-1] == 3, "xyz must be (N,3)"
+        assert dirs.dim() == 2 and dirs.shape[-1] == 3, "dirs must be (N,3)"
+        dirs = torch.nn.functional.normalize(dirs.to(xyz.device).float(), dim=-1)
+        out = self._evaluate_expert_keys(torch.cat([xyz.float(), dirs], dim=-1), params, active_module)
+        return out[:, :3].to(dtype=xyz.dtype)
 
     # ---- background ---------------------------------------------------------------
     def background_color(self, d: torch.Tensor) -> torch.Tensor:

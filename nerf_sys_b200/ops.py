@@ -10,6 +10,7 @@ import ctypes as C
 from typing import List, Optional, Sequence, Tuple
 
 import torch
+from torch.autograd.function import once_differentiable
 
 from . import _lib
 from ._lib import (ACN_MAX_EXPERTS, ACN_NGP_LAYERS, ACN_TILE, AcnA2aRoute, AcnGridDesc, AcnNgpExpert, AcnNgpExpertGrads, AcnPairs,
@@ -218,8 +219,13 @@ class PairList:
     """Routed (point, expert) pairs grouped by expert; identity when point is None."""
 
     def __init__(self, M: int, point: Optional[Tensor] = None, weight: Optional[Tensor] = None, seg: Optional[Tensor] = None,
-                 seg_host: Optional[List[int]] = None):
+                 seg_host: Optional[List[int]] = None, store_out: Optional[Tensor] = None):
+        """``seg_host`` None with a routed list = the host never read the segment table (speculative capacity; every expert
+        is treated as live and the device-side flags of `route_status` / `acn_p2p_plan` tell the optimiser otherwise).
+        ``weight`` None with ``point`` given = unit weights, unique point ids: the expert kernels STORE their rows, into
+        ``store_out`` (P,4) when given (an owner's result rows inside its exchange slab)."""
         self.M, self.point, self.weight, self.seg, self.seg_host = int(M), point, weight, seg, seg_host
+        self.store_out = store_out
 
     @property
     def identity(self) -> bool:
@@ -445,35 +451,46 @@ def make_route(bases: Sequence[int], row0: Sequence[int]) -> AcnA2aRoute:
     return r
 
 
-def a2a_push_rows(pts: PointSet, pairs: PairList, K: int, offs: Tensor, route: AcnA2aRoute, M: int) -> Tuple[Tensor, Tensor]:
+def a2a_push_rows(pts: PointSet, pairs: PairList, K: int, offs: Tensor, route: AcnA2aRoute, M: int, row0_dev: Optional[Tensor] = None,
+                  cap_rows: int = 0) -> Tuple[Tensor, Tensor]:
     """Writes the [xyz,dir] rows of the live pairs into their experts' owners (route); returns the compact
-    (point (M,) int32, weight (M,)) of the pairs for the combine."""
+    (point (M,) int32, weight (M,)) of the pairs for the combine.  ``row0_dev`` (K int64 on the device, from
+    `p2p_plan`) replaces the host's route rows; ``M`` is then an upper bound (the pair capacity)."""
     dev = pts.device
     point = torch.empty(M, device=dev, dtype=torch.int32)
     weight = torch.empty(M, device=dev, dtype=torch.float32)
     cp, cq = pts.c(), pairs.c()
     with _on(dev), _timed("a2a_push_rows"):
-        check(lib().acn_a2a_push_rows(C.byref(cp), C.byref(cq), K, _ptr(offs), C.byref(route), _ptr(point), _ptr(weight), _stream()),
-              "acn_a2a_push_rows")
+        check(lib().acn_a2a_push_rows(C.byref(cp), C.byref(cq), K, _ptr(offs), C.byref(route), _ptr(row0_dev), int(cap_rows), _ptr(point),
+                                      _ptr(weight), _stream()), "acn_a2a_push_rows")
     _count(1)
     return point, weight
 
 
-def a2a_pull_combine(route: AcnA2aRoute, point: Tensor, weight: Tensor, offs: Tensor, K: int, P: int) -> Tensor:
+def a2a_pull_combine(route: AcnA2aRoute, point: Tensor, weight: Tensor, offs: Tensor, K: int, P: int, row0_dev: Optional[Tensor] = None) -> Tensor:
     dev = point.device
     out = torch.zeros(P, 4, device=dev, dtype=torch.float32)
     with _on(dev), _timed("a2a_pull_combine"):
-        check(lib().acn_a2a_pull_combine(C.byref(route), _ptr(point), _ptr(weight), _ptr(offs), K, point.numel(), _ptr(out), _stream()),
-              "acn_a2a_pull_combine")
+        check(lib().acn_a2a_pull_combine(C.byref(route), _ptr(row0_dev), _ptr(point), _ptr(weight), _ptr(offs), K, point.numel(), _ptr(out),
+                                         _stream()), "acn_a2a_pull_combine")
     _count(1)
     return out
 
 
-def a2a_push_grad(d_out: Tensor, point: Tensor, weight: Tensor, offs: Tensor, K: int, route: AcnA2aRoute) -> None:
+def a2a_push_grad(d_out: Tensor, point: Tensor, weight: Tensor, offs: Tensor, K: int, route: AcnA2aRoute, row0_dev: Optional[Tensor] = None,
+                  cap_rows: int = 0) -> None:
     g = _f32(d_out, "d_out")
     with _on(g.device), _timed("a2a_push_grad"):
-        check(lib().acn_a2a_push_grad(_ptr(g), _ptr(point), _ptr(weight), _ptr(offs), K, point.numel(), C.byref(route), _stream()),
-              "acn_a2a_push_grad")
+        check(lib().acn_a2a_push_grad(_ptr(g), _ptr(point), _ptr(weight), _ptr(offs), K, point.numel(), C.byref(route), _ptr(row0_dev),
+                                      int(cap_rows), _stream()), "acn_a2a_push_grad")
+    _count(1)
+
+
+def route_status(seg: Tensor, K: int, Mcap: int, live: Optional[Tensor], status: Optional[Tensor]) -> None:
+    """Device-side reading of a segment table nobody reads back: live[k] = expert k received a sample; status |= 1 when the
+    pair list overflowed its speculative capacity (sticky)."""
+    with _on(seg.device):
+        check(lib().acn_route_status(_ptr(seg), int(K), int(Mcap), _ptr(live), _ptr(status), _stream()), "acn_route_status")
     _count(1)
 
 
@@ -495,6 +512,7 @@ class A2aCombineFn(torch.autograd.Function):
         return out
 
     @staticmethod
+    @once_differentiable  # first-order ops: create_graph=True (algo='maml', meta_core.py:54-59) fails loudly instead of silently dropping terms
     def backward(ctx, d_out):
         pt, wt = ctx.saved_tensors
         g = _f32(d_out, "d_out")
@@ -537,6 +555,7 @@ class HashGridFn(torch.autograd.Function):
         return y.reshape(*x01.shape[:-1], g.levels * g.features)
 
     @staticmethod
+    @once_differentiable  # first-order ops: create_graph=True (algo='maml', meta_core.py:54-59) fails loudly instead of silently dropping terms
     def backward(ctx, dy):
         (x,) = ctx.saved_tensors
         g = ctx.g
@@ -634,6 +653,7 @@ class NgpEncodeFn(torch.autograd.Function):
         return enc
 
     @staticmethod
+    @once_differentiable  # first-order ops: create_graph=True (algo='maml', meta_core.py:54-59) fails loudly instead of silently dropping terms
     def backward(ctx, d_enc):
         L = lib()
         tb = ctx.saved_tensors
@@ -643,7 +663,7 @@ class NgpEncodeFn(torch.autograd.Function):
         outs = []
         for e in range(spec.E):
             if ctx.needs_input_grad[3 + e] and _segment_len(pairs, e) > 0:
-                g = torch.zeros_like(tb[e])
+                g = _table_grad(tb[e])
                 grads[e].table = _ptr(g)
                 outs.append(g)
             else:
@@ -660,7 +680,58 @@ class NgpEncodeFn(torch.autograd.Function):
 def _segment_len(pairs: PairList, e: int) -> int:
     if pairs.identity:
         return pairs.M
+    if pairs.seg_host is None:  # never read back: live as far as the host knows
+        return 1
     return pairs.seg_host[e + 1] - pairs.seg_host[e]
+
+
+def _out_buffer(pts: "PointSet", pairs: PairList) -> Tensor:
+    """(P,4) result buffer: plain stores for identity / unique-point lists, zero-filled for the weighted blend."""
+    if pairs.store_out is not None:
+        if not (pairs.store_out.is_cuda and pairs.store_out.dtype == torch.float32 and pairs.store_out.is_contiguous()
+                and tuple(pairs.store_out.shape) == (pts.P, 4)):
+            raise ValueError(f"store_out must be a contiguous CUDA fp32 ({pts.P},4) tensor")
+        return pairs.store_out.detach()  # a fresh alias per call: the caller's tensor object never acquires a grad_fn
+    if pairs.identity or pairs.weight is None:
+        return torch.empty(pts.P, 4, device=pts.device, dtype=torch.float32)
+    return torch.zeros(pts.P, 4, device=pts.device, dtype=torch.float32)
+
+
+# ---- persistent gradient buffers for the hash tables ---------------------------------------------------------------
+# A 128 MiB table gradient costs a 128 MiB zero-fill per step when the backward allocates it.  An optimiser that zeroes
+# the gradient while it reads it (FusedAdam(persistent_grads=True): ACN_ADAM_ZERO_GRAD) registers one buffer per table here;
+# the backward then scatters into that buffer, which is all zeros between an optimiser step and the next backward.
+_grad_arena = {}  # table data_ptr -> [buffer, in_use, weakref to the parameter]
+
+
+def register_grad_buffer(table: Tensor, buf: Tensor) -> None:
+    import weakref
+    _grad_arena[table.data_ptr()] = [buf, False, weakref.ref(table)]
+
+
+def unregister_grad_buffer(table: Tensor) -> None:
+    _grad_arena.pop(table.data_ptr(), None)
+
+
+def release_grad_buffer(table: Tensor, clean: bool) -> None:
+    """The optimiser is done with the buffer (``clean``: it zeroed it on the device; otherwise it is zero-filled here)."""
+    ent = _grad_arena.get(table.data_ptr())
+    if ent is not None and ent[1]:
+        if not clean:
+            ent[0].zero_()
+        ent[1] = False
+
+
+def _table_grad(table: Tensor) -> Tensor:
+    ent = _grad_arena.get(table.data_ptr())
+    if ent is not None and not ent[1] and ent[0].shape == table.shape and ent[0].device == table.device:
+        owner = ent[2]()
+        # a parameter that still holds a .grad (zero_grad(set_to_none=False), gradient accumulation) gets a fresh tensor:
+        # autograd would otherwise add the buffer to itself
+        if owner is not None and owner.grad is None:
+            ent[1] = True
+            return ent[0].detach()  # a fresh alias: autograd adopts it as .grad without a copy
+    return torch.zeros_like(table)
 
 
 class NgpMlpFn(torch.autograd.Function):
@@ -673,8 +744,7 @@ class NgpMlpFn(torch.autograd.Function):
         enc_c = _need(enc.detach(), "enc")
         need_grad = any(ctx.needs_input_grad)  # False under no_grad: inference keeps no activations
         dev = pts.device
-        out = torch.empty(pts.P, 4, device=dev, dtype=torch.float32) if pairs.identity else torch.zeros(pts.P, 4, device=dev,
-                                                                                                        dtype=torch.float32)
+        out = _out_buffer(pts, pairs)
         tc = _mlp_math == "f16tc"
         save = None
         if need_grad and not tc:  # the tensor-core backward recomputes the forward per tile instead
@@ -693,6 +763,7 @@ class NgpMlpFn(torch.autograd.Function):
         return out
 
     @staticmethod
+    @once_differentiable  # first-order ops: create_graph=True (algo='maml', meta_core.py:54-59) fails loudly instead of silently dropping terms
     def backward(ctx, d_out):
         L = lib()
         enc, *ws = ctx.saved_tensors
@@ -792,8 +863,7 @@ class NgpExpertsTcFn(torch.autograd.Function):
         dev = pts.device
         ld = int(L.acn_ngp_ld(pairs.M))
         enc = torch.empty(32, ld, device=dev, dtype=torch.float32)
-        out = torch.empty(pts.P, 4, device=dev, dtype=torch.float32) if pairs.identity else torch.zeros(pts.P, 4, device=dev,
-                                                                                                        dtype=torch.float32)
+        out = _out_buffer(pts, pairs)
         cp, cq = pts.c(), pairs.c()
         with _on(dev):
             with _timed("hash_fwd"):
@@ -809,6 +879,7 @@ class NgpExpertsTcFn(torch.autograd.Function):
         return out
 
     @staticmethod
+    @once_differentiable  # first-order ops: create_graph=True (algo='maml', meta_core.py:54-59) fails loudly instead of silently dropping terms
     def backward(ctx, d_out):
         L = lib()
         pts, pairs, spec = ctx.pts, ctx.pairs, ctx.spec
@@ -824,7 +895,7 @@ class NgpExpertsTcFn(torch.autograd.Function):
         for e in range(E):
             live = _segment_len(pairs, e) > 0
             if ctx.needs_input_grad[3 + e] and live:
-                g = torch.zeros_like(tb[e])
+                g = _table_grad(tb[e])
                 grads[e].table = _ptr(g)
                 t_out.append(g)
                 want_table = True
@@ -900,6 +971,7 @@ class BgFn(torch.autograd.Function):
         return rgb
 
     @staticmethod
+    @once_differentiable  # first-order ops: create_graph=True (algo='maml', meta_core.py:54-59) fails loudly instead of silently dropping terms
     def backward(ctx, d_rgb):
         L = lib()
         w0, b0, w1, b1 = ctx.saved_tensors
@@ -951,6 +1023,7 @@ class CompositeFn(torch.autograd.Function):
         return rgb, depth, w, acc
 
     @staticmethod
+    @once_differentiable  # first-order ops: create_graph=True (algo='maml', meta_core.py:54-59) fails loudly instead of silently dropping terms
     def backward(ctx, g_rgb, g_depth, g_w, g_acc):
         rs, tt, b = ctx.saved_tensors
         N, S = tt.shape
@@ -1011,6 +1084,7 @@ class MseFn(torch.autograd.Function):
         return loss.reshape(())
 
     @staticmethod
+    @once_differentiable  # first-order ops: create_graph=True (algo='maml', meta_core.py:54-59) fails loudly instead of silently dropping terms
     def backward(ctx, g):
         (d_pred,) = ctx.saved_tensors
         return d_pred * g, None, None
@@ -1032,6 +1106,9 @@ def adam_step(param: Tensor, grad: Tensor, exp_avg: Tensor, exp_avg_sq: Tensor, 
 
 
 def sgd_axpy(w: Tensor, g: Tensor, lr: float) -> Tensor:
+    if isinstance(g, torch.Tensor) and g.requires_grad:
+        raise RuntimeError("sgd_axpy: the gradient carries an autograd graph (create_graph=True / algo='maml'); the sm_100a ops are "
+                           "first-order - use algo='fomaml' or 'reptile'")
     ww, gg = _need(w.detach(), "w"), _need(g.detach(), "g")
     out = torch.empty_like(ww)
     with _on(ww.device):

@@ -120,30 +120,67 @@ class SharedGradReducer:
 # ---------------------------------------------------------------------------------------------
 # ray-sharded full-frame render
 # ---------------------------------------------------------------------------------------------
+def to_uint8(rgb: Tensor) -> Tensor:
+    """[0,1] floats -> round-to-nearest 8-bit (what a viewer / video writer receives)."""
+    return (rgb.clamp(0, 1) * 255.0 + 0.5).to(torch.uint8)
+
+
 def render_image_sharded(render_rows: Callable[[int, int], Tuple[Tensor, Tensor, Tensor]], H: int, W: int, group=None,
-                         gather: bool = True):
+                         gather: bool = True, as_uint8: bool = False, dst: Optional[int] = None):
     """``render_rows(r0, r1)`` renders image rows [r0, r1) on this rank and returns (rgb (rows*W,3), depth (rows*W,),
-    acc (rows*W,)).  Rows are split in contiguous blocks; with ``gather`` every rank returns the full frame
-    (rgb (H,W,3), depth (H*W,), acc (H*W,)), otherwise its own block and its row range."""
+    acc (rows*W,)).  Rows are split in contiguous blocks (`shard_range`).
+      gather=False            -> ((rgb, depth, acc) of this rank's block, (r0, r1))
+      as_uint8=True, dst=r    -> the viewer's frame: 8-bit rgb tiles (3 B / pixel, 6.2 MB at 1080p) gathered on rank ``r``
+                                 only, received in place in the frame buffer; returns (rgb8 (H,W,3) uint8, None, None) there
+                                 and (None, None, None) elsewhere
+      default                 -> every rank gets the fp32 frame (rgb (H,W,3), depth (H*W,), acc (H*W,)): one
+                                 all-gather of (rows*W, 5) tiles straight into the frame-ordered buffer."""
     world, rank = _world(group)
     r0, r1 = shard_range(H, world, rank)
     rgb, depth, acc = render_rows(r0, r1)
     if world == 1:
+        if as_uint8:
+            return to_uint8(rgb).view(H, W, 3), None, None
         return rgb.view(H, W, 3), depth.view(-1), acc.view(-1)
     if not gather:
         return (rgb, depth, acc), (r0, r1)
+    even = H % world == 0
     rows_max = (H + world - 1) // world
-    tile = torch.zeros(rows_max * W, 5, device=rgb.device, dtype=rgb.dtype)  # one message: rgb | depth | acc
     n = (r1 - r0) * W
+    if as_uint8:
+        dst = 0 if dst is None else int(dst)
+        tile = to_uint8(rgb).reshape(-1)
+        if not even and tile.numel() < rows_max * W * 3:
+            tile = torch.cat([tile, tile.new_zeros(rows_max * W * 3 - tile.numel())])
+        if rank != dst:
+            dist.gather(tile, None, dst=dst, group=group)
+            return None, None, None
+        if even:  # tiles land in place: the gather list is the frame itself, viewed per rank
+            frame = torch.empty(world, rows_max * W * 3, device=rgb.device, dtype=torch.uint8)
+            dist.gather(tile, list(frame.unbind(0)), dst=dst, group=group)
+            return frame.view(H, W, 3), None, None
+        tiles = [torch.empty_like(tile) for _ in range(world)]
+        dist.gather(tile, tiles, dst=dst, group=group)
+        parts = []
+        for r in range(world):
+            a, b = shard_range(H, world, r)
+            parts.append(tiles[r][:(b - a) * W * 3])
+        return torch.cat(parts).view(H, W, 3), None, None
+    tile = torch.empty(rows_max * W, 5, device=rgb.device, dtype=rgb.dtype)  # one message: rgb | depth | acc
     tile[:n, 0:3], tile[:n, 3], tile[:n, 4] = rgb.view(-1, 3), depth.view(-1), acc.view(-1)
-    tiles = [torch.empty_like(tile) for _ in range(world)]
-    dist.all_gather(tiles, tile, group=group)
-    parts = []
-    for r in range(world):
-        a, b = shard_range(H, world, r)
-        parts.append(tiles[r][:(b - a) * W])
-    full = torch.cat(parts, 0)
-    return full[:, 0:3].reshape(H, W, 3).contiguous(), full[:, 3].contiguous(), full[:, 4].contiguous()
+    if n < rows_max * W:
+        tile[n:].zero_()
+    full = torch.empty(world, rows_max * W, 5, device=rgb.device, dtype=rgb.dtype)
+    dist.all_gather_into_tensor(full.view(world * rows_max * W, 5), tile, group=group)
+    if even:
+        full = full.view(H * W, 5)
+    else:
+        parts = []
+        for r in range(world):
+            a, b = shard_range(H, world, r)
+            parts.append(full[r, :(b - a) * W])
+        full = torch.cat(parts, 0)
+    return full[:, 0:3].reshape(H, W, 3), full[:, 3], full[:, 4]
 
 
 # ---------------------------------------------------------------------------------------------
@@ -310,20 +347,25 @@ class PeerExchange:
     """One exchange slab per rank, mapped by every peer (CUDA IPC over NVLink / NVSwitch), holding up to ``rows_cap``
     received rows: sync area | rows (cap,6) | y (cap,4) | g (cap,4).  Senders write sample rows and result gradients
     straight into the owner's slab and read the owner's [rgb,sigma] rows out of it (csrc/a2a.cu); no collective carries
-    data.  Ordering between the phases is `barrier()`: one 32-thread kernel per rank that raises this rank's flag in every
-    slab and waits for every flag in its own (release / acquire at system scope), stream-ordered like any other launch."""
+    data.  Ordering between the phases is `barrier()`: one small kernel per rank that raises this rank's flag in every
+    slab and waits for every flag in its own (release / acquire at system scope), stream-ordered like any other launch.
+    The barrier number lives in the slab and is advanced on the device, the routed-sample counts and the slab layout
+    (`plan`) never visit the host, and small all-reduces (background-head gradients, the clip norm) ride on a barrier:
+    a whole expert-parallel training step is a fixed launch sequence and can be captured in a CUDA graph."""
 
     ROW_FLOATS = (6, 4, 4)
 
-    def __init__(self, rows_cap: int, group=None, device=None):
+    def __init__(self, rows_cap: int, group=None, device=None, timeout_s: Optional[float] = None):
         import ctypes as C
-        from ._lib import ACN_MAX_PEERS, ACN_P2P_SYNC_BYTES, check, lib
+        import os
+        from ._lib import ACN_MAX_EXPERTS, ACN_MAX_PEERS, ACN_P2P_SYNC_BYTES, ACN_TILE, check, lib
         self.group = group
         self.world, self.rank = _world(group)
         if self.world > ACN_MAX_PEERS:
             raise ValueError(f"PeerExchange spans one box: at most {ACN_MAX_PEERS} ranks")
         self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
-        self.cap = int(rows_cap)
+        self.cap = (int(rows_cap) + ACN_TILE - 1) // ACN_TILE * ACN_TILE
+        self.timeout_s = float(os.environ.get("ACN_P2P_TIMEOUT_S", 120.0) if timeout_s is None else timeout_s)
         self._lib, self._check, self._C = lib(), check, C
         head = ACN_P2P_SYNC_BYTES // 4
         n_floats = head + self.cap * sum(self.ROW_FLOATS)
@@ -347,41 +389,94 @@ class PeerExchange:
             self._opened.append(int(q.value))
         self._bases = (C.c_void_p * self.world)(*self.peer)
         flat = torch.as_tensor(_Slab(self._ptr, n_floats), device=self.device)
-        self.sync = flat[:head].view(torch.int32)  # flag[16] | status | pad | table[16][ACN_MAX_EXPERTS+1] at int 32
+        self.sync = flat[:head].view(torch.int32)  # flag[16] | status | epoch | pad | table[16][ACN_MAX_EXPERTS+1] at int 32 | payload
         o0 = head
         o1, o2 = o0 + self.cap * 6, o0 + self.cap * 10
         self.rows, self.y, self.g = flat[o0:o1].view(self.cap, 6), flat[o1:o2].view(self.cap, 4), flat[o2:].view(self.cap, 4)
         self._byte_off = {"rows": o0 * 4, "y": o1 * 4, "g": o2 * 4}
-        self._epoch = 0
-        self._seg_pin = torch.empty(32, dtype=torch.int32).pin_memory()
+        # device-side plan of one exchange (acn_p2p_plan)
+        dev = self.device
+        self.row0_dev = torch.zeros(ACN_MAX_EXPERTS, dtype=torch.int64, device=dev)
+        self.seg_own = torch.zeros(ACN_MAX_EXPERTS + 1, dtype=torch.int32, device=dev)
+        self.point_own = torch.full((self.cap,), -1, dtype=torch.int32, device=dev)
+        self.live_own = torch.zeros(ACN_MAX_EXPERTS, dtype=torch.int32, device=dev)
+        self.status = torch.zeros(1, dtype=torch.int32, device=dev)
+        self._routes = {}
+        self._owner_arr = {}
+        self.reducer = None  # SlabGradReducer: shared-parameter gradients that ride on the backward's barrier
         if self.world > 1:
-            dist.barrier(group=group)  # every slab is mapped (and its sync area zeroed) before the first flag is written
+            dist.barrier(group=group)  # every slab is mapped (and zeroed) before the first flag is written
         self.barrier()
 
     def base(self, kind: str, r: int) -> int:
         return self.peer[r] + self._byte_off[kind]
 
-    def barrier(self, counts: Optional[Tensor] = None) -> None:
+    def route(self, kind: str, K: int, owner: Sequence[int]):
+        """Static half of an exchange route: the owners' buffers as mapped here (the rows come from `plan`)."""
+        from . import ops
+        key = (kind, K, tuple(owner))
+        if key not in self._routes:
+            self._routes[key] = ops.make_route([self.base(kind, owner[e]) for e in range(K)], [0] * K)
+        return self._routes[key]
+
+    def barrier(self, counts: Optional[Tensor] = None, payload: Optional[Tensor] = None, reduced: Optional[Tensor] = None,
+                scale: float = 1.0) -> None:
         """Every rank's earlier work on its stream (including stores into peers) is complete and visible before any rank's
-        later work.  With ``counts`` (int32, <= 17 entries) the ranks also exchange them: afterwards ``table()`` holds
-        every rank's row."""
+        later work.  ``counts`` (int32, <= 17 entries): the ranks also exchange them (`plan` reads the table on the
+        device).  ``payload`` (fp32, <= 1024 entries): all-reduced (sum in rank order, times ``scale``) into ``reduced``."""
         C = self._C
-        self._epoch += 1
         n = 0 if counts is None else int(counts.numel())
-        with torch.cuda.device(self.device):
-            self._check(self._lib.acn_p2p_barrier(self._bases, self.world, self.rank, self._epoch,
+        npay = 0 if payload is None else int(payload.numel())
+        if npay and (reduced is None or reduced.numel() != npay or not payload.is_contiguous() or not reduced.is_contiguous()):
+            raise ValueError("barrier payload needs a contiguous `reduced` tensor of the same size")
+        from . import ops
+        with torch.cuda.device(self.device), ops._timed("p2p_barrier"):
+            self._check(self._lib.acn_p2p_barrier(self._bases, self.world, self.rank,
                                                   None if counts is None else C.c_void_p(counts.data_ptr()), n,
+                                                  None if not npay else C.c_void_p(payload.data_ptr()), npay,
+                                                  None if not npay else C.c_void_p(reduced.data_ptr()), float(scale), self.timeout_s,
                                                   C.c_void_p(torch.cuda.current_stream().cuda_stream)), "acn_p2p_barrier")
+        ops._count(1)
+
+    def allreduce_small(self, x: Tensor, scale: float = 1.0) -> Tensor:
+        """Sum of a small fp32 tensor (<= 1024 elements) over the ranks, identical bits on every rank."""
+        flat = x.reshape(-1).contiguous()
+        out = torch.empty_like(flat)
+        self.barrier(payload=flat, reduced=out, scale=scale)
+        return out.view_as(x)
+
+    def plan(self, K: int, owner: Sequence[int]) -> None:
+        """Slab layout of the exchange whose counts the last `barrier(counts=...)` gathered: fills row0_dev, seg_own,
+        point_own, live_own on the device (see `peer_layout` for the same arithmetic on the host)."""
+        from ._lib import i32
+        C = self._C
+        key = (K, tuple(owner))
+        if key not in self._owner_arr:
+            self._owner_arr[key] = (i32 * K)(*[int(o) for o in owner])
+        from . import ops
+        with torch.cuda.device(self.device), ops._timed("p2p_plan"):
+            self._check(self._lib.acn_p2p_plan(C.c_void_p(self._ptr), self.world, self.rank, K, self._owner_arr[key], self.cap,
+                                               C.c_void_p(self.row0_dev.data_ptr()), C.c_void_p(self.seg_own.data_ptr()),
+                                               C.c_void_p(self.point_own.data_ptr()), C.c_void_p(self.live_own.data_ptr()),
+                                               C.c_void_p(self.g.data_ptr()), C.c_void_p(self.status.data_ptr()),
+                                               C.c_void_p(torch.cuda.current_stream().cuda_stream)), "acn_p2p_plan")
+        ops._count(1)
 
     def table(self, n: int) -> List[List[int]]:
-        """Host copy of the exchanged counts, one row of ``n`` ints per rank (the step's one device->host read); raises if
-        a barrier timed out."""
+        """Host copy of the last exchanged counts, one row of ``n`` ints per rank (diagnostics / tests; a host sync)."""
         from ._lib import ACN_MAX_EXPERTS
         w = ACN_MAX_EXPERTS + 1
-        host = self.sync[16:32 + self.world * w].tolist()
-        if host[0] != 0:
-            raise RuntimeError("PeerExchange: a rank did not reach a barrier within its time limit")
-        return [host[16 + r * w:16 + r * w + n] for r in range(self.world)]
+        host = self.sync[32:32 + self.world * w].tolist()
+        return [host[r * w:r * w + n] for r in range(self.world)]
+
+    def check(self) -> None:
+        """One host read: raises if an exchange overflowed a slab or a pair list since the last check (the steps in
+        between then computed on truncated lists).  Call it every so often, and before trusting a checkpoint."""
+        st = int(self.status.item())
+        if st & 2:
+            raise RuntimeError(f"PeerExchange: an owner received more rows than the slab capacity {self.cap}; allocate a larger rows_cap")
+        if st & 4:
+            raise RuntimeError("PeerExchange: a rank's routed pair list overflowed its speculative capacity (acn_route_pack_capacity)")
 
     def close(self) -> None:
         if self._lib is None:
@@ -396,35 +491,89 @@ class PeerExchange:
         self._lib = None
 
 
+class SlabGradReducer:
+    """Sum of the replicated parameters' gradients (the background head: 643 floats) over the ranks WITHOUT a collective
+    kernel: the flat gradient rides as the payload of the barrier the expert-parallel backward needs anyway (between
+    "gradient rows pushed" and "owner backward"), so nothing runs beside the persistent tensor-core backward kernel.
+    ``wait()`` goes between backward() and optimizer.step(): it copies the reduced values into the .grad tensors, or - if
+    the backward did not pass that barrier with every gradient ready - performs the reduction on a barrier of its own."""
+
+    def __init__(self, ex: PeerExchange, params: Sequence[Tensor], scale: float = 1.0):
+        self.ex, self.scale = ex, float(scale)
+        self.params = [p for p in params if p.requires_grad]
+        n = sum(p.numel() for p in self.params)
+        self.flat = torch.zeros(max(n, 1), device=ex.device)
+        self.reduced = torch.zeros(max(n, 1), device=ex.device)
+        self._done = False
+        ex.reducer = self
+
+    def ready(self) -> bool:
+        return bool(self.params) and all(p.grad is not None for p in self.params)
+
+    def pack(self) -> Tensor:
+        torch.cat([p.grad.reshape(-1) for p in self.params], out=self.flat)
+        return self.flat
+
+    def mark_done(self) -> None:
+        self._done = True
+
+    def wait(self) -> None:
+        if not self.params or self.ex.world == 1:
+            self._done = False
+            return
+        if not self._done:
+            if not self.ready():
+                for p in self.params:  # a parameter without a gradient this step contributes zeros
+                    if p.grad is None:
+                        p.grad = torch.zeros_like(p)
+            self.ex.barrier(payload=self.pack(), reduced=self.reduced, scale=self.scale)
+        o = 0
+        for p in self.params:
+            p.grad.copy_(self.reduced[o:o + p.numel()].view_as(p))
+            o += p.numel()
+        self._done = False
+
+    def remove(self) -> None:
+        if self.ex.reducer is self:
+            self.ex.reducer = None
+
+
 class _PeerCombine(torch.autograd.Function):
-    """forward: publish this rank's results in its slab, barrier, pull the rows of this rank's pairs from their owners and
-    blend (out[point] += w*y).  backward: push w*d_out[point] into the owners' gradient rows, barrier, hand this rank's
-    gradient rows to the expert backward."""
+    """forward: barrier (every owner's results are in its slab), pull the rows of this rank's pairs from their owners and
+    blend (out[point] += w*y).  backward: push w*d_out[point] into the owners' gradient rows, barrier (carrying the shared
+    gradients when a SlabGradReducer is attached), hand this rank's gradient rows to the expert backward.  ``anchor`` is a
+    dummy input that requires grad, so that every rank takes part in the backward exchange even if its own experts are
+    frozen (config 4)."""
 
     @staticmethod
-    def forward(ctx, y_owner: Tensor, ex: PeerExchange, route_y, route_g, sel_point: Tensor, sel_weight: Tensor, offs: Tensor, K: int, P: int):
+    def forward(ctx, y_owner: Tensor, anchor: Tensor, ex: PeerExchange, route_y, route_g, sel_point: Tensor, sel_weight: Tensor, offs: Tensor,
+                K: int, P: int):
         from . import ops
-        R = y_owner.shape[0]
-        if R:
-            ex.y[:R].copy_(y_owner.detach())
-            ex.g[:R].zero_()  # padding rows of the gradient block stay zero (peers only write live rows, after this barrier)
         ex.barrier()
-        out = ops.a2a_pull_combine(route_y, sel_point, sel_weight, offs, K, P)
-        ctx.ex, ctx.route_g, ctx.K, ctx.R = ex, route_g, K, R
+        out = ops.a2a_pull_combine(route_y, sel_point, sel_weight, offs, K, P, row0_dev=ex.row0_dev)
+        ctx.ex, ctx.route_g, ctx.K = ex, route_g, K
         ctx.save_for_backward(sel_point, sel_weight, offs)
         return out
 
     @staticmethod
+    @torch.autograd.function.once_differentiable
     def backward(ctx, d_out):
         from . import ops
+        ex = ctx.ex
         sel_point, sel_weight, offs = ctx.saved_tensors
-        ops.a2a_push_grad(d_out, sel_point, sel_weight, offs, ctx.K, ctx.route_g)
-        ctx.ex.barrier()
-        return ctx.ex.g[:ctx.R], None, None, None, None, None, None, None, None
+        ops.a2a_push_grad(d_out, sel_point, sel_weight, offs, ctx.K, ctx.route_g, row0_dev=ex.row0_dev, cap_rows=ex.cap)
+        red = ex.reducer
+        if red is not None and ex.world > 1 and red.ready():
+            ex.barrier(payload=red.pack(), reduced=red.reduced, scale=red.scale)
+            red.mark_done()
+        else:
+            ex.barrier()
+        return ex.g, torch.zeros(1, device=d_out.device), None, None, None, None, None, None, None, None
 
 
 def peer_layout(table: Sequence[Sequence[int]], owner: Sequence[int], rank: int, tile: int = 128):
-    """Row layout of the owners' slabs for one exchange.  table[s][e] = routed samples rank s holds for expert e.
+    """Row layout of the owners' slabs for one exchange (the host statement of csrc/a2a.cu k_p2p_plan; the CPU tests and
+    the GPU test of the kernel both use it).  table[s][e] = routed samples rank s holds for expert e.
     An owner's slab holds its experts in order, each expert's block = the sub-blocks of source ranks 0..world-1 back to
     back, blocks padded to ``tile`` rows.  Returns (start[e] first row of e's block in its owner's slab, tot[e] rows of e
     over all sources, used[r] rows of rank r's slab, row0[e] first row of THIS rank's sub-block of e)."""
@@ -440,12 +589,13 @@ def peer_layout(table: Sequence[Sequence[int]], owner: Sequence[int], rank: int,
 
 def container_evaluate_p2p(model, pts, ex: PeerExchange, params=None) -> Tensor:
     """`container_evaluate_ep` with the data path in our own kernels: the routed samples of expert e are written by the
-    routing rank directly into the slab of e's owner (24 B rows over NVLink), the owner evaluates its experts in place,
-    and the routing rank pulls the [rgb,sigma] rows it needs (16 B) while blending.  Layout of an owner's slab: its
-    experts in order, each expert's block = the sub-blocks of source ranks 0..world-1, blocks padded to 128 rows: an
-    expert's rows are contiguous, so the received rows need no regrouping.  Per call: three barrier kernels (the
-    first one carries the (K+1) routed-sample counts of every rank: the only host read); the backward pass adds one push
-    and one barrier.  No NCCL call on the path."""
+    routing rank directly into the slab of e's owner (24 B rows over NVLink), the owner evaluates its experts in place
+    (results stored straight into the slab), and the routing rank pulls the [rgb,sigma] rows it needs (16 B) while
+    blending.  Layout of an owner's slab: its experts in order, each expert's block = the sub-blocks of source ranks
+    0..world-1, blocks padded to 128 rows: an expert's rows are contiguous, so the received rows need no regrouping.
+    Nothing is read back by the host: the counts travel with the opening barrier, `acn_p2p_plan` turns them into rows
+    and segment tables on the device, the pair lists keep their speculative capacity (`ex.check()` reports an overflow
+    after the fact).  Per call: three barrier kernels, one more in the backward pass.  No NCCL call on the path."""
     from . import ops
     world, rank = ex.world, ex.rank
     K = len(model.submodules)
@@ -453,38 +603,26 @@ def container_evaluate_p2p(model, pts, ex: PeerExchange, params=None) -> Tensor:
     mine = [e for e in range(K) if owner[e] == rank]
     dev = pts.device
     with torch.no_grad():
-        # no host read here: the pair list keeps its speculative capacity and is checked with the counts below
         pairs = ops.route_pack(pts, model.centroids_host(), K, model.boundary_margin, model.cluster_2d, sync=False)
         counts, offs = ops.a2a_count(pairs, K)
-        # counts travel with the step's opening barrier: nobody writes into a slab before its owner is done with the
-        # previous step, and every rank ends up with the whole table
-        ex.barrier(counts)
-        table = ex.table(K + 1)  # the one host read of the step
-        if any(row[K] < 0 for row in table):  # seen identically by every rank: all of them raise
-            raise RuntimeError(f"routing produced more (sample, expert) pairs than the speculative capacity {pairs.M} of the pair "
-                               f"list on some rank (margin {model.boundary_margin}): raise acn_route_pack_capacity")
-        M = table[rank][K]
-        start, tot, used, row0 = peer_layout(table, owner, rank, ops.ACN_TILE)
-        if max(used) > ex.cap:
-            raise RuntimeError(f"PeerExchange capacity {ex.cap} rows is too small for {max(used)} received rows")
-        route = {k: ops.make_route([ex.base(k, owner[e]) for e in range(K)], row0) for k in ("rows", "y", "g")}
-        sel_point, sel_weight = ops.a2a_push_rows(pts, pairs, K, offs, route["rows"], M)
+        # the counts travel with the step's opening barrier: nobody writes into a slab before its owner is done with the
+        # previous step, and every rank ends up with the whole table in its own slab
+        ex.barrier(counts=counts)
+        ex.plan(K, owner)
+        sel_point, sel_weight = ops.a2a_push_rows(pts, pairs, K, offs, ex.route("rows", K, owner), pairs.M, row0_dev=ex.row0_dev,
+                                                  cap_rows=ex.cap)
         ex.barrier()
-        R = used[rank]
-        point = torch.arange(R, device=dev, dtype=torch.int32)
-        segs = [0]
+    if mine:
+        spec_all = model.expert_spec()
+        spec = ops.ExpertSpec(spec_all.grid, [spec_all.box_min[e] for e in mine], [spec_all.extent[e] for e in mine])
+        tables = [model.submodules[e].xyz_encoder.hash_table for e in mine]
+        mlp: List[Tensor] = []
         for e in mine:
-            segs.append(start[e] + (tot[e] + ops.ACN_TILE - 1) // ops.ACN_TILE * ops.ACN_TILE)
-            point[start[e] + tot[e]:segs[-1]] = -1
-    if R and mine:
-        # segment table through a pinned staging buffer: a pageable host->device copy would drain the stream (and with it
-        # wait for every peer to reach the barrier above) before the expert kernels could even be enqueued
-        ex._seg_pin[:len(segs)] = torch.tensor(segs, dtype=torch.int32)
-        seg_dev = ex._seg_pin[:len(segs)].to(dev, non_blocking=True)
-        y_owner = _evaluate_local(model, params, ex.rows[:R], mine, point, segs, seg_dev)
+            mlp.extend(model.submodules[e].mlp_tensors(model._sub_params(params, e)))
+        # the owner's rows are its slab, row id == point id: results are stored in place (no blend, no copy)
+        pl = ops.PairList(ex.cap, ex.point_own, None, ex.seg_own[:len(mine) + 1], None, store_out=ex.y)
+        y_owner = ops.ngp_experts(ops.PointSet(x6=ex.rows), pl, spec, tables, mlp)
     else:
-        y_owner = torch.zeros(R, 4, device=dev)
-    if torch.is_grad_enabled() and not y_owner.requires_grad:
-        # every rank takes part in the backward exchange even if its own experts are frozen (config 4)
-        y_owner = y_owner + torch.zeros(1, device=dev, requires_grad=True)
-    return _PeerCombine.apply(y_owner, ex, route["y"], route["g"], sel_point, sel_weight, offs, K, pts.P)
+        y_owner = ex.y
+    anchor = torch.zeros(1, device=dev, requires_grad=torch.is_grad_enabled())
+    return _PeerCombine.apply(y_owner, anchor, ex, ex.route("y", K, owner), ex.route("g", K, owner), sel_point, sel_weight, offs, K, pts.P)

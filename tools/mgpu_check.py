@@ -103,14 +103,14 @@ for n, p in ep_m.named_parameters():
     mine = (n.startswith("submodules.") and owner[int(n.split(".")[1])] == rank) or n.startswith("bg_mlp")
     if mine:
         perr = max(perr, (p.detach() - ref_p[n].detach()).abs().max().item())
-stats = torch.tensor([abs(mean_loss.item() - ref_loss.item()), abs(ep_opt._coef.item() - ref_opt._coef.item()) / ref_opt._coef.item(), perr],
+stats = torch.tensor([abs(mean_loss.item() - ref_loss.item()), abs(ep_opt.clip_coef.item() - ref_opt.clip_coef.item()) / ref_opt.clip_coef.item(), perr],
                      device=dev)
 dist.all_reduce(stats, op=dist.ReduceOp.MAX)
-good = stats[0].item() <= 1e-6 and stats[1].item() <= 1e-4 and ref_opt._coef.item() < 0.999 and stats[2].item() <= 2e-4
+good = stats[0].item() <= 1e-6 and stats[1].item() <= 1e-4 and ref_opt.clip_coef.item() < 0.999 and stats[2].item() <= 2e-4
 ok = ok and good
 if rank == 0:
-    print(f"expert-parallel optimisation step, world {world}: loss diff {stats[0].item():.1e}, clip coefficient {ep_opt._coef.item():.6f} vs "
-          f"{ref_opt._coef.item():.6f} (rel {stats[1].item():.1e}), owner parameters max-abs diff {stats[2].item():.1e} -> {'ok' if good else 'MISMATCH'}",
+    print(f"expert-parallel optimisation step, world {world}: loss diff {stats[0].item():.1e}, clip coefficient {ep_opt.clip_coef.item():.6f} vs "
+          f"{ref_opt.clip_coef.item():.6f} (rel {stats[1].item():.1e}), owner parameters max-abs diff {stats[2].item():.1e} -> {'ok' if good else 'MISMATCH'}",
           flush=True)
 ep_m.set_expert_parallel(False)
 
