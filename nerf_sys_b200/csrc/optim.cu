@@ -72,6 +72,7 @@ struct MultiDesc {
   AcnAdamTensor t[ACN_ADAM_MAX_TENSORS];
   int blk0[ACN_ADAM_MAX_TENSORS + 1];  // first block of each tensor
   int count;
+  unsigned long long vec;  // bit i: every pointer of tensor i is 16-byte aligned (float4 path); else scalar
 };
 
 __device__ __forceinline__ int find_tensor(const MultiDesc& d, int b) {
@@ -92,7 +93,7 @@ __global__ void __launch_bounds__(256) k_sumsq_multi(const __grid_constant__ Mul
   if (!tensor_live(d.t[t], live)) return;  // block-uniform: a tensor without a gradient this step (torch: p.grad is None)
   const int nb = d.blk0[t + 1] - d.blk0[t], b = blockIdx.x - d.blk0[t];
   const float* __restrict__ x = d.t[t].grad;
-  const int64_t n = d.t[t].n, n4 = n >> 2;
+  const int64_t n = d.t[t].n, n4 = ((d.vec >> t) & 1ull) ? (n >> 2) : 0;
   const float4* x4 = reinterpret_cast<const float4*>(x);
   float s = 0.f;
   for (int64_t i = b * 256 + threadIdx.x; i < n4; i += (int64_t)nb * 256) {
@@ -167,7 +168,7 @@ __global__ void __launch_bounds__(256) k_adam_multi(const __grid_constant__ Mult
   const AdamK k = sk;
   const float gs = coef ? __ldg(coef) : 1.f;
   const int nb = d.blk0[t + 1] - d.blk0[t], b = blockIdx.x - d.blk0[t];
-  const int64_t n = a.n, n4 = n >> 2;
+  const int64_t n = a.n, n4 = ((d.vec >> t) & 1ull) ? (n >> 2) : 0;
   float4* p4 = reinterpret_cast<float4*>(a.param);
   float4* g4 = reinterpret_cast<float4*>(const_cast<float*>(a.grad));
   float4* m4 = reinterpret_cast<float4*>(a.exp_avg);
@@ -179,8 +180,6 @@ __global__ void __launch_bounds__(256) k_adam_multi(const __grid_constant__ Mult
   }
   for (int64_t i = b * 256 + threadIdx.x; i < n4; i += (int64_t)nb * 256) {
     float4 pa = p4[i], gb = g4[i], mc = m4[i], vd = v4[i];
-    // the gradient line was just read: writing zeros over it costs the write-back only and replaces the next step's 128 MiB memset
-    if (zero) g4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     adam_one(pa.x, gb.x, mc.x, vd.x, k, gs);
     adam_one(pa.y, gb.y, mc.y, vd.y, k, gs);
     adam_one(pa.z, gb.z, mc.z, vd.z, k, gs);
@@ -188,6 +187,12 @@ __global__ void __launch_bounds__(256) k_adam_multi(const __grid_constant__ Mult
     p4[i] = pa;
     m4[i] = mc;
     v4[i] = vd;
+    // Zero the gradient it just read (replaces the next step's 128 MiB memset per table).  The store must not be issued while
+    // the line's own fill is still in flight: a plain `g4[i] = 0` right behind the load runs the kernel at 2.1 TB/s instead of
+    // 6.4 TB/s (tools/adam_bench.py, profiles/r2_adam_zero_store.txt).  Naming loaded values as operands holds it back until
+    // the data has arrived.
+    if (zero)
+      asm volatile("{ .reg .f32 z; mov.f32 z, 0f00000000; st.global.v4.f32 [%0], {z, z, z, z}; }" ::"l"(g4 + i), "f"(pa.x), "f"(vd.w) : "memory");
   }
   for (int64_t i = (n4 << 2) + b * 256 + threadIdx.x; i < n; i += (int64_t)nb * 256) {
     float g = a.grad[i];
@@ -200,11 +205,15 @@ static int fill_multi(MultiDesc& d, const AcnAdamTensor* tensors, int count, con
   ACN_REQUIRE(tensors && count >= 1 && count <= ACN_ADAM_MAX_TENSORS, "%s: 1..%d tensors per call", who, ACN_ADAM_MAX_TENSORS);
   int64_t per_wave = (int64_t)num_sms_cached() * 8;
   int blk = 0;
+  d.vec = 0;
   for (int i = 0; i < count; ++i) {
     d.t[i] = tensors[i];
     ACN_REQUIRE(tensors[i].grad && tensors[i].n >= 0, "%s: tensor %d has no gradient pointer", who, i);
-    ACN_REQUIRE((((uintptr_t)tensors[i].param | (uintptr_t)tensors[i].grad | (uintptr_t)tensors[i].exp_avg | (uintptr_t)tensors[i].exp_avg_sq) & 15) == 0,
-                "%s: tensor %d is not 16-byte aligned", who, i);
+    // a gradient that is a view into a flat buffer (the PE-MLP's weight-gradient slab) may sit at any 4-byte offset
+    ACN_REQUIRE((((uintptr_t)tensors[i].param | (uintptr_t)tensors[i].grad | (uintptr_t)tensors[i].exp_avg | (uintptr_t)tensors[i].exp_avg_sq) & 3) == 0,
+                "%s: tensor %d is not 4-byte aligned", who, i);
+    if ((((uintptr_t)tensors[i].param | (uintptr_t)tensors[i].grad | (uintptr_t)tensors[i].exp_avg | (uintptr_t)tensors[i].exp_avg_sq) & 15) == 0)
+      d.vec |= 1ull << i;
     int64_t nb = (tensors[i].n / 4 + 1023) / 1024;  // >= 4 float4 per thread before adding blocks
     if (nb < 1) nb = 1;
     if (nb > per_wave) nb = per_wave;

@@ -117,7 +117,7 @@ class PeMlpFn(torch.autograd.Function):
         return y
 
     @staticmethod
-    @torch.autograd.function.once_differentiable
+    @ops.first_order
     def backward(ctx, d_out: Tensor):
         L = lib()
         y, *ws = ctx.saved_tensors

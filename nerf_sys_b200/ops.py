@@ -7,10 +7,28 @@ libacnerf_sm100a.so; inputs must be CUDA fp32 tensors - CPU tensors raise.
 from __future__ import annotations
 
 import ctypes as C
+import functools
 from typing import List, Optional, Sequence, Tuple
 
 import torch
-from torch.autograd.function import once_differentiable
+
+
+def first_order(backward):
+    """Decorator for the `backward` of every op in this package.  The engine evaluates a backward pass with grad mode ON
+    only when the caller asked for a differentiable gradient (`create_graph=True`: algo='maml', meta_core.py:54-59); the
+    sm_100a kernels are first-order, so that request fails here instead of silently returning gradients without a graph.
+    (`torch.autograd.function.once_differentiable` does not do this: it only raises when such a gradient is differentiated
+    AND an incoming gradient already carried a graph.)"""
+
+    @functools.wraps(backward)
+    def wrapper(ctx, *grads):
+        if torch.is_grad_enabled():
+            raise RuntimeError("the sm_100a ops are first-order: autograd.grad(..., create_graph=True) (algo='maml') is not supported - "
+                               "use algo='fomaml' or 'reptile'")
+        return backward(ctx, *grads)
+
+    return wrapper
+
 
 from . import _lib
 from ._lib import (ACN_MAX_EXPERTS, ACN_NGP_LAYERS, ACN_TILE, AcnA2aRoute, AcnGridDesc, AcnNgpExpert, AcnNgpExpertGrads, AcnPairs,
@@ -512,7 +530,7 @@ class A2aCombineFn(torch.autograd.Function):
         return out
 
     @staticmethod
-    @once_differentiable  # first-order ops: create_graph=True (algo='maml', meta_core.py:54-59) fails loudly instead of silently dropping terms
+    @first_order
     def backward(ctx, d_out):
         pt, wt = ctx.saved_tensors
         g = _f32(d_out, "d_out")
@@ -555,7 +573,7 @@ class HashGridFn(torch.autograd.Function):
         return y.reshape(*x01.shape[:-1], g.levels * g.features)
 
     @staticmethod
-    @once_differentiable  # first-order ops: create_graph=True (algo='maml', meta_core.py:54-59) fails loudly instead of silently dropping terms
+    @first_order
     def backward(ctx, dy):
         (x,) = ctx.saved_tensors
         g = ctx.g
@@ -653,7 +671,7 @@ class NgpEncodeFn(torch.autograd.Function):
         return enc
 
     @staticmethod
-    @once_differentiable  # first-order ops: create_graph=True (algo='maml', meta_core.py:54-59) fails loudly instead of silently dropping terms
+    @first_order
     def backward(ctx, d_enc):
         L = lib()
         tb = ctx.saved_tensors
@@ -763,7 +781,7 @@ class NgpMlpFn(torch.autograd.Function):
         return out
 
     @staticmethod
-    @once_differentiable  # first-order ops: create_graph=True (algo='maml', meta_core.py:54-59) fails loudly instead of silently dropping terms
+    @first_order
     def backward(ctx, d_out):
         L = lib()
         enc, *ws = ctx.saved_tensors
@@ -879,7 +897,7 @@ class NgpExpertsTcFn(torch.autograd.Function):
         return out
 
     @staticmethod
-    @once_differentiable  # first-order ops: create_graph=True (algo='maml', meta_core.py:54-59) fails loudly instead of silently dropping terms
+    @first_order
     def backward(ctx, d_out):
         L = lib()
         pts, pairs, spec = ctx.pts, ctx.pairs, ctx.spec
@@ -971,7 +989,7 @@ class BgFn(torch.autograd.Function):
         return rgb
 
     @staticmethod
-    @once_differentiable  # first-order ops: create_graph=True (algo='maml', meta_core.py:54-59) fails loudly instead of silently dropping terms
+    @first_order
     def backward(ctx, d_rgb):
         L = lib()
         w0, b0, w1, b1 = ctx.saved_tensors
@@ -1023,7 +1041,7 @@ class CompositeFn(torch.autograd.Function):
         return rgb, depth, w, acc
 
     @staticmethod
-    @once_differentiable  # first-order ops: create_graph=True (algo='maml', meta_core.py:54-59) fails loudly instead of silently dropping terms
+    @first_order
     def backward(ctx, g_rgb, g_depth, g_w, g_acc):
         rs, tt, b = ctx.saved_tensors
         N, S = tt.shape
@@ -1084,7 +1102,7 @@ class MseFn(torch.autograd.Function):
         return loss.reshape(())
 
     @staticmethod
-    @once_differentiable  # first-order ops: create_graph=True (algo='maml', meta_core.py:54-59) fails loudly instead of silently dropping terms
+    @first_order
     def backward(ctx, g):
         (d_pred,) = ctx.saved_tensors
         return d_pred * g, None, None

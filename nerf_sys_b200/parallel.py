@@ -24,6 +24,11 @@ import torch.distributed as dist
 Tensor = torch.Tensor
 
 
+def _first_order_backward(fn):
+    from .ops import first_order  # deferred: ops loads the shared library
+    return first_order(fn)
+
+
 # ---------------------------------------------------------------------------------------------
 # partitions
 # ---------------------------------------------------------------------------------------------
@@ -556,7 +561,7 @@ class _PeerCombine(torch.autograd.Function):
         return out
 
     @staticmethod
-    @torch.autograd.function.once_differentiable
+    @_first_order_backward
     def backward(ctx, d_out):
         from . import ops
         ex = ctx.ex
