@@ -478,6 +478,7 @@ def parity_check(ctx, tr):
     prev = ops.set_mlp_math("fp32")
     model, ex = tr.model, tr.ex
     owner = PL.expert_owner(K_EXPERTS, world)
+    PL.sync_expert_params(model)  # the timed steps trained each expert on its owner only: every rank gets the owners' copies
     rays = SY.aerial_rays(N_RAYS, tr.aabb, seed=4000 + rank).to(dev)
     g = torch.Generator().manual_seed(40 + rank)
     u, cot = torch.rand(N_RAYS, S_TRAIN, generator=g).to(dev), torch.randn(N_RAYS * S_TRAIN, 4, generator=g).to(dev)
@@ -529,8 +530,8 @@ def parity_check(ctx, tr):
         ops.release_grad_buffer(p, clean=False)
     del tab_sum, mlp_ref, y, y_ref
     torch.cuda.empty_cache()
-    # (2) one optimisation step, fresh models on both sides (clip active: max_norm small)
-    Nc = 2048
+    # (2) one optimisation step, fresh models on both sides (clip active: max_norm far below the gradient norm)
+    Nc, CLIP_CHECK = 2048, 1e-4
     rays = SY.aerial_rays(Nc, tr.aabb, seed=4100 + rank).to(dev)
     g = torch.Generator().manual_seed(60 + rank)
     u, gt = torch.rand(Nc, S_TRAIN, generator=g).to(dev), torch.rand(Nc, 3, generator=g).to(dev)
@@ -539,7 +540,7 @@ def parity_check(ctx, tr):
         dist.all_gather_into_tensor(dst, src.contiguous())
     ref_m, _ = build_container(dev, seed=21)
     ref_m.train()
-    ref_opt = build_optimizer(ref_m, max_grad_norm=0.02)
+    ref_opt = build_optimizer(ref_m, max_grad_norm=CLIP_CHECK)
     rgb, *_ = render_rays(ref_m, all_rays, ray_samples=S_TRAIN, u=all_u)
     ref_loss = ops.mse_loss(rgb, all_gt, "identity")
     ref_loss.backward()
@@ -548,7 +549,7 @@ def parity_check(ctx, tr):
     ep_m.train()
     ep_m.set_expert_parallel(True, exchange=ex)
     groups, shared = PL.owned_param_groups(ep_m)
-    ep_opt = FusedAdam([{"params": gr["params"], "lr": LRS[n]} for n, gr in groups.items()], max_grad_norm=0.02).shard_grad_norm(None, shared, exchange=ex)
+    ep_opt = FusedAdam([{"params": gr["params"], "lr": LRS[n]} for n, gr in groups.items()], max_grad_norm=CLIP_CHECK).shard_grad_norm(None, shared, exchange=ex)
     bind_expert_liveness(ep_opt, ep_m)
     red = PL.SlabGradReducer(ex, shared, scale=1.0)
     rgb, *_ = render_rays(ep_m, rays, ray_samples=S_TRAIN, u=u)

@@ -338,6 +338,30 @@ def owned_param_groups(model, group=None):
     return groups, shared
 
 
+@torch.no_grad()
+def sync_expert_params(model, group=None) -> None:
+    """Under expert parallelism only the owner's copy of an expert is trained; every other rank's copy goes stale.  Before
+    anything that needs the whole container on one rank - a checkpoint written by rank 0, replicated-expert rendering
+    (`render_image_sharded`), evaluation - broadcast each expert's tensors from its owner (one flat message per expert)."""
+    world, rank = _world(group)
+    if world == 1:
+        return
+    owner = expert_owner(len(model.submodules), world)
+    for e, sub in enumerate(model.submodules):
+        ps = [p.data for p in sub.parameters()]
+        small = [p for p in ps if p.numel() < (1 << 20)]
+        for p in ps:
+            if p.numel() >= (1 << 20):  # hash table: in place, no staging copy
+                dist.broadcast(p, src=dist.get_global_rank(group, owner[e]) if group is not None else owner[e], group=group)
+        if small:
+            flat = torch.cat([p.reshape(-1) for p in small])
+            dist.broadcast(flat, src=dist.get_global_rank(group, owner[e]) if group is not None else owner[e], group=group)
+            o = 0
+            for p in small:
+                p.copy_(flat[o:o + p.numel()].view_as(p))
+                o += p.numel()
+
+
 # ---------------------------------------------------------------------------------------------
 # the same exchange through NVLink peer memory: the kernels write / read the owner's buffers themselves
 # ---------------------------------------------------------------------------------------------

@@ -251,3 +251,35 @@ def test_peer_layout_tiles_every_slab_without_overlap():
             for e in mine:  # the sources tile the expert's block exactly
                 rows = sum(b - a for a, b, ee in spans if ee == e)
                 assert rows == tot[e]
+
+
+# ---- owner -> everyone parameter sync ---------------------------------------------------------------
+def _sync_worker(rank, world):
+    import torch.nn as nn
+
+    class Sub(nn.Module):
+        def __init__(self, big):
+            super().__init__()
+            self.table = nn.Parameter(torch.zeros((1 << 20) + 8 if big else 64, 2))
+            self.w, self.b = nn.Parameter(torch.zeros(5, 3)), nn.Parameter(torch.zeros(5))
+
+    class M(nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.submodules = nn.ModuleList([Sub(big=(e == 1)) for e in range(5)])
+
+    m = M()
+    owner = PL.expert_owner(5, world)
+    with torch.no_grad():  # every rank "trained" every copy differently; only the owner's counts
+        for e, sub in enumerate(m.submodules):
+            for j, p in enumerate(sub.parameters()):
+                p.fill_(1000.0 * rank + 10.0 * e + j)
+    PL.sync_expert_params(m)
+    for e, sub in enumerate(m.submodules):
+        for j, p in enumerate(sub.parameters()):
+            assert float(p.min()) == float(p.max()) == 1000.0 * owner[e] + 10.0 * e + j, (rank, e, j)
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_sync_expert_params_broadcasts_from_the_owner(world):
+    _spawn(_sync_worker, world)
