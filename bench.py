@@ -712,7 +712,9 @@ def adapt_c4(ctx, steps=10, warmup=3):
     (nadir rays over those two tiles); the other six experts get no sample, so their parameters and Adam state are not touched
     (asserted bit-unchanged: the device-side liveness flags stand in for `p.grad is None`) and the step costs two experts' worth of
     scatter and optimiser traffic.  Same graph-captured step as the headline; at N > 1 the experts are sharded."""
-    tr = ContainerTrainer(ctx)
+    # every ray of every rank lands in experts 2 and 5: their owners receive world x 4096 x 96 rows each (a deliberately
+    # unbalanced exchange), so the slab is sized for that instead of the 3x-balanced default
+    tr = ContainerTrainer(ctx, rows_cap=max(3, ctx.world + 1) * N_RAYS * S_TRAIN)
     model = tr.model
     cent = model.centroids.detach().cpu()
     aabb = tr.aabb

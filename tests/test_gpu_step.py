@@ -33,7 +33,9 @@ def test_routing_of_nan_and_inf_positions_matches_torch(K):
     w, _ = ops.routing(ops.PointSet(x6=x6.to(DEV)), cent.reshape(-1).tolist(), K, 1.05, True)
     member_ref = torch.nan_to_num(w_ref, nan=0.0) > 0
     assert not member_ref[bad].any()  # the reference gives a non-finite point no expert
-    assert torch.equal((torch.nan_to_num(w.cpu(), nan=0.0) > 0), member_ref)
+    member = torch.nan_to_num(w.cpu(), nan=0.0) > 0
+    rows = (member != member_ref).any(1).nonzero().squeeze(1)
+    assert rows.numel() == 0, (rows[:8].tolist(), x[rows[:8]].tolist(), w.cpu()[rows[:8]].tolist(), w_ref[rows[:8]].tolist())
     pairs = ops.route_pack(ops.PointSet(x6=x6.to(DEV)), cent.reshape(-1).tolist(), K, 1.05, True)
     pt = pairs.point.cpu()
     for k in range(K):
