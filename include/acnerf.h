@@ -43,6 +43,13 @@ int acn_version(void);                  /* ABI version, currently 1 */
 const char* acn_last_error(void);       /* thread-local, never NULL */
 int acn_device_ok(int device);          /* ACN_OK iff `device` is compute capability 10.x */
 int acn_num_sms(int device);            /* multiprocessor count (148 on B200), <0 on error */
+/* Launch-sizing hints of the CALLING THREAD (no device state; launches read them on the host at launch time).  Returns
+ * the previous value, -1 for an unknown key.  Tuning knobs only: results are identical for every value.
+ *   ACN_HINT_GATHER_LEVELS = 1, 2, 4, 8 or 16: levels of the hash grid one thread of acn_ngp_encode_fwd walks
+ *   (0 = default: 8 for lists of >= 4 Mi slots, else 4). */
+#define ACN_HINT_GATHER_LEVELS 1
+#define ACN_HINT_COUNT 4
+int acn_launch_hint(int key, int value);
 
 /* ---- descriptors -------------------------------------------------------- */
 /* models/encodings.py:180-286 (HashGridEncoder ctor): levels, features_per_level,

@@ -56,6 +56,7 @@ ACN_MAX_PEERS = 16
 ACN_P2P_PAYLOAD_FLOATS = 1024
 ACN_P2P_SYNC_BYTES = 4096 + 2 * ACN_MAX_PEERS * ACN_P2P_PAYLOAD_FLOATS * 4
 ACN_ADAM_ZERO_GRAD = 0x100
+ACN_HINT_GATHER_LEVELS = 1
 P = C.POINTER
 fp = P(f32)  # host float arrays
 
@@ -65,6 +66,7 @@ SIGNATURES = {
     "acn_last_error": (C.c_char_p, []),
     "acn_device_ok": (C.c_int, [C.c_int]),
     "acn_num_sms": (C.c_int, [C.c_int]),
+    "acn_launch_hint": (C.c_int, [C.c_int, C.c_int]),
     "acn_ray_directions": (C.c_int, [C.c_int, C.c_int, f32, f32, f32, f32, C.c_int, vp, vp]),
     "acn_get_rays": (C.c_int, [vp, i64, fp, fp, f32, f32, f32, f32, vp, vp]),
     "acn_raygen": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, f32, f32, f32, f32, C.c_int, fp, fp, f32, f32, vp, vp]),

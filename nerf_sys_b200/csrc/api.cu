@@ -29,9 +29,20 @@ int num_sms_cached() {
   return cached_sms;
 }
 
+static thread_local int g_hints[ACN_HINT_COUNT] = {0};
+
+int launch_hint(int key) { return (key >= 0 && key < ACN_HINT_COUNT) ? g_hints[key] : 0; }
+
 }  // namespace acn
 
 extern "C" {
+
+int acn_launch_hint(int key, int value) {
+  if (key < 0 || key >= ACN_HINT_COUNT) return -1;
+  int prev = acn::g_hints[key];
+  acn::g_hints[key] = value;
+  return prev;
+}
 
 int acn_version(void) { return 1; }
 

@@ -10,6 +10,7 @@ namespace acn {
 
 void set_error(const char* fmt, ...);
 int num_sms_cached();
+int launch_hint(int key);  // thread-local launch-sizing hints (acn_launch_hint)
 
 #define ACN_REQUIRE(cond, ...)          \
   do {                                  \

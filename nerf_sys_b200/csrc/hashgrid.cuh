@@ -118,6 +118,61 @@ __device__ __forceinline__ float2 level_encode(const float2* __restrict__ table,
   return o;
 }
 
+// The same gather split in two, branch-free, so that a thread can have the reads of several levels in flight:
+// level_fetch issues 4 LDG.128 of the aligned 16-byte pairs that hold rows[0..3] (for even ix the x-neighbour's row is the
+// other half of the pair; for odd ix that half is simply unused - same sector, same wavefront as an LDG.64) plus, predicated
+// on odd ix, 4 LDG.64 of rows[4..7]; level_blend picks the halves and interpolates exactly as level_encode does.
+struct LevelFetch {
+  float4 q[4];
+  float2 h[4];
+  uint32_t par;  // bit i: rows[i] is the odd half of its pair; bit 4: ix is odd
+};
+__device__ __forceinline__ void level_fetch(const float2* __restrict__ table, const Cell& c, uint32_t mask, uint32_t base, LevelFetch& f) {
+  uint32_t rows[8];
+  corner_rows(c, mask, base, rows);
+  const float4* t4 = reinterpret_cast<const float4*>(table);
+  const bool odd_x = (c.ix & 1u) != 0u;
+  f.par = odd_x ? 16u : 0u;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    f.q[i] = __ldg(t4 + (rows[i] >> 1));
+    f.par |= (rows[i] & 1u) << i;
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    f.h[i] = make_float2(0.f, 0.f);
+    if (odd_x) f.h[i] = __ldg(table + rows[i + 4]);
+  }
+}
+__device__ __forceinline__ float2 level_blend(const Cell& c, const LevelFetch& t) {
+  float2 f[8];
+  const bool odd_x = (t.par & 16u) != 0u;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const bool odd = (t.par >> i) & 1u;
+    const float2 lo = make_float2(t.q[i].x, t.q[i].y), hi = make_float2(t.q[i].z, t.q[i].w);
+    f[i] = odd ? hi : lo;
+    f[i + 4] = odd_x ? t.h[i] : (odd ? lo : hi);
+  }
+  float ax = 1.f - c.wx, ay = 1.f - c.wy, az = 1.f - c.wz;
+  float2 c00, c01, c10, c11, c0, c1, o;
+  c00.x = f[0].x * ax + f[4].x * c.wx;
+  c00.y = f[0].y * ax + f[4].y * c.wx;
+  c01.x = f[1].x * ax + f[5].x * c.wx;
+  c01.y = f[1].y * ax + f[5].y * c.wx;
+  c10.x = f[2].x * ax + f[6].x * c.wx;
+  c10.y = f[2].y * ax + f[6].y * c.wx;
+  c11.x = f[3].x * ax + f[7].x * c.wx;
+  c11.y = f[3].y * ax + f[7].y * c.wx;
+  c0.x = c00.x * ay + c10.x * c.wy;
+  c0.y = c00.y * ay + c10.y * c.wy;
+  c1.x = c01.x * ay + c11.x * c.wy;
+  c1.y = c01.y * ay + c11.y * c.wy;
+  o.x = c0.x * az + c1.x * c.wz;
+  o.y = c0.y * az + c1.y * c.wz;
+  return o;
+}
+
 // Scatter of one level's upstream gradient into the fp32 gradient table.
 __device__ __forceinline__ void level_scatter(float2* __restrict__ gtable, const Cell& c, uint32_t mask, uint32_t base,
                                               int interp, float2 g) {

@@ -50,31 +50,78 @@ __device__ __forceinline__ int find_expert(const int* s_seg, int E, int64_t m) {
 }
 
 // ---------------------------------------------------------------------------------------
-// hash-grid forward over pairs: grid.y = level
+// hash-grid forward over pairs
 // ---------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_ngp_hash_fwd(PointSrc src, const int32_t* __restrict__ pair_point, const int32_t* __restrict__ seg,
-                                                      int64_t M_ident, ExpertTable tab, GridParams g, float* __restrict__ enc, int64_t ld) {
+// One thread = one pair slot x LG consecutive levels.  Everything that does not depend on the level - the slot's point id,
+// its expert, o + d*t, the three IEEE divisions of the unit-cube map - is computed once per LG levels (the one-level form
+// spent 330 warp instructions per level, 72 % issue-slot utilisation: profiles/r2_hash_fwd_ncu.md), and the table reads of the
+// LG levels are issued together, branch-free (level_fetch), before any of them is consumed.
+// CTA order = expert-major, then level group, then 256-slot chunk: the CTA waves walk one expert's LG x 8 MiB slabs at a time,
+// so the hot set in L2 is LG x 8 MiB instead of "one level of every expert" (64 MiB with 8 experts, which the streaming
+// encoding writes kept evicting).
+template <int LG>
+__global__ void __launch_bounds__(256, 4) k_ngp_hash_fwd(PointSrc src, const int32_t* __restrict__ pair_point, const int32_t* __restrict__ seg,
+                                                         int64_t M_ident, ExpertTable tab, GridParams g, float* __restrict__ enc, int64_t ld) {
+  constexpr int NLG = 16 / LG;
   __shared__ int s_seg[ACN_MAX_EXPERTS + 1];
   if (threadIdx.x <= tab.E) s_seg[threadIdx.x] = seg ? min(seg[threadIdx.x], (int)M_ident) : (threadIdx.x == 0 ? 0 : (int)M_ident);  // never past the capacity
   __syncthreads();
-  int64_t M = seg ? s_seg[tab.E] : M_ident;
-  int l = blockIdx.y;
-  uint32_t mask = (1u << g.log2_T) - 1u, base = (uint32_t)l << g.log2_T;
-  for (int64_t m = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; m < M; m += (int64_t)gridDim.x * blockDim.x) {
-    int64_t p = pair_point ? (int64_t)pair_point[m] : m;
-    float2 v = make_float2(0.f, 0.f);
-    if (p >= 0) {
-      int e = seg ? find_expert(s_seg, tab.E, m) : 0;
-      const AcnNgpExpert& ex = tab.ex[e];
-      float x, y, z;
-      load_xyz(src, p, x, y, z);
-      Cell c = make_cell(to_unit(x, ex.box_min[0], ex.extent[0]), to_unit(y, ex.box_min[1], ex.extent[1]),
-                         to_unit(z, ex.box_min[2], ex.extent[2]), g.res[l], g.interp);
-      v = level_encode(reinterpret_cast<const float2*>(ex.table), c, mask, base, g.interp);
+  const uint32_t mask = (1u << g.log2_T) - 1u;
+  int jobs = 0;
+  for (int e = 0; e < tab.E; ++e) jobs += ((s_seg[e + 1] - s_seg[e] + 255) >> 8) * NLG;
+  for (int job = blockIdx.x; job < jobs; job += gridDim.x) {  // CTA-uniform
+    // job -> (expert, level group, 256-slot chunk), expert-major
+    int b = job, e = 0, n = 0;
+    for (; e < tab.E; ++e) {
+      n = (s_seg[e + 1] - s_seg[e] + 255) >> 8;
+      if (b < n * NLG) break;
+      b -= n * NLG;
     }
-    // streaming stores: the encoding is read once by the next kernel and must not push the table slabs out of L2
-    __stcs(enc + (int64_t)(2 * l) * ld + m, v.x);
-    __stcs(enc + (int64_t)(2 * l + 1) * ld + m, v.y);
+    const int lg = b / n, c = b - lg * n, l0 = lg * LG;
+    const int64_t m = (int64_t)s_seg[e] + (c << 8) + threadIdx.x;
+    if (m >= s_seg[e + 1]) continue;
+    const int64_t p = pair_point ? (int64_t)pair_point[m] : m;
+    if (p < 0) {
+#pragma unroll
+      for (int j = 0; j < LG; ++j) {
+        __stcs(enc + (int64_t)(2 * (l0 + j)) * ld + m, 0.f);
+        __stcs(enc + (int64_t)(2 * (l0 + j) + 1) * ld + m, 0.f);
+      }
+      continue;
+    }
+    const AcnNgpExpert& ex = tab.ex[e];
+    const float2* __restrict__ table = reinterpret_cast<const float2*>(ex.table);
+    float x, y, z;
+    load_xyz(src, p, x, y, z);
+    const float ux = to_unit(x, ex.box_min[0], ex.extent[0]), uy = to_unit(y, ex.box_min[1], ex.extent[1]),
+                uz = to_unit(z, ex.box_min[2], ex.extent[2]);
+    if (g.interp == 2) {
+#pragma unroll
+      for (int j = 0; j < LG; ++j) {
+        Cell cc = make_cell(ux, uy, uz, g.res[l0 + j], 2);
+        float2 v = level_encode(table, cc, mask, (uint32_t)(l0 + j) << g.log2_T, 2);
+        __stcs(enc + (int64_t)(2 * (l0 + j)) * ld + m, v.x);
+        __stcs(enc + (int64_t)(2 * (l0 + j) + 1) * ld + m, v.y);
+      }
+      continue;
+    }
+    // two levels in flight: the reads of level j+1 are issued before level j is blended
+    Cell c0 = make_cell(ux, uy, uz, g.res[l0], g.interp), c1 = c0;
+    LevelFetch f0, f1;
+    level_fetch(table, c0, mask, (uint32_t)l0 << g.log2_T, f0);
+#pragma unroll
+    for (int j = 0; j < LG; ++j) {
+      if (j + 1 < LG) {
+        c1 = make_cell(ux, uy, uz, g.res[l0 + j + 1], g.interp);
+        level_fetch(table, c1, mask, (uint32_t)(l0 + j + 1) << g.log2_T, f1);
+      }
+      const float2 v = level_blend(c0, f0);
+      // streaming stores: the encoding is read once by the next kernel and must not push the table slabs out of L2
+      __stcs(enc + (int64_t)(2 * (l0 + j)) * ld + m, v.x);
+      __stcs(enc + (int64_t)(2 * (l0 + j) + 1) * ld + m, v.y);
+      c0 = c1;
+      f0 = f1;
+    }
   }
 }
 
@@ -506,8 +553,23 @@ int acn_ngp_encode_fwd(const AcnPoints* pts, const AcnPairs* pairs, const AcnNgp
   if (Mcap == 0) return ACN_OK;
   ExpertTable tab;
   fill_table(tab, experts, E);
-  dim3 hg(persistent_grid((Mcap + 255) / 256, 4), g->levels);
-  k_ngp_hash_fwd<<<hg, 256, 0, as_stream(stream)>>>(make_src(pts), pairs->point, pairs->seg, Mcap, tab, make_grid(g), enc, h_round_ld(Mcap));
+  // one CTA per (expert, level group, 256-slot chunk); an expert's last chunk may be partial, hence the + E
+  const int64_t chunks = (Mcap + 255) / 256 + E;
+  int lg = launch_hint(ACN_HINT_GATHER_LEVELS);
+  const PointSrc src = make_src(pts);
+  const GridParams gp = make_grid(g);
+  const int64_t ld = h_round_ld(Mcap);
+  cudaStream_t st = as_stream(stream);
+  const int64_t total = chunks * 16;
+  const int per_sm = 4;  // 4 CTAs of 256 threads x 64 registers fill an SM
+  if (lg == 0) lg = Mcap >= ((int64_t)4 << 20) ? 8 : 4;  // measured: 8 for the renderer's 17 M-slot blocks, 4 for a training batch
+  switch (lg) {
+    case 1: k_ngp_hash_fwd<1><<<persistent_grid(total, per_sm), 256, 0, st>>>(src, pairs->point, pairs->seg, Mcap, tab, gp, enc, ld); break;
+    case 2: k_ngp_hash_fwd<2><<<persistent_grid(total / 2, per_sm), 256, 0, st>>>(src, pairs->point, pairs->seg, Mcap, tab, gp, enc, ld); break;
+    case 8: k_ngp_hash_fwd<8><<<persistent_grid(total / 8, per_sm), 256, 0, st>>>(src, pairs->point, pairs->seg, Mcap, tab, gp, enc, ld); break;
+    case 16: k_ngp_hash_fwd<16><<<persistent_grid(total / 16, per_sm), 256, 0, st>>>(src, pairs->point, pairs->seg, Mcap, tab, gp, enc, ld); break;
+    default: k_ngp_hash_fwd<4><<<persistent_grid(total / 4, per_sm), 256, 0, st>>>(src, pairs->point, pairs->seg, Mcap, tab, gp, enc, ld); break;
+  }
   ACN_LAUNCH_CHECK();
   return ACN_OK;
 }

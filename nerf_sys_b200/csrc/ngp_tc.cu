@@ -269,12 +269,12 @@ __device__ __forceinline__ void dir_sh16(const PointSrc& src, int64_t p, float* 
 // forward
 // =============================================================================================
 constexpr int FWD_PIPES = 7;
-constexpr int FWD_THREADS = 128 * FWD_PIPES;
 constexpr uint32_t ABUF = 10 * CH;  // chunk 0 ones | chunks 1..8 data | chunk 9 zero (chunk 5 zero for 32-wide inputs)
-constexpr size_t FWD_SMEM = W_BYTES + FWD_PIPES * ABUF;
-constexpr uint32_t FWD_TMEM_COLS = 512;  // power of two >= 64 * FWD_PIPES
+constexpr size_t fwd_smem(int pipes) { return W_BYTES + (size_t)pipes * ABUF; }
+constexpr uint32_t fwd_tmem_cols(int pipes) { return pipes * 64 <= 256 ? 256u : 512u; }  // power of two >= 64 * pipes
 
-__global__ void __launch_bounds__(FWD_THREADS, 1)
+template <int FWD_PIPES, int MAXREG>
+__global__ void __launch_bounds__(128 * FWD_PIPES, 1) __maxnreg__(MAXREG)
     k_ngp_mlp_fwd_tc(PointSrc src, const int32_t* __restrict__ pair_point, const float* __restrict__ pair_w, const int32_t* __restrict__ seg,
                      int64_t M_ident, ExpertTableTc tab, const float* __restrict__ enc, int64_t ld, float* __restrict__ out) {
   extern __shared__ __align__(128) uint8_t smem[];
@@ -293,6 +293,8 @@ __global__ void __launch_bounds__(FWD_THREADS, 1)
     for (int i = 0; i < FWD_PIPES; ++i) mbar_init(smem_u32(&s_bar[i]), 1);
     mbar_init_fence();
   }
+  constexpr int FWD_THREADS = 128 * FWD_PIPES;
+  constexpr uint32_t FWD_TMEM_COLS = fwd_tmem_cols(FWD_PIPES);
   if (tid < 32) tmem_alloc(&s_tmem, FWD_TMEM_COLS);
   __syncthreads();
   const CtaPart part = s_part;
@@ -974,7 +976,7 @@ static int set_tc_attrs() {
   int dev = 0;
   ACN_CUDA(cudaGetDevice(&dev));
   if (done_dev != dev) {
-    ACN_CUDA(cudaFuncSetAttribute(k_ngp_mlp_fwd_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FWD_SMEM));
+    ACN_CUDA(cudaFuncSetAttribute(k_ngp_mlp_fwd_tc<FWD_PIPES, 72>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fwd_smem(FWD_PIPES)));
     ACN_CUDA(cudaFuncSetAttribute(k_ngp_mlp_bwd_tc<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BWD_SMEM));
     ACN_CUDA(cudaFuncSetAttribute(k_ngp_mlp_bwd_tc<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BWD_SMEM));
     ACN_CUDA(cudaFuncSetAttribute(k_tc_selftest, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
@@ -1004,8 +1006,8 @@ int acn_ngp_mlp_fwd_tc(const AcnPoints* pts, const AcnPairs* pairs, const AcnNgp
   ExpertTableTc tab;
   fill_table_tc(tab, experts, E);
   int64_t ld = (Mcap + 127) / 128 * 128;
-  k_ngp_mlp_fwd_tc<<<tc_grid(Mcap), FWD_THREADS, FWD_SMEM, as_stream(stream)>>>(make_src(pts), pairs->point, pairs->weight, pairs->seg, Mcap,
-                                                                               tab, enc, ld, out);
+  k_ngp_mlp_fwd_tc<FWD_PIPES, 72><<<tc_grid(Mcap), 128 * FWD_PIPES, fwd_smem(FWD_PIPES), as_stream(stream)>>>(
+      make_src(pts), pairs->point, pairs->weight, pairs->seg, Mcap, tab, enc, ld, out);
   ACN_LAUNCH_CHECK();
   return ACN_OK;
 }

@@ -8,6 +8,7 @@ from __future__ import annotations
 
 import ctypes as C
 import functools
+import os
 from typing import List, Optional, Sequence, Tuple
 
 import torch
@@ -881,12 +882,12 @@ class NgpExpertsTcFn(torch.autograd.Function):
         dev = pts.device
         ld = int(L.acn_ngp_ld(pairs.M))
         enc = torch.empty(32, ld, device=dev, dtype=torch.float32)
-        out = _out_buffer(pts, pairs)
         cp, cq = pts.c(), pairs.c()
         with _on(dev):
             with _timed("hash_fwd"):
                 check(L.acn_ngp_encode_fwd(C.byref(cp), C.byref(cq), _expert_array(spec, tb, None), E, C.byref(spec.grid), _ptr(enc), _stream()),
                       "acn_ngp_encode_fwd")
+            out = _out_buffer(pts, pairs)
             with _timed("mlp_fwd"):
                 check(L.acn_ngp_mlp_fwd_tc(C.byref(cp), C.byref(cq), _expert_array(spec, None, ws), E, _ptr(enc), _ptr(out), _stream()),
                       "acn_ngp_mlp_fwd_tc")

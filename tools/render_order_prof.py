@@ -10,12 +10,13 @@ sys.path.insert(0, ROOT)
 import bench  # noqa: E402
 from nerf_sys_b200 import ops  # noqa: E402
 from nerf_sys_b200.nerfs.ray_rendering import render_rays  # noqa: E402
-from oracle import acnerf_oracle as O  # noqa: E402
+from nerf_sys_b200 import synthetic as SY  # noqa: E402
 
 dev = torch.device("cuda", 0)
 ops.set_mlp_math("f16tc")
-model, aabb = bench.build_c5(dev)
-rays = ops.raygen(1080, 1920, 1480.0, 1480.0, 960.0, 540.0, True, O.ring_pose(1, 20, radius=0.9), aabb.to(dev), dev, row0=400, rows=136)
+model, aabb = bench.build_container(dev)
+model.eval()
+rays = ops.raygen(1080, 1920, 1480.0, 1480.0, 960.0, 540.0, True, SY.ring_pose(1, 20, radius=0.9), aabb.to(dev), dev, row0=400, rows=136)
 with torch.no_grad():
     for coherent in (False, True, False, True):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
