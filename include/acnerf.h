@@ -217,6 +217,11 @@ int acn_ngp_mlp_bwd(const AcnPairs* pairs, const AcnNgpExpert* experts, int E, c
  * grads[e].w/b are overwritten (NULL = not wanted); d_enc (32, ld) as in acn_ngp_mlp_bwd. */
 int acn_ngp_mlp_fwd_tc(const AcnPoints* pts, const AcnPairs* pairs, const AcnNgpExpert* experts, int E,
                        const float* enc, float* out, void* stream);
+/* The same forward with the hash-grid gather inside the kernel (models/inr/meta_ngp.py:192-241 -> models/encodings.py:331-381
+ * in one launch): experts[e].table is read directly, the (32, ld) encoding is never written.  Inference only (no
+ * activations are kept); interpolation "linear" or "smoothstep".  out as acn_ngp_mlp_fwd_tc. */
+int acn_ngp_fused_fwd_tc(const AcnPoints* pts, const AcnPairs* pairs, const AcnNgpExpert* experts, int E,
+                         const AcnGridDesc* g, float* out, void* stream);
 int64_t acn_ngp_bwd_tc_ws_bytes(void);
 int acn_ngp_mlp_bwd_tc(const AcnPoints* pts, const AcnPairs* pairs, const AcnNgpExpert* experts, int E,
                        const float* enc, const float* d_out, const AcnNgpExpertGrads* grads, float* d_enc,

@@ -92,6 +92,7 @@ SIGNATURES = {
     "acn_ngp_mlp_fwd": (C.c_int, [P(AcnPoints), P(AcnPairs), P(AcnNgpExpert), C.c_int, vp, vp, vp, vp]),
     "acn_ngp_mlp_bwd": (C.c_int, [P(AcnPairs), P(AcnNgpExpert), C.c_int, vp, vp, vp, P(AcnNgpExpertGrads), vp, vp, vp]),
     "acn_ngp_mlp_fwd_tc": (C.c_int, [P(AcnPoints), P(AcnPairs), P(AcnNgpExpert), C.c_int, vp, vp, vp]),
+    "acn_ngp_fused_fwd_tc": (C.c_int, [P(AcnPoints), P(AcnPairs), P(AcnNgpExpert), C.c_int, P(AcnGridDesc), vp, vp]),
     "acn_ngp_bwd_tc_ws_bytes": (i64, []),
     "acn_ngp_mlp_bwd_tc": (C.c_int, [P(AcnPoints), P(AcnPairs), P(AcnNgpExpert), C.c_int, vp, vp, P(AcnNgpExpertGrads), vp, vp, vp]),
     "acn_ngp_bwd_tc_pipelined_ws_bytes": (i64, [C.c_int]),

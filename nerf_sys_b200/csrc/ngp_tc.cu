@@ -15,7 +15,7 @@
 //                      written once as a per-CTA partial; k_tc_wgrad_reduce sums partials in a fixed order.
 // CTAs are partitioned over experts in proportion to their tile counts, so a CTA loads one expert's
 // weights once and the partial sums of an expert live in a contiguous CTA range (deterministic reduce).
-#include "common.cuh"
+#include "hashgrid.cuh"
 #include "tc.cuh"
 #include <cstdio>
 #include <cstdlib>
@@ -269,19 +269,30 @@ __device__ __forceinline__ void dir_sh16(const PointSrc& src, int64_t p, float* 
 // forward
 // =============================================================================================
 constexpr int FWD_PIPES = 7;
+constexpr int FUSED_PIPES = 5, FUSED_MAXREG = 96;  // the gather needs registers for two levels of reads in flight (measured: 4 pipelines 37.3 ms per 1080p frame, 5: 35.1, 6: 35.6, 7: 37.3)
 constexpr uint32_t ABUF = 10 * CH;  // chunk 0 ones | chunks 1..8 data | chunk 9 zero (chunk 5 zero for 32-wide inputs)
 constexpr size_t fwd_smem(int pipes) { return W_BYTES + (size_t)pipes * ABUF; }
 constexpr uint32_t fwd_tmem_cols(int pipes) { return pipes * 64 <= 256 ? 256u : 512u; }  // power of two >= 64 * pipes
 
-template <int FWD_PIPES, int MAXREG>
+// FUSED = false: the encoding comes from HBM (`enc`, written by k_ngp_hash_fwd); a CTA serves ONE expert (cta_partition).
+//         The training forward: the backward needs the encoding anyway.
+// FUSED = true : the hash-grid gather runs inside the kernel - the thread that owns a row of the 128-row tile walks the 16
+//         levels of its sample (two levels of table reads in flight, as k_ngp_hash_fwd) and writes the 32 features straight
+//         into the fp16 A-operand chunks; the (32, ld) fp32 encoding never exists (at 1080p: 2.2 GB written and 2.8 GB read
+//         back per 17 M-slot block).  While one pipeline gathers, the others run their MMA / epilogue steps.  The grid walks
+//         the experts ONE AFTER ANOTHER (weights reloaded per expert), so that one 128 MiB table is hot in L2 at a time
+//         instead of all of them.  Inference only (no_grad rendering).
+template <int FWD_PIPES, int MAXREG, bool FUSED>
 __global__ void __launch_bounds__(128 * FWD_PIPES, 1) __maxnreg__(MAXREG)
     k_ngp_mlp_fwd_tc(PointSrc src, const int32_t* __restrict__ pair_point, const float* __restrict__ pair_w, const int32_t* __restrict__ seg,
-                     int64_t M_ident, ExpertTableTc tab, const float* __restrict__ enc, int64_t ld, float* __restrict__ out) {
+                     int64_t M_ident, ExpertTableTc tab, const float* __restrict__ enc, int64_t ld, float* __restrict__ out, GridParams g) {
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ __align__(8) uint64_t s_bar[FWD_PIPES];
   __shared__ uint32_t s_tmem;
   __shared__ int s_seg[ACN_MAX_EXPERTS + 1];
   __shared__ CtaPart s_part;
+  __shared__ float s_box[6];
+  __shared__ const float2* s_table;
   const int tid = threadIdx.x, q = tid >> 7;
   const uint32_t r = tid & 127;
   // a pair list truncated at its speculative capacity (route_pack without the host read) is consumed up to its last whole tile
@@ -300,26 +311,80 @@ __global__ void __launch_bounds__(128 * FWD_PIPES, 1) __maxnreg__(MAXREG)
   const CtaPart part = s_part;
   const uint32_t sw = smem_u32(smem), abuf = sw + W_BYTES + q * ABUF;
   const uint32_t sw16 = sw >> 4, abuf16 = sw16 + (W_BYTES + q * ABUF) / 16;  // smem base is 128-byte aligned
-  if (part.e >= 0) load_weights_tc(smem, pick_expert(tab, part.e), tid, FWD_THREADS);
   store_ones_chunk(abuf, r, 0);
   store_zero_chunk(abuf, r, 9);
-  fence_async_smem();
-  fence_before();
-  __syncthreads();
-  fence_after();
   const uint32_t tbase = s_tmem;
   const uint32_t dcol = tbase + q * 64;                       // this pipeline's accumulator columns
   const uint32_t trow = dcol + ((uint32_t)((tid >> 5) & 3) << 21);  // + lane base (32 * warp-in-group) << 16
   const uint32_t bar = smem_u32(&s_bar[q]);
   uint32_t phase = 0;
+  const uint32_t hmask = (1u << g.log2_T) - 1u;
 
-  if (part.e >= 0) {
-    for (int tile = part.tile0 + q; tile < part.tile1; tile += FWD_PIPES) {
+  // FUSED: every expert in turn, tiles dealt round-robin over (CTA, pipeline); else: the one expert of this CTA
+  const int e_first = FUSED ? 0 : part.e, e_last = FUSED ? tab.E : part.e + 1;
+  for (int e = e_first; e < e_last && e >= 0; ++e) {
+    int tile_begin, tile_end, tile_step;
+    if (FUSED) {
+      const int t0 = s_seg[e] / (int)ROWS, t1 = s_seg[e + 1] / (int)ROWS;
+      if (t1 <= t0) continue;  // CTA-uniform
+      tile_begin = t0 + (int)blockIdx.x * FWD_PIPES + q;
+      tile_end = t1;
+      tile_step = (int)gridDim.x * FWD_PIPES;
+      __syncthreads();  // every pipeline is done with the previous expert's weights
+      if (tid == 0) {
+        const AcnNgpExpert ex = pick_expert(tab, e);
+        s_table = reinterpret_cast<const float2*>(ex.table);
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+          s_box[a] = ex.box_min[a];
+          s_box[3 + a] = ex.extent[a];
+        }
+      }
+    } else {
+      tile_begin = part.tile0 + q;
+      tile_end = part.tile1;
+      tile_step = FWD_PIPES;
+    }
+    load_weights_tc(smem, pick_expert(tab, e), tid, FWD_THREADS);
+    fence_async_smem();
+    fence_before();
+    __syncthreads();
+    fence_after();
+
+    for (int tile = tile_begin; tile < tile_end; tile += tile_step) {
       const int64_t m = (int64_t)tile * ROWS + r;
       const bool in_range = m < M;
       const int64_t p = in_range ? (pair_point ? (int64_t)pair_point[m] : m) : -1;
       const int64_t mm = in_range ? m : 0;
-      {  // encoding -> chunks 1..4, chunk 5 zero
+      if (FUSED) {  // gather -> chunks 1..4 (8 features = 4 levels per chunk), chunk 5 zero
+        if (p >= 0) {
+          const float2* __restrict__ table = s_table;
+          float x, y, z;
+          load_xyz(src, p, x, y, z);
+          const float ux = to_unit(x, s_box[0], s_box[3]), uy = to_unit(y, s_box[1], s_box[4]), uz = to_unit(z, s_box[2], s_box[5]);
+          Cell c0 = make_cell(ux, uy, uz, g.res[0], g.interp), c1 = c0;
+          LevelFetch f0, f1;
+          level_fetch(table, c0, hmask, 0u, f0);
+          float v8[8];
+#pragma unroll
+          for (int l = 0; l < 16; ++l) {
+            if (l + 1 < 16) {
+              c1 = make_cell(ux, uy, uz, g.res[l + 1], g.interp);
+              level_fetch(table, c1, hmask, (uint32_t)(l + 1) << g.log2_T, f1);
+            }
+            const float2 v = level_blend(c0, f0);
+            v8[2 * (l & 3)] = v.x;
+            v8[2 * (l & 3) + 1] = v.y;
+            if ((l & 3) == 3) store_h<8>(abuf, r, 1 + (l >> 2), v8);
+            c0 = c1;
+            f0 = f1;
+          }
+        } else {
+#pragma unroll
+          for (int c = 1; c <= 4; ++c) store_zero_chunk(abuf, r, c);
+        }
+        store_zero_chunk(abuf, r, 5);
+      } else {  // encoding -> chunks 1..4, chunk 5 zero
         float x[32];
 #pragma unroll
         for (int i = 0; i < 32; ++i) x[i] = in_range ? __ldg(enc + (int64_t)i * ld + mm) : 0.f;
@@ -976,7 +1041,10 @@ static int set_tc_attrs() {
   int dev = 0;
   ACN_CUDA(cudaGetDevice(&dev));
   if (done_dev != dev) {
-    ACN_CUDA(cudaFuncSetAttribute(k_ngp_mlp_fwd_tc<FWD_PIPES, 72>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fwd_smem(FWD_PIPES)));
+    ACN_CUDA(cudaFuncSetAttribute(k_ngp_mlp_fwd_tc<FWD_PIPES, 72, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fwd_smem(FWD_PIPES)));
+    ACN_CUDA(cudaFuncSetAttribute(k_ngp_mlp_fwd_tc<FUSED_PIPES, FUSED_MAXREG, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)fwd_smem(FUSED_PIPES)));
+
     ACN_CUDA(cudaFuncSetAttribute(k_ngp_mlp_bwd_tc<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BWD_SMEM));
     ACN_CUDA(cudaFuncSetAttribute(k_ngp_mlp_bwd_tc<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BWD_SMEM));
     ACN_CUDA(cudaFuncSetAttribute(k_tc_selftest, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
@@ -1006,8 +1074,35 @@ int acn_ngp_mlp_fwd_tc(const AcnPoints* pts, const AcnPairs* pairs, const AcnNgp
   ExpertTableTc tab;
   fill_table_tc(tab, experts, E);
   int64_t ld = (Mcap + 127) / 128 * 128;
-  k_ngp_mlp_fwd_tc<FWD_PIPES, 72><<<tc_grid(Mcap), 128 * FWD_PIPES, fwd_smem(FWD_PIPES), as_stream(stream)>>>(
-      make_src(pts), pairs->point, pairs->weight, pairs->seg, Mcap, tab, enc, ld, out);
+  GridParams gp{};
+  k_ngp_mlp_fwd_tc<FWD_PIPES, 72, false><<<tc_grid(Mcap), 128 * FWD_PIPES, fwd_smem(FWD_PIPES), as_stream(stream)>>>(
+      make_src(pts), pairs->point, pairs->weight, pairs->seg, Mcap, tab, enc, ld, out, gp);
+  ACN_LAUNCH_CHECK();
+  return ACN_OK;
+}
+
+int acn_ngp_fused_fwd_tc(const AcnPoints* pts, const AcnPairs* pairs, const AcnNgpExpert* experts, int E, const AcnGridDesc* g, float* out,
+                         void* stream) {
+  ACN_REQUIRE(pts && pairs && experts && g && out, "acn_ngp_fused_fwd_tc: NULL argument");
+  ACN_REQUIRE(E >= 1 && E <= ACN_MAX_EXPERTS, "acn_ngp_fused_fwd_tc: E must be in [1,%d]", ACN_MAX_EXPERTS);
+  ACN_REQUIRE(g->levels == 16 && g->features == 2 && g->log2_T >= 1 && g->log2_T <= 24 && g->interp >= 0 && g->interp <= 1,
+              "acn_ngp_fused_fwd_tc: needs L=16, F=2, linear or smoothstep interpolation");
+  ACN_REQUIRE(pts->x6 || (pts->rays && pts->t && pts->S >= 1), "acn_ngp_fused_fwd_tc: points need x6 or (rays,t,S)");
+  bool ident = pairs->point == nullptr;
+  ACN_REQUIRE(ident ? (E == 1 && pairs->Mcap == pts->P) : (pairs->seg != nullptr), "acn_ngp_fused_fwd_tc: inconsistent pair list");
+  ACN_REQUIRE(pairs->Mcap < ((int64_t)1 << 31) - 128, "acn_ngp_fused_fwd_tc: chunk the pair list below 2^31");
+  for (int e = 0; e < E; ++e) ACN_REQUIRE(experts[e].table, "acn_ngp_fused_fwd_tc: expert %d has no table", e);
+  int64_t Mcap = pairs->Mcap;
+  if (Mcap == 0) return ACN_OK;
+  int rc = set_tc_attrs();
+  if (rc) return rc;
+  ExpertTableTc tab;
+  fill_table_tc(tab, experts, E);
+  const PointSrc src = make_src(pts);
+  const GridParams gp = make_grid(g);
+  cudaStream_t st = as_stream(stream);
+  k_ngp_mlp_fwd_tc<FUSED_PIPES, FUSED_MAXREG, true><<<tc_grid(Mcap), 128 * FUSED_PIPES, fwd_smem(FUSED_PIPES), st>>>(
+      src, pairs->point, pairs->weight, pairs->seg, Mcap, tab, nullptr, 0, out, gp);
   ACN_LAUNCH_CHECK();
   return ACN_OK;
 }

@@ -957,9 +957,40 @@ class NgpExpertsTcFn(torch.autograd.Function):
         return (None, None, None, *t_out, *m_out)
 
 
+_fused_inference = True  # no_grad + tensor-core mode: gather and MLPs in one kernel (acn_ngp_fused_fwd_tc)
+
+
+def set_fused_inference(enabled: bool) -> bool:
+    global _fused_inference
+    prev, _fused_inference = _fused_inference, bool(enabled)
+    return prev
+
+
+@torch.no_grad()
+def ngp_experts_fused(pts: PointSet, pairs: PairList, spec: ExpertSpec, tables: Sequence[Tensor], mlp: Sequence[Tensor]) -> Tensor:
+    """Inference form of `ngp_experts`: one launch, no (32, ld) encoding in HBM."""
+    L = lib()
+    E = spec.E
+    tb = [_need(t.detach(), "hash_table") for t in tables]
+    ws = _check_mlp(mlp, E)
+    rows = spec.grid.levels << spec.grid.log2_T
+    for t in tb:
+        if tuple(t.shape) != (rows, 2):
+            raise ValueError(f"hash_table must be ({rows},2), got {tuple(t.shape)}")
+    out = _out_buffer(pts, pairs)
+    cp, cq = pts.c(), pairs.c()
+    with _on(pts.device), _timed("fused_fwd"):
+        check(L.acn_ngp_fused_fwd_tc(C.byref(cp), C.byref(cq), _expert_array(spec, tb, ws), E, C.byref(spec.grid), _ptr(out), _stream()),
+              "acn_ngp_fused_fwd_tc")
+    _count(1)
+    return out
+
+
 def ngp_experts(pts: PointSet, pairs: PairList, spec: ExpertSpec, tables: Sequence[Tensor], mlp: Sequence[Tensor]) -> Tensor:
     """(P,4) [rgb, sigma] of E hash-grid experts over `pairs` (MetaNGP.forward / MetaContainer.forward)."""
     if _mlp_math == "f16tc":
+        if _fused_inference and not torch.is_grad_enabled() and spec.grid.interp != INTERP["nearest"] and spec.grid.levels == 16:
+            return ngp_experts_fused(pts, pairs, spec, tables, mlp)
         return NgpExpertsTcFn.apply(pts, pairs, spec, *tables, *mlp)
     enc = NgpEncodeFn.apply(pts, pairs, spec, *tables)
     return NgpMlpFn.apply(enc, pts, pairs, spec, *mlp)

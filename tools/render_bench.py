@@ -38,15 +38,11 @@ def run(tag, **kw):
     return out
 
 
-from nerf_sys_b200 import _lib  # noqa: E402
-L = _lib.lib()
-outs = {}
-for lg in (0, 4, 8, 16):
-    L.acn_launch_hint(_lib.ACN_HINT_GATHER_LEVELS, lg)
-    outs[lg] = run(f"gather levels/thread = {lg or 'default'}")
-L.acn_launch_hint(_lib.ACN_HINT_GATHER_LEVELS, 0)
-for lg in (4, 8, 16):
-    print(f"levels/thread {lg} vs default: max |diff| rgb/depth/acc:", [float((x - y).abs().max()) for x, y in zip(outs[0], outs[lg])])
+prev = ops.set_fused_inference(False)
+two = run("two kernels (gather, then MLP)")
+ops.set_fused_inference(True)
+one = run("fused gather + MLP kernel")
+print("fused vs two-kernel: max |diff| rgb/depth/acc:", [float((x - y).abs().max()) for x, y in zip(two, one)])
 timing = ops.kernel_timing(True)
 render_image(model, H=H, W=W, fx=f, fy=f, cx=W / 2, cy=H / 2, c2w=poses[0], scene_box=sb, ray_samples=64)
 torch.cuda.synchronize()
