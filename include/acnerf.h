@@ -432,9 +432,47 @@ int acn_p2p_plan(const void* sync_base_own, int world, int rank, int K, const in
                  int64_t* row0_dev, int32_t* seg_own, int32_t* point_own, int32_t* live_own, float* g_rows,
                  int32_t* status, void* stream);
 
+/* ---- a21 / (f)-1: occupancy-guided rendering (nerfs/ray_rendering.py:349-558; models/inr/meta_ngp.py:389-443) ----------
+ * The reference calls nerfacc 0.5.3 (OccGridEstimator.sampling, render_weight_from_density, accumulate_along_rays) and merges
+ * the experts' segments in a Python loop over rays; these entry points are what replaces both.  nerfacc is not vendored and
+ * absent here: the traversal follows its documented semantics, restated in oracle/acnerf_oracle.py (parity unpinned).
+ * Grid: binaries (levels, R, R, R) uint8, cell = (ix*R + iy)*R + iz; aabbs_host (levels, 6) host floats, level l = the region
+ * of interest scaled by 2^l about its centre (OccGridEstimator.aabbs).  Packed lists: offsets (N,) int64 = first segment of
+ * ray r, counts (N,) int32. */
+#define ACN_OCC_MAX_LEVELS 8
+/* pass 1: counts[r] = samples of ray r (<= max_samples).  near_jitter (N,) in [0,1) or NULL: near += jitter * step (training) */
+int acn_occ_march_count(const float* rays, const float* near_jitter, int64_t N, const uint8_t* binaries, const float* aabbs_host,
+                        int levels, int R, float step, float cone_angle, int max_samples, int32_t* counts, void* stream);
+/* pass 2: offsets = exclusive scan of counts; writes ray_idx / t0 / t1 (and, if not NULL, cells = level*R^3 + cell per sample) */
+int acn_occ_march_write(const float* rays, const float* near_jitter, int64_t N, const uint8_t* binaries, const float* aabbs_host,
+                        int levels, int R, float step, float cone_angle, int max_samples, const int64_t* offsets, int32_t* ray_idx,
+                        float* t0, float* t1, int32_t* cells, void* stream);
+/* nerfacc.render_visibility_from_density: visible[i] = (T_i >= early_stop_eps) && (alpha_i >= alpha_thre) */
+int acn_occ_visibility(const int64_t* offsets, const int32_t* counts, int64_t N, const float* t0, const float* t1, const float* sigma,
+                       float early_stop_eps, float alpha_thre, uint8_t* visible, void* stream);
+/* _merge_segments_union (ray_rendering.py:196-256) as a per-ray K-way merge.  out_offsets NULL = count pass (out_counts[r] =
+ * merged segments of ray r); else write pass. */
+typedef struct {
+  const int64_t* offsets[ACN_MAX_EXPERTS];
+  const int32_t* counts[ACN_MAX_EXPERTS];
+  const float* t0[ACN_MAX_EXPERTS];
+  const float* t1[ACN_MAX_EXPERTS];
+  int32_t K;
+} AcnSegLists;
+int acn_seg_union(const AcnSegLists* lists, int64_t N, const int64_t* out_offsets, int32_t* out_counts, int32_t* ray_idx, float* t0,
+                  float* t1, void* stream);
+/* weights (M,) = alpha_i * prod_{j<i}(1 - alpha_j), alpha = 1 - exp(-sigma (t1 - t0)); rgb_map (N,3) = sum w rgb, depth (N,) =
+ * sum w (t0+t1)/2, acc (N,) = sum w.  Backward: gradients w.r.t. sigma (M,) and rgb (M,3); any d_* may be NULL. */
+int acn_packed_render_fwd(const int64_t* offsets, const int32_t* counts, int64_t N, const float* t0, const float* t1, const float* sigma,
+                          const float* rgb, float* weights, float* rgb_map, float* depth, float* acc, void* stream);
+int acn_packed_render_bwd(const int64_t* offsets, const int32_t* counts, int64_t N, const float* t0, const float* t1, const float* sigma,
+                          const float* rgb, const float* weights, const float* d_rgb_map, const float* d_depth, const float* d_acc,
+                          const float* d_weights, float* g_sigma, float* g_rgb, void* stream);
+
 #if defined(__GNUC__)
 #pragma GCC visibility pop
 #endif
+
 #ifdef __cplusplus
 }
 #endif

@@ -47,6 +47,11 @@ class AcnAdamTensor(C.Structure):
                 ("step_index", i32), ("flags", i32)]
 
 
+class AcnSegLists(C.Structure):
+    _fields_ = [("offsets", vp * ACN_MAX_EXPERTS), ("counts", vp * ACN_MAX_EXPERTS), ("t0", vp * ACN_MAX_EXPERTS), ("t1", vp * ACN_MAX_EXPERTS),
+                ("K", i32)]
+
+
 class AcnA2aRoute(C.Structure):
     _fields_ = [("base", vp * ACN_MAX_EXPERTS), ("row0", i64 * ACN_MAX_EXPERTS)]
 
@@ -56,6 +61,7 @@ ACN_MAX_PEERS = 16
 ACN_P2P_PAYLOAD_FLOATS = 1024
 ACN_P2P_SYNC_BYTES = 4096 + 2 * ACN_MAX_PEERS * ACN_P2P_PAYLOAD_FLOATS * 4
 ACN_ADAM_ZERO_GRAD = 0x100
+ACN_OCC_MAX_LEVELS = 8
 ACN_HINT_GATHER_LEVELS = 1
 P = C.POINTER
 fp = P(f32)  # host float arrays
@@ -67,6 +73,12 @@ SIGNATURES = {
     "acn_device_ok": (C.c_int, [C.c_int]),
     "acn_num_sms": (C.c_int, [C.c_int]),
     "acn_launch_hint": (C.c_int, [C.c_int, C.c_int]),
+    "acn_occ_march_count": (C.c_int, [vp, vp, i64, vp, fp, C.c_int, C.c_int, f32, f32, C.c_int, vp, vp]),
+    "acn_occ_march_write": (C.c_int, [vp, vp, i64, vp, fp, C.c_int, C.c_int, f32, f32, C.c_int, vp, vp, vp, vp, vp, vp]),
+    "acn_occ_visibility": (C.c_int, [vp, vp, i64, vp, vp, vp, f32, f32, vp, vp]),
+    "acn_seg_union": (C.c_int, [P(AcnSegLists), i64, vp, vp, vp, vp, vp, vp]),
+    "acn_packed_render_fwd": (C.c_int, [vp, vp, i64, vp, vp, vp, vp, vp, vp, vp, vp, vp]),
+    "acn_packed_render_bwd": (C.c_int, [vp, vp, i64, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]),
     "acn_ray_directions": (C.c_int, [C.c_int, C.c_int, f32, f32, f32, f32, C.c_int, vp, vp]),
     "acn_get_rays": (C.c_int, [vp, i64, fp, fp, f32, f32, f32, f32, vp, vp]),
     "acn_raygen": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, f32, f32, f32, f32, C.c_int, fp, fp, f32, f32, vp, vp]),

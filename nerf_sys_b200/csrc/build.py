@@ -32,6 +32,7 @@ SOURCES = {
     "render.cu": [],
     "optim.cu": [],
     "a2a.cu": ["-fmad=false"],
+    "occ.cu": ["-fmad=false"],
 }
 
 

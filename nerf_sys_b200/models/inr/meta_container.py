@@ -212,15 +212,25 @@ class MetaContainer(MetaModule):
         rgb = ops.background(d.reshape(-1, 3) if d.dim() == 3 else d, l0.weight, l0.bias, l1.weight, l1.bias)
         return rgb.view(*d.shape[:-1], 3)
 
-    # ---- occupancy hooks (not built) -------------------------------
+    # ---- occupancy hooks (meta_container.py:385-470) -----------------------------------
     def maybe_update_expert_occupancies(self, step: int, params=None) -> None:
-        return None
+        for sub in self.submodules:  # `params` is handed over as it is, container-level keys included (meta_container.py:385-388)
+            sub.maybe_update_occ_grid(step, params)
 
     def freeze_expert_occupancies(self, flag: bool) -> None:
-        return None
+        for sub in self.submodules:
+            sub.occ_frozen = flag
 
+    @torch.no_grad()
     def premark_invisible_expert_cells(self, metas, near_plane: float = 0.0, chunk: int = 32 ** 3) -> List[int]:
-        return [0] * len(self.submodules)
+        """One-time visibility pruning of every expert's grid from the camera metadata; returns the marked cells per expert."""
+        if self.cells_premarked or not self.use_occ:
+            return [0] * len(self.submodules)
+        marked = []
+        for sub in self.submodules:
+            sub.premark_invisible_cells(metas, near_plane=float(near_plane), chunk=chunk)
+            marked.append(int((sub.occ_grid.occs < 0).sum().item()) if hasattr(sub.occ_grid, "occs") else 0)
+        return marked
 
     @property
     def occ_ready(self) -> bool:

@@ -3,7 +3,8 @@ same constructor arguments, sub-module names (hence state_dict keys) and ``forwa
 color`` signatures, evaluated by the fused sm_100a kernels (csrc/ngp.cu)."""
 from __future__ import annotations
 
-from typing import Dict, List, Optional, Union
+import math
+from typing import Dict, List, Optional, Tuple, Union
 
 import torch
 from torch import Tensor
@@ -12,6 +13,7 @@ from ... import ops
 from ...nerfs.scene_box import SceneBox
 from ..encodings import FrequencyEncoder, HashGridEncoder, SHEncoder
 from ..metamodule import MetaLayerBlock, MetaLinear, MetaModule, MetaSequential
+from ..occ_grid import OccGridEstimator
 from ..trunc_exp import trunc_exp
 
 
@@ -22,9 +24,7 @@ class MetaNGP(MetaModule):
         super().__init__()
         hash_enc_conf = hash_enc_conf or {}
         occ_conf = occ_conf or {}
-        if bool(occ_conf.get("use_occ", False)):
-            raise NotImplementedError("occupancy-grid marching (SURVEY 8(f)-1) is not built yet; construct with use_occ=False")
-        self.use_occ = False
+        self.use_occ = bool(occ_conf.get("use_occ", False))
         self.occ_ready = False
         self.occ_premarked = False
         self.register_buffer("aabb_extent", scene_box.extent.clone().float())
@@ -64,6 +64,30 @@ class MetaNGP(MetaModule):
         color.append(MetaLinear(last, 3))
         self.color_mlp = MetaSequential(*color)
         self.rgb_act = torch.nn.Sigmoid() if self.use_sigmoid_rgb else torch.nn.Identity()
+
+        # occupancy state, as meta_ngp.py:103-142 (same attribute and buffer names: `scene_aabb`, `occ_grid.*` are checkpointed)
+        if self.use_occ:
+            self.render_step_size = (float(occ_conf["render_step_size"]) if occ_conf.get("render_step_size") is not None
+                                     else float(scene_box.get_diagonal_length()) / 1000.0)
+            self.occ_thre = float(occ_conf.get("occ_thre", 1e-2))
+            self.alpha_thre = float(occ_conf.get("alpha_thre", 1e-2))
+            self.cone_angle = float(occ_conf.get("cone_angle", 1.0 / 256.0))
+            self.near_plane = float(occ_conf.get("near_plane", 0.05))
+            self.far_plane = float(occ_conf.get("far_plane", 1e3))
+            self.occ_update_interval = int(occ_conf.get("update_interval", 16))
+            self.occ_warmup_steps = int(occ_conf.get("warmup_steps", 256))
+            self.occ_cosine_anneal = bool(occ_conf.get("cosine_anneal", True))
+            self.occ_alpha_thre_start = float(occ_conf.get("alpha_thre_start", 0.0))
+            self.occ_alpha_thre_end = float(occ_conf.get("alpha_thre_end", self.alpha_thre))
+            self.occ_ema_decay = float(occ_conf.get("ema_decay", 0.95))
+            self.occ_resolution = int(occ_conf.get("resolution", 128))
+            self.occ_levels = int(occ_conf.get("levels", 4))
+            self.register_buffer("scene_aabb", torch.cat([scene_box.min, scene_box.max]).flatten().float())
+            self.occ_grid = OccGridEstimator(roi_aabb=self.scene_aabb, resolution=self.occ_resolution, levels=self.occ_levels)
+            self._check_aabb()
+            self.occ_frozen = bool(occ_conf.get("occ_frozen", False))
+            self.occ_ready = bool(occ_conf.get("occ_ready", False))
+            self.num_occ_updates = 0
 
         # the fused kernel is specialised on the shape nerf_runner.py actually builds
         self._fused_ok = (self.xyz_encoder.levels == 16 and hidden == 64 and sigma_depth == 2 and color_hidden == 64
@@ -134,8 +158,88 @@ class MetaNGP(MetaModule):
         h = torch.cat([geo_feat, self.dir_encoder(d)], dim=-1)
         return self.rgb_act(self.color_mlp(h, params=self.get_subdict(params, "color_mlp")))
 
+    # ---- occupancy (meta_ngp.py:244-443) ----------------------------------------------
+    def _check_aabb(self) -> None:
+        aabb = self.scene_aabb
+        assert aabb.dtype == torch.float32 and aabb.isfinite().all() and aabb.numel() == 6
+        if not (aabb[:3] < aabb[3:]).all():
+            raise ValueError(f"AABB invalid: min>=max ({aabb[:3]} vs {aabb[3:]})")
+
+    def _anneal_alpha_thre(self, step: int) -> None:
+        """alpha threshold from start to end over the warm-up (cosine or linear), then held (meta_ngp.py:245-259)."""
+        if step < self.occ_warmup_steps:
+            t = step / max(1, self.occ_warmup_steps - 1)
+            if self.occ_cosine_anneal:
+                t = 0.5 * (1 - math.cos(math.pi * t))
+            self.alpha_thre = (1 - t) * self.occ_alpha_thre_start + t * self.occ_alpha_thre_end
+        else:
+            self.alpha_thre = self.occ_alpha_thre_end
+
+    @torch.no_grad()
+    def density_at(self, x: Tensor, params=None) -> Tensor:
+        """sigma (N,) at world points through the fused kernels (the occupancy update evaluates 4 x 128^3 points and the
+        training-time visibility filter every marched sample: not a job for the layer-wise `density`)."""
+        x = x.reshape(-1, 3).float()
+        d = torch.zeros_like(x)
+        d[:, 2] = 1.0  # the colour branch is evaluated and dropped; any unit direction does
+        return self.evaluate(ops.PointSet(x6=torch.cat([x, d], dim=-1)), params)[:, 3]
+
+    @torch.no_grad()
+    def premark_invisible_cells(self, mds, near_plane: float = 0.05, chunk: int = 32 ** 3) -> None:
+        """One-time visibility pruning (meta_ngp.py:319-353): cells no camera sees get occupancy -1."""
+        if not self.use_occ or self.occ_premarked:
+            return
+        mds = [md for md in mds if md is not None]
+        if len(mds) == 0:
+            self.occ_premarked = True
+            return
+        device = self.occ_grid.aabbs.device
+
+        def make_K(md):
+            k = torch.as_tensor(md.intrinsics, dtype=torch.float32)
+            if k.numel() == 9:
+                return k.view(3, 3)
+            if k.numel() == 4:
+                fx, fy, cx, cy = k.unbind()
+                return torch.tensor([[fx, 0.0, cx], [0.0, fy, cy], [0.0, 0.0, 1.0]], dtype=torch.float32)
+            raise ValueError(f"Unsupported intrinsics shape: {tuple(k.shape)}")
+
+        K = torch.stack([make_K(md) for md in mds]).to(device)
+        c2w = torch.stack([torch.as_tensor(md.c2w, dtype=torch.float32) for md in mds]).to(device).clone()
+        c2w[:, :3, :3] = c2w[:, :3, :3] @ torch.diag(torch.tensor([1.0, -1.0, -1.0], device=device))  # RUB -> RDF camera axes
+        self.occ_grid.mark_invisible_cells(K=K, c2w=c2w, width=int(mds[0].W), height=int(mds[0].H), near_plane=float(near_plane), chunk=chunk)
+        self.occ_premarked = True
+
+    @torch.no_grad()
     def maybe_update_occ_grid(self, step: int, params=None) -> None:
-        return None
+        """Periodic EMA update of the occupancy grid during training (meta_ngp.py:355-387)."""
+        if not (self.training and self.use_occ and not self.occ_frozen):
+            return
+        self.occ_ready = step >= self.occ_warmup_steps
+        self._anneal_alpha_thre(step)
+        self.occ_grid.update_every_n_steps(step=step, occ_eval_fn=lambda x: self.density_at(x, params) * self.render_step_size,
+                                           occ_thre=self.occ_thre, ema_decay=self.occ_ema_decay, warmup_steps=self.occ_warmup_steps,
+                                           n=self.occ_update_interval)
+        self.num_occ_updates += 1
+
+    @torch.no_grad()
+    def occupancy_marching(self, rays: Tensor, *, params=None, render_step_size: Optional[float] = None, alpha_thre: Optional[float] = None,
+                           cone_angle: Optional[float] = None) -> Tuple[Tensor, Tensor, Tensor]:
+        """(ray_indices, t_starts, t_ends) of this expert's occupancy grid along (N,8) rays (meta_ngp.py:389-443); in training
+        the samples are jittered and filtered by the current density (transmittance early stop + alpha threshold)."""
+        if getattr(self, "occ_grid", None) is None:
+            raise RuntimeError("MetaNGP: occ_grid missing")
+        rays = rays.contiguous()
+        o, d = rays[:, :3], rays[:, 3:6]
+        sigma_fn = None
+        if self.training:
+            def sigma_fn(t_starts, t_ends, ray_indices):
+                mids = 0.5 * (t_starts + t_ends)
+                return self.density_at(o[ray_indices] + d[ray_indices] * mids[:, None], params)
+        return self.occ_grid.sampling(rays_o=o, rays_d=d, sigma_fn=sigma_fn, t_min=rays[:, 6], t_max=rays[:, 7],
+                                      render_step_size=self.render_step_size if render_step_size is None else render_step_size,
+                                      stratified=self.training, cone_angle=self.cone_angle if cone_angle is None else cone_angle,
+                                      alpha_thre=self.alpha_thre if alpha_thre is None else alpha_thre)
 
     def get_param_groups(self) -> Dict[str, Dict]:
         return {"encoding": {"params": list(self.xyz_encoder.parameters())},

@@ -95,9 +95,125 @@ def render_rays_stratified(model, rays: Tensor, ray_samples: int, params=None, a
     return ops.composite(rgb_sigma.view(N, S, 4), t_vals, bg_rgb, float(sigma_scale))
 
 
+# ============================== occupancy rendering (ray_rendering.py:171-256, 349-558) ===============================
+@torch.no_grad()
+def _intersect_rays_aabb(rays: Tensor, scene_box) -> Tensor:
+    """(N,) bool: the ray's [near, far] overlaps the box (slab test with the reference's 1e-9 direction guard, :171-193)."""
+    o, d = rays[:, :3], rays[:, 3:6]
+    near, far = rays[:, 6:7], rays[:, 7:8]
+    eps = 1e-9
+    invd = torch.where(torch.abs(d) > eps, 1.0 / d, torch.full_like(d, 1.0 / eps))
+    t0 = (scene_box.min[None, :].to(rays.device) - o) * invd
+    t1 = (scene_box.max[None, :].to(rays.device) - o) * invd
+    tmin = torch.minimum(t0, t1).amax(dim=-1, keepdim=True)
+    tmax = torch.maximum(t0, t1).amin(dim=-1, keepdim=True)
+    return (torch.minimum(tmax, far) > torch.maximum(tmin, near)).squeeze(-1)
+
+
+@torch.no_grad()
+def _merge_segments_union(ray_indices_list, t0_list, t1_list, n_rays: Optional[int] = None):
+    """Per-ray union of the experts' segment boundaries (:196-256) - one kernel (csrc/occ.cu k_seg_union) instead of the
+    reference's Python loop over rays.  ``n_rays`` defaults to max ray id + 1."""
+    if len(t0_list) == 0:
+        z = torch.zeros(0)
+        return z.long(), z.float(), z.float()
+    N = int(n_rays) if n_rays is not None else int(max(int(r.max().item()) for r in ray_indices_list if r.numel()) + 1)
+    lists = [ops.pack_segments(ri, a, b, N) for ri, a, b in zip(ray_indices_list, t0_list, t1_list)]
+    m = ops.seg_union(lists, N)
+    return m.ray_idx.long(), m.t0, m.t1
+
+
+def _packed_integrate(model, rays: Tensor, params, seg: "ops.PackedSegments", sigma: Tensor, rgb: Tensor, bg_color_default: str):
+    """nerfacc.render_weight_from_density + accumulate_along_rays + background (:477-491, :543-558)."""
+    N = rays.shape[0]
+    rgb_map, depth, w, acc = ops.packed_render(sigma, rgb, seg)
+    bg_rgb = _get_bg_rgb(model, rays[:, 3:6], params, rgb_map, N, bg_color_default)
+    rgb_map = rgb_map + (1.0 - acc)[..., None] * bg_rgb
+    return rgb_map, depth, w[:, None], acc
+
+
+def _empty_occ_result(model, rays: Tensor, params, bg_color_default: str):
+    N = rays.shape[0]
+    acc = rays.new_zeros(N)
+    bg_rgb = _get_bg_rgb(model, rays[:, 3:6], params, None, N, bg_color_default)
+    return bg_rgb, acc.clone(), torch.zeros(1, 1, device=rays.device, dtype=rays.dtype), acc
+
+
+def render_expert_occ(model, rays: Tensor, *, params=None, bg_color_default: str = "white", chunk: int = 1_000_000,
+                      render_step_size=None, alpha_thre=None, cone_angle=None):
+    """One expert through its own occupancy grid (:494-558): march, evaluate the expert at the segment midpoints, integrate."""
+    rays = ops._f32(rays, "rays")
+    N = rays.shape[0]
+    ri, t0, t1 = model.occupancy_marching(rays, params=params, render_step_size=render_step_size, alpha_thre=alpha_thre, cone_angle=cone_angle)
+    if t0.numel() == 0:
+        return _empty_occ_result(model, rays, params, bg_color_default)
+    seg = ops.pack_segments(ri, t0, t1, N)
+    t_mid = 0.5 * (t0 + t1)
+    x6 = torch.cat([rays[ri, :3] + rays[ri, 3:6] * t_mid[:, None], rays[ri, 3:6]], dim=-1)
+    out = model(x6, params=params)
+    return _packed_integrate(model, rays, params, seg, out[:, 3], out[:, :3], bg_color_default)
+
+
+def render_rays_occ(model, rays: Tensor, *, params=None, bg_color_default: str = "white", chunk: int = 1_000_000, render_step_size=None,
+                    alpha_thre=None, cone_angle=None, active_module: Optional[int] = None, **kwargs):
+    """Occupancy-guided soft mixture-of-experts renderer (:349-491): per-expert AABB prefilter and grid marching, per-ray
+    union of the experts' segments, experts evaluated at the midpoints where their routing weight is positive,
+    sigma = sum_k w_k sigma_k and rgb = sum_k w_k sigma_k rgb_k / sigma blended BEFORE one integration.
+    Returns rgb (N,3), depth (N,), weights (M,1) packed, acc (N,)."""
+    rays = ops._f32(rays, "rays")
+    N = rays.shape[0]
+    if active_module is not None:
+        return render_expert_occ(model.submodules[active_module], rays, params=params, bg_color_default=bg_color_default, chunk=chunk,
+                                 render_step_size=render_step_size, alpha_thre=alpha_thre, cone_angle=cone_angle)
+    lists = []
+    for k, expert in enumerate(model.submodules):
+        hit = _intersect_rays_aabb(rays, expert.scene_box)
+        if not bool(hit.any()):
+            continue
+        hit_idx = hit.nonzero(as_tuple=False).squeeze(1)
+        ri_k, t0_k, t1_k = expert.occupancy_marching(rays[hit_idx], params=(model.get_subdict(params, f"submodules.{k}") if params is not None else None),
+                                                     render_step_size=render_step_size, alpha_thre=alpha_thre, cone_angle=cone_angle)
+        if t0_k.numel() == 0:
+            continue
+        lists.append(ops.pack_segments(hit_idx[ri_k], t0_k, t1_k, N))
+    if not lists:
+        return _empty_occ_result(model, rays, params, bg_color_default)
+    seg = ops.seg_union(lists, N)
+    if seg.M == 0:
+        return _empty_occ_result(model, rays, params, bg_color_default)
+    ri = seg.ray_idx.long()
+    t_mid = 0.5 * (seg.t0 + seg.t1)
+    x_mid = rays[ri, :3] + rays[ri, 3:6] * t_mid[:, None]
+    d_mid = rays[ri, 3:6]
+    K = len(model.submodules)
+    with torch.no_grad():
+        W, hard = model._routing(x_mid)
+        if W is None:
+            W = torch.nn.functional.one_hot(hard.view(-1), K).to(x_mid.dtype)
+    # sum_k W sigma_k (clamped at 1e-12) and sum_k W sigma_k rgb_k, accumulated expert by expert (the reference fills dense (M,K)
+    # and (M,K,3) tensors first; the sums are the same terms in the same order k = 0..K-1)
+    s_num = x_mid.new_zeros(seg.M)
+    c_num = x_mid.new_zeros(seg.M, 3)
+    for k, expert in enumerate(model.submodules):
+        idx = torch.nonzero(W[:, k] > 1e-8, as_tuple=False).squeeze(1)
+        if idx.numel() == 0:
+            continue
+        out = expert(torch.cat([x_mid[idx], d_mid[idx]], dim=-1), params=(model.get_subdict(params, f"submodules.{k}") if params is not None else None))
+        ws = W[idx, k] * out[:, 3]
+        s_num = s_num.index_add(0, idx, ws)
+        c_num = c_num.index_add(0, idx, ws[:, None] * out[:, :3])
+    sigma_mix = s_num.clamp_min(1e-12)
+    rgb_mix = c_num / sigma_mix[:, None]
+    return _packed_integrate(model, rays, params, seg, sigma_mix, rgb_mix, bg_color_default)
+
+
 def render_rays(model, rays, *args, **kwargs):
+    """Dispatch of ray_rendering.py:563-574: the occupancy renderer once the model's grids are ready, else stratified."""
     if getattr(model, "use_occ", False) and getattr(model, "occ_ready", False):
-        raise NotImplementedError("occupancy renderer (SURVEY 8(f)-1) is not built; the stratified renderer is the production path")
+        kwargs.pop("ray_samples", None)
+        for k in ("u", "coherent", "route_checks", "sigma_scale"):
+            kwargs.pop(k, None)
+        return render_rays_occ(model, rays, *args, **kwargs)
     return render_rays_stratified(model, rays, *args, **kwargs)
 
 

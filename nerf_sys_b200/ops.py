@@ -1172,3 +1172,148 @@ def sumsq_accum(x: Tensor, acc: Tensor):
     with _on(xx.device), _timed("sumsq"):
         check(lib().acn_sumsq_accum(_ptr(xx), xx.numel(), _ptr(acc), _stream()), "acn_sumsq_accum")
     _count(1)
+
+
+# --------------------------------------------------------------------------
+# a21 / (f)-1: occupancy-guided rendering (csrc/occ.cu)
+# --------------------------------------------------------------------------
+ACN_OCC_MAX_LEVELS = _lib.ACN_OCC_MAX_LEVELS
+
+
+class PackedSegments:
+    """Per-ray lists of [t0, t1) segments, packed ray by ray: ray_idx (M,) int32, t0 / t1 (M,), offsets (N,) int64 (first
+    segment of each ray), counts (N,) int32.  (nerfacc's ray_indices + packed_info.)"""
+
+    def __init__(self, N: int, ray_idx: Tensor, t0: Tensor, t1: Tensor, offsets: Tensor, counts: Tensor, cells: Optional[Tensor] = None):
+        self.N, self.ray_idx, self.t0, self.t1, self.offsets, self.counts, self.cells = int(N), ray_idx, t0, t1, offsets, counts, cells
+
+    @property
+    def M(self) -> int:
+        return int(self.t0.shape[0])
+
+
+def _exclusive_offsets(counts: Tensor) -> Tuple[Tensor, int]:
+    """(offsets int64, total): the one host read of a packed-list construction (nerfacc reads the same total)."""
+    inc = torch.cumsum(counts, 0, dtype=torch.int64)
+    total = int(inc[-1].item()) if counts.numel() else 0
+    return inc - counts, total
+
+
+@torch.no_grad()
+def occ_march(rays: Tensor, near_jitter: Optional[Tensor], binaries: Tensor, aabbs_host: Sequence[float], step: float, cone_angle: float,
+              max_samples: int = 4096, return_cells: bool = False) -> PackedSegments:
+    """Multi-level occupancy-grid traversal of (N,8) rays [o, d, near, far] (OccGridEstimator.sampling before its visibility
+    filter): count pass, exclusive scan, write pass."""
+    rays = _need(rays, "rays")
+    if binaries.dtype not in (torch.bool, torch.uint8) or binaries.dim() != 4 or not binaries.is_cuda:
+        raise TypeError("binaries must be a CUDA bool/uint8 (levels, R, R, R) tensor")
+    b8 = binaries.contiguous().view(torch.uint8)
+    levels, R = int(b8.shape[0]), int(b8.shape[1])
+    jit = None if near_jitter is None else _need(near_jitter, "near_jitter")
+    N = rays.shape[0]
+    dev = rays.device
+    ah = host_floats(aabbs_host)
+    counts = torch.zeros(N, dtype=torch.int32, device=dev)
+    L = lib()
+    with _on(dev), _timed("occ_march"):
+        check(L.acn_occ_march_count(_ptr(rays), _ptr(jit), N, _ptr(b8), ah, levels, R, float(step), float(cone_angle), int(max_samples), _ptr(counts),
+                                    _stream()), "acn_occ_march_count")
+    offsets, M = _exclusive_offsets(counts)
+    ray_idx = torch.empty(M, dtype=torch.int32, device=dev)
+    t0, t1 = torch.empty(M, device=dev), torch.empty(M, device=dev)
+    cells = torch.empty(M, dtype=torch.int32, device=dev) if return_cells else None
+    if M:
+        with _on(dev), _timed("occ_march"):
+            check(L.acn_occ_march_write(_ptr(rays), _ptr(jit), N, _ptr(b8), ah, levels, R, float(step), float(cone_angle), int(max_samples), _ptr(offsets),
+                                        _ptr(ray_idx), _ptr(t0), _ptr(t1), _ptr(cells), _stream()), "acn_occ_march_write")
+    _count(2)
+    return PackedSegments(N, ray_idx, t0, t1, offsets, counts, cells)
+
+
+@torch.no_grad()
+def occ_visibility(seg: PackedSegments, sigma: Tensor, early_stop_eps: float, alpha_thre: float) -> Tensor:
+    """bool (M,): nerfacc.render_visibility_from_density."""
+    sg = _need(sigma.detach().reshape(-1), "sigma")
+    if sg.numel() != seg.M:
+        raise ValueError(f"sigma has {sg.numel()} entries for {seg.M} segments")
+    vis = torch.empty(seg.M, dtype=torch.uint8, device=sg.device)
+    with _on(sg.device), _timed("occ_visibility"):
+        check(lib().acn_occ_visibility(_ptr(seg.offsets), _ptr(seg.counts), seg.N, _ptr(seg.t0), _ptr(seg.t1), _ptr(sg), float(early_stop_eps),
+                                       float(alpha_thre), _ptr(vis), _stream()), "acn_occ_visibility")
+    _count(1)
+    return vis.bool()
+
+
+def pack_segments(ray_idx: Tensor, t0: Tensor, t1: Tensor, N: int) -> PackedSegments:
+    """Packed lists from sorted ray ids (nerfacc.pack_info): counts by bincount, offsets by scan."""
+    counts = torch.bincount(ray_idx.long(), minlength=N).to(torch.int32)
+    offsets = torch.cumsum(counts, 0, dtype=torch.int64) - counts
+    return PackedSegments(N, ray_idx.to(torch.int32).contiguous(), _f32(t0, "t0"), _f32(t1, "t1"), offsets, counts)
+
+
+@torch.no_grad()
+def seg_union(lists: Sequence[PackedSegments], N: int) -> PackedSegments:
+    """_merge_segments_union (ray_rendering.py:196-256) as one kernel: per ray, the sorted distinct boundaries of every
+    list's segments; consecutive boundaries are the merged segments.  Every list covers the same N rays."""
+    from ._lib import AcnSegLists
+    if not 1 <= len(lists) <= ACN_MAX_EXPERTS:
+        raise ValueError(f"1..{ACN_MAX_EXPERTS} lists")
+    dev = lists[0].t0.device
+    sl = AcnSegLists()
+    sl.K = len(lists)
+    for k, s in enumerate(lists):
+        if s.N != N:
+            raise ValueError("every list must cover the same rays")
+        sl.offsets[k], sl.counts[k], sl.t0[k], sl.t1[k] = s.offsets.data_ptr(), s.counts.data_ptr(), s.t0.data_ptr(), s.t1.data_ptr()
+    counts = torch.zeros(N, dtype=torch.int32, device=dev)
+    L = lib()
+    with _on(dev), _timed("seg_union"):
+        check(L.acn_seg_union(C.byref(sl), N, None, _ptr(counts), None, None, None, _stream()), "acn_seg_union")
+    offsets, M = _exclusive_offsets(counts)
+    ray_idx = torch.empty(M, dtype=torch.int32, device=dev)
+    t0, t1 = torch.empty(M, device=dev), torch.empty(M, device=dev)
+    if M:
+        with _on(dev), _timed("seg_union"):
+            check(L.acn_seg_union(C.byref(sl), N, _ptr(offsets), None, _ptr(ray_idx), _ptr(t0), _ptr(t1), _stream()), "acn_seg_union")
+    _count(2)
+    return PackedSegments(N, ray_idx, t0, t1, offsets, counts)
+
+
+class PackedRenderFn(torch.autograd.Function):
+    """render_weight_from_density + the three accumulate_along_rays of the occupancy renderer (ray_rendering.py:477-487)."""
+
+    @staticmethod
+    def forward(ctx, sigma: Tensor, rgb: Tensor, seg: PackedSegments):
+        sg, cl = _need(sigma.detach().reshape(-1), "sigma"), _need(rgb.detach(), "rgb")
+        if sg.numel() != seg.M or tuple(cl.shape) != (seg.M, 3):
+            raise ValueError("sigma (M,) / rgb (M,3) do not match the packed segments")
+        dev, N = sg.device, seg.N
+        w = torch.empty(seg.M, device=dev)
+        rgb_map, depth, acc = torch.empty(N, 3, device=dev), torch.empty(N, device=dev), torch.empty(N, device=dev)
+        with _on(dev), _timed("packed_render_fwd"):
+            check(lib().acn_packed_render_fwd(_ptr(seg.offsets), _ptr(seg.counts), N, _ptr(seg.t0), _ptr(seg.t1), _ptr(sg), _ptr(cl), _ptr(w),
+                                              _ptr(rgb_map), _ptr(depth), _ptr(acc), _stream()), "acn_packed_render_fwd")
+        _count(1)
+        ctx.seg = seg
+        ctx.save_for_backward(sg, cl, w)
+        ctx.sigma_shape = sigma.shape
+        return rgb_map, depth, w, acc
+
+    @staticmethod
+    @first_order
+    def backward(ctx, d_rgb, d_depth, d_w, d_acc):
+        sg, cl, w = ctx.saved_tensors
+        seg = ctx.seg
+        g_sigma, g_rgb = torch.empty_like(sg), torch.empty_like(cl)
+        opt = lambda t, n: None if t is None else _f32(t, n)  # noqa: E731
+        with _on(sg.device), _timed("packed_render_bwd"):
+            check(lib().acn_packed_render_bwd(_ptr(seg.offsets), _ptr(seg.counts), seg.N, _ptr(seg.t0), _ptr(seg.t1), _ptr(sg), _ptr(cl), _ptr(w),
+                                              _ptr(opt(d_rgb, "d_rgb")), _ptr(opt(d_depth, "d_depth")), _ptr(opt(d_acc, "d_acc")),
+                                              _ptr(opt(d_w, "d_w")), _ptr(g_sigma), _ptr(g_rgb), _stream()), "acn_packed_render_bwd")
+        _count(1)
+        return g_sigma.view(ctx.sigma_shape), g_rgb, None
+
+
+def packed_render(sigma: Tensor, rgb: Tensor, seg: PackedSegments):
+    """rgb_map (N,3), depth (N,), weights (M,), acc (N,) - without background."""
+    return PackedRenderFn.apply(sigma, rgb, seg)
