@@ -7,6 +7,7 @@ What changes is the data flow, not the arithmetic: sample positions are never ma
 the kernels read the packed rays and the (N,S) sample distances directly."""
 from __future__ import annotations
 
+import math
 from typing import Optional, Tuple
 
 import torch
@@ -61,9 +62,36 @@ def stratified_t_vals(near: Tensor, far: Tensor, ray_samples: int, randomized: b
     return ops.stratified_t(rays, int(ray_samples), u if randomized else None)
 
 
+@torch.no_grad()
+def _evaluate_front_to_back(model, rays: Tensor, t_vals: Tensor, params, route_checks, eps: float, group: int, sigma_scale: float) -> Tensor:
+    """(S*N, 4) [rgb, sigma] in sample-major order, evaluated group by group; terminated rays are skipped (see the caller)."""
+    N, S = t_vals.shape
+    out = torch.empty(S * N, 4, device=rays.device, dtype=torch.float32)
+    delta = torch.empty_like(t_vals)
+    delta[:, :-1] = (t_vals[:, 1:] - t_vals[:, :-1]).clamp_min(1e-4)  # ray_rendering.py:141-146
+    delta[:, -1] = delta[:, -2]
+    tau = torch.zeros(N, device=rays.device)  # optical depth so far
+    alive = None
+    for s0 in range(0, S, group):
+        s1 = min(S, s0 + group)
+        t_g = t_vals[:, s0:s1]
+        if alive is not None:
+            t_g = torch.where(alive[:, None], t_g, torch.full_like(t_g, float("nan")))
+        pts_g = ops.PointSet(rays=rays, t=t_g.contiguous())
+        pts_g.route_checks = route_checks
+        y = model.evaluate(pts_g.sample_major(), params=params)
+        out[s0 * N:s1 * N] = y
+        if s1 < S:
+            sig = y.view(s1 - s0, N, 4)[..., 3].clamp_min(0) * sigma_scale
+            tau += (sig * delta[:, s0:s1].t()).sum(0)
+            alive = tau < -math.log(eps)  # T = exp(-tau) >= eps
+    return out
+
+
 def render_rays_stratified(model, rays: Tensor, ray_samples: int, params=None, active_module: Optional[int] = None,
                            bg_color_default: str = "white", chunk: int = 1_000_000, sigma_scale=1.0, u: Optional[Tensor] = None,
-                           coherent: bool = False, route_checks: Optional[list] = None, **kwargs):
+                           coherent: bool = False, route_checks: Optional[list] = None, early_stop_eps: float = 0.0,
+                           early_stop_group: int = 16, **kwargs):
     """Stratified renderer: rgb (N,3), depth (N,), weights (N,S), acc (N,).
 
     ``chunk`` is accepted for signature compatibility; nothing is staged per point, so there is
@@ -85,9 +113,21 @@ def render_rays_stratified(model, rays: Tensor, ray_samples: int, params=None, a
     # 53.9 -> 48 ms); the compositor reads the (S,N,4) result in place.  Every kernel is order-agnostic (a single expert's
     # identity slot list simply becomes sample-major too); sharded experts keep ray-major rows.
     sample_major = coherent and not torch.is_grad_enabled() and getattr(model, "_ep", None) is None
-    if sample_major:
+    # Transmittance early termination (additive: the reference declares `early_stop_eps` in its viewer presets,
+    # viewer/viewer.py:46-57, and never passes it on; 0 = off = the reference's arithmetic).  Front to back in groups of
+    # `early_stop_group` samples: a ray whose transmittance has fallen below eps gets NaN sample distances for the rest of
+    # its samples, the routing kernel gives a non-finite position no expert (meta_container.py:119-126), so neither the
+    # gather nor the MLPs see those samples and their [rgb, sigma] rows stay zero.  The image differs from the full
+    # evaluation by at most eps per channel (the dropped weights sum to less than T < eps).
+    if (early_stop_eps > 0.0 and sample_major and active_module is None and len(getattr(model, "submodules", ())) > 1
+            and S > early_stop_group):
+        rgb_sigma = _evaluate_front_to_back(model, rays, t_vals, params, route_checks, float(early_stop_eps), int(early_stop_group),
+                                            float(sigma_scale))
         pts = pts.sample_major()
-    rgb_sigma = model_eff.evaluate(pts, params=params)
+    else:
+        if sample_major:
+            pts = pts.sample_major()
+        rgb_sigma = model_eff.evaluate(pts, params=params)
     bg_view = rgb_sigma.view(S, N, 4).transpose(0, 1) if sample_major else rgb_sigma.view(N, S, 4)  # only for the bg policy's shape / last sample
     bg_rgb = _get_bg_rgb(model, rays[:, 3:6], params, bg_view, N=N, bg_color_default=bg_color_default)
     if sample_major:
@@ -221,7 +261,7 @@ def render_rays(model, rays, *args, **kwargs):
 def render_image(model, *, H: int, W: int, fx: float, fy: float, cx: float, cy: float, c2w: Tensor, scene_box, params=None,
                  active_module: Optional[int] = None, ray_samples: int = 64, chunk_points: int = 1 << 16,
                  bg_color_default: str = "white", center_pixels: bool = True, use_amp: bool = False, rows_per_chunk: Optional[int] = None,
-                 row_range: Optional[Tuple[int, int]] = None):
+                 row_range: Optional[Tuple[int, int]] = None, early_stop_eps: float = 0.0):
     """Full frame: rays are generated on the device (fused a1+a2) and rendered in row blocks.
     ``row_range=(r0, r1)`` renders only those image rows (the ray-sharded multi-GPU render,
     nerf_sys_b200.parallel.render_image_sharded) and returns rgb ((r1-r0)*W, 3), depth, acc for them."""
@@ -244,7 +284,8 @@ def render_image(model, *, H: int, W: int, fx: float, fy: float, cx: float, cy: 
             rows = min(rows_per_chunk, R1 - r0)
             rays = ops.raygen(H, W, fx, fy, cx, cy, center_pixels, c2w, aabb, device, row0=r0, rows=rows)
             c, d, _, a = render_rays(model, rays, ray_samples=ray_samples, params=params, active_module=active_module,
-                                     bg_color_default=bg_color_default, chunk=chunk_points, coherent=True, route_checks=checks)
+                                     bg_color_default=bg_color_default, chunk=chunk_points, coherent=True, route_checks=checks,
+                                     early_stop_eps=early_stop_eps)
             sl = slice((r0 - R0) * W, (r0 - R0 + rows) * W)
             rgb[sl], depth[sl], acc[sl] = c, d, a
         if checks is None or ops.route_capacity_ok(checks):

@@ -181,3 +181,31 @@ def test_fused_gather_mlp_inference_kernel_matches_the_two_kernel_path(K, gy, gz
         close(b[0], rgb_o, 2e-3, "fused rgb vs oracle")
         close(b[1], depth_o, 2e-3, "fused depth vs oracle")
         close(b[3], acc_o, 2e-3, "fused acc vs oracle")
+
+
+def test_transmittance_early_termination_is_within_eps_and_off_by_default():
+    """`early_stop_eps` (additive; 0 = the reference's arithmetic): terminated rays' remaining samples are never evaluated
+    (NaN sample distances -> no expert), and the frame differs from the full evaluation by at most eps per channel
+    (depth: eps * far).  The default reproduces the full evaluation bit for bit."""
+    from nerf_sys_b200 import ops
+    from nerf_sys_b200.nerfs.ray_rendering import render_image
+    from nerf_sys_b200.nerfs.scene_box import SceneBox
+    m, st, cfg, mins, aabb = _big_scene(8, 2, 4, 14, seed=7, table_std=0.5)
+    with torch.no_grad():
+        for sub in m.submodules:
+            sub.sigma_head.bias.add_(5.0)  # densities x 150: most rays saturate within the first groups
+    m.eval()
+    H, W = 48, 80
+    kw = dict(H=H, W=W, fx=70.0, fy=70.0, cx=W / 2, cy=H / 2, c2w=O.ring_pose(3, 20, radius=0.9), scene_box=SceneBox(aabb.to(DEV)), ray_samples=64)
+    with ops.mlp_math("f16tc"):
+        full = render_image(m, **kw)
+        again = render_image(m, early_stop_eps=0.0, **kw)
+        n0 = ops.launches()
+        for eps in (1e-2, 1e-4):
+            cut = render_image(m, early_stop_eps=eps, **kw)
+            assert float((cut[0] - full[0]).abs().max()) <= eps * 1.05 + 1e-6, eps
+            assert float((cut[2] - full[2]).abs().max()) <= eps * 1.05 + 1e-6, eps
+            assert float((cut[1] - full[1]).abs().max()) <= eps * 4.0 + 1e-5, eps  # depth: eps * far (far < 4 in this scene)
+    for a, b in zip(full, again):
+        assert torch.equal(a, b)
+    assert float(full[2].mean()) > 0.8  # the scene is opaque: termination has something to cut

@@ -43,6 +43,9 @@ two = run("two kernels (gather, then MLP)")
 ops.set_fused_inference(True)
 one = run("fused gather + MLP kernel")
 print("fused vs two-kernel: max |diff| rgb/depth/acc:", [float((x - y).abs().max()) for x, y in zip(two, one)])
+for eps in (1e-2, 1e-3):
+    cut = run(f"fused kernel + early termination, eps = {eps}", early_stop_eps=eps)
+    print(f"   max |rgb diff| vs full evaluation: {float((cut[0] - one[0]).abs().max()):.2e}; mean acc {float(one[2].mean()):.3f}")
 timing = ops.kernel_timing(True)
 render_image(model, H=H, W=W, fx=f, fy=f, cx=W / 2, cy=H / 2, c2w=poses[0], scene_box=sb, ray_samples=64)
 torch.cuda.synchronize()
