@@ -469,6 +469,17 @@ int acn_packed_render_bwd(const int64_t* offsets, const int32_t* counts, int64_t
                           const float* rgb, const float* weights, const float* d_rgb_map, const float* d_depth, const float* d_acc,
                           const float* d_weights, float* g_sigma, float* g_rgb, void* stream);
 
+/* ---- (f)-3: episode-sampler routing (data/task_dataset.py:130-171, 242-351, 353-418, 544-627) --------------------------
+ * Per ray: clip to the region box and [near, far] (valid), pick the micro-cell (policy 0 = "dda": the cell with the longest
+ * in-cell path along a 64-step grid walk; policy 1 = "alpha": the cell of the alpha point or the best of its 6 neighbours by
+ * overlap), and test the overlap with the chosen cell against that cell's tolerance (keep).  rays (N, ncol) with ncol = 6 or
+ * >= 8 ([o, d, near, far, ...]); aabb_host [lo(3), hi(3)]; cells_host (nx, ny, nz); cell_bounds (C, 6) [lo, hi] per cell and
+ * tol_per_cell (C,) on the device (TaskDataset.cell_bounds and max(1e-6 |cell diagonal|, 1e-9)); tol_abs: the alpha policy's
+ * absolute tolerance.  cid = -1 for invalid rays.  Integer outputs are bit-exact against the reference. */
+int acn_episode_route(const float* rays, int ncol, int64_t N, const float* aabb_host, const int32_t* cells_host,
+                      const float* cell_bounds, const float* tol_per_cell, int policy, float alpha, float tol_abs, int max_steps,
+                      uint8_t* valid, int32_t* cid, float* len_best, uint8_t* keep, void* stream);
+
 #if defined(__GNUC__)
 #pragma GCC visibility pop
 #endif

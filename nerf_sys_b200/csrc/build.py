@@ -33,6 +33,7 @@ SOURCES = {
     "optim.cu": [],
     "a2a.cu": ["-fmad=false"],
     "occ.cu": ["-fmad=false"],
+    "episode.cu": ["-fmad=false"],
 }
 
 
