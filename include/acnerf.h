@@ -480,6 +480,16 @@ int acn_episode_route(const float* rays, int ncol, int64_t N, const float* aabb_
                       const float* cell_bounds, const float* tol_per_cell, int policy, float alpha, float tol_abs, int max_steps,
                       uint8_t* valid, int32_t* cid, float* len_best, uint8_t* keep, void* stream);
 
+/* ---- (f)-4: Voronoi mask builder (scripts/create_clusters.py:386-634; reductions :898-904, 928-932) ----------------------
+ * rays (N,8) [o, d, near, far]; per ray `ray_samples` positions at lerp(near, far, linspace(0,1,S)); a sample belongs to the
+ * centroids with d^2 <= margin^2 * min d^2 (margin == 1: the nearest, first index on ties), distances over components (1,2)
+ * when cluster_2d else (0,1,2); mask (N,C) uint8 = any sample of the ray belongs to c.  mins_io / maxs_io (C,3) fp32 and
+ * counts_io (C,) int64 (all three or none): running per-expert bounding box and count of the member sample positions,
+ * updated in place (the caller all-reduces them MIN / MAX / SUM across ranks); ws: acn_voronoi_ws_bytes() bytes. */
+int64_t acn_voronoi_ws_bytes(void);
+int acn_voronoi_masks(const float* rays, int64_t N, int ray_samples, const float* centroids_host, int C, int cluster_2d, float margin,
+                      uint8_t* mask, float* mins_io, float* maxs_io, int64_t* counts_io, void* ws, void* stream);
+
 #if defined(__GNUC__)
 #pragma GCC visibility pop
 #endif

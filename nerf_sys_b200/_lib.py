@@ -74,6 +74,8 @@ SIGNATURES = {
     "acn_num_sms": (C.c_int, [C.c_int]),
     "acn_launch_hint": (C.c_int, [C.c_int, C.c_int]),
     "acn_episode_route": (C.c_int, [vp, C.c_int, i64, fp, P(i32), vp, vp, C.c_int, f32, f32, C.c_int, vp, vp, vp, vp, vp]),
+    "acn_voronoi_ws_bytes": (i64, []),
+    "acn_voronoi_masks": (C.c_int, [vp, i64, C.c_int, fp, C.c_int, C.c_int, f32, vp, vp, vp, vp, vp, vp]),
     "acn_occ_march_count": (C.c_int, [vp, vp, i64, vp, fp, C.c_int, C.c_int, f32, f32, C.c_int, vp, vp]),
     "acn_occ_march_write": (C.c_int, [vp, vp, i64, vp, fp, C.c_int, C.c_int, f32, f32, C.c_int, vp, vp, vp, vp, vp, vp]),
     "acn_occ_visibility": (C.c_int, [vp, vp, i64, vp, vp, vp, f32, f32, vp, vp]),

@@ -34,6 +34,7 @@ SOURCES = {
     "a2a.cu": ["-fmad=false"],
     "occ.cu": ["-fmad=false"],
     "episode.cu": ["-fmad=false"],
+    "voronoi.cu": ["-fmad=false"],
 }
 
 

@@ -192,3 +192,14 @@ def test_episode_routing_oracle_equals_the_reference(tag, policy):
     # (and the GPU router) keep the original ray order inside a cell, which is what the reference's comment asks for
     for mine, ref in zip(bins, torch.split(T(z[f"{tag}_{policy}_bins"]), sizes)):
         assert torch.equal(mine, torch.sort(ref).values)
+
+
+# ----------------------------------------------------------------------------- (f)-4 Voronoi mask builder
+@pytest.mark.parametrize("tag", ["soft2d", "hard2d", "soft3d"])
+def test_voronoi_oracle_equals_the_reference(tag):
+    """oracle/voronoi_oracle.voronoi_orig against the unmodified compute_voronoi_orig (tests/golden/make_golden_voronoi.py)."""
+    from oracle import voronoi_oracle as VO
+    z = load_golden("voronoi")
+    c2d, margin, S = z[f"{tag}_cfg"]
+    m = VO.voronoi_orig(T(z["rays"]), int(S), T(z["centroids"]), bool(c2d), float(margin))
+    assert torch.equal(m, T(z[f"{tag}_mask"]))

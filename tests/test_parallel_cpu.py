@@ -283,3 +283,18 @@ def _sync_worker(rank, world):
 @pytest.mark.parametrize("world", [2, 3])
 def test_sync_expert_params_broadcasts_from_the_owner(world):
     _spawn(_sync_worker, world)
+
+
+# ---- Voronoi box reduction (scripts/create_clusters.py:928-932) ------------------------------------
+def _boxes_worker(rank, world):
+    from nerf_sys_b200.data.voronoi_masks import reduce_boxes
+    mins = torch.tensor([[float(rank), -float(rank), 0.5]] * 3)
+    maxs = torch.tensor([[float(rank), 10.0 + rank, 0.5]] * 3)
+    cnts = torch.tensor([rank + 1, 0, 5], dtype=torch.int64)
+    reduce_boxes(mins, maxs, cnts)
+    assert mins[0].tolist() == [0.0, -float(world - 1), 0.5] and maxs[0].tolist() == [float(world - 1), 10.0 + world - 1, 0.5]
+    assert cnts.tolist() == [world * (world + 1) // 2, 0, 5 * world]
+
+
+def test_voronoi_box_reduction_min_max_sum():
+    _spawn(_boxes_worker, 2)
