@@ -22,7 +22,7 @@ INTERPOLATIONS = ("Nearest", "Linear", "Smoothstep")
 
 
 class SHEncoder(nn.Module):
-    def __init__(self, levels: int = 4, implementation: str = "sm100") -> None:
+    def __init__(self, levels: int = 4, implementation: str = "tcnn") -> None:
         super().__init__()
         if levels != 4:
             raise ValueError(f"the sm_100a SH kernel implements levels=4 (16 components), got {levels}")
@@ -42,7 +42,7 @@ class SHEncoder(nn.Module):
 
 class HashGridEncoder(nn.Module):
     def __init__(self, levels: int = 16, min_res: int = 16, max_res: int = 4096, log2_hashmap_size: int = 19,
-                 features_per_level: int = 2, hash_init_scale: float = 1e-3, implementation: str = "sm100",
+                 features_per_level: int = 2, hash_init_scale: float = 1e-3, implementation: str = "tcnn",
                  interpolation: Optional[str] = None) -> None:
         super().__init__()
         self.levels, self.min_res, self.max_res = int(levels), int(min_res), int(max_res)

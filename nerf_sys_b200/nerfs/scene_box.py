@@ -65,3 +65,24 @@ class SceneBox:
         if p.ndim == 0:
             p = p.repeat(3)
         return SceneBox(aabb=torch.stack([self.aabb[0] - p, self.aabb[1] + p], dim=0))
+
+    # ---- box utilities the dataset / clustering tools call (scene_box.py:119-147, 208-217) ----
+    def get_centered_and_scaled_scene_box(self, scale_factor: Union[float, Tensor] = 1.0) -> "SceneBox":
+        s = torch.as_tensor(scale_factor, device=self.aabb.device, dtype=self.aabb.dtype)
+        return SceneBox(aabb=(self.aabb - self.center) * s)
+
+    @staticmethod
+    def get_normalized_positions(positions: Tensor, aabb: Tensor) -> Tensor:
+        return (positions - aabb[0]) / (aabb[1] - aabb[0])
+
+    @staticmethod
+    def from_camera_poses(poses: Tensor, scale_factor: float = 1.0) -> "SceneBox":
+        centres = poses[..., :3, -1]
+        return SceneBox(aabb=torch.stack([centres.min(dim=-2).values, centres.max(dim=-2).values], dim=0) * scale_factor)
+
+    def union(self, other: "SceneBox") -> "SceneBox":
+        return SceneBox(aabb=torch.stack([torch.minimum(self.min, other.min), torch.maximum(self.max, other.max)], dim=0))
+
+    @staticmethod
+    def reduce_union(aabbs: Tensor) -> "SceneBox":
+        return SceneBox(aabb=torch.stack([aabbs[:, 0, :].min(dim=0).values, aabbs[:, 1, :].max(dim=0).values], dim=0))

@@ -17,19 +17,41 @@ dump() {  # object, mangled-name regex, label
   echo
 }
 {
-dump ngp_tc.o 16k_ngp_mlp_fwd_tc k_ngp_mlp_fwd_tc
+dump ngp_tc.o "16k_ngp_mlp_fwd_tcILi7ELi72ELb0" k_ngp_mlp_fwd_tc
+dump ngp_tc.o "16k_ngp_mlp_fwd_tcILi5ELi96ELb1" k_ngp_fused_fwd_tc
 dump ngp_tc.o "16k_ngp_mlp_bwd_tcILi4" k_ngp_mlp_bwd_tc_512
 dump ngp_tc.o "16k_ngp_mlp_bwd_tcILi2" k_ngp_mlp_bwd_tc_256
+dump ngp_tc.o 17k_tc_wgrad_reduce k_tc_wgrad_reduce
+dump ngp_tc.o 8k_absmax k_absmax
 dump dense_tc.o "10k_dense_tcILi64" k_dense_tc_64
 dump dense_tc.o 10k_wgrad_tc k_wgrad_tc
-dump ngp.o 14k_ngp_hash_fwd k_ngp_hash_fwd
+dump dense_tc.o 6k_pe_h k_pe_h
+dump dense_tc.o 14k_pe_final_fwd k_pe_final_fwd
+dump dense_tc.o 14k_pe_final_bwd k_pe_final_bwd
+dump ngp.o "14k_ngp_hash_fwdILi4" k_ngp_hash_fwd_4
+dump ngp.o "14k_ngp_hash_fwdILi8" k_ngp_hash_fwd_8
 dump ngp.o 14k_ngp_hash_bwd k_ngp_hash_bwd
-dump render.o 15k_composite_fwd k_composite_fwd
-dump render.o 15k_composite_bwd k_composite_bwd
+dump render.o "15k_composite_fwdEPK" k_composite_fwd
+dump render.o 18k_composite_fwd_sm k_composite_fwd_sm
+dump render.o "15k_composite_bwdILi32" k_composite_bwd
+dump render.o 8k_bg_fwd k_bg_fwd
+dump render.o 14k_bg_bwd_fused k_bg_bwd_fused
+dump render.o 13k_mse_partial k_mse_partial
+dump rays.o 8k_raygen k_raygen
+dump rays.o 9k_strat_t k_strat_t
 dump routing.o "13k_route_writeILi8ELb0" k_route_write
 dump routing.o "13k_route_countILi8ELb0" k_route_count
 dump a2a.o 15k_a2a_push_rows k_a2a_push_rows
 dump a2a.o 18k_a2a_pull_combine k_a2a_pull_combine
 dump a2a.o 15k_a2a_push_grad k_a2a_push_grad
+dump a2a.o 13k_p2p_barrier k_p2p_barrier
+dump a2a.o 10k_p2p_plan k_p2p_plan
 dump optim.o 12k_adam_multi k_adam_multi
+dump optim.o 13k_sumsq_multi k_sumsq_multi
+dump occ.o 11k_occ_march k_occ_march
+dump occ.o 11k_seg_union k_seg_union
+dump occ.o 12k_packed_fwd k_packed_fwd
+dump occ.o 12k_packed_bwd k_packed_bwd
+dump episode.o 15k_episode_route k_episode_route
+dump voronoi.o 9k_voronoi k_voronoi
 } | tee $out/CENSUS.txt
