@@ -1305,11 +1305,12 @@ class PackedRenderFn(torch.autograd.Function):
         sg, cl, w = ctx.saved_tensors
         seg = ctx.seg
         g_sigma, g_rgb = torch.empty_like(sg), torch.empty_like(cl)
-        opt = lambda t, n: None if t is None else _f32(t, n)  # noqa: E731
+        # contiguous copies of expanded incoming gradients must outlive the launch (a temporary freed inside the argument list
+        # is handed to the next temporary by the caching allocator)
+        gr, gd, ga, gw = (None if t is None else _f32(t, "gradient") for t in (d_rgb, d_depth, d_acc, d_w))
         with _on(sg.device), _timed("packed_render_bwd"):
             check(lib().acn_packed_render_bwd(_ptr(seg.offsets), _ptr(seg.counts), seg.N, _ptr(seg.t0), _ptr(seg.t1), _ptr(sg), _ptr(cl), _ptr(w),
-                                              _ptr(opt(d_rgb, "d_rgb")), _ptr(opt(d_depth, "d_depth")), _ptr(opt(d_acc, "d_acc")),
-                                              _ptr(opt(d_w, "d_w")), _ptr(g_sigma), _ptr(g_rgb), _stream()), "acn_packed_render_bwd")
+                                              _ptr(gr), _ptr(gd), _ptr(ga), _ptr(gw), _ptr(g_sigma), _ptr(g_rgb), _stream()), "acn_packed_render_bwd")
         _count(1)
         return g_sigma.view(ctx.sigma_shape), g_rgb, None
 

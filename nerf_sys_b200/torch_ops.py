@@ -50,10 +50,11 @@ def volume_render_backward(rgb_sigma: Tensor, t_vals: Tensor, bg_rgb: Tensor, si
     rs, tt, b = ops._f32(rgb_sigma, "rgb_sigma"), ops._f32(t_vals, "t_vals"), ops._f32(bg_rgb, "bg_rgb")
     N, S = tt.shape
     d_rs, d_bg = torch.empty_like(rs), torch.empty_like(b)
+    # incoming gradients may be expanded views (e.g. of a .sum()): the contiguous copies must stay alive until the launch
+    gr, gd, ga, gw = (ops._f32(g, "gradient") for g in (g_rgb, g_depth, g_acc, g_w))
     with ops._on(rs.device):
-        check(lib().acn_composite_bwd(ops._ptr(rs), ops._ptr(tt), ops._ptr(b), N, S, float(sigma_scale), ops._ptr(ops._f32(g_rgb, "g")),
-                                      ops._ptr(ops._f32(g_depth, "g")), ops._ptr(ops._f32(g_acc, "g")), ops._ptr(ops._f32(g_w, "g")), ops._ptr(d_rs),
-                                      ops._ptr(d_bg), ops._stream()), "acn_composite_bwd")
+        check(lib().acn_composite_bwd(ops._ptr(rs), ops._ptr(tt), ops._ptr(b), N, S, float(sigma_scale), ops._ptr(gr), ops._ptr(gd), ops._ptr(ga),
+                                      ops._ptr(gw), ops._ptr(d_rs), ops._ptr(d_bg), ops._stream()), "acn_composite_bwd")
     ops._count(1)
     return d_rs, d_bg
 
@@ -156,10 +157,10 @@ def packed_render_backward(sigma: Tensor, rgb: Tensor, t0: Tensor, t1: Tensor, o
                            g_depth: Tensor, g_w: Tensor, g_acc: Tensor) -> Tuple[Tensor, Tensor]:
     sg, cl = ops._f32(sigma.reshape(-1), "sigma"), ops._f32(rgb, "rgb")
     g_sigma, g_c = torch.empty_like(sg), torch.empty_like(cl)
+    gr, gd, ga, gw = (ops._f32(g, "gradient") for g in (g_rgb, g_depth, g_acc, g_w))  # kept alive until the launch
     with ops._on(sg.device):
         check(lib().acn_packed_render_bwd(ops._ptr(offsets), ops._ptr(counts), offsets.shape[0], ops._ptr(t0), ops._ptr(t1), ops._ptr(sg), ops._ptr(cl),
-                                          ops._ptr(weights), ops._ptr(ops._f32(g_rgb, "g")), ops._ptr(ops._f32(g_depth, "g")),
-                                          ops._ptr(ops._f32(g_acc, "g")), ops._ptr(ops._f32(g_w, "g")), ops._ptr(g_sigma), ops._ptr(g_c),
+                                          ops._ptr(weights), ops._ptr(gr), ops._ptr(gd), ops._ptr(ga), ops._ptr(gw), ops._ptr(g_sigma), ops._ptr(g_c),
                                           ops._stream()), "acn_packed_render_bwd")
     ops._count(1)
     return g_sigma.view_as(sigma), g_c

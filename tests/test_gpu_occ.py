@@ -103,6 +103,14 @@ def test_packed_render_forward_backward_vs_oracle():
     s, c = sigma.clone().to(DEV).requires_grad_(True), rgb.clone().to(DEV).requires_grad_(True)
     outs = ops.packed_render(s, c, seg)
     sum(((a * b.to(DEV)).sum() for a, b in zip(outs, cot))).backward()
+    # expanded (stride-0) incoming gradients, as a bare .sum() produces them
+    s2, c2 = sigma.clone().to(DEV).requires_grad_(True), rgb.clone().to(DEV).requires_grad_(True)
+    o2 = ops.packed_render(s2, c2, seg)
+    (o2[0].sum() + 0.5 * o2[1].sum() + 0.25 * o2[3].sum()).backward()
+    s3, c3 = sigma.clone().requires_grad_(True), rgb.clone().requires_grad_(True)
+    o3 = OO.packed_render(seg.ray_idx.cpu().long(), seg.t0.cpu(), seg.t1.cpu(), s3, c3, 200)
+    (o3[0].sum() + 0.5 * o3[1].sum() + 0.25 * o3[3].sum()).backward()
+    rel_close(s2.grad, s3.grad, 2e-5, "d/d sigma, expanded gradients")
     for name, a, b in zip(("rgb", "depth", "weights", "acc"), outs, outs_o):
         close(a, b, 2e-6, name)
     rel_close(s.grad, s_o.grad, 2e-5, "d/d sigma")
