@@ -141,6 +141,12 @@ int acn_clamp_near_far(const float* rays_in, int64_t n, int override_none, int h
  * jitter in [0,1) or NULL (eval).  t (N,S). */
 int acn_stratified_t(const float* rays, int64_t N, int S, const float* tau, const float* u, float* t,
                      void* stream);
+/* Proposal (hierarchical) resampling - ADDITIVE: the reference has no proposal sampler (SURVEY headline 4; north_star names
+ * one).  t, weights (N,S) from a coarse pass (3 <= S <= 256), u (N,S2) in [0,1) ASCENDING per ray.  t_new (N,S2): inverse-CDF
+ * samples of the piecewise-constant pdf over the midpoint bins (weights[1..S-2] + 1e-5); t_merged (N,S+S2) or NULL: the
+ * coarse and the new distances merged in ascending order. */
+int acn_sample_pdf(const float* t, const float* weights, const float* u, int64_t N, int S, int S2, float* t_new,
+                   float* t_merged, void* stream);
 /* nerfs/ray_rendering.py:317-319: (N,8),(N,S) -> x6 (N*S,6).  API parity / tests only;
  * the render path never materialises this. */
 int acn_sample_points(const float* rays, const float* t, int64_t N, int S, float* x6, void* stream);

@@ -88,6 +88,7 @@ SIGNATURES = {
     "acn_ray_aabb": (C.c_int, [vp, vp, i64, fp, f32, f32, vp, vp, vp]),
     "acn_clamp_near_far": (C.c_int, [vp, i64, C.c_int, C.c_int, f32, C.c_int, f32, f32, f32, vp, vp, vp]),
     "acn_stratified_t": (C.c_int, [vp, i64, C.c_int, vp, vp, vp, vp]),
+    "acn_sample_pdf": (C.c_int, [vp, vp, vp, i64, C.c_int, C.c_int, vp, vp, vp]),
     "acn_sample_points": (C.c_int, [vp, vp, i64, C.c_int, vp, vp]),
     "acn_routing": (C.c_int, [P(AcnPoints), fp, C.c_int, f32, C.c_int, vp, vp, vp]),
     "acn_route_pack_capacity": (i64, [i64, C.c_int]),

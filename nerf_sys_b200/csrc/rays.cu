@@ -210,6 +210,56 @@ static int fill_cam(Cam& c, const float* c2w, const float* aabb, float near_c, f
   return 0;
 }
 
+
+// Proposal (hierarchical) resampling, the inverse-CDF step of NeRF's coarse-to-fine sampler.  ADDITIVE: the reference has no
+// proposal sampler (its importance sampler is the occupancy grid); north_star names one.  Per ray: bins = midpoints of the S
+// coarse distances (S-1 edges), weights = w[1..S-2] + 1e-5, cdf = [0, cumsum(pdf)]; each u in [0,1) lands in the bin where the
+// cdf passes it (searchsorted, right side) and is placed linearly inside it; then the S2 new distances (u ascending -> ascending)
+// are merged with the S coarse ones into one ascending list of S + S2.  One thread per ray; the cdf lives in local memory.
+constexpr int PDF_MAX_S = 256;
+__global__ void __launch_bounds__(128) k_sample_pdf(const float* __restrict__ t, const float* __restrict__ w, const float* __restrict__ u, int64_t N,
+                                                    int S, int S2, float* __restrict__ t_new, float* __restrict__ t_merged) {
+  const int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (r >= N) return;
+  const float* tr = t + r * S;
+  const float* wr = w + r * S;
+  float cdf[PDF_MAX_S];
+  const int nb = S - 1;  // bin edges; nb - 1 intervals
+  float sum = 0.f;
+  for (int i = 0; i < nb - 1; ++i) sum = sum + (wr[i + 1] + 1e-5f);
+  cdf[0] = 0.f;
+  float acc = 0.f;
+  for (int i = 0; i < nb - 1; ++i) {
+    acc = acc + (wr[i + 1] + 1e-5f) / sum;
+    cdf[i + 1] = acc;
+  }
+  int ci = 0;      // merge cursor into the coarse list
+  int64_t mo = r * (int64_t)(S + S2);
+  int mcount = 0;
+  for (int j = 0; j < S2; ++j) {
+    const float uj = u[r * (int64_t)S2 + j];
+    // searchsorted(cdf, u, right=True): first index with cdf[idx] > u
+    int lo = 0, hi = nb;
+    while (lo < hi) {
+      const int mid = (lo + hi) >> 1;
+      if (cdf[mid] <= uj) lo = mid + 1; else hi = mid;
+    }
+    const int below = lo - 1 < 0 ? 0 : lo - 1, above = lo > nb - 1 ? nb - 1 : lo;
+    float denom = cdf[above] - cdf[below];
+    if (denom < 1e-5f) denom = 1.f;
+    const float frac = (uj - cdf[below]) / denom;
+    const float b0 = 0.5f * (tr[below] + tr[below + 1]), b1 = 0.5f * (tr[above] + tr[above + 1]);
+    const float tn = b0 + frac * (b1 - b0);
+    t_new[r * (int64_t)S2 + j] = tn;
+    if (t_merged) {
+      while (ci < S && tr[ci] <= tn) t_merged[mo + mcount++] = tr[ci++];
+      t_merged[mo + mcount++] = tn;
+    }
+  }
+  if (t_merged)
+    while (ci < S) t_merged[mo + mcount++] = tr[ci++];
+}
+
 }  // namespace acn
 
 using namespace acn;
@@ -275,6 +325,15 @@ int acn_stratified_t(const float* rays, int64_t N, int S, const float* tau, cons
   if (N == 0) return ACN_OK;
   int64_t total = N * S;
   k_strat_t<<<persistent_grid((total + 255) / 256, 8), 256, 0, as_stream(stream)>>>(rays, N, S, tau, u, t);
+  ACN_LAUNCH_CHECK();
+  return ACN_OK;
+}
+
+int acn_sample_pdf(const float* t, const float* weights, const float* u, int64_t N, int S, int S2, float* t_new, float* t_merged, void* stream) {
+  ACN_REQUIRE(t && weights && u && t_new && N >= 0 && S2 >= 1, "acn_sample_pdf: bad arguments");
+  ACN_REQUIRE(S >= 3 && S <= PDF_MAX_S, "acn_sample_pdf: 3 <= S <= %d coarse samples", PDF_MAX_S);
+  if (N == 0) return ACN_OK;
+  k_sample_pdf<<<(unsigned)((N + 127) / 128), 128, 0, as_stream(stream)>>>(t, weights, u, N, S, S2, t_new, t_merged);
   ACN_LAUNCH_CHECK();
   return ACN_OK;
 }

@@ -417,6 +417,21 @@ def route_pack(pts: PointSet, centroids_host: Sequence[float], K: int, margin: f
     return PairList(M, point[:M], weight[:M], seg, seg_host)
 
 
+@torch.no_grad()
+def sample_pdf(t: Tensor, weights: Tensor, u: Tensor, merge: bool = True):
+    """Proposal resampling (additive, see acn_sample_pdf): (N,S) coarse distances + weights, (N,S2) ascending u in [0,1) ->
+    t_new (N,S2) and, with ``merge``, the ascending union (N,S+S2)."""
+    tt, ww, uu = _need(t, "t"), _need(weights.detach(), "weights"), _need(u, "u")
+    N, S = tt.shape
+    S2 = uu.shape[1]
+    t_new = torch.empty(N, S2, device=tt.device)
+    merged = torch.empty(N, S + S2, device=tt.device) if merge else None
+    with _on(tt.device), _timed("sample_pdf"):
+        check(lib().acn_sample_pdf(_ptr(tt), _ptr(ww), _ptr(uu), N, S, S2, _ptr(t_new), _ptr(merged), _stream()), "acn_sample_pdf")
+    _count(1)
+    return t_new, merged
+
+
 def route_capacity_ok(checks: Sequence[Tuple[Tensor, int]]) -> bool:
     """One device->host read for a whole frame: did every deferred route_pack(sync=False) fit its speculative capacity?"""
     if not checks:
