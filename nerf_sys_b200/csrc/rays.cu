@@ -225,13 +225,16 @@ __global__ void __launch_bounds__(128) k_sample_pdf(const float* __restrict__ t,
   const float* wr = w + r * S;
   float cdf[PDF_MAX_S];
   const int nb = S - 1;  // bin edges; nb - 1 intervals
-  float sum = 0.f;
-  for (int i = 0; i < nb - 1; ++i) sum = sum + (wr[i + 1] + 1e-5f);
+  // running sums in double, rounded to fp32 per entry (what torch.cumsum does for fp32 on the CPU): a sample in a bin of mass m
+  // moves by (cdf error / m) of the bin width, and peaked weights leave bins with m ~ 1e-5
+  double dsum = 0.0;
+  for (int i = 0; i < nb - 1; ++i) dsum += (double)(wr[i + 1] + 1e-5f);
+  const float sum = (float)dsum;
   cdf[0] = 0.f;
-  float acc = 0.f;
+  double acc = 0.0;
   for (int i = 0; i < nb - 1; ++i) {
-    acc = acc + (wr[i + 1] + 1e-5f) / sum;
-    cdf[i + 1] = acc;
+    acc += (double)((wr[i + 1] + 1e-5f) / sum);
+    cdf[i + 1] = (float)acc;
   }
   int ci = 0;      // merge cursor into the coarse list
   int64_t mo = r * (int64_t)(S + S2);

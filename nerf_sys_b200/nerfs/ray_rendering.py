@@ -247,6 +247,32 @@ def render_rays_occ(model, rays: Tensor, *, params=None, bg_color_default: str =
     return _packed_integrate(model, rays, params, seg, sigma_mix, rgb_mix, bg_color_default)
 
 
+def render_rays_hierarchical(model, rays: Tensor, ray_samples: int, proposal_samples: int, params=None, active_module: Optional[int] = None,
+                             bg_color_default: str = "white", sigma_scale=1.0, **kwargs):
+    """Coarse-to-fine rendering with proposal resampling - ADDITIVE: the reference has no proposal sampler (SURVEY headline 4);
+    north_star names one.  A no-grad coarse pass over `ray_samples` stratified samples gives the weights; `proposal_samples`
+    new distances are drawn from them by inverse-CDF (ops.sample_pdf: stratified u in training, bin centres in eval) and merged
+    with the coarse ones; the fine pass over the merged distances is the differentiable one.  Returns the fine pass's
+    (rgb, depth, weights (N, S+S2), acc)."""
+    rays = ops._f32(rays, "rays")
+    N, S, S2 = rays.shape[0], int(ray_samples), int(proposal_samples)
+    with torch.no_grad():
+        u_c = torch.rand(N, S, device=rays.device) if model.training else None  # the coarse pass and the bins share one jitter
+        _, _, w, _ = render_rays_stratified(model, rays, S, params=params, active_module=active_module, bg_color_default=bg_color_default,
+                                            sigma_scale=sigma_scale, u=u_c)
+        t = ops.stratified_t(rays, S, u_c)
+        base = (torch.arange(S2, device=rays.device, dtype=torch.float32) + 0.5) / S2
+        u = base[None, :].expand(N, S2)
+        if model.training:
+            u = (torch.arange(S2, device=rays.device, dtype=torch.float32)[None, :] + torch.rand(N, S2, device=rays.device)) / S2
+        _, t_all = ops.sample_pdf(t, w.contiguous(), u.contiguous())
+    model_eff = model.submodules[active_module] if active_module is not None else model
+    pts = ops.PointSet(rays=rays, t=t_all)
+    rgb_sigma = model_eff.evaluate(pts, params=params)
+    bg_rgb = _get_bg_rgb(model, rays[:, 3:6], params, rgb_sigma.view(N, S + S2, 4), N=N, bg_color_default=bg_color_default)
+    return ops.composite(rgb_sigma.view(N, S + S2, 4), t_all, bg_rgb, float(sigma_scale))
+
+
 def render_rays(model, rays, *args, **kwargs):
     """Dispatch of ray_rendering.py:563-574: the occupancy renderer once the model's grids are ready, else stratified."""
     if getattr(model, "use_occ", False) and getattr(model, "occ_ready", False):

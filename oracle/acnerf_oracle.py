@@ -491,3 +491,23 @@ def render_rays_pe(rays: Tensor, p: Dict[str, Tensor], *, S: int, u: Optional[Te
 # uses it directly, so no timed region calls into this file); re-exported here for the tests.
 # --------------------------------------------------------------------------
 from nerf_sys_b200.synthetic import GLOBAL_AABB, HASH_CFG, aerial_rays, grid_scene, init_ngp_state, ring_pose  # noqa: E402,F401
+
+
+# --------------------------------------------------------------------------
+# proposal (hierarchical) resampling - ADDITIVE: the reference has none (SURVEY headline 4); the canonical NeRF sample_pdf
+# --------------------------------------------------------------------------
+def sample_pdf(t: Tensor, weights: Tensor, u: Tensor) -> Tuple[Tensor, Tensor]:
+    """(N,S) coarse distances + weights, (N,S2) ascending u in [0,1) -> t_new (N,S2), merged ascending (N,S+S2)."""
+    bins = 0.5 * (t[:, 1:] + t[:, :-1])
+    w = weights[:, 1:-1] + 1e-5
+    pdf = w / torch.cumsum(w, -1)[:, -1:]  # a sequential fp32 sum, as the kernel's (a pairwise sum moves the cdf by an ulp, and a
+    # sample in a near-empty bin by (1 ulp / bin mass) of the bin width)
+    cdf = torch.cat([torch.zeros_like(pdf[:, :1]), torch.cumsum(pdf, -1)], -1)
+    inds = torch.searchsorted(cdf.contiguous(), u.contiguous(), right=True)
+    below, above = (inds - 1).clamp_min(0), inds.clamp_max(cdf.shape[-1] - 1)
+    c0, c1 = torch.gather(cdf, 1, below), torch.gather(cdf, 1, above)
+    b0, b1 = torch.gather(bins, 1, below), torch.gather(bins, 1, above)
+    denom = c1 - c0
+    denom = torch.where(denom < 1e-5, torch.ones_like(denom), denom)
+    t_new = b0 + (u - c0) / denom * (b1 - b0)
+    return t_new, torch.sort(torch.cat([t, t_new], -1), -1).values
