@@ -527,6 +527,8 @@ int launch_hash_bwd_range(const AcnPoints* pts, const AcnPairs* pairs, const Acn
     unsigned long long st_l = (g->interp != 2 && r < 512) ? (r <= 20 ? 3 : r <= 40 ? 2 : r <= 80 ? 1 : 0) : 0;
     agg |= st_l << (4 * l);
   }
+  // (a level-group form like the gather's was measured slower: 1020 vs 777 us over 8 tables, 430 vs 340 us over one - the
+  // reductions want ONE level's slabs hot in L2 at a time; profiles/r2_gather_scatter_levels.txt)
   dim3 hg(grid_x > 0 ? grid_x : persistent_grid((span + 255) / 256, 4), g->levels);
   k_ngp_hash_bwd<<<hg, 256, 0, st>>>(make_src(pts), pairs->point, pairs->seg, Mcap, tab, make_grid(g), d_enc, h_round_ld(Mcap), gts, m_lo, m_hi,
                                      agg);
