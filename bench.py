@@ -680,7 +680,7 @@ def train_c2(ctx, K, W):
     ex = red = None
     if ctx.world > 1:
         ex = PL.PeerExchange(rows_cap=128)
-        red = PL.SlabGradReducer(ex, list(model.bg_mlp.parameters()), scale=1.0 / ctx.world)
+        red = PL.SlabGradReducer(ex, list(model.bg_mlp.parameters()), scale=1.0 / ctx.world, early=True)  # posted inside the backward
     gstep = GraphedTrainStep(opt, lambda r, c: compute_mse_loss(P, model, {"rays": r, "rgbs": c}), (pool[0], rgbs[0]), warmup=W,
                              post_backward=(red.wait if red is not None else None))
     for i in range(W):
@@ -701,6 +701,8 @@ def train_c2(ctx, K, W):
               "config": "800x800 x 64 samples, one expert per GPU, eval, no_grad, raygen on device"}
     gstep = None
     opt.release_persistent_grads()
+    if red is not None:
+        red.remove()
     if ex is not None:
         ex.close()
     del model, opt

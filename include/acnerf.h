@@ -425,6 +425,13 @@ int acn_p2p_close(void* ptr);
  * synchronisation. */
 int acn_p2p_barrier(void* const* sync_bases_host, int world, int rank, const int32_t* counts, int n_counts,
                     const float* payload, int n_payload, float* reduced, float scale, float timeout_s, void* stream);
+/* The barrier in two launches: ARRIVE publishes the payload and raises this rank's flag without waiting; WAIT blocks until every
+ * rank's flag of that epoch is up, then reduces the payload slots.  Kernels enqueued between the two absorb the skew between the
+ * ranks (gradients that are complete early in a backward pass).  Each arrive must be followed by its wait before any other
+ * barrier on the same slabs. */
+int acn_p2p_arrive(void* const* sync_bases_host, int world, int rank, const float* payload, int n_payload, void* stream);
+int acn_p2p_wait(void* const* sync_bases_host, int world, int rank, int n_payload, float* reduced, float scale, float timeout_s,
+                 void* stream);
 /* Device-side layout of one exchange (parallel.peer_layout on the GPU).  Reads the count table of this rank's slab
  * (filled by the counts barrier); owner_host[e] = rank owning expert e.  Layout of an owner's slab: its experts in
  * order, each expert's block = the sub-blocks of source ranks 0..world-1 back to back, blocks padded to ACN_TILE rows.

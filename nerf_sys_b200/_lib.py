@@ -149,6 +149,8 @@ SIGNATURES = {
     "acn_p2p_open": (C.c_int, [vp, P(C.c_void_p)]),
     "acn_p2p_close": (C.c_int, [vp]),
     "acn_p2p_barrier": (C.c_int, [P(C.c_void_p), C.c_int, C.c_int, vp, C.c_int, vp, C.c_int, vp, f32, f32, vp]),
+    "acn_p2p_arrive": (C.c_int, [P(vp), C.c_int, C.c_int, vp, C.c_int, vp]),
+    "acn_p2p_wait": (C.c_int, [P(vp), C.c_int, C.c_int, C.c_int, vp, f32, f32, vp]),
     "acn_p2p_plan": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, P(i32), i64, vp, vp, vp, vp, vp, vp, vp]),
     "acn_route_status": (C.c_int, [vp, C.c_int, i64, vp, vp, vp]),
 }

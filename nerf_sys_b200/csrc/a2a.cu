@@ -232,21 +232,27 @@ constexpr int BARRIER_THREADS = 128;
 
 __global__ void __launch_bounds__(BARRIER_THREADS) k_p2p_barrier(PeerSync peers, int world, int rank, const int32_t* __restrict__ counts,
                                                                  int n_counts, const float* __restrict__ payload, int n_payload,
-                                                                 float* __restrict__ reduced, float scale, unsigned long long timeout_ns) {
+                                                                 float* __restrict__ reduced, float scale, unsigned long long timeout_ns,
+                                                                 int phase) {
+  // phase 0: arrive + wait.  Split form: phase 1 = ARRIVE (advance the epoch, publish counts / payload, raise this rank's flag in
+  // every slab, return at once); phase 2 = WAIT for the epoch of the last arrive, then reduce.  Work a rank enqueues between its
+  // arrive and its wait absorbs the skew between the ranks (the reduction of gradients that are ready early in a backward pass).
+  // Every arrive is followed by its wait before the next barrier of any kind on the same exchange.
   __shared__ int32_t s_epoch;
   const int t = threadIdx.x;
   if (t == 0) {
     int32_t* e = peers.base[rank] + SYNC_EPOCH;
-    s_epoch = *e + 1;
+    s_epoch = (phase == 2) ? *e : *e + 1;
     *e = s_epoch;
   }
   __syncthreads();
   const int32_t epoch = s_epoch;
+  const int slot = (epoch & 1) * ACN_MAX_PEERS * ACN_P2P_PAYLOAD_FLOATS;
+  if (phase == 2) goto wait_phase;
   if (counts != nullptr && t < world) {
     int32_t* row = peers.base[t] + SYNC_TABLE + rank * (ACN_MAX_EXPERTS + 1);
     for (int i = 0; i < n_counts; ++i) row[i] = counts[i];
   }
-  const int slot = (epoch & 1) * ACN_MAX_PEERS * ACN_P2P_PAYLOAD_FLOATS;
   if (payload != nullptr) {
     for (int s = 0; s < world; ++s) {
       float* dst = reinterpret_cast<float*>(peers.base[s]) + SYNC_PAYLOAD + slot + rank * ACN_P2P_PAYLOAD_FLOATS;
@@ -256,6 +262,8 @@ __global__ void __launch_bounds__(BARRIER_THREADS) k_p2p_barrier(PeerSync peers,
   __threadfence_system();
   __syncthreads();
   if (t < world) st_release_sys(peers.base[t] + rank, epoch);
+  if (phase == 1) return;
+wait_phase:
   if (t < world) {
     const int32_t* mine = peers.base[rank] + t;
     const unsigned long long t0 = global_ns();
@@ -269,7 +277,7 @@ __global__ void __launch_bounds__(BARRIER_THREADS) k_p2p_barrier(PeerSync peers,
     }
   }
   __syncthreads();
-  if (payload != nullptr && reduced != nullptr) {
+  if (n_payload > 0 && reduced != nullptr) {
     const float* src = reinterpret_cast<const float*>(peers.base[rank]) + SYNC_PAYLOAD + slot;
     for (int i = t; i < n_payload; i += BARRIER_THREADS) {
       float acc = 0.f;
@@ -516,11 +524,30 @@ int acn_p2p_close(void* ptr) {
   return ACN_OK;
 }
 
+static int launch_barrier(void* const* sync_bases_host, int world, int rank, const int32_t* counts, int n_counts, const float* payload, int n_payload,
+                          float* reduced, float scale, float timeout_s, int phase, void* stream);
+
 int acn_p2p_barrier(void* const* sync_bases_host, int world, int rank, const int32_t* counts, int n_counts, const float* payload, int n_payload,
                     float* reduced, float scale, float timeout_s, void* stream) {
+  ACN_REQUIRE(n_payload == 0 || (payload && reduced), "acn_p2p_barrier: bad payload");
+  return launch_barrier(sync_bases_host, world, rank, counts, n_counts, payload, n_payload, reduced, scale, timeout_s, 0, stream);
+}
+
+int acn_p2p_arrive(void* const* sync_bases_host, int world, int rank, const float* payload, int n_payload, void* stream) {
+  ACN_REQUIRE(n_payload == 0 || payload, "acn_p2p_arrive: bad payload");
+  return launch_barrier(sync_bases_host, world, rank, nullptr, 0, payload, n_payload, nullptr, 1.f, 0.f, 1, stream);
+}
+
+int acn_p2p_wait(void* const* sync_bases_host, int world, int rank, int n_payload, float* reduced, float scale, float timeout_s, void* stream) {
+  ACN_REQUIRE(n_payload == 0 || reduced, "acn_p2p_wait: bad payload");
+  return launch_barrier(sync_bases_host, world, rank, nullptr, 0, nullptr, n_payload, reduced, scale, timeout_s, 2, stream);
+}
+
+static int launch_barrier(void* const* sync_bases_host, int world, int rank, const int32_t* counts, int n_counts, const float* payload, int n_payload,
+                          float* reduced, float scale, float timeout_s, int phase, void* stream) {
   ACN_REQUIRE(sync_bases_host && world >= 1 && world <= ACN_MAX_PEERS && rank >= 0 && rank < world, "acn_p2p_barrier: bad world / rank");
   ACN_REQUIRE(n_counts >= 0 && n_counts <= ACN_MAX_EXPERTS + 1 && (n_counts == 0 || counts), "acn_p2p_barrier: bad counts");
-  ACN_REQUIRE(n_payload >= 0 && n_payload <= ACN_P2P_PAYLOAD_FLOATS && (n_payload == 0 || (payload && reduced)), "acn_p2p_barrier: bad payload");
+  ACN_REQUIRE(n_payload >= 0 && n_payload <= ACN_P2P_PAYLOAD_FLOATS, "acn_p2p_barrier: bad payload size");
   PeerSync ps;
   for (int r = 0; r < ACN_MAX_PEERS; ++r) {
     ps.base[r] = r < world ? static_cast<int32_t*>(sync_bases_host[r]) : nullptr;
@@ -528,7 +555,7 @@ int acn_p2p_barrier(void* const* sync_bases_host, int world, int rank, const int
   }
   if (!(timeout_s > 0.f)) timeout_s = 120.f;
   k_p2p_barrier<<<1, BARRIER_THREADS, 0, as_stream(stream)>>>(ps, world, rank, n_counts ? counts : nullptr, n_counts, n_payload ? payload : nullptr,
-                                                             n_payload, reduced, scale, (unsigned long long)((double)timeout_s * 1e9));
+                                                             n_payload, reduced, scale, (unsigned long long)((double)timeout_s * 1e9), phase);
   ACN_LAUNCH_CHECK();
   return ACN_OK;
 }

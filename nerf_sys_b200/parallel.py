@@ -467,6 +467,25 @@ class PeerExchange:
                                                   C.c_void_p(torch.cuda.current_stream().cuda_stream)), "acn_p2p_barrier")
         ops._count(1)
 
+    def arrive(self, payload: Optional[Tensor] = None) -> None:
+        """First half of a barrier: publish ``payload`` (fp32, <= 1024 entries) and raise this rank's flag, without waiting."""
+        C = self._C
+        npay = 0 if payload is None else int(payload.numel())
+        from . import ops
+        with torch.cuda.device(self.device), ops._timed("p2p_arrive"):
+            self._check(self._lib.acn_p2p_arrive(self._bases, self.world, self.rank, None if not npay else C.c_void_p(payload.data_ptr()), npay,
+                                                 C.c_void_p(torch.cuda.current_stream().cuda_stream)), "acn_p2p_arrive")
+        ops._count(1)
+
+    def wait(self, n_payload: int = 0, reduced: Optional[Tensor] = None, scale: float = 1.0) -> None:
+        """Second half: wait for every rank's `arrive`, then sum the payload slots (rank order, times ``scale``) into ``reduced``."""
+        C = self._C
+        from . import ops
+        with torch.cuda.device(self.device), ops._timed("p2p_wait"):
+            self._check(self._lib.acn_p2p_wait(self._bases, self.world, self.rank, int(n_payload), None if reduced is None else C.c_void_p(reduced.data_ptr()),
+                                               float(scale), self.timeout_s, C.c_void_p(torch.cuda.current_stream().cuda_stream)), "acn_p2p_wait")
+        ops._count(1)
+
     def allreduce_small(self, x: Tensor, scale: float = 1.0) -> Tensor:
         """Sum of a small fp32 tensor (<= 1024 elements) over the ranks, identical bits on every rank."""
         flat = x.reshape(-1).contiguous()
@@ -527,14 +546,30 @@ class SlabGradReducer:
     ``wait()`` goes between backward() and optimizer.step(): it copies the reduced values into the .grad tensors, or - if
     the backward did not pass that barrier with every gradient ready - performs the reduction on a barrier of its own."""
 
-    def __init__(self, ex: PeerExchange, params: Sequence[Tensor], scale: float = 1.0):
+    def __init__(self, ex: PeerExchange, params: Sequence[Tensor], scale: float = 1.0, early: bool = False):
+        """``early``: post the gradients from inside the backward pass, as soon as the last of them exists (`PeerExchange.arrive`
+        from a post-accumulate hook), and only wait for the peers in ``wait()`` - the expert backward between the two absorbs the
+        skew between the ranks.  For steps with NO other barrier between the background head's backward and the optimiser (one
+        expert per rank, config 2); the expert-parallel container step carries the payload on its own backward barrier instead."""
         self.ex, self.scale = ex, float(scale)
         self.params = [p for p in params if p.requires_grad]
         n = sum(p.numel() for p in self.params)
         self.flat = torch.zeros(max(n, 1), device=ex.device)
         self.reduced = torch.zeros(max(n, 1), device=ex.device)
         self._done = False
-        ex.reducer = self
+        self._posted = False
+        self._ready = 0
+        self._hooks = []
+        if early and ex.world > 1:
+            self._hooks = [p.register_post_accumulate_grad_hook(self._on_grad) for p in self.params]
+        else:
+            ex.reducer = self
+
+    def _on_grad(self, _p) -> None:
+        self._ready += 1
+        if self._ready == len(self.params):
+            self.ex.arrive(self.pack())
+            self._posted = True
 
     def ready(self) -> bool:
         return bool(self.params) and all(p.grad is not None for p in self.params)
@@ -550,19 +585,33 @@ class SlabGradReducer:
         if not self.params or self.ex.world == 1:
             self._done = False
             return
+        if self._hooks:
+            if not self._posted:  # some parameter got no gradient this step: post what there is now
+                for p in self.params:
+                    if p.grad is None:
+                        p.grad = torch.zeros_like(p)
+                self.ex.arrive(self.pack())
+            self.ex.wait(self.flat.numel(), self.reduced, self.scale)
+            self._posted, self._ready = False, 0
+            self._done = True
         if not self._done:
             if not self.ready():
                 for p in self.params:  # a parameter without a gradient this step contributes zeros
                     if p.grad is None:
                         p.grad = torch.zeros_like(p)
             self.ex.barrier(payload=self.pack(), reduced=self.reduced, scale=self.scale)
+        # the reduced values become the gradients in place: .grad is re-pointed at slices of the (static) reduction buffer - no copy
+        # kernels, and under CUDA-graph capture the optimiser's launch records these very addresses
         o = 0
         for p in self.params:
-            p.grad.copy_(self.reduced[o:o + p.numel()].view_as(p))
+            p.grad = self.reduced[o:o + p.numel()].view_as(p)
             o += p.numel()
         self._done = False
 
     def remove(self) -> None:
+        for h in self._hooks:
+            h.remove()
+        self._hooks = []
         if self.ex.reducer is self:
             self.ex.reducer = None
 

@@ -19,4 +19,4 @@ def test_two_rank_nccl_a2a_and_sharded_render():
            "--master-port", "29533", os.path.join(ROOT, "tools", "mgpu_check.py")]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
-    assert r.stdout.count("-> ok") == 6, r.stdout
+    assert r.stdout.count("-> ok") == 7, r.stdout

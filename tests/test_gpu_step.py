@@ -389,3 +389,41 @@ def test_second_order_requests_fail_loudly():
     assert g.shape == w.shape and not g.requires_grad
     with pytest.raises(RuntimeError):
         ops.sgd_axpy(w, (g * w).sum() * w, 0.015)  # a gradient that still carries a graph
+
+
+def test_split_barrier_arrive_then_wait_reduces_and_replays_in_a_graph():
+    """acn_p2p_arrive / acn_p2p_wait (world 1: every slab local): one epoch per pair, the payload reduced at the wait, work
+    enqueued between the two halves, replayable from a CUDA graph; SlabGradReducer(early=True) leaves the gradients scaled."""
+    from nerf_sys_b200 import parallel as PL
+    ex = PL.PeerExchange(rows_cap=256)
+    try:
+        e0 = int(ex.sync[17].item())
+        x = torch.arange(643, device=DEV, dtype=torch.float32)
+        out = torch.zeros_like(x)
+        ex.arrive(x)
+        busy = torch.randn(1 << 20, device=DEV).sin().sum()  # work between the two halves
+        ex.wait(643, out, 0.25)
+        close(out, x.cpu() * 0.25, 0, "split barrier payload")
+        assert int(ex.sync[17].item()) == e0 + 1 and torch.isfinite(busy)
+        ex.barrier()  # a full barrier afterwards keeps counting
+        assert int(ex.sync[17].item()) == e0 + 2
+        s = torch.cuda.Stream()
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):
+            ex.arrive(x)
+            ex.wait(643, out, 1.0)
+        torch.cuda.current_stream().wait_stream(s)
+        torch.cuda.synchronize()
+        gr = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(gr):
+            ex.arrive(x)
+            y = x * 2
+            ex.wait(643, out, 2.0)
+        e1 = int(ex.sync[17].item())
+        for _ in range(3):
+            gr.replay()
+        torch.cuda.synchronize()
+        assert int(ex.sync[17].item()) == e1 + 3
+        close(out, x.cpu() * 2.0, 0, "graph-replayed split barrier")
+    finally:
+        ex.close()

@@ -114,6 +114,31 @@ if rank == 0:
           flush=True)
 ep_m.set_expert_parallel(False)
 
+# early-posting shared-gradient reducer (config 2 at N ranks): hooks post inside backward(), wait() reduces; vs dist.all_reduce
+qs = [torch.nn.Parameter(torch.randn(32, 16, device=dev)), torch.nn.Parameter(torch.randn(3, device=dev))]
+red = PL.SlabGradReducer(ex, qs, scale=1.0 / world, early=True)
+worst = 0.0
+for it in range(3):
+    for q in qs:
+        q.grad = None
+    ((qs[0] ** 2).sum() * (rank + 1 + it) + (qs[1] * torch.arange(3.0, device=dev)).sum() * (rank + 2)).backward()
+    loc = torch.cat([q.grad.reshape(-1) for q in qs])
+    allg = [torch.zeros_like(loc) for _ in range(world)]
+    dist.all_gather(allg, loc)
+    terms = torch.stack(allg).double()
+    exact, mag = terms.sum(0) / world, terms.abs().sum(0) / world  # the ranks' terms have mixed signs: errors scale with sum |term|
+    red.wait()
+    mine = torch.cat([q.grad.reshape(-1) for q in qs]).double()
+    worst = max(worst, ((mine - exact).abs() / mag.clamp_min(1e-30)).max().item())
+red.remove()
+flag = torch.tensor([worst], device=dev)
+dist.all_reduce(flag, op=dist.ReduceOp.MAX)
+good = flag.item() <= 1e-6  # fp32 sum of `world` terms in rank order against the fp64 sum, relative to sum |term|
+ok = ok and good
+if rank == 0:
+    print(f"early-posting slab reducer (arrive in backward, wait before the optimiser), world {world}: max error vs the fp64 sum, relative to sum |term| "
+          f"{flag.item():.1e} -> {'ok' if good else 'MISMATCH'}", flush=True)
+
 # ray-sharded render
 ops.set_mlp_math("f16tc")
 m, st, cfg, mins, aabb = _big_scene(8, 2, 4, 14)
