@@ -131,8 +131,12 @@ __global__ void __launch_bounds__(RT) k_routing(PointSrc src, int64_t P, RouteCf
 // sample (squared distances, candidate count), then the warp works through its "exact" samples together: 32/KT samples per
 // pass, ONE (sample, centroid) pair per lane - one sqrt, one reciprocal, one division per lane - with the weight sum
 // accumulated in ascending centroid order by a shuffle chain, i.e. the same operations in the same order as route_point().
+constexpr uint32_t UNIT_W = 0x80000000u;  // decision word: membership mask | UNIT_W when every member weight is exactly 1
+
+// Returns the decision word of this lane's sample p; the weights of a sample with a member weight != 1 are written to
+// pw[p*KT + k] by the lanes that computed them (one 4*KT-byte row per sample).
 template <int KT, bool D3>
-__device__ __forceinline__ uint32_t route_warp(const RouteCfg& cfg, bool valid, float x, float y, float z, float* w) {
+__device__ __forceinline__ uint32_t route_warp(const RouteCfg& cfg, bool valid, int p, float x, float y, float z, float* __restrict__ pw) {
   constexpr uint32_t FULL = 0xffffffffu;
   constexpr int PPP = 32 / KT;  // samples per pass
   const int lane = threadIdx.x & 31, g = lane / KT, k = lane % KT;
@@ -162,9 +166,7 @@ __device__ __forceinline__ uint32_t route_warp(const RouteCfg& cfg, bool valid, 
     c = in ? kk : c;
   }
   const bool fast = ncand == 1 && smin > 1e-11f && smin < 1e11f;  // see route_point()
-  uint32_t mask = (valid && fast) ? (1u << c) : 0u;
-#pragma unroll
-  for (int kk = 0; kk < KT; ++kk) w[kk] = (fast && kk == c) ? 1.0f : 0.0f;
+  uint32_t word = (valid && fast) ? ((1u << c) | UNIT_W) : UNIT_W;
   uint32_t slow = __ballot_sync(FULL, valid && !fast);
   while (slow) {  // warp-uniform
     // this pass takes the first PPP exact samples; group g of KT lanes works for the g-th of them
@@ -186,6 +188,7 @@ __device__ __forceinline__ uint32_t route_warp(const RouteCfg& cfg, bool valid, 
       const float t = __shfl_sync(FULL, sq[kk], from);
       v = (kk == k) ? t : v;
     }
+    const int p_from = __shfl_sync(FULL, p, from);
     float d = sqrtf(v);
     if (soft) d = (d < 1e-6f) ? 1e-6f : d;  // NaN stays NaN (torch.clamp_min): a non-finite sample is a member of no expert
     if (!active) d = INFINITY;
@@ -214,36 +217,52 @@ __device__ __forceinline__ uint32_t route_warp(const RouteCfg& cfg, bool valid, 
       member = active && wv > 0.f;  // membership is "weight > 0" (meta_container.py:308)
     }
     const uint32_t bal = __ballot_sync(FULL, member);
-    // hand the results to the lanes that own the samples of this pass
+    const uint32_t odd = __ballot_sync(FULL, member && wv != 1.0f);
+    if (active && ((odd >> gshift) & gmask)) pw[(int64_t)p_from * KT + k] = wv;
+    // hand the decision to the lane that owns the sample
     const bool mine = (taken >> lane) & 1u;
-    const int my_g = __popc(taken & ((1u << lane) - 1u));
-    if (mine) mask = (bal >> (my_g * KT)) & gmask;
-#pragma unroll
-    for (int kk = 0; kk < KT; ++kk) {
-      const float t = __shfl_sync(FULL, wv, (mine ? my_g * KT : 0) + kk);
-      if (mine) w[kk] = t;
-    }
+    const int my_shift = __popc(taken & ((1u << lane) - 1u)) * KT;
+    if (mine) word = ((bal >> my_shift) & gmask) | (((odd >> my_shift) & gmask) ? 0u : UNIT_W);
   }
-  return mask;
+  return word;
 }
 
-// ---- pass 1: per-block, per-expert member counts: counts[k*nb + b] ------------
+// member counts of up to 4 experts as one byte each: bit i of a nibble -> bit 8*i
+__device__ __forceinline__ uint32_t spread4(uint32_t nib) { return (nib * 0x00204081u) & 0x01010101u; }
+
+// ---- pass 1: per-block, per-expert member counts: counts[k*nb + b].  The decisions are kept for pass 3: pmask[p] = decision
+// word, pw[p*KT ..] = the weights of the samples whose word lacks UNIT_W (1 in 20).
 template <int KT, bool D3>
-__global__ void __launch_bounds__(RT) k_route_count(PointSrc src, int64_t P, RouteCfg cfg, int nb, int32_t* __restrict__ counts) {
+__global__ void __launch_bounds__(RT) k_route_count(PointSrc src, int64_t P, RouteCfg cfg, int nb, int32_t* __restrict__ counts,
+                                                    uint32_t* __restrict__ pmask, float* __restrict__ pw) {
+  constexpr int NW = (KT + 3) / 4;
   __shared__ int cnt[ACN_MAX_EXPERTS];
+  const uint32_t keep = ((1u << cfg.K) - 1u) | UNIT_W;  // never a padding expert
   for (int b = blockIdx.x; b < nb; b += gridDim.x) {
     if (threadIdx.x < ACN_MAX_EXPERTS) cnt[threadIdx.x] = 0;
     __syncthreads();
+    uint32_t acc[NW];  // this thread's member count per expert, one byte each (<= RPT)
+#pragma unroll
+    for (int i = 0; i < NW; ++i) acc[i] = 0u;
 #pragma unroll
     for (int j = 0; j < RPT; ++j) {
       const int64_t p = (int64_t)b * RB + j * RT + threadIdx.x;
-      float x = 0.f, y = 0.f, z = 0.f, w[KT];
+      float x = 0.f, y = 0.f, z = 0.f;
       if (p < P) load_xyz(src, p, x, y, z);
-      const uint32_t mask = route_warp<KT, D3>(cfg, p < P, x, y, z, w) & ((1u << cfg.K) - 1u);  // never a padding expert
+      const uint32_t word = route_warp<KT, D3>(cfg, p < P, (int)p, x, y, z, pw) & keep;
+      if (p < P) pmask[p] = word;
 #pragma unroll
-      for (int k = 0; k < KT; ++k) {
-        unsigned bal = __ballot_sync(0xffffffffu, (mask >> k) & 1u);
-        if ((threadIdx.x & 31) == 0 && bal) atomicAdd(&cnt[k], __popc(bal));
+      for (int i = 0; i < NW; ++i) acc[i] += spread4((word >> (4 * i)) & 0xFu);
+    }
+#pragma unroll
+    for (int i = 0; i < NW; ++i) {
+      const uint32_t s = __reduce_add_sync(0xffffffffu, acc[i]);  // bytes stay <= 32*RPT = 128: no carry between experts
+      if ((threadIdx.x & 31) == 0) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const int c = (s >> (8 * q)) & 0xFF;
+          if (c) atomicAdd(&cnt[4 * i + q], c);
+        }
       }
     }
     __syncthreads();
@@ -301,50 +320,56 @@ __global__ void k_route_seg(const int32_t* __restrict__ totals, int K, int32_t* 
   }
 }
 
-// ---- pass 3: stable write of (point, weight) pairs into each expert's segment ----
-template <int KT, bool D3>
-__global__ void __launch_bounds__(RT) k_route_write(PointSrc src, int64_t P, RouteCfg cfg, int nb, const int32_t* __restrict__ base,
-                                                    const int32_t* __restrict__ seg, int32_t* __restrict__ pair_point,
-                                                    float* __restrict__ pair_w, int64_t Mcap) {
-  __shared__ int run[ACN_MAX_EXPERTS];
-  __shared__ int wcnt[ACN_MAX_EXPERTS][RT / 32];
-  int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+// ---- pass 3: stable write of (point, weight) pairs into each expert's segment, from the decisions pass 1 kept (no distance
+// arithmetic, no point fetch): per-warp member counts of the block's 4 x 8 warp rows -> one serial scan per expert -> offsets
+template <int KT>
+__global__ void __launch_bounds__(RT) k_route_write(int64_t P, int K, int nb, const int32_t* __restrict__ base, const int32_t* __restrict__ seg,
+                                                    const uint32_t* __restrict__ pmask, const float* __restrict__ pw,
+                                                    int32_t* __restrict__ pair_point, float* __restrict__ pair_w, int64_t Mcap) {
+  constexpr int ROWS = RPT * (RT / 32);  // warp rows of a block, in point order
+  __shared__ int wcnt[KT][ROWS + 1];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   for (int b = blockIdx.x; b < nb; b += gridDim.x) {
-    if (threadIdx.x < cfg.K) run[threadIdx.x] = seg[threadIdx.x] + base[(int64_t)threadIdx.x * nb + b];
-    __syncthreads();
-#pragma unroll 1
+    uint32_t m[RPT];
+#pragma unroll
     for (int j = 0; j < RPT; ++j) {
       const int64_t p = (int64_t)b * RB + j * RT + threadIdx.x;
-      float x = 0.f, y = 0.f, z = 0.f, w[KT];
-      if (p < P) load_xyz(src, p, x, y, z);
-      const uint32_t mask = route_warp<KT, D3>(cfg, p < P, x, y, z, w) & ((1u << cfg.K) - 1u);  // never a padding expert
-      unsigned bals[KT];
+      m[j] = (p < P) ? pmask[p] : 0u;
+    }
+#pragma unroll
+    for (int j = 0; j < RPT; ++j)
 #pragma unroll
       for (int k = 0; k < KT; ++k) {
-        bals[k] = __ballot_sync(0xffffffffu, (mask >> k) & 1u);
-        if (lane == 0) wcnt[k][warp] = __popc(bals[k]);
+        const unsigned bal = __ballot_sync(0xffffffffu, (m[j] >> k) & 1u);
+        if (lane == 0) wcnt[k][j * (RT / 32) + warp] = __popc(bal);
       }
-      __syncthreads();
+    __syncthreads();
+    if (threadIdx.x < K) {
+      int run = seg[threadIdx.x] + base[(int64_t)threadIdx.x * nb + b];
+      for (int i = 0; i < ROWS; ++i) {
+        const int c = wcnt[threadIdx.x][i];
+        wcnt[threadIdx.x][i] = run;
+        run += c;
+      }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < RPT; ++j) {
+      const int64_t p = (int64_t)b * RB + j * RT + threadIdx.x;
+      const bool unit = (m[j] & UNIT_W) != 0u;
 #pragma unroll
       for (int k = 0; k < KT; ++k) {
-        if ((mask >> k) & 1u) {
-          int off = run[k];
-          for (int ww = 0; ww < warp; ++ww) off += wcnt[k][ww];
-          off += __popc(bals[k] & ((1u << lane) - 1u));
+        const unsigned bal = __ballot_sync(0xffffffffu, (m[j] >> k) & 1u);
+        if ((m[j] >> k) & 1u) {
+          const int off = wcnt[k][j * (RT / 32) + warp] + __popc(bal & ((1u << lane) - 1u));
           if (off < Mcap) {
             pair_point[off] = (int32_t)p;
-            pair_w[off] = w[k];
+            pair_w[off] = unit ? 1.0f : pw[p * KT + k];
           }
         }
       }
-      __syncthreads();
-      if (threadIdx.x < cfg.K) {
-        int s = 0;
-        for (int ww = 0; ww < RT / 32; ++ww) s += wcnt[threadIdx.x][ww];
-        run[threadIdx.x] += s;
-      }
-      __syncthreads();
     }
+    __syncthreads();
   }
 }
 
@@ -400,9 +425,13 @@ int64_t acn_route_pack_capacity(int64_t P, int K) {
   return P + P / 4 + (int64_t)K * ACN_TILE;
 }
 
+static inline int route_kt(int K) { return K <= 2 ? 2 : (K <= 4 ? 4 : (K <= 8 ? 8 : 16)); }
+static inline int64_t align256(int64_t v) { return (v + 255) / 256 * 256; }
+
+// workspace: per-block counts (nb*K + 64 ints) | per-point decision word (P) | per-point weights of the non-unit samples (P*KT)
 int64_t acn_route_pack_ws_bytes(int64_t P, int K) {
   int64_t nb = (P + RB - 1) / RB;
-  return sizeof(int32_t) * (nb * K + 64);
+  return align256(sizeof(int32_t) * (nb * K + 64)) + align256(sizeof(uint32_t) * P) + sizeof(float) * P * route_kt(K) + 256;
 }
 
 int acn_route_pack(const AcnPoints* pts, const float* centroids_host, int K, float margin, int cluster_2d, int32_t* pair_point,
@@ -415,11 +444,14 @@ int acn_route_pack(const AcnPoints* pts, const float* centroids_host, int K, flo
   int nb = (int)((P + RB - 1) / RB);
   RouteCfg cfg;
   fill_cfg(cfg, centroids_host, K, margin, cluster_2d);
+  ACN_REQUIRE((reinterpret_cast<uintptr_t>(ws) & 15) == 0, "acn_route_pack: ws must be 16-byte aligned");
   int32_t* counts = reinterpret_cast<int32_t*>(ws);
+  uint32_t* pmask = reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(ws) + align256(sizeof(int32_t) * ((int64_t)nb * K + 64)));
+  float* pw = reinterpret_cast<float*>(reinterpret_cast<char*>(pmask) + align256(sizeof(uint32_t) * P));
   ACN_CUDA(cudaMemsetAsync(pair_point, 0xFF, sizeof(int32_t) * Mcap, st));
   ACN_CUDA(cudaMemsetAsync(pair_weight, 0, sizeof(float) * Mcap, st));
   if (nb > 0) {
-    ROUTE_DISPATCH(K, cluster_2d, k_route_count, persistent_grid(nb, 8), st, make_src(pts), P, cfg, nb, counts);
+    ROUTE_DISPATCH(K, cluster_2d, k_route_count, persistent_grid(nb, 8), st, make_src(pts), P, cfg, nb, counts, pmask, pw);
     ACN_LAUNCH_CHECK();
   }
   int32_t* totals = counts + (int64_t)nb * K;  // the 64 spare ints of the workspace
@@ -428,7 +460,13 @@ int acn_route_pack(const AcnPoints* pts, const float* centroids_host, int K, flo
   k_route_seg<<<1, 32, 0, st>>>(totals, K, seg);
   ACN_LAUNCH_CHECK();
   if (nb > 0) {
-    ROUTE_DISPATCH(K, cluster_2d, k_route_write, persistent_grid(nb, 8), st, make_src(pts), P, cfg, nb, counts, seg, pair_point, pair_weight, Mcap);
+    const int grid = persistent_grid(nb, 8);
+    switch (route_kt(K)) {
+      case 2: k_route_write<2><<<grid, RT, 0, st>>>(P, K, nb, counts, seg, pmask, pw, pair_point, pair_weight, Mcap); break;
+      case 4: k_route_write<4><<<grid, RT, 0, st>>>(P, K, nb, counts, seg, pmask, pw, pair_point, pair_weight, Mcap); break;
+      case 8: k_route_write<8><<<grid, RT, 0, st>>>(P, K, nb, counts, seg, pmask, pw, pair_point, pair_weight, Mcap); break;
+      default: k_route_write<16><<<grid, RT, 0, st>>>(P, K, nb, counts, seg, pmask, pw, pair_point, pair_weight, Mcap); break;
+    }
     ACN_LAUNCH_CHECK();
   }
   return ACN_OK;
