@@ -161,7 +161,10 @@ int acn_routing(const AcnPoints* pts, const float* centroids_host, int K, float 
  * meta_container.py:305-337).  Outputs the pair arrays (capacity Mcap slots; a
  * speculative size comes from acn_route_pack_capacity) and seg (K+1).  Nothing is
  * written past Mcap; seg[K] always reports the slots NEEDED, so a caller that reads
- * seg[K] > Mcap re-runs with larger arrays.  ws: acn_route_pack_ws_bytes(P,K). */
+ * seg[K] > Mcap re-runs with larger arrays.  ws: acn_route_pack_ws_bytes(P,K) bytes of
+ * device memory, 16-byte aligned (per-block counts, one decision word per point and a
+ * weight row per point for the samples with more than one member: 4 + 4*KT bytes per
+ * point, KT = K rounded up to 2/4/8/16). */
 int64_t acn_route_pack_capacity(int64_t P, int K);
 int64_t acn_route_pack_ws_bytes(int64_t P, int K);
 int acn_route_pack(const AcnPoints* pts, const float* centroids_host, int K, float margin, int cluster_2d,
