@@ -1,8 +1,11 @@
 """CPU oracle of the occupancy-guided renderer's per-ray work (TEST INFRASTRUCTURE: imported by tests/ only).
 
-**Parity: UNPINNED.**  The reference delegates this arithmetic to nerfacc 0.5.3 (requirements.txt:8; call sites
-models/inr/meta_ngp.py:430-442, nerfs/ray_rendering.py:477-487, 543-554), which is neither vendored under /root/reference nor
-installed here, so there is nothing to run it against.  What is restated below:
+**Parity: nerfacc's arithmetic UNPINNED, the reference's own assembly PINNED.**  The reference delegates the traversal, the
+visibility filter and the packed integration to nerfacc 0.5.3 (requirements.txt:8; call sites models/inr/meta_ngp.py:430-442,
+nerfs/ray_rendering.py:477-487, 543-554), which is neither vendored under /root/reference nor installed here, so there is
+nothing to run those against.  The code AROUND those calls is the reference's own (prefilter, union of the experts' segments,
+midpoints, routing, blend, background): the functions at the end of this file restate it and are checked against vectors made
+by the unmodified reference (tests/golden/make_golden_occ.py -> occ_assembly.npz, tests/test_oracle_golden.py).  Restated here:
 
 * ``march`` - ``OccGridEstimator.sampling`` up to its visibility filter, i.e. nerfacc's ``traverse_grids``: nested level boxes
   (level l = the region of interest scaled by 2^l), the finest box containing the current position is traversed cell by cell,
@@ -18,7 +21,8 @@ nerf_sys_b200/csrc/occ.cu (compiled -fmad=false): cell ids, sample counts and ra
 """
 from __future__ import annotations
 
-from typing import List, Sequence, Tuple
+import math
+from typing import Callable, List, Sequence, Tuple
 
 import numpy as np
 import torch
@@ -197,3 +201,96 @@ def packed_render(ray_idx: torch.Tensor, t0: torch.Tensor, t1: torch.Tensor, sig
     depth = torch.zeros(n_rays).index_add(0, ray_idx, w * t_mid)
     acc = torch.zeros(n_rays).index_add(0, ray_idx, w)
     return rgb_map, depth, w, acc
+
+
+# --------------------------------------------------------------------------------------------------------------------------
+# The reference's OWN part of the occupancy renderer (nerfs/ray_rendering.py), pinned: tests/golden/occ_assembly.npz holds
+# the outputs of the unmodified _intersect_rays_aabb / _merge_segments_union / render_rays_occ / render_expert_occ, run with
+# nerfacc's three packed primitives supplied by the functions below (tests/golden/make_golden_occ.py).  What stays unpinned
+# is nerfacc's arithmetic itself (march / visibility / the primitives).
+# --------------------------------------------------------------------------------------------------------------------------
+def pack_info(ray_idx: torch.Tensor, n_rays: int) -> torch.Tensor:
+    """nerfacc.pack_info: (n_rays, 2) [start, count] of each ray's run in a ray-sorted sample list."""
+    counts = torch.bincount(ray_idx, minlength=n_rays)
+    starts = torch.cumsum(counts, 0) - counts
+    return torch.stack([starts, counts], 1)
+
+
+def weights_from_density(t0: torch.Tensor, t1: torch.Tensor, sigma: torch.Tensor, ray_idx: torch.Tensor):
+    """nerfacc.render_weight_from_density -> (weights, transmittance, alphas)."""
+    alpha = 1.0 - torch.exp(-sigma * (t1 - t0))
+    T = torch.ones_like(alpha)
+    for r in torch.unique(ray_idx).tolist():
+        idx = (ray_idx == r).nonzero().squeeze(1)
+        T = T.index_copy(0, idx, torch.cumprod(torch.cat([torch.ones(1), 1.0 - alpha[idx]]), 0)[:-1])
+    return alpha * T, T, alpha
+
+
+def accumulate(w: torch.Tensor, values, ray_idx: torch.Tensor, n_rays: int) -> torch.Tensor:
+    """nerfacc.accumulate_along_rays: (n_rays, D) segmented sums of w * values (values None: of w, D = 1)."""
+    src = w[:, None] if values is None else w[:, None] * values
+    return torch.zeros(n_rays, src.shape[1], dtype=src.dtype).index_add(0, ray_idx, src)
+
+
+def toy_field(xd: torch.Tensor, k: int) -> torch.Tensor:
+    """A closed-form expert for the assembly goldens: (m,6) [x, d] -> (m,4) [rgb, sigma]."""
+    x, d = xd[:, :3], xd[:, 3:6]
+    c = 0.3 * torch.tensor([math.sin(k + 1.0), math.cos(2.0 * k + 1.0), math.sin(3.0 * k + 2.0)])
+    sigma = 6.0 * torch.exp(-4.0 * ((x - c) ** 2).sum(-1)) + 0.05 * (k + 1)
+    rgb = 0.5 + 0.5 * torch.sin(3.0 * x + (k + 1.0) * d)
+    return torch.cat([rgb, sigma[:, None]], 1)
+
+
+def toy_background(d: torch.Tensor) -> torch.Tensor:
+    return 0.5 + 0.5 * d
+
+
+def intersect_rays_aabb(rays: torch.Tensor, lo: torch.Tensor, hi: torch.Tensor) -> torch.Tensor:
+    """nerfs/ray_rendering.py:172-193: slab test against [near, far]; |d| <= 1e-9 uses 1/1e-9."""
+    o, d = rays[:, :3], rays[:, 3:6]
+    invd = torch.where(d.abs() > 1e-9, 1.0 / d, torch.full_like(d, 1.0 / 1e-9))
+    a, b = (lo[None] - o) * invd, (hi[None] - o) * invd
+    t_in = torch.maximum(torch.minimum(a, b).amax(-1), rays[:, 6])
+    t_out = torch.minimum(torch.maximum(a, b).amin(-1), rays[:, 7])
+    return t_out > t_in
+
+
+def assemble_expert(rays: torch.Tensor, ray_idx: torch.Tensor, t0: torch.Tensor, t1: torch.Tensor, field: Callable, bg_rgb: torch.Tensor):
+    """nerfs/ray_rendering.py:494-559 (render_expert_occ) from the marching result on: midpoints, one expert call, one packed
+    integration, background.  -> rgb (N,3), depth (N,), weights (M,1), acc (N,)"""
+    N = rays.shape[0]
+    if t0.numel() == 0:
+        return bg_rgb, torch.zeros(N), torch.zeros(1, 1), torch.zeros(N)
+    t_mid = 0.5 * (t0 + t1)
+    y = field(torch.cat([rays[ray_idx, :3] + rays[ray_idx, 3:6] * t_mid[:, None], rays[ray_idx, 3:6]], 1))
+    w, _, _ = weights_from_density(t0, t1, y[:, 3], ray_idx)
+    acc = accumulate(w, None, ray_idx, N)[:, 0]
+    rgb = accumulate(w, y[:, :3], ray_idx, N) + (1.0 - acc)[:, None] * bg_rgb
+    return rgb, accumulate(w, t_mid[:, None], ray_idx, N)[:, 0], w[:, None], acc
+
+
+def assemble_container(rays: torch.Tensor, lists: Sequence[Tuple[torch.Tensor, torch.Tensor, torch.Tensor]], route: Callable,
+                       fields: Sequence[Callable], bg_rgb: torch.Tensor):
+    """nerfs/ray_rendering.py:400-491 (render_rays_occ, full container) from the per-expert marching results on: union of the
+    segments per ray, routing weights at the midpoints (route(x) -> (M,K)), experts evaluated where their weight > 1e-8, sigma
+    and sigma-weighted rgb blended BEFORE one packed integration, background.  lists: per expert (global ray ids, t0, t1), the
+    experts without a sample left out.  -> rgb (N,3), depth (N,), weights (M,1), acc (N,), (merged ray ids, t0, t1)"""
+    N, K = rays.shape[0], len(fields)
+    if len(lists) == 0:
+        return bg_rgb, torch.zeros(N), torch.zeros(1, 1), torch.zeros(N), None
+    ri, t0, t1 = union([l[0] for l in lists], [l[1] for l in lists], [l[2] for l in lists])
+    t_mid = 0.5 * (t0 + t1)
+    x, d = rays[ri, :3] + rays[ri, 3:6] * t_mid[:, None], rays[ri, 3:6]
+    W = route(x)
+    SIG, RGB = torch.zeros(len(ri), K), torch.zeros(len(ri), K, 3)
+    for k in range(K):
+        idx = (W[:, k] > 1e-8).nonzero().squeeze(1)
+        if idx.numel():
+            y = fields[k](torch.cat([x[idx], d[idx]], 1))
+            SIG[idx, k], RGB[idx, k] = y[:, 3], y[:, :3]
+    s_num = (W * SIG).sum(1, keepdim=True).clamp_min(1e-12)
+    rgb_mix = (W[..., None] * SIG[..., None] * RGB).sum(1) / s_num
+    w, _, _ = weights_from_density(t0, t1, s_num[:, 0], ri)
+    acc = accumulate(w, None, ri, N)[:, 0]
+    rgb = accumulate(w, rgb_mix, ri, N) + (1.0 - acc)[:, None] * bg_rgb
+    return rgb, accumulate(w, t_mid[:, None], ri, N)[:, 0], w[:, None], acc, (ri, t0, t1)

@@ -1,11 +1,14 @@
 """GPU parity of the occupancy-guided renderer against oracle/occ_oracle.py.  nerfacc 0.5.3 is absent:
-parity is UNPINNED (the oracle restates its documented behaviour); integer outputs (ray ids, DDA cell ids, sample / segment
-counts) and the sample boundaries are bit-exact against that oracle, floating-point sums carry their tolerance."""
+the parity of ITS arithmetic (traversal, visibility, packed weights) is UNPINNED (the oracle restates its documented behaviour);
+the reference's own part - prefilter, segment union, the container / single-expert assembly - is pinned to vectors produced by
+the unmodified reference (tests/golden/occ_assembly.npz).  Integer outputs (ray ids, DDA cell ids, sample / segment counts) and
+the sample boundaries are bit-exact against the oracle, floating-point sums carry their tolerance."""
 import pytest
 import torch
 
 from oracle import acnerf_oracle as O
 from oracle import occ_oracle as OO
+from conftest import T, load_golden
 from test_gpu_parity import close, rel_close
 
 pytestmark = pytest.mark.gpu
@@ -87,6 +90,29 @@ def test_segment_union_and_visibility_vs_oracle():
     assert 0.05 < vis.float().mean().item() < 0.95
 
 
+def test_prefilter_and_union_equal_the_reference_vectors():
+    """The drop-ins of _intersect_rays_aabb / _merge_segments_union (ray_rendering.py:172-256) on the inputs of
+    tests/golden/occ_assembly.npz: the hit masks and the merged (ray, t0, t1) lists of the UNMODIFIED reference, bit for bit;
+    and the traversal kernel reproduces the per-expert lists those vectors were built from."""
+    from nerf_sys_b200 import ops
+    from nerf_sys_b200.nerfs.ray_rendering import _intersect_rays_aabb, _merge_segments_union
+    from nerf_sys_b200.nerfs.scene_box import SceneBox
+    z = load_golden("occ_assembly")
+    rays = T(z["rays"]).to(DEV)
+    lists = []
+    for k in range(4):
+        hit = _intersect_rays_aabb(rays, SceneBox(T(z["boxes"][k]).to(DEV)))
+        assert torch.equal(hit.cpu(), T(z[f"hit{k}"])), k
+        idx = hit.nonzero().squeeze(1)
+        seg = ops.occ_march(rays[idx], None, T(z[f"binaries{k}"]).to(DEV), T(z[f"aabbs{k}"]).reshape(-1).tolist(), float(z["step_cone"][0]), float(z["step_cone"][1]))
+        gl = idx[seg.ray_idx.long()]
+        assert torch.equal(gl.cpu(), T(z[f"list{k}_ri"])) and torch.equal(seg.t0.cpu(), T(z[f"list{k}_t0"])) and torch.equal(seg.t1.cpu(), T(z[f"list{k}_t1"]))
+        if seg.M:
+            lists.append((gl, seg.t0, seg.t1))
+    ri, t0, t1 = _merge_segments_union([l[0] for l in lists], [l[1] for l in lists], [l[2] for l in lists])
+    assert torch.equal(ri.cpu(), T(z["union_ri"])) and torch.equal(t0.cpu(), T(z["union_t0"])) and torch.equal(t1.cpu(), T(z["union_t1"]))
+
+
 def test_packed_render_forward_backward_vs_oracle():
     from nerf_sys_b200 import ops
     binaries, aabbs = _grid(2, 16, 0.4, seed=77)
@@ -165,20 +191,12 @@ def test_occupancy_renderer_end_to_end_vs_oracle_assembly():
             idx = hit.nonzero().squeeze(1)
             r, a, b, _, _ = OO.march(rays[idx], sub.occ_grid.binaries.cpu(), sub.occ_grid.aabbs.cpu(), sub.render_step_size, sub.cone_angle)
             lists.append((idx[r], a, b))
-        ri, t0, t1 = OO.union([l[0] for l in lists], [l[1] for l in lists], [l[2] for l in lists])
-        t_mid = 0.5 * (t0 + t1)
-        x = rays[ri, :3] + rays[ri, 3:6] * t_mid[:, None]
-        W, _ = O.routing(x, st["centroids"], 1.05, True, direct=True)
-        s_num, c_num = torch.zeros(len(ri)), torch.zeros(len(ri), 3)
+        # oracle/occ_oracle.assemble_container is pinned to the unmodified render_rays_occ (tests/test_oracle_golden.py)
+        fields = [lambda xd, k=k: O.ngp_forward(xd, O.subdict(st, f"submodules.{k}"), boxes[k][0], cfg) for k in range(2)]
         with torch.no_grad():
-            for k in range(2):
-                idx = (W[:, k] > 1e-8).nonzero().squeeze(1)
-                y = O.ngp_forward(torch.cat([x[idx], rays[ri[idx], 3:6]], 1), O.subdict(st, f"submodules.{k}"), boxes[k][0], cfg)
-                s_num = s_num.index_add(0, idx, W[idx, k] * y[:, 3])
-                c_num = c_num.index_add(0, idx, (W[idx, k] * y[:, 3])[:, None] * y[:, :3])
-            sig = s_num.clamp_min(1e-12)
-            rgb_o, depth_o, w_o, acc_o = OO.packed_render(ri, t0, t1, sig, c_num / sig[:, None], N)
-            rgb_o = rgb_o + (1 - acc_o)[:, None] * O.background_color(rays[:, 3:6], st)
+            rgb_o, depth_o, w_o, acc_o, (ri, t0, t1) = OO.assemble_container(
+                rays, lists, lambda x: O.routing(x, st["centroids"], 1.05, True, direct=True)[0], fields, O.background_color(rays[:, 3:6], st))
+        w_o = w_o[:, 0]
         assert w.shape == (len(ri), 1)
         close(rgb, rgb_o, 5e-6, "rgb")
         close(depth, depth_o, 5e-6, "depth")

@@ -203,3 +203,61 @@ def test_voronoi_oracle_equals_the_reference(tag):
     c2d, margin, S = z[f"{tag}_cfg"]
     m = VO.voronoi_orig(T(z["rays"]), int(S), T(z["centroids"]), bool(c2d), float(margin))
     assert torch.equal(m, T(z[f"{tag}_mask"]))
+
+
+# ----------------------------------------------------------------------------- a21 occupancy renderer: the reference's own assembly
+def _occ_lists(z, K=4):
+    return [(T(z[f"list{k}_ri"]), T(z[f"list{k}_t0"]), T(z[f"list{k}_t1"])) for k in range(K) if z[f"list{k}_ri"].size]
+
+
+def test_occ_prefilter_and_union_oracle_equal_the_reference():
+    """oracle intersect_rays_aabb / union against the unmodified _intersect_rays_aabb / _merge_segments_union
+    (tests/golden/make_golden_occ.py): hit masks equal, merged (ray, t0, t1) lists bit-equal."""
+    from oracle import occ_oracle as OO
+    z = load_golden("occ_assembly")
+    rays, boxes = T(z["rays"]), T(z["boxes"])
+    for k in range(4):
+        hit = OO.intersect_rays_aabb(rays, boxes[k, 0], boxes[k, 1])
+        assert torch.equal(hit, T(z[f"hit{k}"])), k
+        assert not hit[:6].any()  # empty [near, far]
+    lists = _occ_lists(z)
+    assert len(lists) == 3  # expert 3 proposes nothing
+    ri, t0, t1 = OO.union([l[0] for l in lists], [l[1] for l in lists], [l[2] for l in lists])
+    assert torch.equal(ri, T(z["union_ri"])) and torch.equal(t0, T(z["union_t0"])) and torch.equal(t1, T(z["union_t1"]))
+
+
+@pytest.mark.parametrize("tag", ["soft2d", "hard3d"])
+def test_occ_container_assembly_oracle_equals_the_reference(tag):
+    """oracle assemble_container against the unmodified render_rays_occ (full container: union, routing at the midpoints
+    by the real MetaContainer._routing, evaluation where the weight is positive, sigma / rgb blend before ONE integration,
+    background) on the same per-expert marching lists and closed-form experts."""
+    from oracle import occ_oracle as OO
+    z = load_golden("occ_assembly")
+    rays, cent = T(z["rays"]), T(z["centroids"])
+    margin, c2d = float(z[f"{tag}_cfg"][0]), bool(z[f"{tag}_cfg"][1])
+
+    def route(x):
+        W, hard = O.routing(x, cent, margin, c2d)
+        return W if W is not None else torch.nn.functional.one_hot(hard, 4).float()
+
+    fields = [lambda xd, k=k: OO.toy_field(xd, k) for k in range(4)]
+    rgb, depth, w, acc, merged = OO.assemble_container(rays, _occ_lists(z), route, fields, OO.toy_background(rays[:, 3:6]))
+    assert w.shape == z[f"{tag}_w"].shape and float(acc.mean()) > 0.05
+    for got, name in ((rgb, "rgb"), (depth, "depth"), (w, "w"), (acc, "acc")):
+        torch.testing.assert_close(got, T(z[f"{tag}_{name}"]), rtol=1e-6, atol=1e-7, msg=lambda m, name=name: f"{name}: {m}")
+
+
+@pytest.mark.parametrize("k", [1, 3])
+def test_occ_single_expert_assembly_oracle_equals_the_reference(k):
+    """oracle assemble_expert against the unmodified render_expert_occ; expert 3's grid is empty: background only, weights
+    of shape (1,1) as the reference returns them."""
+    from oracle import occ_oracle as OO
+    z = load_golden("occ_assembly")
+    rays = T(z["rays"])
+    # render_expert_occ does not prefilter: the lists hold ids into ALL rays (the grid's outer level reaches past the expert box)
+    ri, a, b, _, _ = OO.march(rays, T(z[f"binaries{k}"]), T(z[f"aabbs{k}"]), float(z["step_cone"][0]), float(z["step_cone"][1]))
+    rgb, depth, w, acc = OO.assemble_expert(rays, ri, a, b, lambda xd: OO.toy_field(xd, k), OO.toy_background(rays[:, 3:6]))
+    for got, name in ((rgb, "rgb"), (depth, "depth"), (w, "w"), (acc, "acc")):
+        torch.testing.assert_close(got, T(z[f"expert{k}_{name}"]), rtol=1e-6, atol=1e-7, msg=lambda m, name=name: f"{name}: {m}")
+    if k == 3:
+        assert w.shape == (1, 1) and float(acc.abs().max()) == 0.0
