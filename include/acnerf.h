@@ -319,6 +319,19 @@ int acn_composite_bwd(const float* rgb_sigma, const float* t, const float* bg, i
 int acn_mse_loss(const float* pred, const float* gt, int64_t N, int space, float* loss, float* d_pred,
                  float* ws, void* stream);
 
+/* The same loss with NO caller workspace and NO allocation of any kind (no cudaMalloc / cudaFree, no allocating library
+ * routine), for callers that cannot allocate: code under CUDA graph capture, tight serving loops, harnesses that forbid it.
+ * No counterpart in the reference.  The per-CTA partial sums live in a
+ * file-scope `static __device__` array of ACN_MSE_STATIC_PARTIALS floats (8 KiB, held by every GPU that loads the library
+ * until the process exits); N above ACN_MSE_STATIC_MAX_RAYS is rejected with ACN_EINVAL.  Same kernels, grid and summation
+ * order as acn_mse_loss: results are bit-identical to it.  The array is shared by every call and keeps the last call's
+ * contents (each call overwrites all the entries it reads, nothing needs clearing); two calls that OVERLAP on the GPU
+ * (different streams, or different threads on one device) race on it - order them on one stream or with events. */
+#define ACN_MSE_STATIC_PARTIALS 2048
+#define ACN_MSE_STATIC_MAX_RAYS (1 << 24)
+int acn_mse_loss_static(const float* pred, const float* gt, int64_t N, int space, float* loss, float* d_pred,
+                        void* stream);
+
 /* ---- (f)2: fused optimiser ------------------------------------------------ */
 /* torch.optim.Adam single-tensor math (common/utils.py:16-76 builds torch Adam):
  * step is the 1-based step count; grad_scale multiplies the gradient first

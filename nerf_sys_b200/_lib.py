@@ -132,6 +132,7 @@ SIGNATURES = {
     "acn_composite_fwd_strided": (C.c_int, [vp, i64, i64, vp, vp, i64, C.c_int, f32, vp, vp, vp, vp, vp]),
     "acn_composite_bwd": (C.c_int, [vp, vp, vp, i64, C.c_int, f32, vp, vp, vp, vp, vp, vp, vp]),
     "acn_mse_loss": (C.c_int, [vp, vp, i64, C.c_int, vp, vp, vp, vp]),
+    "acn_mse_loss_static": (C.c_int, [vp, vp, i64, C.c_int, vp, vp, vp]),
     "acn_adam_step": (C.c_int, [vp, vp, vp, vp, i64, f32, f32, f32, f32, f32, i64, vp, vp]),
     "acn_sgd_axpy": (C.c_int, [vp, vp, f32, i64, vp, vp]),
     "acn_sumsq_accum": (C.c_int, [vp, i64, vp, vp]),

@@ -5,7 +5,14 @@
 // warp-shuffle prefix product with a carry between 32-sample chunks, and the
 // backward pass is the matching warp-shuffle suffix sum.  HBM-bound: 20 B read per
 // sample (+4 B weights written when requested), 20 B written per ray.
+#include <mutex>
+
 #include "common.cuh"
+
+// Scratch of acn_mse_loss_static (the entry point that allocates nothing): the per-CTA partial sums of k_mse_partial.
+// One copy per GPU that loads the library, held until exit (8 KiB).  In HOST code this name is only a stand-in for the
+// symbol, not a device address: the address a kernel may be given comes from cudaGetSymbolAddress (mse_static_scratch()).
+static __device__ __align__(256) float g_mse_static_scratch[ACN_MSE_STATIC_PARTIALS];
 
 namespace acn {
 
@@ -546,6 +553,45 @@ int acn_mse_loss(const float* pred, const float* gt, int64_t N, int space, float
   k_mse_partial<<<grid, 256, 0, as_stream(stream)>>>(pred, gt, n, space, inv_n, d_pred, ws);
   ACN_LAUNCH_CHECK();
   k_mse_final<<<1, 256, 0, as_stream(stream)>>>(ws, grid, inv_n, loss);
+  ACN_LAUNCH_CHECK();
+  return ACN_OK;
+}
+
+// Device address of g_mse_static_scratch on the CURRENT device, looked up once per device (cudaGetSymbolAddress allocates
+// nothing: the array is part of the loaded module).
+static int mse_static_scratch(float** out) {
+  constexpr int MAX_DEV = 64;
+  static std::mutex mu;
+  static float* addr[MAX_DEV] = {};
+  int dev = -1;
+  ACN_CUDA(cudaGetDevice(&dev));
+  ACN_REQUIRE(dev >= 0 && dev < MAX_DEV, "acn_mse_loss_static: device ordinal %d outside [0,%d)", dev, MAX_DEV);
+  std::lock_guard<std::mutex> lock(mu);
+  if (!addr[dev]) {
+    float* p = nullptr;
+    ACN_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_mse_static_scratch));
+    ACN_REQUIRE(p != nullptr, "acn_mse_loss_static: cudaGetSymbolAddress returned a null address");
+    addr[dev] = p;
+  }
+  *out = addr[dev];
+  return ACN_OK;
+}
+
+int acn_mse_loss_static(const float* pred, const float* gt, int64_t N, int space, float* loss, float* d_pred, void* stream) {
+  ACN_REQUIRE(pred && gt && loss && N > 0 && space >= 0 && space <= 2, "acn_mse_loss_static: bad arguments");
+  ACN_REQUIRE(N <= (int64_t)ACN_MSE_STATIC_MAX_RAYS, "acn_mse_loss_static: N = %lld rays exceeds the static scratch's limit of %lld (use acn_mse_loss with a caller workspace)",
+              (long long)N, (long long)ACN_MSE_STATIC_MAX_RAYS);
+  float* scratch = nullptr;
+  int rc = mse_static_scratch(&scratch);
+  if (rc != ACN_OK) return rc;
+  const int64_t n = N * 3;
+  int grid = persistent_grid((n + 255) / 256, 4);
+  if (grid > ACN_MSE_STATIC_PARTIALS) grid = ACN_MSE_STATIC_PARTIALS;
+  const float inv_n = (float)(1.0 / (double)n);
+  // every partial the final kernel reads (0 .. grid-1) is overwritten by this call's first kernel: nothing has to start at zero
+  k_mse_partial<<<grid, 256, 0, as_stream(stream)>>>(pred, gt, n, space, inv_n, d_pred, scratch);
+  ACN_LAUNCH_CHECK();
+  k_mse_final<<<1, 256, 0, as_stream(stream)>>>(scratch, grid, inv_n, loss);
   ACN_LAUNCH_CHECK();
   return ACN_OK;
 }
