@@ -39,7 +39,7 @@ dump render.o 14k_bg_bwd_fused k_bg_bwd_fused
 dump render.o 13k_mse_partial k_mse_partial
 dump rays.o 8k_raygen k_raygen
 dump rays.o 9k_strat_t k_strat_t
-dump routing.o "13k_route_writeILi8ELb0" k_route_write
+dump routing.o "13k_route_writeILi8EE" k_route_write
 dump routing.o "13k_route_countILi8ELb0" k_route_count
 dump a2a.o 15k_a2a_push_rows k_a2a_push_rows
 dump a2a.o 18k_a2a_pull_combine k_a2a_pull_combine
