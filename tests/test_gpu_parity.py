@@ -168,6 +168,43 @@ def test_route_pack_is_a_stable_partition():
                     assert (weight[seg[k]:seg[k] + live.numel()] == 1).all()
 
 
+@pytest.mark.parametrize("K", [1, 2, 4, 6, 9, 12, 16])
+@pytest.mark.parametrize("c2d", [True, False])
+def test_route_pack_every_kernel_width_vs_oracle(K, c2d):
+    """The pack kernels are compiled for 2 / 4 / 8 / 16 centroid slots (K rounded up, padding centroids at +inf): members in
+    nonzero() order, weights (2e-7) and segment tables for expert counts on both sides of every width, random centroids,
+    distances over (y,z) and over (x,y,z), hard and soft margins wide enough for 3- and 4-way memberships."""
+    from nerf_sys_b200 import ops
+    g = torch.Generator().manual_seed(100 + K)
+    P = 20_011
+    cent = torch.rand(K, 3, generator=g) * 2 - 1
+    pts = torch.rand(P, 3, generator=g) * 2 - 1
+    pts[:K] = cent  # samples ON a centroid: distance clamps to 1e-6
+    if K >= 2:
+        pts[K:K + 64] = 0.5 * (cent[0] + cent[1])  # exact ties between two centroids
+    ps = ops.PointSet(x6=torch.cat([pts, torch.zeros_like(pts)], -1).to(DEV))
+    for margin in (1.0, 1.08, 1.7):
+        pairs = ops.route_pack(ps, cent.reshape(-1).tolist(), K, margin, c2d)
+        wd, hd = O.routing(pts, cent, margin, c2d, direct=True)
+        seg = pairs.seg_host
+        assert len(seg) == K + 1 and seg[0] == 0 and all(s % 128 == 0 for s in seg) and seg[-1] == pairs.M
+        point, weight = pairs.point.cpu(), pairs.weight.cpu()
+        n_multi = 0
+        for k in range(K):
+            sl = point[seg[k]:seg[k + 1]]
+            live = sl[sl >= 0]
+            exp = ((wd[:, k] > 0) if wd is not None else (hd == k)).nonzero().squeeze(1)
+            assert torch.equal(live.long(), exp), (K, c2d, margin, k)
+            assert (sl[live.numel():] == -1).all()
+            if wd is not None:
+                close(weight[seg[k]:seg[k] + live.numel()], wd[exp, k], 2e-7, "pair weights")
+                n_multi += int((wd[exp, k] < 1).sum())
+            else:
+                assert (weight[seg[k]:seg[k] + live.numel()] == 1).all()
+        if margin > 1.5 and K >= 4:
+            assert n_multi > P // 4  # the weight rows of multi-member samples are exercised, not only the unit-weight fast path
+
+
 def test_sample_major_point_ids_give_the_same_partition_and_frame():
     """AcnPoints.t_T (sample-major point ids, p = sample * N + ray): positions are bit-identical, every expert gets the same
     members with the same weights (listed in sample-major order), and a frame rendered through it equals the frame
