@@ -4,8 +4,9 @@
 //
 // Distances are the direct fp32 form sqrt(sum((x-c)^2)) (compiled -fmad=false); the
 // integer decisions (argmin / membership mask) are the bit-exact contract.
-// HBM-bound: 12 B read per point (36 B/ray + 4 B/point in the implicit form),
-// 8 B written per (point, expert) pair.
+// Algorithmic traffic: 12 B read per point (36 B/ray + 4 B/point in the implicit form), 8 B written per (point, expert)
+// pair; the pack additionally keeps one 4 B decision word per point between its count and write passes.  Measured
+// binding resource: instruction issue in the count pass (profiles/r2_route_kernels.json), not HBM.
 #include "common.cuh"
 
 namespace acn {
